@@ -1,0 +1,55 @@
+// Library-level entry points: error reporting, version, device query.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace dli {
+
+static thread_local char g_err[512] = {0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int sm_count_cached() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+}  // namespace dli
+
+extern "C" {
+
+const char* dli_last_error(void) { return dli::g_err; }
+
+int dli_version(void) { return 1000; }
+
+int dli_sm_count(void) {
+  int n = dli::sm_count_cached();
+  if (n <= 0) {
+    cudaGetLastError();
+    return dli::fail(DLI_ERR_CUDA, "dli_sm_count: no usable CUDA device");
+  }
+  return n;
+}
+
+}  // extern "C"

@@ -1,0 +1,332 @@
+// Paged-KV decode attention: one query token per sequence, split-KV, GQA-aware.
+//
+// Grid = (num_splits, KV heads, sequences).  A CTA owns one KV head of one
+// sequence and a contiguous range of 64-token KV tiles; the G = H/KV query
+// heads that share this KV head form the (zero-padded) 16-row M tile, so every
+// K/V byte is read from HBM exactly once for all of them.  K/V tiles are staged
+// page by page into shared memory with 16-byte cp.async (each page row segment
+// is a contiguous hd*2-byte run, fully coalesced), double-buffered; scores and
+// P.V use warp-level m16n8k16 MMAs, the softmax is an online (running max/sum)
+// softmax in fp32 with quad shuffles.  The 4 warps split each tile's tokens and
+// are merged through shared memory at the end; with num_splits > 1 the CTA
+// writes an un-normalised partial (O, max, sum) to scratch and a second tiny
+// kernel merges the splits.
+//
+// Algorithmic bytes per launch: sum_b min(S_b, window) * KV * hd * 2 (K and V)
+// * 2 bytes; q/out/scratch are negligible.
+#include "mma_utils.cuh"
+
+namespace dli {
+
+constexpr int kAttnThreads = 128;
+constexpr int kAttnTile = 64;
+
+template <int HD>
+struct DecodeSmem {
+  static constexpr int kRowBytes = HD * 2;
+  static constexpr int kQBytes = 16 * kRowBytes;
+  static constexpr int kTileBytes = kAttnTile * kRowBytes;
+  static constexpr int kTotal = kQBytes + 4 * kTileBytes;  // Q + 2 stages x (K, V)
+};
+
+template <int HD>
+__global__ void __launch_bounds__(kAttnThreads)
+paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
+                         const bf16* __restrict__ k_cache, const bf16* __restrict__ v_cache,
+                         const int32_t* __restrict__ page_table, int max_pages,
+                         const int32_t* __restrict__ seq_lens, bf16* __restrict__ out,
+                         float* __restrict__ part_o, float* __restrict__ part_ml, int H, int KV,
+                         int page_shift, int num_splits, float scale_log2, int window) {
+  using L = DecodeSmem<HD>;
+  constexpr int RB = L::kRowBytes;
+  constexpr int CH = HD / 8;  // 16-byte chunks per row
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t sQ = smem_u32(smem);
+  const uint32_t sK = sQ + L::kQBytes;
+  const uint32_t sV = sK + 2 * L::kTileBytes;
+
+  const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int G = H / KV;
+  const int seq_len = seq_lens[b];
+  const int first_tok = (window > 0 && seq_len > window) ? seq_len - window : 0;
+  const int tile_lo = first_tok / kAttnTile;
+  const int tile_hi = (seq_len + kAttnTile - 1) / kAttnTile;
+  const int tps = (tile_hi - tile_lo + num_splits - 1) / num_splits;
+  const int t_begin = tile_lo + split * tps;
+  const int t_end = min(t_begin + tps, tile_hi);
+  const int page_mask = (1 << page_shift) - 1;
+  const int32_t* pt = page_table + (size_t)b * max_pages;
+
+  // ---- stage Q (rows >= G are zero) -------------------------------------------------
+  for (int id = tid; id < 16 * CH; id += kAttnThreads) {
+    const int row = id / CH, c = id - row * CH;
+    const bool valid = row < G;
+    const bf16* src = q + (size_t)b * q_stride + (size_t)(kvh * G + (valid ? row : 0)) * HD + c * 8;
+    cp_async_16B(sQ + swz<RB>(row, c), src, valid ? 16 : 0);
+  }
+
+  auto load_tile = [&](int tile, int stage) {
+    const uint32_t dK = sK + stage * L::kTileBytes, dV = sV + stage * L::kTileBytes;
+#pragma unroll
+    for (int i = 0; i < kAttnTile * CH / kAttnThreads; ++i) {
+      const int id = tid + i * kAttnThreads;
+      const int row = id / CH, c = id - row * CH;
+      const int tok = tile * kAttnTile + row;
+      const bool valid = tok < seq_len;
+      size_t off = 0;
+      if (valid) {
+        const int page = pt[tok >> page_shift];
+        off = ((((size_t)page * KV + kvh) << page_shift) + (tok & page_mask)) * HD + c * 8;
+      }
+      cp_async_16B(dK + swz<RB>(row, c), k_cache + off, valid ? 16 : 0);
+      cp_async_16B(dV + swz<RB>(row, c), v_cache + off, valid ? 16 : 0);
+    }
+  };
+
+  float m_run[2] = {-INFINITY, -INFINITY};  // rows g and g+8 (raw score units)
+  float l_run[2] = {0.f, 0.f};
+  float o[HD / 8][4];
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+  uint32_t qf[HD / 16][4];
+
+  if (t_begin < t_end) load_tile(t_begin, 0);
+  cp_async_commit();
+
+  for (int tile = t_begin; tile < t_end; ++tile) {
+    const int stage = (tile - t_begin) & 1;
+    if (tile + 1 < t_end) {
+      load_tile(tile + 1, stage ^ 1);
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    if (tile == t_begin) {
+#pragma unroll
+      for (int kk = 0; kk < HD / 16; ++kk) {
+        const int mi = lane >> 3;
+        ldmatrix_x4(qf[kk], sQ + swz<RB>((mi & 1) * 8 + (lane & 7), kk * 2 + (mi >> 1)));
+      }
+    }
+    const uint32_t cK = sK + stage * L::kTileBytes, cV = sV + stage * L::kTileBytes;
+
+    // ---- S = Q K^T for this warp's 16 tokens ---------------------------------------
+    float s[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < HD / 16; ++kk) {
+      uint32_t kf[4];
+      const int mi = lane >> 3;
+      ldmatrix_x4(kf, cK + swz<RB>(warp * 16 + (mi >> 1) * 8 + (lane & 7), kk * 2 + (mi & 1)));
+      mma_16816(s[0], qf[kk], kf[0], kf[1]);
+      mma_16816(s[1], qf[kk], kf[2], kf[3]);
+    }
+    // ---- mask + online softmax --------------------------------------------------------
+    const int tok0 = tile * kAttnTile + warp * 16 + 2 * (lane & 3);
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int tok = tok0 + j * 8 + (e & 1);
+        if (tok >= seq_len || tok < first_tok) s[j][e] = -INFINITY;
+      }
+    uint32_t pa[4];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      float mx = fmaxf(fmaxf(s[0][2 * r], s[0][2 * r + 1]), fmaxf(s[1][2 * r], s[1][2 * r + 1]));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float m_new = fmaxf(m_run[r], mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float corr = exp2f((m_run[r] - m_use) * scale_log2);
+      m_run[r] = m_new;
+      float p[4];
+      p[0] = exp2f((s[0][2 * r] - m_use) * scale_log2);
+      p[1] = exp2f((s[0][2 * r + 1] - m_use) * scale_log2);
+      p[2] = exp2f((s[1][2 * r] - m_use) * scale_log2);
+      p[3] = exp2f((s[1][2 * r + 1] - m_use) * scale_log2);
+      l_run[r] = l_run[r] * corr + (p[0] + p[1] + p[2] + p[3]);
+      pa[r] = pack_bf16(p[0], p[1]);      // a0 (row g) / a1 (row g+8): tokens 2t,2t+1
+      pa[2 + r] = pack_bf16(p[2], p[3]);  // a2 / a3: tokens 8+2t, 8+2t+1
+#pragma unroll
+      for (int i = 0; i < HD / 8; ++i) {
+        o[i][2 * r] *= corr;
+        o[i][2 * r + 1] *= corr;
+      }
+    }
+    // ---- O += P V ------------------------------------------------------------------------
+#pragma unroll
+    for (int jp = 0; jp < HD / 16; ++jp) {
+      uint32_t vf[4];
+      const int mi = lane >> 3;
+      ldmatrix_x4_trans(vf, cV + swz<RB>(warp * 16 + (mi & 1) * 8 + (lane & 7), jp * 2 + (mi >> 1)));
+      mma_16816(o[2 * jp], pa, vf[0], vf[1]);
+      mma_16816(o[2 * jp + 1], pa, vf[2], vf[3]);
+    }
+    __syncthreads();  // stage may be refilled by the next iteration's prefetch
+  }
+  cp_async_wait<0>();
+  __syncthreads();
+
+  // ---- merge the 4 warps (reuse the K/V staging memory) ------------------------------
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+  }
+  float* red_o = reinterpret_cast<float*>(smem + L::kQBytes);                        // [4][16][HD]
+  float* red_ml = reinterpret_cast<float*>(smem + L::kQBytes + 2 * L::kTileBytes);   // [4][16][2]
+  {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) {
+      float* p0 = red_o + ((size_t)(warp * 16 + g) * HD + i * 8 + 2 * t);
+      float* p1 = red_o + ((size_t)(warp * 16 + g + 8) * HD + i * 8 + 2 * t);
+      p0[0] = o[i][0]; p0[1] = o[i][1];
+      p1[0] = o[i][2]; p1[1] = o[i][3];
+    }
+    if (t == 0) {
+      red_ml[(warp * 16 + g) * 2 + 0] = m_run[0];
+      red_ml[(warp * 16 + g) * 2 + 1] = l_run[0];
+      red_ml[(warp * 16 + g + 8) * 2 + 0] = m_run[1];
+      red_ml[(warp * 16 + g + 8) * 2 + 1] = l_run[1];
+    }
+  }
+  __syncthreads();
+  for (int idx = tid; idx < G * HD; idx += kAttnThreads) {
+    const int row = idx / HD, col = idx - row * HD;
+    float mmax = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) mmax = fmaxf(mmax, red_ml[(w * 16 + row) * 2]);
+    float acc = 0.f, lsum = 0.f;
+    if (mmax != -INFINITY) {
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        const float f = exp2f((red_ml[(w * 16 + row) * 2] - mmax) * scale_log2);
+        acc += f * red_o[(size_t)(w * 16 + row) * HD + col];
+        lsum += f * red_ml[(w * 16 + row) * 2 + 1];
+      }
+    }
+    const int h = kvh * G + row;
+    if (num_splits == 1) {
+      out[((size_t)b * H + h) * HD + col] = __float2bfloat16_rn(lsum > 0.f ? acc / lsum : 0.f);
+    } else {
+      const size_t slot = ((size_t)b * H + h) * num_splits + split;
+      part_o[slot * HD + col] = acc;
+      if (col == 0) {
+        part_ml[slot * 2 + 0] = mmax;
+        part_ml[slot * 2 + 1] = lsum;
+      }
+    }
+  }
+}
+
+// Merge the per-split partials: one warp per (sequence, head).
+template <int HD>
+__global__ void __launch_bounds__(kAttnThreads)
+attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
+                        bf16* __restrict__ out, int n_bh, int num_splits, float scale_log2) {
+  const int bh = blockIdx.x * (kAttnThreads / 32) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (bh >= n_bh) return;
+  const float* ml = part_ml + (size_t)bh * num_splits * 2;
+  float mmax = -INFINITY;
+  for (int s = 0; s < num_splits; ++s) mmax = fmaxf(mmax, ml[s * 2]);
+  float acc[HD / 32];
+#pragma unroll
+  for (int i = 0; i < HD / 32; ++i) acc[i] = 0.f;
+  float lsum = 0.f;
+  if (mmax != -INFINITY) {
+    for (int s = 0; s < num_splits; ++s) {
+      const float f = exp2f((ml[s * 2] - mmax) * scale_log2);
+      lsum += f * ml[s * 2 + 1];
+      const float* po = part_o + ((size_t)bh * num_splits + s) * HD;
+#pragma unroll
+      for (int i = 0; i < HD / 32; ++i) acc[i] += f * po[lane + 32 * i];
+    }
+  }
+  const float inv = lsum > 0.f ? 1.f / lsum : 0.f;
+#pragma unroll
+  for (int i = 0; i < HD / 32; ++i)
+    out[(size_t)bh * HD + lane + 32 * i] = __float2bfloat16_rn(acc[i] * inv);
+}
+
+template <int HD>
+static int launch_decode(const void* q, int q_stride, const void* k_cache, const void* v_cache,
+                         const int32_t* page_table, int max_pages, const int32_t* seq_lens,
+                         void* out, void* scratch, int B, int H, int KV, int page_shift,
+                         int num_splits, float scale, int window, cudaStream_t s) {
+  using L = DecodeSmem<HD>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DLI_CUDA_CALL(cudaFuncSetAttribute(paged_attn_decode_kernel<HD>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    attr_set = true;
+  }
+  const float scale_log2 = scale * 1.4426950408889634f;
+  float* part_o = reinterpret_cast<float*>(scratch);
+  float* part_ml = part_o ? part_o + (size_t)B * H * num_splits * HD : nullptr;
+  dim3 grid(num_splits, KV, B);
+  paged_attn_decode_kernel<HD><<<grid, kAttnThreads, L::kTotal, s>>>(
+      (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table, max_pages,
+      seq_lens, (bf16*)out, part_o, part_ml, H, KV, page_shift, num_splits, scale_log2, window);
+  DLI_CUDA_LAUNCH_CHECK("paged_attn_decode_kernel");
+  if (num_splits > 1) {
+    const int n_bh = B * H;
+    const int per_cta = kAttnThreads / 32;
+    attn_split_merge_kernel<HD><<<(n_bh + per_cta - 1) / per_cta, kAttnThreads, 0, s>>>(
+        part_o, part_ml, (bf16*)out, n_bh, num_splits, scale_log2);
+    DLI_CUDA_LAUNCH_CHECK("attn_split_merge_kernel");
+  }
+  return DLI_OK;
+}
+
+}  // namespace dli
+
+extern "C" {
+
+size_t dli_paged_attn_decode_scratch_bytes(int B, int H, int hd, int num_splits) {
+  if (B <= 0 || H <= 0 || hd <= 0 || num_splits <= 1) return 0;
+  return sizeof(float) * (size_t)B * H * num_splits * (hd + 2);
+}
+
+int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
+                               const void* v_cache, const int32_t* page_table, int max_pages,
+                               const int32_t* seq_lens, void* out, void* scratch,
+                               size_t scratch_bytes, int B, int H, int KV, int hd, int page_size,
+                               int num_splits, float scale, int window, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(q && k_cache && v_cache && page_table && seq_lens && out,
+                "dli_paged_attn_decode_bf16: null pointer");
+  DLI_CHECK_ARG(hd == 64 || hd == 128, "dli_paged_attn_decode_bf16: hd must be 64 or 128 (got %d)", hd);
+  DLI_CHECK_ARG(B >= 0 && H > 0 && KV > 0 && H % KV == 0 && H / KV <= 16,
+                "dli_paged_attn_decode_bf16: need H %% KV == 0 and H/KV <= 16 (got H=%d KV=%d)", H, KV);
+  DLI_CHECK_ARG(page_size >= 8 && (page_size & (page_size - 1)) == 0,
+                "dli_paged_attn_decode_bf16: page_size must be a power of two >= 8 (got %d)", page_size);
+  DLI_CHECK_ARG(num_splits >= 1 && num_splits <= 65535 && KV <= 65535 && B <= 65535,
+                "dli_paged_attn_decode_bf16: num_splits/KV/B out of grid range");
+  DLI_CHECK_ARG(q_stride >= H * hd && q_stride % 8 == 0 && max_pages > 0 && window >= 0,
+                "dli_paged_attn_decode_bf16: bad q_stride/max_pages/window");
+  DLI_CHECK_ARG(aligned16(q) && aligned16(k_cache) && aligned16(v_cache) && aligned16(scratch),
+                "dli_paged_attn_decode_bf16: pointers must be 16-byte aligned");
+  if (num_splits > 1) {
+    const size_t need = dli_paged_attn_decode_scratch_bytes(B, H, hd, num_splits);
+    DLI_CHECK_ARG(scratch && scratch_bytes >= need,
+                  "dli_paged_attn_decode_bf16: scratch too small (%zu < %zu bytes)", scratch_bytes, need);
+  }
+  if (B == 0) return DLI_OK;
+  int shift = 0;
+  while ((1 << shift) < page_size) ++shift;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (hd == 128)
+    return launch_decode<128>(q, q_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out,
+                              scratch, B, H, KV, shift, num_splits, scale, window, s);
+  return launch_decode<64>(q, q_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out,
+                           scratch, B, H, KV, shift, num_splits, scale, window, s);
+}
+
+}  // extern "C"

@@ -1,0 +1,100 @@
+// Shared device/host helpers for the dli_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/dli.h"
+
+namespace dli {
+
+// ---- host-side error plumbing (abi.cu owns the storage) -------------------
+void set_error(const char* fmt, ...);
+int fail(int code, const char* fmt, ...);
+
+#define DLI_CHECK_ARG(cond, ...)                                  \
+  do {                                                            \
+    if (!(cond)) return ::dli::fail(DLI_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+#define DLI_CUDA_LAUNCH_CHECK(what)                                             \
+  do {                                                                          \
+    cudaError_t e__ = cudaGetLastError();                                       \
+    if (e__ != cudaSuccess)                                                     \
+      return ::dli::fail(DLI_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e__)); \
+  } while (0)
+
+#define DLI_CUDA_CALL(expr)                                                       \
+  do {                                                                            \
+    cudaError_t e__ = (expr);                                                     \
+    if (e__ != cudaSuccess)                                                       \
+      return ::dli::fail(DLI_ERR_CUDA, "%s: %s", #expr, cudaGetErrorString(e__)); \
+  } while (0)
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+int sm_count_cached();
+
+// ---- device helpers ----------------------------------------------------------
+typedef __nv_bfloat16 bf16;
+typedef __nv_bfloat162 bf162;
+
+struct __align__(16) bf16x8 {
+  bf162 v[4];
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// 128-bit streaming load that does not pollute L1 (weights / KV are read once).
+__device__ __forceinline__ uint4 ld_stream_16B(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 ld_16B(const void* p) {
+  return *reinterpret_cast<const uint4*>(p);
+}
+__device__ __forceinline__ void st_16B(void* p, uint4 v) { *reinterpret_cast<uint4*>(p) = v; }
+
+// bf16 pair packed in a u32 -> two floats (exact: bf16 is the top half of fp32).
+__device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  bf162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float round_bf16(float x) {
+  return __bfloat162float(__float2bfloat16_rn(x));
+}
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  f[0] = bf_lo(u.x); f[1] = bf_hi(u.x); f[2] = bf_lo(u.y); f[3] = bf_hi(u.y);
+  f[4] = bf_lo(u.z); f[5] = bf_hi(u.z); f[6] = bf_lo(u.w); f[7] = bf_hi(u.w);
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 u;
+  u.x = pack_bf16(f[0], f[1]); u.y = pack_bf16(f[2], f[3]);
+  u.z = pack_bf16(f[4], f[5]); u.w = pack_bf16(f[6], f[7]);
+  return u;
+}
+
+// Activations, evaluated the way torch evaluates them on a bf16 tensor:
+// upcast to fp32, compute, round once to bf16 (the caller rounds).
+__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
+// gelu_new (tanh approximation), TF:activations.py:59-66
+__device__ __forceinline__ float gelu_new_f(float x) {
+  const float k = 0.7978845608028654f;  // sqrt(2/pi)
+  return 0.5f * x * (1.0f + tanhf(k * (x + 0.044715f * x * x * x)));
+}
+
+}  // namespace dli

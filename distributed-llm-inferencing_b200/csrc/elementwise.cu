@@ -1,0 +1,117 @@
+// Embedding gather (+ learned positions) and the greedy argmax epilogue.
+#include "common.cuh"
+
+namespace dli {
+
+// One CTA per token row; 16-byte gathers.  Bytes per row: d*2 read (+ d*2 for
+// the position row), d*2 written.
+__global__ void __launch_bounds__(128)
+embedding_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ positions,
+                 const bf16* __restrict__ table, const bf16* __restrict__ pos_table,
+                 bf16* __restrict__ out, int d, int vocab) {
+  const size_t row = blockIdx.x;
+  int id = ids[row];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const uint4* src = reinterpret_cast<const uint4*>(table + (size_t)id * d);
+  const uint4* psrc = pos_table ? reinterpret_cast<const uint4*>(pos_table + (size_t)positions[row] * d) : nullptr;
+  uint4* dst = reinterpret_cast<uint4*>(out + row * d);
+  for (int v = threadIdx.x; v < (d >> 3); v += blockDim.x) {
+    uint4 u = ld_16B(src + v);
+    if (psrc) {
+      float a[8], p[8];
+      unpack8(u, a);
+      unpack8(ld_16B(psrc + v), p);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) a[e] += p[e];
+      u = pack8(a);
+    }
+    st_16B(dst + v, u);
+  }
+}
+
+// Argmax over a bf16 row, lowest index on ties (torch.argmax behaviour).
+// One CTA per row; V*2 bytes read per row.
+constexpr int kArgmaxThreads = 512;
+
+__device__ __forceinline__ void argmax_combine(float& v, int& i, float ov, int oi) {
+  if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
+}
+
+__global__ void __launch_bounds__(kArgmaxThreads)
+argmax_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out, int V) {
+  __shared__ float sv[kArgmaxThreads / 32];
+  __shared__ int si[kArgmaxThreads / 32];
+  const bf16* row = logits + (size_t)blockIdx.x * ld;
+  float best = -INFINITY;
+  int besti = 0x7fffffff;
+  // rows are only guaranteed 2-byte aligned relative to each other when ld % 8 != 0
+  const bool vec_ok = ((reinterpret_cast<uintptr_t>(row) & 15u) == 0);
+  const int nvec = vec_ok ? (V >> 3) : 0;
+  for (int v = threadIdx.x; v < nvec; v += kArgmaxThreads) {
+    float f[8];
+    unpack8(ld_16B(reinterpret_cast<const uint4*>(row) + v), f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      // NaN never wins here; torch would return a NaN's index, logits are finite in practice
+      if (f[e] > best) { best = f[e]; besti = v * 8 + e; }
+    }
+  }
+  for (int i = nvec * 8 + threadIdx.x; i < V; i += kArgmaxThreads) {
+    const float f = __bfloat162float(row[i]);
+    if (f > best || (f == best && i < besti)) { best = f; besti = i; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+    argmax_combine(best, besti, ov, oi);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { sv[warp] = best; si[warp] = besti; }
+  __syncthreads();
+  if (warp == 0) {
+    best = lane < kArgmaxThreads / 32 ? sv[lane] : -INFINITY;
+    besti = lane < kArgmaxThreads / 32 ? si[lane] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+      argmax_combine(best, besti, ov, oi);
+    }
+    if (lane == 0) out[blockIdx.x] = besti == 0x7fffffff ? 0 : besti;
+  }
+}
+
+}  // namespace dli
+
+extern "C" {
+
+int dli_embedding_bf16(const int32_t* ids, const int32_t* positions, const void* table,
+                       const void* pos_table, void* out, int rows, int d, int vocab,
+                       dli_stream_t stream) {
+  using namespace dli;
+  if (rows == 0) return DLI_OK;
+  DLI_CHECK_ARG(ids && table && out, "dli_embedding_bf16: null pointer");
+  DLI_CHECK_ARG(!pos_table || positions, "dli_embedding_bf16: pos_table needs positions");
+  DLI_CHECK_ARG(rows >= 0 && d > 0 && d % 8 == 0 && vocab > 0,
+                "dli_embedding_bf16: need d %% 8 == 0 (got rows=%d d=%d vocab=%d)", rows, d, vocab);
+  DLI_CHECK_ARG(aligned16(table) && aligned16(pos_table) && aligned16(out),
+                "dli_embedding_bf16: pointers must be 16-byte aligned");
+  if (rows == 0) return DLI_OK;
+  embedding_kernel<<<rows, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      ids, positions, (const bf16*)table, (const bf16*)pos_table, (bf16*)out, d, vocab);
+  DLI_CUDA_LAUNCH_CHECK("dli_embedding_bf16");
+  return DLI_OK;
+}
+
+int dli_argmax_bf16(const void* logits, int ld, int32_t* out, int B, int V, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(logits && out, "dli_argmax_bf16: null pointer");
+  DLI_CHECK_ARG(B >= 0 && V > 0 && ld >= V, "dli_argmax_bf16: bad sizes B=%d V=%d ld=%d", B, V, ld);
+  if (B == 0) return DLI_OK;
+  argmax_kernel<<<B, kArgmaxThreads, 0, static_cast<cudaStream_t>(stream)>>>((const bf16*)logits, ld, out, V);
+  DLI_CUDA_LAUNCH_CHECK("dli_argmax_bf16");
+  return DLI_OK;
+}
+
+}  // extern "C"

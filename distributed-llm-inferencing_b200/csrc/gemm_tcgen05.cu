@@ -1,0 +1,475 @@
+// bf16 GEMM on the 5th-generation tensor cores: tcgen05.mma with the fp32
+// accumulator in TMEM, operands staged in shared memory by TMA, hand-written
+// in inline PTX (no CUTLASS/CuTe).
+//
+//   y[M,N] = epi( x[M,K] . w[N,K]^T )          both operands K-major (row-major,
+//                                              K contiguous) = HF Linear layout
+//
+// One 128-row UMMA tile per CTA, BLOCK_K = 64 (one 128-byte swizzle span of
+// bf16), a kStages-deep TMA->MMA ring of mbarriers, and three warp roles:
+//   warp 0  : TMA producer (one elected lane issues cp.async.bulk.tensor)
+//   warp 1  : TMEM allocator + MMA issuer (one elected lane issues tcgen05.mma,
+//             tcgen05.commit releases smem slots / publishes the accumulator)
+//   warps 2-5: epilogue — tcgen05.ld 32 lanes x 32 columns per warp, fused
+//             bias / gelu / residual / silu*up, bf16 pack, 16-byte stores.
+//
+// Two operand assignments (template kSwap):
+//   kSwap = false (prefill, M large):  A = x tile [128 m, 64 k], B = w tile
+//       [BN n, 64 k]; TMEM lane = output row m, column = n.
+//   kSwap = true  (batched decode, M <= 128): A = w tile [128 n, 64 k], B = x
+//       tile [BN >= M rows m, 64 k] (TMA zero-fills rows >= M); TMEM lane = n,
+//       column = m, so no MMA work is wasted on padding and the kernel is a pure
+//       weight stream; the epilogue writes y[m, n] with the warp's 32 lanes on
+//       32 consecutive n.
+// Gated MLP (template kGated): w is the [gate128 | up128]-interleaved matrix;
+//   non-swap uses one BN=256 tile (TMEM columns 0-127 gate, 128-255 up), swap
+//   issues two M=128 MMAs per k-step into two accumulators.  The epilogue
+//   computes bf16(silu(bf16(g))) * bf16(u) — the HF rounding points.
+//
+// Tensor-bound for prefill: 2*M*N*K FLOPs per launch; HBM-bound weight stream
+// for decode: N*K*2 bytes per launch.
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace dli {
+
+constexpr int kGemmThreads = 192;
+constexpr int kBlockM = 128;  // UMMA M (TMEM lanes)
+constexpr int kBlockK = 64;   // elements: 128 bytes = one SWIZZLE_128B span
+constexpr int kUmmaK = 16;
+constexpr uint32_t kSpinTimeoutCycles = 0;  // unused; see mbar_wait
+
+// ---- PTX wrappers ------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_addr(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Bounded wait: a protocol bug traps (surfacing as a CUDA error) instead of
+// hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  const long long t0 = clock64();
+  while (true) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if (clock64() - t0 > 4000000000LL) {
+      printf("dli gemm_tcgen05: mbarrier wait timed out (block %d,%d thread %d)\n", blockIdx.x,
+             blockIdx.y, threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]; one thread issues for the CTA.
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrive once all MMAs issued so far by this thread have completed.
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 lanes x 32 columns of fp32 from TMEM: thread i of the warp gets lane
+// (base lane + i), registers = 32 consecutive columns.
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+        "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]),
+        "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]),
+        "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+        "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (sm_100 format):
+// start address >> 4 | LBO (=1, unused for swizzled K-major) << 16 |
+// SBO (8 rows * 128 B = 1024 B >> 4 = 64) << 32 | version 1 << 46 | layout 2 << 61.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3ffffu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)64 << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128, N=n.
+__host__ __device__ constexpr uint32_t make_idesc(int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+}
+
+template <int BN, bool kSwap, bool kGated>
+struct GemmCfg {
+  // A tile rows: 128, or 256 for the swap-gated case (gate128 | up128 in one box)
+  static constexpr int kARows = (kSwap && kGated) ? 256 : 128;
+  static constexpr int kABytes = kARows * kBlockK * 2;
+  static constexpr int kBBytes = BN * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagesRaw = (220 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  // accumulator columns: BN, or 2*BN for the two swap-gated accumulators
+  static constexpr int kAccCols = (kSwap && kGated) ? 2 * BN : BN;
+  static constexpr int kTmemCols = kAccCols <= 32 ? 32 : kAccCols <= 64 ? 64 : kAccCols <= 128 ? 128 : kAccCols <= 256 ? 256 : 512;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static_assert(kStageBytes % 1024 == 0, "stages must keep 1024-byte alignment");
+  static_assert(BN % 16 == 0 && BN >= 16 && BN <= 256, "UMMA N");
+  static_assert(!kGated || kSwap || BN == 256, "non-swap gated tile is gate128|up128");
+};
+
+template <int BN, bool kSwap, bool kGated>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const bf16* __restrict__ bias, const bf16* residual, bf16* y, int M, int N, int K,
+                    int epilogue) {
+  using Cfg = GemmCfg<BN, kSwap, kGated>;
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B operands need 1024-byte alignment
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* bar_mem = smem + Cfg::kStages * Cfg::kStageBytes;
+  const uint32_t full_bar = smem_addr(bar_mem);               // kStages x 8 B
+  const uint32_t empty_bar = full_bar + 8 * Cfg::kStages;     // kStages x 8 B
+  const uint32_t tmem_full_bar = empty_bar + 8 * Cfg::kStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_mem + 8 * (2 * Cfg::kStages + 1));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_kb = K / kBlockK;
+  // blockIdx.x walks the activation-row tiles fastest so CTAs sharing a weight
+  // tile run together and the weight tile is fetched from HBM once.
+  const int a_row0 = (kSwap ? blockIdx.y : blockIdx.x) * Cfg::kARows;  // rows of the A-operand matrix
+  const int b_row0 = (kSwap ? blockIdx.x : blockIdx.y) * BN;           // rows of the B-operand matrix
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(full_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(smem_addr(tmem_ptr_smem), Cfg::kTmemCols);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % Cfg::kStages;
+        const uint32_t ph = (kb / Cfg::kStages) & 1;
+        mbar_wait(empty_bar + 8 * s, ph ^ 1);
+        const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
+        const uint32_t sB = sA + Cfg::kABytes;
+        mbar_expect_tx(full_bar + 8 * s, Cfg::kStageBytes);
+        tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, a_row0);
+        tma_load_2d(sB, &tmB, full_bar + 8 * s, kb * kBlockK, b_row0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % Cfg::kStages;
+        const uint32_t ph = (kb / Cfg::kStages) & 1;
+        mbar_wait(full_bar + 8 * s, ph);
+        tcgen05_fence_after();
+        const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
+        const uint32_t sB = sA + Cfg::kABytes;
+        const uint64_t adesc = make_smem_desc(sA);
+        const uint64_t bdesc = make_smem_desc(sB);
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // advancing 16 elements (32 bytes) along K inside the swizzle span: +2 in the >>4 address field
+          const uint32_t acc = (kb > 0 || k > 0) ? 1u : 0u;
+          umma_bf16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, acc);
+          if (kSwap && kGated) {
+            // second accumulator: the up rows (A rows 128..255 start 128*128 B further)
+            umma_bf16(tmem_base + BN, adesc + (128 * 128 >> 4) + 2 * k, bdesc + 2 * k, idesc, acc);
+          }
+        }
+        umma_commit(empty_bar + 8 * s);  // frees the smem slot when these MMAs retire
+      }
+      umma_commit(tmem_full_bar);  // accumulator complete
+    }
+  } else {
+    // ---- epilogue warps 2..5: TMEM lane quadrant = warp % 4 -----------------------------
+    const int quad = warp & 3;
+    mbar_wait(tmem_full_bar, 0);
+    tcgen05_fence_after();
+    const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
+    if (!kSwap) {
+      const int m = blockIdx.x * kBlockM + quad * 32 + lane;  // this thread's output row
+      constexpr int kOutCols = kGated ? 128 : BN;             // output columns of this tile
+      const int n_tile0 = blockIdx.y * kOutCols;
+#pragma unroll 1
+      for (int c0 = 0; c0 < kOutCols; c0 += 16) {
+        uint32_t r[16], r2[16];
+        tmem_ld_32x16(lane_base + c0, r);
+        if (kGated) tmem_ld_32x16(lane_base + 128 + c0, r2);
+        tmem_ld_wait();
+        const int n0 = n_tile0 + c0;
+        if (m < M && n0 < N) {
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+          if (kGated) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float gte = round_bf16(v[j]), up = round_bf16(__uint_as_float(r2[j]));
+              v[j] = round_bf16(silu_f(gte)) * up;
+            }
+          } else {
+            if (epilogue & DLI_EPI_BIAS) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] += (n0 + j < N) ? __bfloat162float(bias[n0 + j]) : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = round_bf16(v[j]);
+            if (epilogue & DLI_EPI_GELU_NEW) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = round_bf16(gelu_new_f(v[j]));
+            }
+          }
+          const int n_out = kGated ? N / 2 : N;  // gated: N counts gate+up rows of w
+          bf16* dst = y + (size_t)m * n_out + n0;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            if (n0 + h * 8 < n_out) {  // N % 8 == 0 is checked on the host
+              if (!kGated && (epilogue & DLI_EPI_RESIDUAL)) {
+                float rr[8];
+                unpack8(ld_16B(residual + (size_t)m * n_out + n0 + h * 8), rr);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[h * 8 + j] += rr[j];
+              }
+              st_16B(dst + h * 8, pack8(v + h * 8));
+            }
+          }
+        }
+      }
+    } else {
+      // swap: lane = weight row n, columns = activation rows m (only m < M are real)
+      constexpr int kOutRows = 128;
+      const int n = blockIdx.y * kOutRows + quad * 32 + lane;
+      const int n_out = kGated ? N / 2 : N;
+      const int m_tile0 = blockIdx.x * BN;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        if (m_tile0 + c0 >= M) break;  // warp-uniform
+        uint32_t r[16], r2[16];
+        tmem_ld_32x16(lane_base + c0, r);
+        if (kGated) tmem_ld_32x16(lane_base + BN + c0, r2);
+        tmem_ld_wait();
+        if (n < n_out) {
+          const float bv = (!kGated && (epilogue & DLI_EPI_BIAS)) ? __bfloat162float(bias[n]) : 0.f;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int m = m_tile0 + c0 + j;
+            if (m < M) {
+              float v;
+              if (kGated) {
+                const float gte = round_bf16(__uint_as_float(r[j])), up = round_bf16(__uint_as_float(r2[j]));
+                v = round_bf16(silu_f(gte)) * up;
+              } else {
+                v = round_bf16(__uint_as_float(r[j]) + bv);
+                if (epilogue & DLI_EPI_GELU_NEW) v = round_bf16(gelu_new_f(v));
+                if (epilogue & DLI_EPI_RESIDUAL) v += __bfloat162float(residual[(size_t)m * n_out + n]);
+              }
+              y[(size_t)m * n_out + n] = __float2bfloat16_rn(v);
+            }
+          }
+        }
+      }
+    }
+    tcgen05_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D bf16 row-major [rows, K] tensor, box = [box_rows, 64 elements], 128-byte swizzle.
+static int make_tmap(CUtensorMap* tm, const void* base, int rows, int K, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return fail(DLI_ERR_CUDA, "gemm: cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(DLI_ERR_CUDA, "gemm: cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
+  return DLI_OK;
+}
+
+template <int BN, bool kSwap, bool kGated>
+static int launch_gemm(const void* x, const void* w, const void* bias, const void* residual, void* y, int M,
+                       int N /* rows of w */, int K, int epilogue, cudaStream_t s) {
+  using Cfg = GemmCfg<BN, kSwap, kGated>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kGated>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  CUtensorMap tmA, tmB;
+  int rc;
+  dim3 grid;
+  if (!kSwap) {
+    if ((rc = make_tmap(&tmA, x, M, K, 128)) != DLI_OK) return rc;
+    if ((rc = make_tmap(&tmB, w, N, K, BN)) != DLI_OK) return rc;
+    grid = dim3((M + 127) / 128, (N + BN - 1) / BN);
+  } else {
+    if ((rc = make_tmap(&tmA, w, N, K, Cfg::kARows)) != DLI_OK) return rc;
+    if ((rc = make_tmap(&tmB, x, M, K, BN)) != DLI_OK) return rc;
+    grid = dim3((M + BN - 1) / BN, (N + Cfg::kARows - 1) / Cfg::kARows);
+  }
+  gemm_tcgen05_kernel<BN, kSwap, kGated><<<grid, kGemmThreads, Cfg::kSmemBytes, s>>>(
+      tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue);
+  DLI_CUDA_LAUNCH_CHECK("gemm_tcgen05_kernel");
+  return DLI_OK;
+}
+
+}  // namespace dli
+
+extern "C" {
+
+int dli_gemm_bf16(const void* x, const void* w, const void* bias, const void* residual, void* y, int M, int N,
+                  int K, int epilogue, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(x && w && y, "dli_gemm_bf16: null pointer");
+  DLI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && K % 64 == 0 && N % 16 == 0,
+                "dli_gemm_bf16: need K %% 64 == 0 and N %% 16 == 0 (got M=%d N=%d K=%d)", M, N, K);
+  DLI_CHECK_ARG(!(epilogue & DLI_EPI_BIAS) || bias, "dli_gemm_bf16: DLI_EPI_BIAS without bias");
+  DLI_CHECK_ARG(!(epilogue & DLI_EPI_RESIDUAL) || residual, "dli_gemm_bf16: DLI_EPI_RESIDUAL without residual");
+  DLI_CHECK_ARG(aligned16(x) && aligned16(w) && aligned16(y) && aligned16(residual),
+                "dli_gemm_bf16: pointers must be 16-byte aligned");
+  if (M == 0) return DLI_OK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (M <= 16) return launch_gemm<16, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  if (M <= 32) return launch_gemm<32, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  if (M <= 64) return launch_gemm<64, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  if (M <= 128) return launch_gemm<128, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  if (N % 256 == 0 || N >= 2048) return launch_gemm<256, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  if (N % 128 == 0 || N > 128) return launch_gemm<128, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  if (N > 32) return launch_gemm<64, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  return launch_gemm<32, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+}
+
+int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F, int K, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(x && w_gu && y, "dli_gemm_gated_silu_bf16: null pointer");
+  DLI_CHECK_ARG(M >= 0 && F > 0 && F % 128 == 0 && K > 0 && K % 64 == 0,
+                "dli_gemm_gated_silu_bf16: need F %% 128 == 0, K %% 64 == 0 (got M=%d F=%d K=%d)", M, F, K);
+  DLI_CHECK_ARG(aligned16(x) && aligned16(w_gu) && aligned16(y),
+                "dli_gemm_gated_silu_bf16: pointers must be 16-byte aligned");
+  if (M == 0) return DLI_OK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int N2 = 2 * F;  // rows of w_gu
+  if (M <= 16) return launch_gemm<16, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
+  if (M <= 32) return launch_gemm<32, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
+  if (M <= 64) return launch_gemm<64, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
+  if (M <= 128) return launch_gemm<128, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
+  return launch_gemm<256, false, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
+}
+
+int dli_linear_bf16(const void* x, const void* w, const void* bias, const void* residual, void* y, int M, int N,
+                    int K, int epilogue, dli_stream_t stream) {
+  if (M <= 4 || K % 64 != 0 || N % 16 != 0)
+    return dli_gemv_bf16(x, w, bias, residual, y, M, N, K, epilogue, stream);
+  return dli_gemm_bf16(x, w, bias, residual, y, M, N, K, epilogue, stream);
+}
+
+int dli_linear_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F, int K, dli_stream_t stream) {
+  if (M <= 4 || K % 64 != 0) return dli_gemv_gated_silu_bf16(x, w_gu, y, M, F, K, stream);
+  return dli_gemm_gated_silu_bf16(x, w_gu, y, M, F, K, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,201 @@
+"""Thin torch-tensor front end over the C-ABI (include/dli.h).
+
+torch is used only for device memory and streams; every function passes raw
+device pointers to the hand-written kernels and enqueues on torch's current
+stream.  Tensors must be CUDA, contiguous where noted, bf16 unless stated.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import EPI_BIAS, EPI_GELU_NEW, EPI_NONE, EPI_RESIDUAL  # noqa: F401
+
+# number of kernels this process has launched through the C-ABI (bench.py's gpu_launches)
+launch_count = 0
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _req(t, dtype=torch.bfloat16):
+    if t is None:
+        return
+    if not t.is_cuda:
+        raise ValueError("dli ops need CUDA tensors (there is no CPU path)")
+    if t.dtype != dtype:
+        raise ValueError(f"expected {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError("tensor must be contiguous")
+
+
+def sm_count() -> int:
+    n = _lib.load().dli_sm_count()
+    if n <= 0:
+        _lib.check("dli_sm_count", n)
+    return n
+
+
+def embedding(ids, table, out=None, positions=None, pos_table=None):
+    """ids int32 [rows]; table [V, d] -> [rows, d]."""
+    global launch_count
+    _req(ids, torch.int32), _req(table), _req(pos_table), _req(positions, torch.int32)
+    rows, (vocab, d) = ids.numel(), table.shape
+    if out is None:
+        out = torch.empty(rows, d, dtype=torch.bfloat16, device=table.device)
+    _lib.check("dli_embedding_bf16", _lib.load().dli_embedding_bf16(
+        _p(ids), _p(positions), _p(table), _p(pos_table), _p(out), rows, d, vocab, _stream()))
+    launch_count += 1
+    return out
+
+
+def add_rmsnorm(x, weight, eps, residual=None, resid_out=None, out=None):
+    """y = rmsnorm(residual + x) * weight; optionally writes h = residual + x."""
+    global launch_count
+    _req(x), _req(weight), _req(residual), _req(resid_out)
+    rows, d = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    _lib.check("dli_add_rmsnorm_bf16", _lib.load().dli_add_rmsnorm_bf16(
+        _p(x), _p(residual), _p(weight), _p(resid_out), _p(out), rows, d, float(eps), _stream()))
+    launch_count += 1
+    return out
+
+
+def add_layernorm(x, weight, bias, eps, residual=None, resid_out=None, out=None):
+    global launch_count
+    _req(x), _req(weight), _req(bias), _req(residual), _req(resid_out)
+    rows, d = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    _lib.check("dli_add_layernorm_bf16", _lib.load().dli_add_layernorm_bf16(
+        _p(x), _p(residual), _p(weight), _p(bias), _p(resid_out), _p(out), rows, d, float(eps), _stream()))
+    launch_count += 1
+    return out
+
+
+def rope_kv_append(qkv, cos, sin, positions, seq_ids, page_table, k_cache, v_cache, H, KV, hd):
+    """Rotate q,k of packed qkv [rows,(H+2KV)*hd] in place and append k,v to the paged cache."""
+    global launch_count
+    _req(qkv), _req(cos), _req(sin), _req(k_cache), _req(v_cache)
+    _req(positions, torch.int32), _req(seq_ids, torch.int32), _req(page_table, torch.int32)
+    rows = qkv.shape[0]
+    page_size = k_cache.shape[2]
+    _lib.check("dli_rope_kv_append_bf16", _lib.load().dli_rope_kv_append_bf16(
+        _p(qkv), _p(cos), _p(sin), _p(positions), _p(seq_ids), _p(page_table), page_table.shape[1],
+        _p(k_cache), _p(v_cache), rows, H, KV, hd, page_size, _stream()))
+    launch_count += 1
+
+
+def attn_decode_scratch_bytes(B, H, hd, num_splits) -> int:
+    return int(_lib.load().dli_paged_attn_decode_scratch_bytes(B, H, hd, num_splits))
+
+
+def paged_attn_decode(q, q_stride, k_cache, v_cache, page_table, seq_lens, out, H, KV, hd,
+                      scale, num_splits=1, scratch=None, window=0):
+    """q: tensor whose row b starts at q.data_ptr() + b*q_stride elements."""
+    global launch_count
+    _req(k_cache), _req(v_cache), _req(out)
+    _req(page_table, torch.int32), _req(seq_lens, torch.int32)
+    B = seq_lens.numel()
+    page_size = k_cache.shape[2]
+    sbytes = 0 if scratch is None else scratch.numel() * scratch.element_size()
+    _lib.check("dli_paged_attn_decode_bf16", _lib.load().dli_paged_attn_decode_bf16(
+        _p(q), q_stride, _p(k_cache), _p(v_cache), _p(page_table), page_table.shape[1], _p(seq_lens),
+        _p(out), _p(scratch), sbytes, B, H, KV, hd, page_size, num_splits, float(scale), window,
+        _stream()))
+    launch_count += 2 if num_splits > 1 else 1
+    return out
+
+
+def attn_prefill(qkv, out, B, T, H, KV, hd, scale, window=0):
+    global launch_count
+    _req(qkv), _req(out)
+    _lib.check("dli_attn_prefill_bf16", _lib.load().dli_attn_prefill_bf16(
+        _p(qkv), _p(out), B, T, H, KV, hd, float(scale), window, _stream()))
+    launch_count += 1
+    return out
+
+
+def _linear(fn_name, x, w, bias, residual, out, epilogue):
+    global launch_count
+    _req(x), _req(w), _req(bias), _req(residual), _req(out)
+    M, K = x.shape
+    N = w.shape[0]
+    if w.shape[1] != K:
+        raise ValueError(f"linear: x is [{M},{K}] but w is {tuple(w.shape)}")
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+    epi = epilogue | (EPI_BIAS if bias is not None else 0) | (EPI_RESIDUAL if residual is not None else 0)
+    fn = getattr(_lib.load(), fn_name)
+    _lib.check(fn_name, fn(_p(x), _p(w), _p(bias), _p(residual), _p(out), M, N, K, epi, _stream()))
+    launch_count += (M + 3) // 4 if fn_name == "dli_gemv_bf16" else 1
+    return out
+
+
+def linear(x, w, bias=None, residual=None, out=None, epilogue=EPI_NONE):
+    """y = epi(x @ w.T); GEMV for M <= 4, tcgen05 GEMM otherwise."""
+    return _linear("dli_linear_bf16", x, w, bias, residual, out, epilogue)
+
+
+def gemv(x, w, bias=None, residual=None, out=None, epilogue=EPI_NONE):
+    return _linear("dli_gemv_bf16", x, w, bias, residual, out, epilogue)
+
+
+def gemm(x, w, bias=None, residual=None, out=None, epilogue=EPI_NONE):
+    return _linear("dli_gemm_bf16", x, w, bias, residual, out, epilogue)
+
+
+def _gated(fn_name, x, w_gu, out):
+    global launch_count
+    _req(x), _req(w_gu), _req(out)
+    M, K = x.shape
+    F = w_gu.shape[0] // 2
+    if out is None:
+        out = torch.empty(M, F, dtype=torch.bfloat16, device=x.device)
+    fn = getattr(_lib.load(), fn_name)
+    _lib.check(fn_name, fn(_p(x), _p(w_gu), _p(out), M, F, K, _stream()))
+    launch_count += (M + 3) // 4 if fn_name == "dli_gemv_gated_silu_bf16" else 1
+    return out
+
+
+def linear_gated_silu(x, w_gu, out=None):
+    """silu(x @ Wg.T) * (x @ Wu.T) with w_gu = pack_gate_up(Wg, Wu)."""
+    return _gated("dli_linear_gated_silu_bf16", x, w_gu, out)
+
+
+def gemv_gated_silu(x, w_gu, out=None):
+    return _gated("dli_gemv_gated_silu_bf16", x, w_gu, out)
+
+
+def gemm_gated_silu(x, w_gu, out=None):
+    return _gated("dli_gemm_gated_silu_bf16", x, w_gu, out)
+
+
+def pack_gate_up(w_gate, w_up):
+    """Interleave gate and up rows in blocks of 128 (layout dli.h documents)."""
+    F, K = w_gate.shape
+    if F % 128 != 0:
+        raise ValueError("intermediate size must be a multiple of 128")
+    g = w_gate.reshape(F // 128, 128, K)
+    u = w_up.reshape(F // 128, 128, K)
+    return torch.stack((g, u), dim=1).reshape(2 * F, K).contiguous()
+
+
+def argmax(logits, out=None):
+    """logits bf16 [B, V] (row stride may exceed V) -> int32 [B]."""
+    global launch_count
+    if logits.dtype != torch.bfloat16 or not logits.is_cuda or logits.stride(1) != 1:
+        raise ValueError("argmax needs a CUDA bf16 tensor with unit inner stride")
+    B, V = logits.shape
+    if out is None:
+        out = torch.empty(B, dtype=torch.int32, device=logits.device)
+    _lib.check("dli_argmax_bf16", _lib.load().dli_argmax_bf16(
+        _p(logits), logits.stride(0), _p(out), B, V, _stream()))
+    launch_count += 1
+    return out

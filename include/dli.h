@@ -1,0 +1,177 @@
+/*
+ * dli.h — C-ABI of the B200-native sharded decoder forward.
+ *
+ * This is the drop-in boundary for ONE hot path of
+ * MihirPanpatil/Distributed-LLM-Inferencing: the worker's decoder forward,
+ * i.e. what `model.generate(...)` executes at worker/app.py:297-305 and
+ * worker/app.py:359-367 (reference paths are relative to the reference repo;
+ * `TF:` paths are relative to the `transformers` package the reference calls,
+ * which is where the arithmetic lives — SURVEY.md §8c).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is CALLER-OWNED DEVICE memory
+ *     unless the parameter comment says "host";
+ *   - bf16 tensors are `void*` to 2-byte bfloat16, row-major, innermost dim
+ *     contiguous, 16-byte aligned base and row strides;
+ *   - `stream` is a `cudaStream_t` passed as `void*` (NULL = legacy default);
+ *   - every entry point returns DLI_OK or a negative error code and never
+ *     throws; `dli_last_error()` gives the thread-local message of the last
+ *     failure;
+ *   - entry points only ENQUEUE work on `stream`; none synchronises, and none
+ *     allocates device memory (scratch is passed in by the caller).
+ *   - there is no CPU fallback: without a CUDA device the compute entry
+ *     points fail with DLI_ERR_CUDA.
+ */
+#ifndef DLI_H_
+#define DLI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLI_OK 0
+#define DLI_ERR_INVALID (-1)     /* bad argument (shape, alignment, null) */
+#define DLI_ERR_CUDA (-2)        /* a CUDA runtime / driver call failed   */
+#define DLI_ERR_UNSUPPORTED (-3) /* shape outside what the kernels cover  */
+
+/* epilogue selectors for the linear (projection) entry points */
+#define DLI_EPI_NONE 0      /* y = bf16(acc)                                   */
+#define DLI_EPI_BIAS 1      /* y = bf16(acc + bias)          (GPT-2 Conv1D)    */
+#define DLI_EPI_RESIDUAL 2  /* y = bf16(res + bf16(acc[+bias]))                */
+#define DLI_EPI_GELU_NEW 4  /* y = bf16(gelu_new(bf16(acc[+bias])))  (GPT-2)   */
+
+typedef void* dli_stream_t;
+
+/* ---- library ----------------------------------------------------------- */
+
+/* Thread-local message of the last failing call ("" if none). */
+const char* dli_last_error(void);
+/* ABI version: major*1000 + minor. */
+int dli_version(void);
+/* Number of SMs of the current device (used by host code to size grids /
+ * split counts); negative error code without a device. */
+int dli_sm_count(void);
+
+/* ---- embedding ---------------------------------------------------------
+ * out[r,:] = table[ids[r],:] (+ pos_table[positions[r],:] when pos_table != NULL)
+ * Replaces: TF:models/llama/modeling_llama.py:389 (embed_tokens) and
+ * TF:models/gpt2/modeling_gpt2.py:577-585 (wte + wpe), reached from
+ * worker/app.py:297,359.  ids/positions: int32 [rows].  d % 8 == 0. */
+int dli_embedding_bf16(const int32_t* ids, const int32_t* positions,
+                       const void* table, const void* pos_table, void* out,
+                       int rows, int d, int vocab, dli_stream_t stream);
+
+/* ---- norms with fused residual add --------------------------------------
+ * h = residual + x (bf16 add; residual may be NULL => h = x)
+ * y = weight * bf16(h * rsqrt(mean(h^2) + eps))           (RMSNorm)
+ * If resid_out != NULL, h is written there (may alias `residual` or `x`).
+ * Replaces: LlamaRMSNorm TF:models/llama/modeling_llama.py:62-67 plus the
+ * residual adds at :325,:331.  d % 8 == 0, d <= 16384. */
+int dli_add_rmsnorm_bf16(const void* x, const void* residual, const void* weight,
+                         void* resid_out, void* y, int rows, int d, float eps,
+                         dli_stream_t stream);
+
+/* Same with LayerNorm (weight and bias), replacing
+ * TF:models/gpt2/modeling_gpt2.py:252-254,:505 and the adds at :282,:307. */
+int dli_add_layernorm_bf16(const void* x, const void* residual, const void* weight,
+                           const void* bias, void* resid_out, void* y, int rows,
+                           int d, float eps, dli_stream_t stream);
+
+/* ---- RoPE + paged KV-cache append ---------------------------------------
+ * qkv: [rows, (H + 2*KV) * hd] bf16, packed q | k | v per row.
+ * Rotates q and k in place with the rotate-half convention
+ *   (TF:models/llama/modeling_llama.py:138-168; cos/sin are the bf16 tables
+ *   HF computes at :124-135, shape [max_pos, hd/2], passed by the host), then
+ * writes k and v of each row into the paged cache, replacing the torch.cat
+ * append of TF:cache_utils.py:102-121.
+ * cos == NULL => no rotation (GPT-2), append only.
+ * positions[r]: absolute position of row r; seq_ids[r]: its sequence (row of
+ * page_table).  page_table: int32 [n_seqs, max_pages].
+ * k_cache / v_cache: [num_pages, KV, page_size, hd] bf16.
+ * hd in {64, 128}; page_size a power of two >= 8. */
+int dli_rope_kv_append_bf16(void* qkv, const void* cos, const void* sin,
+                            const int32_t* positions, const int32_t* seq_ids,
+                            const int32_t* page_table, int max_pages,
+                            void* k_cache, void* v_cache, int rows, int H, int KV,
+                            int hd, int page_size, dli_stream_t stream);
+
+/* ---- paged decode attention (split-KV, GQA-aware) ------------------------
+ * One query token per sequence against its paged KV cache:
+ *   out[b, h, :] = softmax(q[b,h,:] . K[b, kv(h), :S_b, :]^T * scale) V
+ * Replaces: TF:integrations/sdpa_attention.py:40-104 (default) /
+ * eager TF:models/llama/modeling_llama.py:199-221 at T=1, incl. the GQA
+ * head grouping (repeat_kv) without materialising it.
+ * q: row b at q + b*q_stride elements, [H*hd] (so it can point into qkv).
+ * seq_lens[b]: number of cached tokens INCLUDING the one just appended.
+ * window > 0: only the last `window` tokens are attended (Mistral sliding
+ * window, TF:models/mistral/modeling_mistral.py:172,:372); 0 = full.
+ * num_splits >= 1 KV splits per (sequence, kv head); scratch must hold
+ * dli_paged_attn_decode_scratch_bytes(...) bytes when num_splits > 1
+ * (ignored, may be NULL, when num_splits == 1).
+ * out: [B, H*hd] bf16.  hd in {64,128}; H/KV <= 16. */
+size_t dli_paged_attn_decode_scratch_bytes(int B, int H, int hd, int num_splits);
+int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
+                               const void* v_cache, const int32_t* page_table,
+                               int max_pages, const int32_t* seq_lens, void* out,
+                               void* scratch, size_t scratch_bytes, int B, int H,
+                               int KV, int hd, int page_size, int num_splits,
+                               float scale, int window, dli_stream_t stream);
+
+/* ---- causal prefill attention --------------------------------------------
+ * B sequences of T new tokens each, no earlier context: q, k, v are read from
+ * the packed (already rotated) qkv buffer [B*T, (H+2KV)*hd].
+ * Replaces the same reference code as above at T>1 with a causal mask
+ * (TF:masking_utils create_causal_mask, called at
+ * TF:models/llama/modeling_llama.py:398-405).  window as above.
+ * out: [B*T, H*hd] bf16. */
+int dli_attn_prefill_bf16(const void* qkv, void* out, int B, int T, int H, int KV,
+                          int hd, float scale, int window, dli_stream_t stream);
+
+/* ---- projections -----------------------------------------------------------
+ * y[M,N] = epi(x[M,K] . w[N,K]^T)   — w is the HF nn.Linear layout [out,in].
+ * Replaces q/k/v/o_proj TF:models/llama/modeling_llama.py:262-264,:288, the
+ * MLP projections :183, lm_head :486-487 and GPT-2's Conv1D
+ * (TF:pytorch_utils.py:97-123, weight transposed once at load).
+ * `epilogue` is an OR of DLI_EPI_*; bias [N] / residual [M,N] may be NULL when
+ * their flag is clear.  y may alias residual.  K % 8 == 0.
+ *
+ * dli_gemv_bf16   : CUDA-core weight-streaming kernel for M <= 8 (decode).
+ * dli_gemm_bf16   : tcgen05/TMEM tensor-core GEMM fed by TMA; any M.
+ *                   K % 64 == 0, N % 16 == 0.
+ * dli_linear_bf16 : picks between them by M. */
+int dli_gemv_bf16(const void* x, const void* w, const void* bias,
+                  const void* residual, void* y, int M, int N, int K, int epilogue,
+                  dli_stream_t stream);
+int dli_gemm_bf16(const void* x, const void* w, const void* bias,
+                  const void* residual, void* y, int M, int N, int K, int epilogue,
+                  dli_stream_t stream);
+int dli_linear_bf16(const void* x, const void* w, const void* bias,
+                    const void* residual, void* y, int M, int N, int K,
+                    int epilogue, dli_stream_t stream);
+
+/* Gated MLP up-projection: y[M,F] = bf16(silu(bf16(x.Wg^T))) * bf16(x.Wu^T)
+ * (TF:models/llama/modeling_llama.py:183, act = SiLU).
+ * w_gu: [2F, K] with gate and up rows interleaved in blocks of 128 rows:
+ * rows [256j, 256j+128) = gate rows [128j, 128j+128), next 128 = up rows
+ * (the host packs this once at load).  F % 128 == 0, K % 64 == 0. */
+int dli_gemv_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F,
+                             int K, dli_stream_t stream);
+int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F,
+                             int K, dli_stream_t stream);
+int dli_linear_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M,
+                               int F, int K, dli_stream_t stream);
+
+/* ---- greedy sampling epilogue ----------------------------------------------
+ * out[b] = argmax_v logits[b, v]  (lowest index wins ties, like torch.argmax),
+ * replacing the logits -> argmax step TF:generation/utils.py:2762-2793 with
+ * do_sample=False.  logits: bf16 [B, V] with row stride `ld` elements. */
+int dli_argmax_bf16(const void* logits, int ld, int32_t* out, int B, int V,
+                    dli_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLI_H_ */

@@ -1,0 +1,361 @@
+"""Kernel-level parity: every C-ABI entry point against a plain PyTorch fp32
+restatement of the same op (floating-point kernels; tolerance stated per test).
+Integer/index work (embedding gather, KV-cache placement, argmax) is bit-exact.
+"""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+BF = torch.bfloat16
+
+
+def _ulp_close(a, b, max_ulp=1, min_exact=0.97):
+    """bf16 tensors equal up to `max_ulp` bf16 ulps, and mostly bit-identical."""
+    a32, b32 = a.float(), b.float()
+    ulp = torch.maximum(a32.abs(), b32.abs()).clamp_min(1e-30) * 2.0 ** -7
+    bad = (a32 - b32).abs() > max_ulp * ulp + 1e-30
+    assert not bad.any(), f"{int(bad.sum())} elements differ by more than {max_ulp} bf16 ulp"
+    exact = (a32 == b32).float().mean().item()
+    assert exact >= min_exact, f"only {exact:.4f} bit-identical"
+
+
+# ----------------------------------------------------------------------------- norms
+@pytest.mark.parametrize("rows,d", [(1, 4096), (7, 2048), (64, 8192), (3, 768), (5, 64)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_add_rmsnorm(cuda, rows, d, with_res):
+    from dli_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(rows * 131 + d)
+    x = torch.randn(rows, d, device=cuda, generator=g).to(BF)
+    res = torch.randn(rows, d, device=cuda, generator=g).to(BF) if with_res else None
+    w = (1 + 0.1 * torch.randn(d, device=cuda, generator=g)).to(BF)
+    eps = 1e-5
+    h_out = torch.empty_like(x)
+    y = ops.add_rmsnorm(x, w, eps, residual=res, resid_out=h_out)
+    # HF LlamaRMSNorm (modeling_llama.py:62-67) on h = residual + x
+    h = x if res is None else (res + x)
+    hf = h.float()
+    ref = w * (hf * torch.rsqrt(hf.pow(2).mean(-1, keepdim=True) + eps)).to(BF)
+    assert torch.equal(h_out, h)
+    _ulp_close(y, ref)
+
+
+@pytest.mark.parametrize("rows,d", [(1, 768), (9, 1024), (4, 4096)])
+def test_add_layernorm(cuda, rows, d):
+    from dli_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(d)
+    x = torch.randn(rows, d, device=cuda, generator=g).to(BF)
+    res = torch.randn(rows, d, device=cuda, generator=g).to(BF)
+    w = (1 + 0.1 * torch.randn(d, device=cuda, generator=g)).to(BF)
+    b = (0.1 * torch.randn(d, device=cuda, generator=g)).to(BF)
+    h_out = torch.empty_like(x)
+    y = ops.add_layernorm(x, w, b, 1e-5, residual=res, resid_out=h_out)
+    h = res + x
+    ref = torch.nn.functional.layer_norm(h.float(), (d,), w.float(), b.float(), 1e-5).to(BF)
+    assert torch.equal(h_out, h)
+    _ulp_close(y, ref)
+
+
+# ----------------------------------------------------------------------------- embedding / argmax
+def test_embedding_exact(cuda):
+    from dli_b200 import ops
+
+    V, d = 1000, 256
+    table = torch.randn(V, d, device=cuda).to(BF)
+    pos_t = torch.randn(64, d, device=cuda).to(BF)
+    ids = torch.randint(0, V, (37,), device=cuda, dtype=torch.int32)
+    pos = torch.randint(0, 64, (37,), device=cuda, dtype=torch.int32)
+    assert torch.equal(ops.embedding(ids, table), table[ids.long()])
+    assert torch.equal(ops.embedding(ids, table, positions=pos, pos_table=pos_t), table[ids.long()] + pos_t[pos.long()])
+    assert ops.embedding(ids[:0], table).shape == (0, d)
+
+
+@pytest.mark.parametrize("B,V", [(1, 128256), (32, 32000), (3, 50257), (2, 17)])
+def test_argmax_exact_with_ties(cuda, B, V):
+    from dli_b200 import ops
+
+    logits = torch.randn(B, V, device=cuda).to(BF)
+    # force exact ties of the maximum at several positions: lowest index must win
+    top = logits.float().max().item() + 1.0
+    for b in range(B):
+        idx = torch.randint(0, V, (3,), device=cuda)
+        logits[b, idx] = top
+    out = ops.argmax(logits)
+    ref = torch.stack([(logits[b].float() == logits[b].float().max()).nonzero()[0, 0] for b in range(B)])
+    assert torch.equal(out.long(), ref)
+    # strided rows (logits living inside a wider buffer)
+    if V % 8 == 0:
+        wide = torch.full((B, V + 64), -1e9, device=cuda).to(BF)
+        wide[:, :V] = logits
+        assert torch.equal(ops.argmax(wide[:, :V]).long(), ref)
+
+
+# ----------------------------------------------------------------------------- rope + kv append
+def _hf_rope_tables(hd, theta, max_pos, device):
+    # LlamaRotaryEmbedding (modeling_llama.py:73-135): fp32 angles, cos/sin cast to bf16
+    inv_freq = 1.0 / (theta ** (torch.arange(0, hd, 2, dtype=torch.int64).float() / hd))
+    t = torch.arange(max_pos, dtype=torch.float32)
+    freqs = torch.outer(t, inv_freq)
+    return freqs.cos().to(BF).to(device), freqs.sin().to(BF).to(device)
+
+
+def _rotate_half(x):
+    x1, x2 = x[..., : x.shape[-1] // 2], x[..., x.shape[-1] // 2:]
+    return torch.cat((-x2, x1), dim=-1)
+
+
+@pytest.mark.parametrize("H,KV,hd,page", [(32, 8, 128, 16), (32, 4, 64, 32), (4, 4, 64, 8)])
+def test_rope_kv_append_exact(cuda, H, KV, hd, page):
+    from dli_b200 import ops
+
+    torch.manual_seed(0)
+    B, T, max_pos = 3, 21, 64
+    rows = B * T
+    qkv = torch.randn(rows, (H + 2 * KV) * hd, device=cuda).to(BF)
+    cos, sin = _hf_rope_tables(hd, 10000.0, max_pos, cuda)
+    start = torch.tensor([0, 5, 40], device=cuda)
+    positions = (start[:, None] + torch.arange(T, device=cuda)[None]).reshape(-1).int()
+    seq_ids = torch.arange(B, device=cuda).repeat_interleave(T).int()
+    max_pages = max_pos // page
+    perm = torch.randperm(B * max_pages, device=cuda).int()
+    page_table = perm.reshape(B, max_pages).contiguous()
+    kc = torch.zeros(B * max_pages, KV, page, hd, device=cuda, dtype=BF)
+    vc = torch.zeros_like(kc)
+    ref_qkv = qkv.clone()
+    ops.rope_kv_append(qkv, cos, sin, positions, seq_ids, page_table, kc, vc, H, KV, hd)
+
+    # HF apply_rotary_pos_emb (modeling_llama.py:138-168), bf16 op by op
+    q = ref_qkv[:, : H * hd].reshape(rows, H, hd)
+    k = ref_qkv[:, H * hd: (H + KV) * hd].reshape(rows, KV, hd)
+    v = ref_qkv[:, (H + KV) * hd:].reshape(rows, KV, hd)
+    c = torch.cat((cos, cos), -1)[positions.long()][:, None, :]
+    s = torch.cat((sin, sin), -1)[positions.long()][:, None, :]
+    q_ref = q * c + _rotate_half(q) * s
+    k_ref = k * c + _rotate_half(k) * s
+    assert torch.equal(qkv[:, : H * hd].reshape(rows, H, hd), q_ref)
+    assert torch.equal(qkv[:, H * hd: (H + KV) * hd].reshape(rows, KV, hd), k_ref)
+    assert torch.equal(qkv[:, (H + KV) * hd:], ref_qkv[:, (H + KV) * hd:])
+    for r in range(rows):
+        p, b = int(positions[r]), int(seq_ids[r])
+        pg, off = int(page_table[b, p // page]), p % page
+        assert torch.equal(kc[pg, :, off, :], k_ref[r])
+        assert torch.equal(vc[pg, :, off, :], v[r])
+
+
+def test_kv_append_without_rope(cuda):
+    from dli_b200 import ops
+
+    H = KV = 4
+    hd, page = 64, 16
+    qkv = torch.randn(5, 3 * H * hd, device=cuda).to(BF)
+    before = qkv.clone()
+    positions = torch.arange(5, device=cuda).int()
+    seq_ids = torch.zeros(5, device=cuda).int()
+    page_table = torch.tensor([[1, 0]], device=cuda).int()
+    kc = torch.zeros(2, KV, page, hd, device=cuda, dtype=BF)
+    vc = torch.zeros_like(kc)
+    ops.rope_kv_append(qkv, None, None, positions, seq_ids, page_table, kc, vc, H, KV, hd)
+    assert torch.equal(qkv, before)
+    assert torch.equal(kc[1, :, :5].transpose(0, 1).reshape(5, -1), before[:, H * hd: 2 * H * hd])
+    assert torch.equal(vc[1, :, :5].transpose(0, 1).reshape(5, -1), before[:, 2 * H * hd:])
+
+
+# ----------------------------------------------------------------------------- attention
+def _paged_cache(B, S_max, KV, hd, page, device, gen):
+    max_pages = (S_max + page - 1) // page
+    n_pages = B * max_pages + 3
+    perm = torch.randperm(n_pages, device=device, generator=gen)[: B * max_pages].int()
+    page_table = perm.reshape(B, max_pages).contiguous()
+    # poison unused slots with NaN-free but huge values so leaks show up
+    kc = torch.randn(n_pages, KV, page, hd, device=device, generator=gen).to(BF)
+    vc = torch.randn(n_pages, KV, page, hd, device=device, generator=gen).to(BF)
+    return page_table, kc, vc
+
+
+def _gather_kv(cache, page_table, b, S):
+    page = cache.shape[2]
+    pages = page_table[b, : (S + page - 1) // page].long()
+    x = cache[pages]  # [np, KV, page, hd]
+    return x.permute(1, 0, 2, 3).reshape(cache.shape[1], -1, cache.shape[3])[:, :S]  # [KV, S, hd]
+
+
+@pytest.mark.parametrize(
+    "B,H,KV,hd,page,lens,splits,window",
+    [
+        (1, 32, 8, 128, 16, [2048], 16, 0),
+        (1, 32, 8, 128, 16, [2048], 1, 0),
+        (4, 32, 8, 128, 32, [1, 63, 64, 777], 4, 0),
+        (3, 32, 4, 64, 16, [130, 5, 300], 3, 0),
+        (2, 64, 8, 128, 16, [1000, 513], 8, 0),
+        (2, 32, 8, 128, 16, [900, 200], 4, 256),
+        (2, 12, 12, 64, 16, [40, 97], 2, 0),
+    ],
+)
+def test_paged_attn_decode(cuda, B, H, KV, hd, page, lens, splits, window):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(1234 + B + H)
+    S_max = max(lens)
+    page_table, kc, vc = _paged_cache(B, S_max, KV, hd, page, cuda, gen)
+    q = torch.randn(B, H * hd, device=cuda, generator=gen).to(BF)
+    seq_lens = torch.tensor(lens, device=cuda, dtype=torch.int32)
+    out = torch.empty(B, H * hd, device=cuda, dtype=BF)
+    nbytes = ops.attn_decode_scratch_bytes(B, H, hd, splits)
+    scratch = torch.empty(max(nbytes, 4) // 4, device=cuda, dtype=torch.float32)
+    scale = hd ** -0.5
+    ops.paged_attn_decode(q, H * hd, kc, vc, page_table, seq_lens, out, H, KV, hd, scale,
+                          num_splits=splits, scratch=scratch, window=window)
+    G = H // KV
+    for b in range(B):
+        S = lens[b]
+        k = _gather_kv(kc, page_table, b, S).float()  # [KV, S, hd]
+        v = _gather_kv(vc, page_table, b, S).float()
+        if window and S > window:
+            k, v = k[:, S - window:], v[:, S - window:]
+        qb = q[b].float().reshape(KV, G, hd)
+        p = torch.softmax(torch.einsum("kgd,ksd->kgs", qb, k) * scale, dim=-1)
+        ref = torch.einsum("kgs,ksd->kgd", p, v).reshape(-1)
+        # fp32 reference; kernel rounds P to bf16 before P.V and the output to bf16:
+        # tolerance 2e-2 absolute on O(1) values (|out| <= max|v| ~ 4)
+        torch.testing.assert_close(out[b].float(), ref, rtol=2e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize(
+    "B,T,H,KV,hd,window",
+    [(1, 2048, 32, 8, 128, 0), (2, 100, 32, 4, 64, 0), (1, 1, 4, 4, 64, 0), (1, 300, 8, 2, 128, 128),
+     (3, 65, 12, 12, 64, 0)],
+)
+def test_attn_prefill(cuda, B, T, H, KV, hd, window):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(7 + T)
+    qkv = torch.randn(B * T, (H + 2 * KV) * hd, device=cuda, generator=gen).to(BF)
+    out = torch.empty(B * T, H * hd, device=cuda, dtype=BF)
+    scale = hd ** -0.5
+    ops.attn_prefill(qkv, out, B, T, H, KV, hd, scale, window=window)
+    G = H // KV
+    x = qkv.float().reshape(B, T, H + 2 * KV, hd)
+    q = x[:, :, :H].permute(0, 2, 1, 3)  # [B,H,T,hd]
+    k = x[:, :, H: H + KV].permute(0, 2, 1, 3).repeat_interleave(G, dim=1)
+    v = x[:, :, H + KV:].permute(0, 2, 1, 3).repeat_interleave(G, dim=1)
+    s = torch.einsum("bhtd,bhsd->bhts", q, k) * scale
+    i = torch.arange(T, device=cuda)
+    mask = i[None, :] > i[:, None]
+    if window:
+        mask = mask | (i[None, :] <= i[:, None] - window)
+    s = s.masked_fill(mask, float("-inf"))
+    ref = torch.einsum("bhts,bhsd->bhtd", torch.softmax(s, -1), v).permute(0, 2, 1, 3).reshape(B * T, H * hd)
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
+
+
+# ----------------------------------------------------------------------------- projections
+def _lin_ref(x, w, bias=None, residual=None, gelu=False):
+    acc = x.float() @ w.float().t()
+    if bias is not None:
+        acc = acc + bias.float()
+    y = acc.to(BF)
+    if gelu:
+        y = torch.nn.functional.gelu(y.float(), approximate="tanh").to(BF)
+    if residual is not None:
+        y = (residual.float() + y.float()).to(BF)
+    return y
+
+
+def _check_linear(y, ref, K, acc_scale=1.0):
+    # fp32-accumulated bf16 GEMM vs fp32 reference.  Both round the accumulator to bf16
+    # once, so a different summation order can move a value sitting on a rounding
+    # boundary by one bf16 ulp (2^-7 relative to the ACCUMULATOR, which after a residual
+    # add or a gate*up product can be larger than the final value): rtol = 2 ulp, atol =
+    # 1 ulp of the typical accumulator magnitude `acc_scale`*sqrt(K/4096).
+    torch.testing.assert_close(y.float(), ref.float(), rtol=1.6e-2,
+                               atol=max(2e-2, 2.0 ** -7 * 4 * acc_scale) * math.sqrt(K / 4096))
+
+
+@pytest.mark.parametrize("M", [1, 2, 3, 4, 7])
+@pytest.mark.parametrize("N,K", [(6144, 4096), (4096, 14336), (2560, 2048), (1000, 264)])
+def test_gemv(cuda, M, N, K):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(M * 7 + N)
+    x = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    w = (torch.randn(N, K, device=cuda, generator=gen) * 0.02).to(BF)
+    bias = torch.randn(N, device=cuda, generator=gen).to(BF)
+    res = torch.randn(M, N, device=cuda, generator=gen).to(BF)
+    _check_linear(ops.gemv(x, w), _lin_ref(x, w), K)
+    _check_linear(ops.gemv(x, w, bias=bias, residual=res), _lin_ref(x, w, bias, res), K)
+    _check_linear(ops.gemv(x, w, bias=bias, epilogue=ops.EPI_GELU_NEW), _lin_ref(x, w, bias, gelu=True), K)
+
+
+def _gated_ref(x, wg, wu):
+    g = (x.float() @ wg.float().t()).to(BF)
+    u = (x.float() @ wu.float().t()).to(BF)
+    return torch.nn.functional.silu(g) * u  # bf16 ops, HF rounding points
+
+
+@pytest.mark.parametrize("M,F,K", [(1, 14336, 4096), (3, 5632, 2048), (4, 256, 128)])
+def test_gemv_gated_silu(cuda, M, F, K):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(F)
+    x = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    wg = (torch.randn(F, K, device=cuda, generator=gen) * 0.03).to(BF)
+    wu = (torch.randn(F, K, device=cuda, generator=gen) * 0.03).to(BF)
+    y = ops.gemv_gated_silu(x, ops.pack_gate_up(wg, wu))
+    torch.testing.assert_close(y.float(), _gated_ref(x, wg, wu).float(), rtol=3.2e-2, atol=2e-2 * math.sqrt(K / 4096))
+
+
+@pytest.mark.parametrize(
+    "M,N,K",
+    [(2048, 6144, 4096), (2048, 4096, 4096), (300, 2560, 2048), (129, 512, 128), (1000, 48, 64),
+     (5, 4096, 4096), (16, 1024, 512), (32, 6144, 4096), (64, 2048, 2048), (100, 384, 256), (128, 128256, 256)],
+)
+def test_gemm_tcgen05(cuda, M, N, K):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(M + N + K)
+    x = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    w = (torch.randn(N, K, device=cuda, generator=gen) * 0.02).to(BF)
+    bias = torch.randn(N, device=cuda, generator=gen).to(BF)
+    res = torch.randn(M, N, device=cuda, generator=gen).to(BF)
+    _check_linear(ops.gemm(x, w), _lin_ref(x, w), K)
+    _check_linear(ops.gemm(x, w, bias=bias, residual=res), _lin_ref(x, w, bias, res), K)
+    _check_linear(ops.gemm(x, w, bias=bias, epilogue=ops.EPI_GELU_NEW), _lin_ref(x, w, bias, gelu=True), K)
+
+
+@pytest.mark.parametrize("M,F,K", [(2048, 14336, 4096), (200, 5632, 2048), (32, 14336, 4096), (8, 256, 128), (130, 128, 64)])
+def test_gemm_gated_silu_tcgen05(cuda, M, F, K):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(M + F)
+    x = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    wg = (torch.randn(F, K, device=cuda, generator=gen) * 0.03).to(BF)
+    wu = (torch.randn(F, K, device=cuda, generator=gen) * 0.03).to(BF)
+    y = ops.gemm_gated_silu(x, ops.pack_gate_up(wg, wu))
+    # silu(g)*u: a 1-ulp move of g or u scales with the other factor (|g|,|u| up to ~8 here)
+    torch.testing.assert_close(y.float(), _gated_ref(x, wg, wu).float(), rtol=3.2e-2, atol=2e-2 * math.sqrt(K / 4096))
+
+
+def test_gemv_matches_gemm_closely(cuda):
+    """The two projection paths agree to bf16 rounding on the same inputs."""
+    from dli_b200 import ops
+
+    x = torch.randn(4, 4096, device=cuda).to(BF)
+    w = (torch.randn(4096, 4096, device=cuda) * 0.02).to(BF)
+    a, b = ops.gemv(x, w).float(), ops.gemm(x, w).float()
+    assert (a - b).abs().max() <= 2.0 ** -7 * a.abs().max()
+
+
+def test_bad_arguments_raise(cuda):
+    from dli_b200 import _lib, ops
+
+    x = torch.randn(2, 100, device=cuda).to(BF)  # K % 8 != 0
+    w = torch.randn(16, 100, device=cuda).to(BF)
+    with pytest.raises(_lib.DliError) as e:
+        ops.gemv(x, w)
+    assert "K % 8" in str(e.value)
+    with pytest.raises(ValueError):
+        ops.add_rmsnorm(x.cpu(), w[0].cpu(), 1e-5)
