@@ -82,9 +82,36 @@ argmax_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out
   }
 }
 
+// Bookkeeping between two decode steps, on device so a captured CUDA graph can be
+// replayed without host involvement: log the tokens just sampled, then advance
+// every sequence's position / cached length and the step counter.
+__global__ void decode_advance_kernel(const int32_t* __restrict__ tokens, int32_t* __restrict__ token_log,
+                                      int32_t* __restrict__ positions, int32_t* __restrict__ seq_lens,
+                                      int32_t* __restrict__ step, int B, int log_capacity) {
+  const int s = *step;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    if (token_log && s < log_capacity) token_log[(size_t)s * B + b] = tokens[b];
+    if (positions) positions[b] += 1;
+    if (seq_lens) seq_lens[b] += 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *step = s + 1;
+}
+
 }  // namespace dli
 
 extern "C" {
+
+int dli_decode_advance(const int32_t* tokens, int32_t* token_log, int32_t* positions, int32_t* seq_lens,
+                       int32_t* step, int B, int log_capacity, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(step && (tokens || !token_log), "dli_decode_advance: null pointer");
+  DLI_CHECK_ARG(B >= 0 && log_capacity >= 0, "dli_decode_advance: bad sizes B=%d cap=%d", B, log_capacity);
+  decode_advance_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(tokens, token_log, positions, seq_lens,
+                                                                         step, B, log_capacity);
+  DLI_CUDA_LAUNCH_CHECK("dli_decode_advance");
+  return DLI_OK;
+}
 
 int dli_embedding_bf16(const int32_t* ids, const int32_t* positions, const void* table,
                        const void* pos_table, void* out, int rows, int d, int vocab,

@@ -1,0 +1,521 @@
+"""ShardEngine — one contiguous layer range of a causal LM on one B200.
+
+This is the host-side mirror of what the reference worker does with a shard
+(reference worker/app.py:332-372 `run_shard_inference`, intended semantics per
+SURVEY.md §0: run layers [start_layer, end_layer] on hidden states and hand the
+result to the next shard) and, with the full range, of the unsharded path
+(worker/app.py:289-308).  Stage 0 additionally owns the embedding, the last
+stage the final norm, lm_head and the greedy argmax.
+
+PyTorch is plumbing here: device memory, streams, CUDA-graph capture.  All
+arithmetic goes through the C-ABI kernels (ops.py -> include/dli.h).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+
+BF = torch.bfloat16
+
+
+@dataclass
+class ModelSpec:
+    """Architecture numbers (same fields as the oracle's spec)."""
+
+    arch: str  # "llama" (Llama / TinyLlama / Mistral) or "gpt2"
+    n_layers: int
+    d_model: int
+    n_heads: int
+    n_kv_heads: int
+    head_dim: int
+    d_ff: int
+    vocab: int
+    eps: float = 1e-5
+    rope_theta: float = 10000.0
+    sliding_window: int = 0
+    max_pos: int = 8192
+    tie_embeddings: bool = False
+
+    @staticmethod
+    def from_hf_config(cfg) -> "ModelSpec":
+        """From a transformers config object or a config.json dict."""
+        g = (lambda k, d=None: cfg.get(k, d)) if isinstance(cfg, dict) else (lambda k, d=None: getattr(cfg, k, d))
+        mt = g("model_type")
+        if mt == "gpt2":
+            d, h = g("n_embd"), g("n_head")
+            return ModelSpec("gpt2", g("n_layer"), d, h, h, d // h, g("n_inner") or 4 * d, g("vocab_size"),
+                             g("layer_norm_epsilon", 1e-5), 0.0, 0, g("n_positions", 1024), True)
+        if mt in ("llama", "mistral"):
+            d, h = g("hidden_size"), g("num_attention_heads")
+            rp = g("rope_parameters") or {}
+            theta = (rp.get("rope_theta") if isinstance(rp, dict) else None) or g("rope_theta", 10000.0)
+            win = (g("sliding_window") or 0) if mt == "mistral" else 0
+            return ModelSpec("llama", g("num_hidden_layers"), d, h, g("num_key_value_heads") or h,
+                             g("head_dim") or d // h, g("intermediate_size"), g("vocab_size"),
+                             g("rms_norm_eps", 1e-6), float(theta), int(win), g("max_position_embeddings", 8192),
+                             bool(g("tie_word_embeddings", False)))
+        raise ValueError(f"unsupported model_type {mt!r} (llama, mistral, gpt2)")
+
+    def layer_weight_bytes(self) -> int:
+        """bf16 bytes of one decoder layer's matrices (SURVEY.md §8d W_layer)."""
+        d, hd = self.d_model, self.head_dim
+        qkv_o = (self.n_heads + 2 * self.n_kv_heads) * hd * d + self.n_heads * hd * d
+        mlp = (3 if self.arch == "llama" else 2) * d * self.d_ff
+        return 2 * (qkv_o + mlp)
+
+    def head_weight_bytes(self) -> int:
+        return 2 * self.d_model * self.vocab
+
+    def kv_bytes_per_token(self, n_layers: Optional[int] = None) -> int:
+        return 2 * 2 * self.n_kv_heads * self.head_dim * (self.n_layers if n_layers is None else n_layers)
+
+
+# SURVEY.md §A.2 shapes (random-init; there are no checkpoints offline)
+NAMED_SPECS = {
+    "gpt2": ModelSpec("gpt2", 12, 768, 12, 12, 64, 3072, 50257, 1e-5, 0.0, 0, 1024, True),
+    "tinyllama-1.1b": ModelSpec("llama", 22, 2048, 32, 4, 64, 5632, 32000, 1e-5, 10000.0, 0, 2048),
+    "llama-3-8b": ModelSpec("llama", 32, 4096, 32, 8, 128, 14336, 128256, 1e-5, 500000.0, 0, 8192),
+    "mistral-7b": ModelSpec("llama", 32, 4096, 32, 8, 128, 14336, 32000, 1e-5, 10000.0, 4096, 32768),
+    "llama-3-70b": ModelSpec("llama", 80, 8192, 64, 8, 128, 28672, 128256, 1e-5, 500000.0, 0, 8192),
+}
+
+
+def rope_tables(spec: ModelSpec, max_pos: int, device) -> tuple:
+    """bf16 cos/sin half tables [max_pos, hd/2], computed on the host with the
+    exact op sequence of LlamaRotaryEmbedding (TF:models/llama/modeling_llama.py:73-135)
+    so they are bit-identical to what the reference's forward multiplies by."""
+    hd = spec.head_dim
+    inv_freq = 1.0 / (spec.rope_theta ** (torch.arange(0, hd, 2, dtype=torch.int64).to(torch.float32) / hd))
+    freqs = torch.arange(max_pos, dtype=torch.float32)[:, None] * inv_freq[None, :]
+    return freqs.cos().to(BF).to(device), freqs.sin().to(BF).to(device)
+
+
+class PagedKVCache:
+    """Paged KV cache of one stage: per layer K and V pools
+    [num_pages, KV, page_size, hd] plus one page table shared by the stage's
+    layers.  Replaces the grow-by-torch.cat cache of TF:cache_utils.py:102-121
+    (an O(S) copy per layer per token) with in-place page writes."""
+
+    def __init__(self, n_layers, n_kv, hd, page_size, max_seqs, max_seq_len, device):
+        self.page_size = page_size
+        self.max_pages = (max_seq_len + page_size - 1) // page_size
+        self.num_pages = max_seqs * self.max_pages
+        self.k = [torch.zeros(self.num_pages, n_kv, page_size, hd, dtype=BF, device=device) for _ in range(n_layers)]
+        self.v = [torch.zeros(self.num_pages, n_kv, page_size, hd, dtype=BF, device=device) for _ in range(n_layers)]
+        self.free: List[int] = list(range(self.num_pages - 1, -1, -1))
+        self.owned: Dict[int, List[int]] = {}
+        self._host_table = torch.zeros(max_seqs, self.max_pages, dtype=torch.int32)
+        self.page_table = self._host_table.to(device)
+
+    def reserve(self, seq: int, n_tokens: int) -> None:
+        """Make sure sequence `seq` owns pages for `n_tokens` tokens."""
+        need = (n_tokens + self.page_size - 1) // self.page_size
+        if need > self.max_pages:
+            raise ValueError(f"sequence of {n_tokens} tokens exceeds max_seq_len of the cache")
+        have = self.owned.setdefault(seq, [])
+        while len(have) < need:
+            if not self.free:
+                raise RuntimeError("KV cache out of pages")
+            p = self.free.pop()
+            self._host_table[seq, len(have)] = p
+            have.append(p)
+
+    def commit(self) -> None:
+        self.page_table.copy_(self._host_table, non_blocking=True)
+
+    def release(self, seq: int) -> None:
+        for p in self.owned.pop(seq, []):
+            self.free.append(p)
+
+    def release_all(self) -> None:
+        for s in list(self.owned):
+            self.release(s)
+
+    def bytes(self) -> int:
+        return sum(t.numel() * 2 for t in self.k) * 2
+
+
+class ShardEngine:
+    def __init__(self, spec: ModelSpec, start_layer: int = 0, end_layer: Optional[int] = None,
+                 device: str = "cuda:0", max_batch: int = 1, max_seq_len: int = 2048, page_size: int = 16,
+                 use_cuda_graph: bool = True):
+        if not torch.cuda.is_available():
+            raise RuntimeError("ShardEngine needs a CUDA device: this package has no CPU path")
+        self.spec = spec
+        self.start = start_layer
+        self.end = spec.n_layers - 1 if end_layer is None else end_layer
+        if not (0 <= self.start <= self.end < spec.n_layers):
+            raise ValueError(f"bad layer range [{self.start}, {self.end}] for {spec.n_layers} layers")
+        self.is_first = self.start == 0
+        self.is_last = self.end == spec.n_layers - 1
+        self.n_local = self.end - self.start + 1
+        self.device = torch.device(device)
+        self.max_batch, self.max_seq_len = max_batch, max_seq_len
+        self.use_cuda_graph = use_cuda_graph
+        torch.cuda.set_device(self.device)
+        self.sms = ops.sm_count()
+        self.w: Dict[str, torch.Tensor] = {}
+        self.layers: List[Dict[str, torch.Tensor]] = []
+        self.kv = PagedKVCache(self.n_local, spec.n_kv_heads, spec.head_dim, page_size, max_batch, max_seq_len,
+                               self.device)
+        if spec.arch == "llama":
+            self.cos, self.sin = rope_tables(spec, max_seq_len, self.device)
+        else:
+            self.cos = self.sin = None
+        self.scale = spec.head_dim ** -0.5
+        self._ws_rows = 0
+        self._graphs: Dict[int, tuple] = {}
+        self._dec: Dict[int, dict] = {}
+
+    # ------------------------------------------------------------------ weights
+    def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        """Take HF-named tensors (any dtype, any device), keep ONLY this stage's
+        layer range (+ embedding on stage 0, final norm/lm_head on the last
+        stage): out-of-range tensors of a reference shard directory are random
+         and are never read."""
+        s, dev = self.spec, self.device
+
+        def t(name, transpose=False):
+            x = sd[name]
+            if transpose:
+                x = x.t()
+            return x.to(dtype=BF).contiguous().to(dev)
+
+        self.layers = []
+        if s.arch == "llama":
+            if self.is_first:
+                self.w["embed"] = t("model.embed_tokens.weight")
+            for i in range(self.start, self.end + 1):
+                p = f"model.layers.{i}."
+                qkv = torch.cat([sd[p + f"self_attn.{n}_proj.weight"] for n in "qkv"], dim=0)
+                self.layers.append({
+                    "ln1": t(p + "input_layernorm.weight"),
+                    "wqkv": qkv.to(BF).contiguous().to(dev),
+                    "wo": t(p + "self_attn.o_proj.weight"),
+                    "ln2": t(p + "post_attention_layernorm.weight"),
+                    "wgu": ops.pack_gate_up(sd[p + "mlp.gate_proj.weight"].to(BF), sd[p + "mlp.up_proj.weight"].to(BF)).to(dev),
+                    "wdown": t(p + "mlp.down_proj.weight"),
+                })
+            if self.is_last:
+                self.w["norm"] = t("model.norm.weight")
+                if "lm_head.weight" in sd and not s.tie_embeddings:
+                    self.w["head"] = t("lm_head.weight")
+                else:
+                    self.w["head"] = self.w["embed"] if self.is_first else t("model.embed_tokens.weight")
+        else:
+            if self.is_first:
+                self.w["embed"] = t("transformer.wte.weight")
+                self.w["wpe"] = t("transformer.wpe.weight")
+            for i in range(self.start, self.end + 1):
+                p = f"transformer.h.{i}."
+                # Conv1D stores [in, out] (TF:pytorch_utils.py:112): transpose once to [out, in]
+                self.layers.append({
+                    "ln1": t(p + "ln_1.weight"), "ln1b": t(p + "ln_1.bias"),
+                    "wqkv": t(p + "attn.c_attn.weight", True), "bqkv": t(p + "attn.c_attn.bias"),
+                    "wo": t(p + "attn.c_proj.weight", True), "bo": t(p + "attn.c_proj.bias"),
+                    "ln2": t(p + "ln_2.weight"), "ln2b": t(p + "ln_2.bias"),
+                    "wfc": t(p + "mlp.c_fc.weight", True), "bfc": t(p + "mlp.c_fc.bias"),
+                    "wdown": t(p + "mlp.c_proj.weight", True), "bdown": t(p + "mlp.c_proj.bias"),
+                })
+            if self.is_last:
+                self.w["norm"] = t("transformer.ln_f.weight")
+                self.w["normb"] = t("transformer.ln_f.bias")
+                self.w["head"] = self.w["embed"] if self.is_first else t("transformer.wte.weight")
+        self._graphs.clear()
+
+    def load_random(self, seed: int = 0, std: float = 0.02) -> None:
+        """Random-init weights generated directly on the device (synthetic
+        benchmark weights of the named architecture; no checkpoints offline)."""
+        s, dev = self.spec, self.device
+        g = torch.Generator(device=dev).manual_seed(seed * 1000 + self.start)
+
+        def n(*shape, mean=0.0):
+            out = torch.empty(*shape, dtype=BF, device=dev)
+            # fill in slices to bound the fp32 temporary
+            flat = out.view(-1)
+            step = 1 << 26
+            for o in range(0, flat.numel(), step):
+                m = min(step, flat.numel() - o)
+                flat[o:o + m] = (mean + std * torch.randn(m, device=dev, generator=g)).to(BF)
+            return out
+
+        d, hd, ff = s.d_model, s.head_dim, s.d_ff
+        self.layers = []
+        if s.arch != "llama":
+            raise NotImplementedError("load_random covers the llama family; use load_state_dict for gpt2")
+        if self.is_first:
+            self.w["embed"] = n(s.vocab, d)
+        for _ in range(self.n_local):
+            self.layers.append({
+                "ln1": n(d, mean=1.0), "wqkv": n((s.n_heads + 2 * s.n_kv_heads) * hd, d), "wo": n(d, s.n_heads * hd),
+                "ln2": n(d, mean=1.0), "wgu": n(2 * ff, d), "wdown": n(d, ff),
+            })
+        if self.is_last:
+            self.w["norm"] = n(d, mean=1.0)
+            self.w["head"] = self.w["embed"] if (s.tie_embeddings and self.is_first) else n(s.vocab, d)
+        self._graphs.clear()
+
+    def weight_bytes(self) -> int:
+        seen, total = set(), 0
+        for t in list(self.w.values()) + [x for l in self.layers for x in l.values()]:
+            if t.data_ptr() not in seen:
+                seen.add(t.data_ptr())
+                total += t.numel() * t.element_size()
+        return total
+
+    def unload(self) -> None:
+        """Free weights and KV pages (reference /unload_model, worker/app.py:208-250)."""
+        self.w.clear()
+        self.layers.clear()
+        self._graphs.clear()
+        self._dec.clear()
+        self.kv.release_all()
+        self.kv.k.clear()
+        self.kv.v.clear()
+        self._ws_rows = 0
+        for name in ("_h", "_x", "_qkv", "_attn", "_act"):
+            if hasattr(self, name):
+                delattr(self, name)
+        torch.cuda.empty_cache()
+
+    # ------------------------------------------------------------------ workspace
+    def _workspace(self, rows: int) -> None:
+        if rows <= self._ws_rows:
+            return
+        s, dev = self.spec, self.device
+        self._h = torch.empty(rows, s.d_model, dtype=BF, device=dev)
+        self._x = torch.empty(rows, s.d_model, dtype=BF, device=dev)
+        self._qkv = torch.empty(rows, (s.n_heads + 2 * s.n_kv_heads) * s.head_dim, dtype=BF, device=dev)
+        self._attn = torch.empty(rows, s.n_heads * s.head_dim, dtype=BF, device=dev)
+        self._act = torch.empty(rows, s.d_ff, dtype=BF, device=dev)
+        self._ws_rows = rows
+        self._graphs.clear()  # captured graphs hold the old workspace pointers
+
+    def _num_splits(self, B: int) -> int:
+        tiles = (self.max_seq_len + 63) // 64
+        want = max(1, (2 * self.sms + B * self.spec.n_kv_heads - 1) // (B * self.spec.n_kv_heads))
+        return max(1, min(tiles, want, 64))
+
+    # ------------------------------------------------------------------ one layer range
+    def _layers_forward(self, h, rows, positions, seq_ids, seq_lens, prefill_shape):
+        """h: [rows, d] residual stream (updated in place).  prefill_shape=(B,T) or None for decode."""
+        s = self.spec
+        x, qkv, attn, act = self._x[:rows], self._qkv[:rows], self._attn[:rows], self._act[:rows]
+        H, KV, hd = s.n_heads, s.n_kv_heads, s.head_dim
+        for li, L in enumerate(self.layers):
+            if s.arch == "llama":
+                ops.add_rmsnorm(h, L["ln1"], s.eps, out=x)
+                ops.linear(x, L["wqkv"], out=qkv)
+            else:
+                ops.add_layernorm(h, L["ln1"], L["ln1b"], s.eps, out=x)
+                ops.linear(x, L["wqkv"], bias=L["bqkv"], out=qkv)
+            ops.rope_kv_append(qkv, self.cos, self.sin, positions, seq_ids, self.kv.page_table,
+                               self.kv.k[li], self.kv.v[li], H, KV, hd)
+            if prefill_shape is not None:
+                ops.attn_prefill(qkv, attn, prefill_shape[0], prefill_shape[1], H, KV, hd, self.scale,
+                                 window=s.sliding_window)
+            else:
+                st = self._dec[rows]
+                ops.paged_attn_decode(qkv, qkv.shape[1], self.kv.k[li], self.kv.v[li], self.kv.page_table, seq_lens,
+                                      attn, H, KV, hd, self.scale, num_splits=st["splits"], scratch=st["scratch"],
+                                      window=s.sliding_window)
+            if s.arch == "llama":
+                ops.linear(attn, L["wo"], residual=h, out=h)
+                ops.add_rmsnorm(h, L["ln2"], s.eps, out=x)
+                ops.linear_gated_silu(x, L["wgu"], out=act)
+                ops.linear(act, L["wdown"], residual=h, out=h)
+            else:
+                ops.linear(attn, L["wo"], bias=L["bo"], residual=h, out=h)
+                ops.add_layernorm(h, L["ln2"], L["ln2b"], s.eps, out=x)
+                ops.linear(x, L["wfc"], bias=L["bfc"], out=act, epilogue=ops.EPI_GELU_NEW)
+                ops.linear(act, L["wdown"], bias=L["bdown"], residual=h, out=h)
+        return h
+
+    def _head(self, h_last, logits, tokens):
+        """final norm + lm_head + greedy argmax on [B, d]."""
+        s = self.spec
+        B = h_last.shape[0]
+        xn = self._x[:B]
+        if s.arch == "llama":
+            ops.add_rmsnorm(h_last, self.w["norm"], s.eps, out=xn)
+        else:
+            ops.add_layernorm(h_last, self.w["norm"], self.w["normb"], s.eps, out=xn)
+        ops.linear(xn, self.w["head"], out=logits)
+        ops.argmax(logits, out=tokens)
+
+    # ------------------------------------------------------------------ prefill
+    def start_batch(self, B: int, prompt_len: int, max_total_len: int) -> None:
+        """Reserve KV pages for B sequences (ids 0..B-1) and reset per-batch state."""
+        if B > self.max_batch:
+            raise ValueError(f"batch {B} > max_batch {self.max_batch}")
+        if max_total_len > self.max_seq_len:
+            raise ValueError(f"total length {max_total_len} > max_seq_len {self.max_seq_len}")
+        self.kv.release_all()
+        for b in range(B):
+            self.kv.reserve(b, max_total_len)
+        self.kv.commit()
+        dev = self.device
+        if B not in self._dec:
+            splits = self._num_splits(B)
+            nbytes = ops.attn_decode_scratch_bytes(B, self.spec.n_heads, self.spec.head_dim, splits)
+            self._dec[B] = {
+                "splits": splits,
+                "scratch": torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=dev),
+                "positions": torch.zeros(B, dtype=torch.int32, device=dev),
+                "seq_lens": torch.zeros(B, dtype=torch.int32, device=dev),
+                "seq_ids": torch.arange(B, dtype=torch.int32, device=dev),
+                "tokens": torch.zeros(B, dtype=torch.int32, device=dev),
+                "step": torch.zeros(1, dtype=torch.int32, device=dev),
+                "h_in": torch.empty(B, self.spec.d_model, dtype=BF, device=dev),
+                "logits": torch.empty(B, self.spec.vocab, dtype=BF, device=dev) if self.is_last else None,
+                # persistent: its address is baked into the captured decode graph
+                "token_log": torch.zeros(self.max_seq_len, B, dtype=torch.int32, device=dev) if self.is_last else None,
+            }
+        st = self._dec[B]
+        st["positions"].fill_(prompt_len)
+        st["seq_lens"].fill_(prompt_len + 1)
+        st["step"].zero_()
+
+    def prefill(self, B: int, T: int, ids: Optional[torch.Tensor] = None, hidden: Optional[torch.Tensor] = None):
+        """Run the stage over B prompts of T tokens.
+        Stage 0 takes `ids` (int32 [B*T] on device), later stages `hidden` [B*T, d].
+        Returns hidden [B*T, d] (a view of the workspace), or on the last stage the
+        int32 next tokens [B] (logits stay in self.last_logits)."""
+        rows = B * T
+        self._workspace(max(rows, B))
+        st = self._dec[B]
+        dev = self.device
+        positions = torch.arange(T, dtype=torch.int32, device=dev).repeat(B)
+        seq_ids = torch.arange(B, dtype=torch.int32, device=dev).repeat_interleave(T)
+        h = self._h[:rows]
+        if self.is_first:
+            if self.spec.arch == "gpt2":
+                ops.embedding(ids, self.w["embed"], out=h, positions=positions, pos_table=self.w["wpe"])
+            else:
+                ops.embedding(ids, self.w["embed"], out=h)
+        else:
+            h.copy_(hidden)
+        self._layers_forward(h, rows, positions, seq_ids, None, (B, T))
+        if not self.is_last:
+            return h
+        last_rows = (torch.arange(B, dtype=torch.int32, device=dev) + 1) * T - 1
+        h_last = ops.embedding(last_rows, h, out=st["h_in"])  # row gather of the last positions
+        self._head(h_last, st["logits"], st["tokens"])
+        return st["tokens"]
+
+    # ------------------------------------------------------------------ decode
+    def _decode_body(self, B: int, hidden_in: Optional[torch.Tensor]):
+        st = self._dec[B]
+        h = self._h[:B]
+        if self.is_first:
+            if self.spec.arch == "gpt2":
+                ops.embedding(st["tokens"], self.w["embed"], out=h, positions=st["positions"], pos_table=self.w["wpe"])
+            else:
+                ops.embedding(st["tokens"], self.w["embed"], out=h)
+        else:
+            h.copy_(hidden_in)
+        self._layers_forward(h, B, st["positions"], st["seq_ids"], st["seq_lens"], None)
+        if self.is_last:
+            self._head(h, st["logits"], st["tokens"])
+        ops.decode_advance(st["tokens"], st["token_log"] if self.is_last else None, st["positions"], st["seq_lens"],
+                           st["step"])
+        return st["tokens"] if self.is_last else h
+
+    def decode_step(self, B: int, hidden_in: Optional[torch.Tensor] = None):
+        """One token for each of the B sequences.  On a full-range engine the whole
+        step (embedding of the previous token .. argmax .. position advance) is a
+        replayed CUDA graph with no host synchronisation."""
+        self._workspace(B)
+        if not (self.use_cuda_graph and self.is_first and self.is_last):
+            return self._decode_body(B, hidden_in)
+        if B not in self._graphs:
+            st = self._dec[B]
+            saved = {k: st[k].clone() for k in ("positions", "seq_lens", "tokens", "step")}
+            side = torch.cuda.Stream(device=self.device)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                self._decode_body(B, None)  # warm-up outside capture (sets func attributes, occupancy caches)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            n0 = ops.launch_count
+            with torch.cuda.graph(g):
+                self._decode_body(B, None)
+            launches = ops.launch_count - n0
+            for k, v in saved.items():  # undo the state changes of warm-up + capture
+                st[k].copy_(v)
+            torch.cuda.synchronize()
+            # the warm-up/capture wrote KV slots at positions >= the prompt; they are overwritten on replay
+            self._graphs[B] = (g, launches)
+        g, launches = self._graphs[B]
+        g.replay()
+        ops.launch_count += launches
+        return self._dec[B]["tokens"]
+
+    def decode_step_host(self, tokens_in: torch.Tensor, tokens_out: torch.Tensor) -> torch.Tensor:
+        """One decode step with HOST buffers, the per-token call a streaming client
+        makes: pinned int32 [B] tokens in -> device, one step, next tokens -> pinned
+        int32 [B] out, then a stream synchronise (4*B bytes each way)."""
+        B = tokens_in.numel()
+        self._dec[B]["tokens"].copy_(tokens_in, non_blocking=True)
+        self.decode_step(B)
+        tokens_out.copy_(self._dec[B]["tokens"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return tokens_out
+
+    # ------------------------------------------------------------------ public API
+    @torch.no_grad()
+    def generate(self, input_ids: torch.Tensor, max_length: int, return_logits: bool = False,
+                 forced: Optional[torch.Tensor] = None):
+        """Greedy generate (the parity mode of worker/app.py:297-305: the reference
+        samples).  input_ids: int [B, T] on any device;
+        `max_length` is the TOTAL length like the reference's.  Returns int64
+        [B, max_length] on the host, plus the per-step last-position logits
+        (fp32, host) when return_logits.  `forced` [B, n_new] teacher-forces the
+        token fed back at each step (parity tests); the returned tokens are still
+        this engine's own argmax.  Either option runs the steps un-graphed."""
+        if not (self.is_first and self.is_last):
+            raise RuntimeError("generate() needs the full layer range; use PipelineEngine for shards")
+        B, T = input_ids.shape
+        n_new = max_length - T
+        if n_new <= 0:
+            return input_ids.cpu().long()[:, :max_length]
+        self.start_batch(B, T, max_length)
+        st = self._dec[B]
+        ids = input_ids.to(device=self.device, dtype=torch.int32, non_blocking=True).reshape(-1).contiguous()
+        eager = return_logits or forced is not None
+        if forced is not None:
+            forced = forced.to(device=self.device, dtype=torch.int32)
+        logits_out, toks = [], []
+        toks.append(self.prefill(B, T, ids=ids).clone())
+        if return_logits:
+            logits_out.append(st["logits"].float().cpu())
+        graph = self.use_cuda_graph
+        if eager:
+            self.use_cuda_graph = False
+        try:
+            for i in range(n_new - 1):
+                if forced is not None:
+                    st["tokens"].copy_(forced[:, i])
+                self.decode_step(B)
+                if eager:
+                    toks.append(st["tokens"].clone())
+                if return_logits:
+                    logits_out.append(st["logits"].float().cpu())
+        finally:
+            self.use_cuda_graph = graph
+        if eager:
+            new = torch.stack(toks, dim=1)
+        else:
+            new = torch.cat((toks[0][None], st["token_log"][: n_new - 1]), dim=0).t()  # [B, n_new]
+        out = torch.cat((input_ids.cpu().long(), new.cpu().long()), dim=1)
+        return (out, logits_out) if return_logits else out
+
+    @property
+    def last_logits(self):
+        return None if not self._dec else next(iter(self._dec.values()))["logits"]

@@ -199,3 +199,15 @@ def argmax(logits, out=None):
         _p(logits), logits.stride(0), _p(out), B, V, _stream()))
     launch_count += 1
     return out
+
+
+def decode_advance(tokens, token_log, positions, seq_lens, step):
+    """Log sampled tokens and advance positions / lengths / step counter on device."""
+    global launch_count
+    for t in (tokens, token_log, positions, seq_lens, step):
+        _req(t, torch.int32)
+    B = tokens.numel()
+    cap = 0 if token_log is None else token_log.numel() // max(B, 1)
+    _lib.check("dli_decode_advance", _lib.load().dli_decode_advance(
+        _p(tokens), _p(token_log), _p(positions), _p(seq_lens), _p(step), B, cap, _stream()))
+    launch_count += 1

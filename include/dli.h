@@ -171,6 +171,16 @@ int dli_linear_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M,
 int dli_argmax_bf16(const void* logits, int ld, int32_t* out, int B, int V,
                     dli_stream_t stream);
 
+/* Device-side bookkeeping between two decode steps, so a whole step can live in
+ * a replayed CUDA graph with no host round trip (the reference syncs the host
+ * every token: stopping criteria at TF:generation/utils.py:2804 and the
+ * torch.cat of input_ids at :2800): token_log[step*B + b] = tokens[b] (when
+ * token_log != NULL and step < log_capacity), positions[b] += 1, seq_lens[b] += 1
+ * (each optional), then *step += 1.  All int32. */
+int dli_decode_advance(const int32_t* tokens, int32_t* token_log, int32_t* positions,
+                       int32_t* seq_lens, int32_t* step, int B, int log_capacity,
+                       dli_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
