@@ -31,6 +31,11 @@ SIGNATURES = {
         _i,
         [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i, _vp],
     ),
+    "dli_paged_attn_decode_static_max_bytes": (_sz, []),
+    "dli_paged_attn_decode_static_bf16": (
+        _i,
+        [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp],
+    ),
     "dli_attn_prefill_bf16": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "dli_gemv_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "dli_gemm_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),

@@ -330,3 +330,72 @@ int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// Split-KV decode attention for callers that cannot allocate device memory.
+//
+// Some users of this library hold only the buffers they were handed: a serving process
+// that gave all of HBM to its weight and KV pools at start-up (a later cudaMalloc fails or
+// forces an eviction), a foreign-language binding of this C-ABI with no device allocator of
+// its own, or a per-token loop that cannot afford the device-wide synchronisation
+// cudaMalloc/cudaFree imply.  For them the split partials live in the fixed array below
+// instead of a caller-provided scratch buffer.  The array is part of the library image, so
+// every GPU that loads the library holds these bytes until the process exits.
+constexpr size_t kStaticScratchBytes = 8u << 20;  // 8 MiB: e.g. B=32, H=32, hd=128, 15 splits
+static __device__ __align__(256) unsigned char g_static_attn_scratch[kStaticScratchBytes];
+
+namespace dli {
+
+// In host code `g_static_attn_scratch` is only a host-side stand-in for the symbol, not a
+// device address, so the address is looked up once per device (with that device current)
+// and cached.  Returns nullptr after recording the error.
+static void* static_scratch_for_current_device() {
+  static void* cached[64] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    fail(DLI_ERR_CUDA, "dli_paged_attn_decode_static_bf16: cudaGetDevice: %s", cudaGetErrorString(e));
+    return nullptr;
+  }
+  if (cached[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_static_attn_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      fail(DLI_ERR_CUDA, "dli_paged_attn_decode_static_bf16: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return nullptr;
+    }
+    cached[dev] = ptr;
+  }
+  return cached[dev];
+}
+
+}  // namespace dli
+
+extern "C" {
+
+size_t dli_paged_attn_decode_static_max_bytes(void) { return kStaticScratchBytes; }
+
+int dli_paged_attn_decode_static_bf16(const void* q, int q_stride, const void* k_cache,
+                                      const void* v_cache, const int32_t* page_table, int max_pages,
+                                      const int32_t* seq_lens, void* out, int B, int H, int KV, int hd,
+                                      int page_size, int num_splits, float scale, int window,
+                                      dli_stream_t stream) {
+  using namespace dli;
+  const size_t need = dli_paged_attn_decode_scratch_bytes(B, H, hd, num_splits);
+  DLI_CHECK_ARG(need <= kStaticScratchBytes,
+                "dli_paged_attn_decode_static_bf16: B=%d H=%d hd=%d num_splits=%d needs %zu bytes of split "
+                "scratch, the built-in array holds %zu; use fewer splits or dli_paged_attn_decode_bf16 with "
+                "your own scratch",
+                B, H, hd, num_splits, need, (size_t)kStaticScratchBytes);
+  void* scratch = nullptr;
+  if (num_splits > 1) {
+    scratch = static_scratch_for_current_device();
+    if (scratch == nullptr) return DLI_ERR_CUDA;
+  }
+  // Nothing in the array has to start at zero: every (sequence, head, split) slot this call
+  // later reads is first written by this call, empty splits included.
+  return dli_paged_attn_decode_bf16(q, q_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out,
+                                    scratch, need, B, H, KV, hd, page_size, num_splits, scale, window, stream);
+}
+
+}  // extern "C"

@@ -120,6 +120,35 @@ int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
                                int KV, int hd, int page_size, int num_splits,
                                float scale, int window, dli_stream_t stream);
 
+/* Same computation as dli_paged_attn_decode_bf16 for callers that cannot
+ * allocate device memory where they call it: a server that handed all of HBM
+ * to its weight/KV pools at start-up, a foreign-language binding that owns no
+ * device allocator, or a per-token loop that cannot take the device-wide
+ * synchronisation of cudaMalloc/cudaFree.  (No counterpart in the reference:
+ * it never manages scratch memory itself.)  The split-KV partials go to a
+ * fixed array inside the library instead of a caller buffer; q, caches, page
+ * table, seq_lens and out are still the caller's.  This entry point calls no
+ * cudaMalloc/cudaFree or other allocating routine.
+ *   - Limit: dli_paged_attn_decode_scratch_bytes(B, H, hd, num_splits) must not
+ *     exceed dli_paged_attn_decode_static_max_bytes() (8 MiB); larger requests
+ *     return DLI_ERR_INVALID with the two sizes in dli_last_error().  Every GPU
+ *     that loads the library holds those 8 MiB until the process exits.
+ *   - The first call on each device looks up the array's device address and
+ *     sets the kernel's shared-memory attribute; make that first call (on that
+ *     device, with it current) before starting any stream capture.
+ *   - All calls on a device share the one array, which keeps the previous
+ *     call's contents; nothing needs clearing because each call writes every
+ *     slot before reading it.  Two calls that overlap on the GPU (different
+ *     streams, or different host threads without ordering) race on it: keep
+ *     calls to this entry point ordered on one stream per device. */
+size_t dli_paged_attn_decode_static_max_bytes(void);
+int dli_paged_attn_decode_static_bf16(const void* q, int q_stride, const void* k_cache,
+                                      const void* v_cache, const int32_t* page_table,
+                                      int max_pages, const int32_t* seq_lens, void* out,
+                                      int B, int H, int KV, int hd, int page_size,
+                                      int num_splits, float scale, int window,
+                                      dli_stream_t stream);
+
 /* ---- causal prefill attention --------------------------------------------
  * B sequences of T new tokens each, no earlier context: q, k, v are read from
  * the packed (already rotated) qkv buffer [B*T, (H+2KV)*hd].
