@@ -168,7 +168,7 @@ def run_single(args, spec, peaks):
     # ---- decode through the host-facing call -----------------------------------------------
     t_in = torch.zeros(B, dtype=torch.int32).pin_memory()
     t_out = torch.zeros(B, dtype=torch.int32).pin_memory()
-    t_in.copy_(eng._dec[B]["tokens"].cpu())
+    t_in.copy_(eng._state(B)["tokens"].cpu())
     for _ in range(3):
         eng.decode_step_host(t_in, t_out)
         t_in.copy_(t_out)
@@ -193,7 +193,7 @@ def run_single(args, spec, peaks):
         "prefill_roofline": {"bound": "tensor", "achieved": pf_flops / (pf_ms / 1e3) / 1e12,
                              "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
                              "frac": pf_flops / (pf_ms / 1e3) / 1e12 / peaks["bf16_tflops"]},
-        "roofline_step": roof_step, "attn_splits": eng._dec[B]["splits"],
+        "roofline_step": roof_step, "attn_splits": eng._state(B)["splits"],
         "weights_gb": eng.weight_bytes() / 1e9, "peaks": peaks["source"],
     }
     if args.batch == 1 and not args.no_extra:

@@ -169,8 +169,8 @@ class ShardEngine:
             self.cos = self.sin = None
         self.scale = spec.head_dim ** -0.5
         self._ws_rows = 0
-        self._graphs: Dict[int, tuple] = {}
-        self._dec: Dict[int, dict] = {}
+        self._graphs: Dict[tuple, tuple] = {}
+        self._dec: Dict[tuple, dict] = {}
 
     # ------------------------------------------------------------------ weights
     def load_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
@@ -302,7 +302,7 @@ class ShardEngine:
         return max(1, min(tiles, want, 64))
 
     # ------------------------------------------------------------------ one layer range
-    def _layers_forward(self, h, rows, positions, seq_ids, seq_lens, prefill_shape):
+    def _layers_forward(self, h, rows, positions, seq_ids, seq_lens, prefill_shape, st):
         """h: [rows, d] residual stream (updated in place).  prefill_shape=(B,T) or None for decode."""
         s = self.spec
         x, qkv, attn, act = self._x[:rows], self._qkv[:rows], self._attn[:rows], self._act[:rows]
@@ -320,7 +320,6 @@ class ShardEngine:
                 ops.attn_prefill(qkv, attn, prefill_shape[0], prefill_shape[1], H, KV, hd, self.scale,
                                  window=s.sliding_window)
             else:
-                st = self._dec[rows]
                 ops.paged_attn_decode(qkv, qkv.shape[1], self.kv.k[li], self.kv.v[li], self.kv.page_table, seq_lens,
                                       attn, H, KV, hd, self.scale, num_splits=st["splits"], scratch=st["scratch"],
                                       window=s.sliding_window)
@@ -349,122 +348,138 @@ class ShardEngine:
         ops.argmax(logits, out=tokens)
 
     # ------------------------------------------------------------------ prefill
-    def start_batch(self, B: int, prompt_len: int, max_total_len: int) -> None:
-        """Reserve KV pages for B sequences (ids 0..B-1) and reset per-batch state."""
-        if B > self.max_batch:
-            raise ValueError(f"batch {B} > max_batch {self.max_batch}")
+    def _state(self, B: int, mb: int = 0) -> dict:
+        return self._dec[(B, mb)]
+
+    def start_batch(self, B: int, prompt_len: int, max_total_len: int, mb: int = 0) -> None:
+        """Reserve KV pages for the B sequences of micro-batch slot `mb` (sequence ids
+        mb*B .. mb*B+B-1) and reset the slot's decode state.  Slot 0 with the full
+        batch is the single-GPU case; a pipeline stage keeps one slot per micro-batch
+        in flight."""
+        if (mb + 1) * B > self.max_batch:
+            raise ValueError(f"micro-batch {mb} of {B} sequences exceeds max_batch {self.max_batch}")
         if max_total_len > self.max_seq_len:
             raise ValueError(f"total length {max_total_len} > max_seq_len {self.max_seq_len}")
-        self.kv.release_all()
-        for b in range(B):
+        for b in range(mb * B, (mb + 1) * B):
+            self.kv.release(b)
             self.kv.reserve(b, max_total_len)
         self.kv.commit()
         dev = self.device
-        if B not in self._dec:
+        if (B, mb) not in self._dec:
             splits = self._num_splits(B)
             nbytes = ops.attn_decode_scratch_bytes(B, self.spec.n_heads, self.spec.head_dim, splits)
-            self._dec[B] = {
+            self._dec[(B, mb)] = {
                 "splits": splits,
                 "scratch": torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=dev),
                 "positions": torch.zeros(B, dtype=torch.int32, device=dev),
                 "seq_lens": torch.zeros(B, dtype=torch.int32, device=dev),
-                "seq_ids": torch.arange(B, dtype=torch.int32, device=dev),
+                "seq_ids": torch.arange(mb * B, (mb + 1) * B, dtype=torch.int32, device=dev),
                 "tokens": torch.zeros(B, dtype=torch.int32, device=dev),
                 "step": torch.zeros(1, dtype=torch.int32, device=dev),
-                "h_in": torch.empty(B, self.spec.d_model, dtype=BF, device=dev),
+                # residual stream of the slot's decode step: stage input (recv target) and output (send source)
+                "h": torch.empty(B, self.spec.d_model, dtype=BF, device=dev),
                 "logits": torch.empty(B, self.spec.vocab, dtype=BF, device=dev) if self.is_last else None,
                 # persistent: its address is baked into the captured decode graph
                 "token_log": torch.zeros(self.max_seq_len, B, dtype=torch.int32, device=dev) if self.is_last else None,
             }
-        st = self._dec[B]
+        st = self._dec[(B, mb)]
         st["positions"].fill_(prompt_len)
         st["seq_lens"].fill_(prompt_len + 1)
         st["step"].zero_()
 
-    def prefill(self, B: int, T: int, ids: Optional[torch.Tensor] = None, hidden: Optional[torch.Tensor] = None):
+    def prefill(self, B: int, T: int, ids: Optional[torch.Tensor] = None, hidden: Optional[torch.Tensor] = None,
+                mb: int = 0):
         """Run the stage over B prompts of T tokens.
         Stage 0 takes `ids` (int32 [B*T] on device), later stages `hidden` [B*T, d].
         Returns hidden [B*T, d] (a view of the workspace), or on the last stage the
-        int32 next tokens [B] (logits stay in self.last_logits)."""
+        int32 next tokens [B] (logits stay in the slot's state)."""
         rows = B * T
         self._workspace(max(rows, B))
-        st = self._dec[B]
+        st = self._dec[(B, mb)]
         dev = self.device
         positions = torch.arange(T, dtype=torch.int32, device=dev).repeat(B)
-        seq_ids = torch.arange(B, dtype=torch.int32, device=dev).repeat_interleave(T)
+        seq_ids = st["seq_ids"].repeat_interleave(T)
         h = self._h[:rows]
         if self.is_first:
             if self.spec.arch == "gpt2":
                 ops.embedding(ids, self.w["embed"], out=h, positions=positions, pos_table=self.w["wpe"])
             else:
                 ops.embedding(ids, self.w["embed"], out=h)
-        else:
+        elif hidden.data_ptr() != h.data_ptr():
             h.copy_(hidden)
-        self._layers_forward(h, rows, positions, seq_ids, None, (B, T))
+        self._layers_forward(h, rows, positions, seq_ids, None, (B, T), st)
         if not self.is_last:
             return h
         last_rows = (torch.arange(B, dtype=torch.int32, device=dev) + 1) * T - 1
-        h_last = ops.embedding(last_rows, h, out=st["h_in"])  # row gather of the last positions
+        h_last = ops.embedding(last_rows, h, out=st["h"])  # row gather of the last positions
         self._head(h_last, st["logits"], st["tokens"])
         return st["tokens"]
 
     # ------------------------------------------------------------------ decode
-    def _decode_body(self, B: int, hidden_in: Optional[torch.Tensor]):
-        st = self._dec[B]
-        h = self._h[:B]
+    def _decode_body(self, B: int, mb: int):
+        """Stage input: st["tokens"] (stage 0) or st["h"] (later stages, written by the
+        caller / the NCCL recv).  Stage output: st["h"] (updated in place) or, on the
+        last stage, st["tokens"]."""
+        st = self._dec[(B, mb)]
+        h = st["h"]
         if self.is_first:
             if self.spec.arch == "gpt2":
                 ops.embedding(st["tokens"], self.w["embed"], out=h, positions=st["positions"], pos_table=self.w["wpe"])
             else:
                 ops.embedding(st["tokens"], self.w["embed"], out=h)
-        else:
-            h.copy_(hidden_in)
-        self._layers_forward(h, B, st["positions"], st["seq_ids"], st["seq_lens"], None)
+        self._layers_forward(h, B, st["positions"], st["seq_ids"], st["seq_lens"], None, st)
         if self.is_last:
             self._head(h, st["logits"], st["tokens"])
         ops.decode_advance(st["tokens"], st["token_log"] if self.is_last else None, st["positions"], st["seq_lens"],
                            st["step"])
         return st["tokens"] if self.is_last else h
 
-    def decode_step(self, B: int, hidden_in: Optional[torch.Tensor] = None):
-        """One token for each of the B sequences.  On a full-range engine the whole
-        step (embedding of the previous token .. argmax .. position advance) is a
-        replayed CUDA graph with no host synchronisation."""
+    def decode_step(self, B: int, hidden_in: Optional[torch.Tensor] = None, mb: int = 0):
+        """One token for each of the B sequences of slot `mb`.  The stage's whole step
+        (embedding of the previous token / received hidden state .. layers .. argmax ..
+        position advance) is a CUDA graph captured once per (B, mb) and replayed, with
+        no host synchronisation."""
         self._workspace(B)
-        if not (self.use_cuda_graph and self.is_first and self.is_last):
-            return self._decode_body(B, hidden_in)
-        if B not in self._graphs:
-            st = self._dec[B]
-            saved = {k: st[k].clone() for k in ("positions", "seq_lens", "tokens", "step")}
+        st = self._dec[(B, mb)]
+        if hidden_in is not None and hidden_in.data_ptr() != st["h"].data_ptr():
+            st["h"].copy_(hidden_in)
+        if not self.use_cuda_graph:
+            return self._decode_body(B, mb)
+        key = (B, mb)
+        if key not in self._graphs:
+            saved = {k: st[k].clone() for k in ("positions", "seq_lens", "tokens", "step", "h")}
             side = torch.cuda.Stream(device=self.device)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                self._decode_body(B, None)  # warm-up outside capture (sets func attributes, occupancy caches)
+                self._decode_body(B, mb)  # warm-up outside capture (function attributes, occupancy caches)
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
+            for k, v in saved.items():
+                st[k].copy_(v)
             g = torch.cuda.CUDAGraph()
             n0 = ops.launch_count
             with torch.cuda.graph(g):
-                self._decode_body(B, None)
+                self._decode_body(B, mb)
             launches = ops.launch_count - n0
-            for k, v in saved.items():  # undo the state changes of warm-up + capture
+            for k, v in saved.items():  # capture does not execute, but keep the state exact
                 st[k].copy_(v)
             torch.cuda.synchronize()
-            # the warm-up/capture wrote KV slots at positions >= the prompt; they are overwritten on replay
-            self._graphs[B] = (g, launches)
-        g, launches = self._graphs[B]
+            # the warm-up wrote the KV slot of the current position; the replay rewrites it identically
+            self._graphs[key] = (g, launches)
+        g, launches = self._graphs[key]
         g.replay()
         ops.launch_count += launches
-        return self._dec[B]["tokens"]
+        return st["tokens"] if self.is_last else st["h"]
 
     def decode_step_host(self, tokens_in: torch.Tensor, tokens_out: torch.Tensor) -> torch.Tensor:
         """One decode step with HOST buffers, the per-token call a streaming client
         makes: pinned int32 [B] tokens in -> device, one step, next tokens -> pinned
         int32 [B] out, then a stream synchronise (4*B bytes each way)."""
         B = tokens_in.numel()
-        self._dec[B]["tokens"].copy_(tokens_in, non_blocking=True)
+        st = self._dec[(B, 0)]
+        st["tokens"].copy_(tokens_in, non_blocking=True)
         self.decode_step(B)
-        tokens_out.copy_(self._dec[B]["tokens"], non_blocking=True)
+        tokens_out.copy_(st["tokens"], non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return tokens_out
 
@@ -486,7 +501,7 @@ class ShardEngine:
         if n_new <= 0:
             return input_ids.cpu().long()[:, :max_length]
         self.start_batch(B, T, max_length)
-        st = self._dec[B]
+        st = self._dec[(B, 0)]
         ids = input_ids.to(device=self.device, dtype=torch.int32, non_blocking=True).reshape(-1).contiguous()
         eager = return_logits or forced is not None
         if forced is not None:

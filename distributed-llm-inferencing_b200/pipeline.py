@@ -1,0 +1,226 @@
+"""Layer-range pipeline over torch.distributed point-to-point (NCCL over NVLink on
+the B200 box, gloo in the CPU tests).
+
+This is the reference's DECLARED design — a model split into N contiguous layer
+ranges on N nodes (shard_model.py:55-66) whose shards pass hidden states along
+(worker/app.py:332-335 comment, never implemented: SURVEY.md §0 F1) — with the
+HTTP/JSON hop replaced by send/recv of the `[b, d]` bf16 hidden tile between
+neighbouring GPUs, and the sampled `[b]` int32 tokens returned from the last
+stage to stage 0.  There is no collective on this path (no tensor parallelism):
+only neighbour exchanges, issued as ONE grouped batch per tick so the forward
+sends, the token return and the matching receives progress together.
+
+Schedule.  Micro-batch slots mb = 0..M-1 (each `b` sequences) are in flight.
+With period P = max(M, N), stage s works at tick t on u = t - s:
+    round r = u // P,  slot mb = u % P   (idle if mb >= M or r outside the run)
+so the token of (r, mb) leaves the last stage at tick r*P + mb + N - 1 and reaches
+stage 0 before tick (r+1)*P + mb.  Every tick ends with the grouped exchange:
+send what was just computed, receive the input of the next tick.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+
+def tick_work(t: int, stage: int, n_stages: int, n_micro: int, n_rounds: int):
+    """(round, slot) stage `stage` works on at tick `t`, or None when idle."""
+    P = max(n_micro, n_stages)
+    u = t - stage
+    if u < 0:
+        return None
+    r, mb = divmod(u, P)
+    if mb >= n_micro or r >= n_rounds:
+        return None
+    return r, mb
+
+
+def total_ticks(n_stages: int, n_micro: int, n_rounds: int) -> int:
+    P = max(n_micro, n_stages)
+    return (n_rounds - 1) * P + n_micro + n_stages - 1
+
+
+class StageBase:
+    """What the schedule needs from a stage.  `recv_buffer(kind, mb)` is where the
+    stage's input for slot mb lands (hidden state; on stage 0 the returned tokens);
+    `compute(kind, mb)` consumes it and returns the tensor to pass on (hidden state;
+    on the last stage the tokens)."""
+
+    is_first: bool
+    is_last: bool
+
+    def recv_buffer(self, kind: str, mb: int) -> torch.Tensor:
+        raise NotImplementedError
+
+    def compute(self, kind: str, mb: int) -> torch.Tensor:
+        raise NotImplementedError
+
+
+class PipelineRunner:
+    def __init__(self, stage: StageBase, rank: int, world: int, n_micro: int, group=None):
+        self.stage, self.rank, self.world, self.M, self.group = stage, rank, world, n_micro, group
+
+    def _exchange(self, t: int, kind: str, n_rounds: int, mine, out: Optional[torch.Tensor], token_return: bool):
+        """Grouped send of this tick's result and receive of the next tick's input."""
+        N, s = self.world, self.rank
+        ops: List[dist.P2POp] = []
+        if mine is not None:
+            r, mb = mine
+            if not self.stage.is_last:
+                ops.append(dist.P2POp(dist.isend, out, s + 1, self.group))
+            elif token_return and N > 1 and (kind == "prefill" or r + 1 < n_rounds):
+                ops.append(dist.P2POp(dist.isend, out, 0, self.group))
+        if s > 0:
+            prev = tick_work(t, s - 1, N, self.M, n_rounds)
+            if prev is not None:
+                ops.append(dist.P2POp(dist.irecv, self.stage.recv_buffer(kind, prev[1]), s - 1, self.group))
+        elif token_return and N > 1:
+            last = tick_work(t, N - 1, N, self.M, n_rounds)
+            if last is not None and (kind == "prefill" or last[0] + 1 < n_rounds):
+                ops.append(dist.P2POp(dist.irecv, self.stage.recv_buffer("decode", last[1]), N - 1, self.group))
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+
+    def run(self, kind: str, n_rounds: int = 1, token_return: bool = True) -> None:
+        """kind='prefill': one pass of every slot's prompt through the stages (the first
+        tokens end up in stage 0's decode input buffers).  kind='decode': n_rounds tokens
+        for every slot."""
+        if kind == "prefill":
+            n_rounds = 1
+        for t in range(total_ticks(self.world, self.M, n_rounds)):
+            mine = tick_work(t, self.rank, self.world, self.M, n_rounds)
+            out = self.stage.compute(kind, mine[1]) if mine is not None else None
+            self._exchange(t, kind, n_rounds, mine, out, token_return)
+
+
+# ------------------------------------------------------------------------------ CUDA stage
+class EngineStage(StageBase):
+    """A ShardEngine as one pipeline stage: slot mb <-> the engine's micro-batch state."""
+
+    def __init__(self, engine, b: int, prompt_len: int, max_total_len: int, n_micro: int):
+        self.eng, self.b, self.T = engine, b, prompt_len
+        self.is_first, self.is_last = engine.is_first, engine.is_last
+        self.prompt_ids = {}  # stage 0: slot -> int32 [b*T] device tensor
+        for mb in range(n_micro):
+            engine.start_batch(b, prompt_len, max_total_len, mb=mb)
+        dev = engine.device
+        self._pf_in = None if self.is_first else torch.empty(b * prompt_len, engine.spec.d_model,
+                                                             dtype=torch.bfloat16, device=dev)
+
+    def recv_buffer(self, kind, mb):
+        st = self.eng._state(self.b, mb)
+        if self.is_first:
+            return st["tokens"]
+        return self._pf_in if kind == "prefill" else st["h"]
+
+    def compute(self, kind, mb):
+        if kind == "prefill":
+            if self.is_first:
+                return self.eng.prefill(self.b, self.T, ids=self.prompt_ids[mb], mb=mb)
+            return self.eng.prefill(self.b, self.T, hidden=self._pf_in, mb=mb)
+        return self.eng.decode_step(self.b, mb=mb)
+
+
+def init_distributed():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    torch.cuda.set_device(local)
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    return rank, world, local
+
+
+def build_stage_engine(spec, rank: int, world: int, local: int, max_batch: int, max_seq_len: int, page_size: int = 16):
+    from .engine import ShardEngine
+    from .sharding import shard_ranges
+
+    a, b = shard_ranges(spec.n_layers, world)[rank]
+    return ShardEngine(spec, a, b, device=f"cuda:{local}", max_batch=max_batch, max_seq_len=max_seq_len,
+                       page_size=page_size)
+
+
+def run_pipeline_bench(args, spec, peaks):
+    """bench.py's N > 1 arm (launched by torchrun, one rank per GPU)."""
+    from . import ops
+
+    rank, world, local = init_distributed()
+    b, ctx, K, W = args.batch, args.ctx, args.steps, max(args.warmup, 3)
+    M = world  # one micro-batch per stage keeps every stage busy
+    max_len = ctx + 2 * (K + W) + 16
+    eng = build_stage_engine(spec, rank, world, local, M * b, max_len, args.page_size)
+    eng.load_random(seed=0)
+    stage = EngineStage(eng, b, ctx, max_len, M)
+    if stage.is_first:
+        g = torch.Generator().manual_seed(1)
+        for mb in range(M):
+            stage.prompt_ids[mb] = torch.randint(0, spec.vocab, (b * ctx,), generator=g, dtype=torch.int32).cuda()
+    runner = PipelineRunner(stage, rank, world, M)
+
+    def timed(fn):
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        return t.item()
+
+    pf_ms = timed(lambda: runner.run("prefill"))
+    runner.run("decode", W)  # warm-up rounds (captures the per-slot CUDA graphs)
+    n0 = ops.launch_count
+    from bench import ClockSampler, decode_step_bytes
+
+    with ClockSampler(index=local) as clk:
+        ms = timed(lambda: runner.run("decode", K))
+    launches = torch.tensor([ops.launch_count - n0], device="cuda")
+    dist.all_reduce(launches)
+
+    # e2e: one round at a time; the pipeline head (rank 0, the stage the master addresses)
+    # copies each round's tokens to pinned host memory and synchronises, as a streaming
+    # client needs.  Inputs of a round are the previous round's tokens, which arrive over
+    # NVLink from the last stage, so there is no host->device copy in steady state.
+    host_tok = torch.zeros(M, b, dtype=torch.int32).pin_memory()
+
+    def host_rounds():
+        for _ in range(K):
+            runner.run("decode", 2)  # 2 rounds: the first round's tokens return to stage 0
+            if rank == 0:
+                for mb in range(M):
+                    host_tok[mb].copy_(eng._state(b, mb)["tokens"], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+    e2e_ms = timed(host_rounds) / 2  # per round
+    n_local = eng.n_local
+    S_mid = ctx + W + K // 2
+    stage_bytes = decode_step_bytes(spec, n_local, eng.is_last, b, S_mid)
+    # a stage pass (one tick) is the roofline unit: bytes of one pass / tick time
+    P = max(M, world)
+    tick_ms = ms / (K * P + world - 1)
+    ach = torch.tensor([stage_bytes / (tick_ms / 1e3) / 1e9], device="cuda")
+    dist.all_reduce(ach, op=dist.ReduceOp.MIN)
+    value = M * b * K / (ms / 1e3)
+    roof = {"bound": "hbm", "kernel": "stage pass (all kernels of one micro-batch on one stage)",
+            "achieved": ach.item(), "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach.item() / peaks["hbm_gbs"],
+            "traffic": None, "bytes_per_launch": stage_bytes, "micro_batches": M,
+            "note": "min over stages; every stage re-reads its weights once per micro-batch (SURVEY 8d)"}
+    return {"value": value, "ms_per_step": ms / K, "gpu_launches": int(launches.item()), "clocks": clk.summary(),
+            "e2e": {"value": M * b * K / (e2e_ms / 1e3), "unit": "tokens/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 4 * M * b, "ms_per_step": e2e_ms / K},
+            "roofline": roof,
+            "extra": {"prefill_tokens_per_s": M * b * ctx / (pf_ms / 1e3), "prefill_ms": pf_ms, "tick_ms": tick_ms,
+                      "peaks": peaks["source"]},
+            "config": {"workload": f"{args.model} bf16 random-init, {world} pipeline stages (contiguous layer ranges, "
+                                   f"reference sharder formula) on {world} GPUs, {M} micro-batches x batch {b} greedy "
+                                   f"decode at {ctx}-token context, NCCL send/recv hand-off",
+                       "batch": M * b, "micro_batches": M, "ctx": ctx, "page_size": args.page_size,
+                       "parallelism": f"pp{world}", "l2": "inputs larger than L2: each stage pass streams its weight "
+                                                          f"slice ({stage_bytes / 1e9:.2f} GB) from HBM"}}

@@ -1,0 +1,141 @@
+"""Shard assignment and shard directories.
+
+Keeps the reference's shard-assignment semantics
+(master/dashboard/management/commands/shard_model.py:55-66, :94-109):
+  * `L // N` layers per shard, the whole remainder on the LAST shard;
+  * directory layout `<out>/<model_name with '/' -> '_'>/shard_<i>/` with a
+    sibling `tokenizer/` directory (consumed at worker/app.py:168,:177);
+  * `metadata.json` = {model_name, shard_id, num_shards, start_layer,
+    end_layer (inclusive), total_layers}.
+What it does NOT keep is the reference's storage defect: the
+reference saves a full-depth model per shard with random out-of-range layers.
+`write_shards` stores only the tensors of the shard's layer range (+ embedding on
+shard 0, final norm / lm_head on the last shard), and `load_hf_state_dict` reads
+only in-range tensors from ANY Hugging Face directory — including the reference's
+full-depth shard directories, whose out-of-range tensors are never trusted.
+"""
+from __future__ import annotations
+
+import json
+import os
+import re
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+_LAYER_RE = re.compile(r"^(?:model\.layers|transformer\.h)\.(\d+)\.")
+_FIRST_ONLY = ("model.embed_tokens.", "transformer.wte.", "transformer.wpe.")
+_LAST_ONLY = ("model.norm.", "lm_head.", "transformer.ln_f.")
+
+
+def shard_ranges(n_layers: int, n_shards: int) -> List[Tuple[int, int]]:
+    """Inclusive (start_layer, end_layer) of every shard (shard_model.py:55-66)."""
+    if n_shards < 1 or n_shards > n_layers:
+        raise ValueError(f"cannot split {n_layers} layers into {n_shards} shards")
+    per, rem = n_layers // n_shards, n_layers % n_shards
+    out = []
+    for i in range(n_shards):
+        start = i * per
+        end = start + per + (rem if i == n_shards - 1 else 0)
+        out.append((start, end - 1))
+    return out
+
+
+def shard_metadata(model_name: str, shard_id: int, n_shards: int, n_layers: int) -> Dict[str, object]:
+    """The metadata.json the reference writes (shard_model.py:99-106)."""
+    start, end = shard_ranges(n_layers, n_shards)[shard_id]
+    return {"model_name": model_name, "shard_id": shard_id, "num_shards": n_shards, "start_layer": start,
+            "end_layer": end, "total_layers": n_layers}
+
+
+def default_metadata(model_name: str, shard_id) -> Dict[str, object]:
+    """What the reference worker synthesises when metadata.json is absent (worker/app.py:181-189)."""
+    return {"model_name": model_name, "shard_id": shard_id, "num_shards": 1, "start_layer": 0, "end_layer": 0,
+            "total_layers": 1}
+
+
+def model_dir_name(model_name: str) -> str:
+    return model_name.replace("/", "_")  # shard_model.py:25
+
+
+def tensor_in_range(name: str, start: int, end: int, is_first: bool, is_last: bool, tied: bool = False) -> bool:
+    """Does a HF tensor name belong to the stage owning layers [start, end]?"""
+    m = _LAYER_RE.match(name)
+    if m:
+        return start <= int(m.group(1)) <= end
+    if name.startswith(_FIRST_ONLY):
+        # a tied lm_head reads the embedding on the last stage too (GPT-2, tie_word_embeddings)
+        return is_first or (is_last and (tied or name.startswith("transformer.wte.")))
+    if name.startswith(_LAST_ONLY):
+        return is_last
+    return False
+
+
+def _tensor_files(path: str) -> List[str]:
+    for index in ("model.safetensors.index.json", "pytorch_model.bin.index.json"):
+        p = os.path.join(path, index)
+        if os.path.exists(p):
+            files = sorted(set(json.load(open(p))["weight_map"].values()))
+            return [os.path.join(path, f) for f in files]
+    for f in ("model.safetensors", "pytorch_model.bin"):
+        p = os.path.join(path, f)
+        if os.path.exists(p):
+            return [p]
+    raise FileNotFoundError(f"no model.safetensors / pytorch_model.bin (or index) in {path}")
+
+
+def load_hf_state_dict(path: str, start_layer: int = 0, end_layer: Optional[int] = None,
+                       total_layers: Optional[int] = None) -> Dict[str, torch.Tensor]:
+    """Read only the tensors a stage needs from a Hugging Face model directory
+    (`save_pretrained` format: safetensors or .bin, single file or sharded index)."""
+    cfg = json.load(open(os.path.join(path, "config.json")))
+    L = total_layers or cfg.get("num_hidden_layers") or cfg.get("n_layer")
+    end = L - 1 if end_layer is None else end_layer
+    is_first, is_last = start_layer == 0, end == L - 1
+    tied = bool(cfg.get("tie_word_embeddings", cfg.get("model_type") == "gpt2"))
+    out: Dict[str, torch.Tensor] = {}
+    for f in _tensor_files(path):
+        if f.endswith(".safetensors"):
+            from safetensors import safe_open
+
+            with safe_open(f, framework="pt", device="cpu") as sf:
+                for name in sf.keys():
+                    if tensor_in_range(name, start_layer, end, is_first, is_last, tied):
+                        out[name] = sf.get_tensor(name)
+        else:
+            sd = torch.load(f, map_location="cpu", weights_only=True)
+            for name, t in sd.items():
+                if tensor_in_range(name, start_layer, end, is_first, is_last, tied):
+                    out[name] = t
+    return out
+
+
+def write_shards(state_dict: Dict[str, torch.Tensor], config: Dict[str, object], model_name: str, n_shards: int,
+                 output_dir: str = "model_shards") -> List[str]:
+    """Real shard materialiser: the same CLI contract as
+    `manage.py shard_model --model_name --num_shards --output_dir`
+    (shard_model.py:11-14), but each shard directory holds only its own tensors."""
+    from safetensors.torch import save_file
+
+    L = config.get("num_hidden_layers") or config.get("n_layer")
+    tied = bool(config.get("tie_word_embeddings", config.get("model_type") == "gpt2"))
+    base = os.path.join(output_dir, model_dir_name(model_name))
+    os.makedirs(os.path.join(base, "tokenizer"), exist_ok=True)
+    paths = []
+    for i, (a, b) in enumerate(shard_ranges(L, n_shards)):
+        p = os.path.join(base, f"shard_{i}")
+        os.makedirs(p, exist_ok=True)
+        part = {k: v.contiguous() for k, v in state_dict.items()
+                if tensor_in_range(k, a, b, a == 0, b == L - 1, tied)}
+        save_file(part, os.path.join(p, "model.safetensors"))
+        json.dump(config, open(os.path.join(p, "config.json"), "w"), indent=2)
+        json.dump(shard_metadata(model_name, i, n_shards, L), open(os.path.join(p, "metadata.json"), "w"), indent=2)
+        paths.append(p)
+    return paths
+
+
+def read_metadata(shard_path: str, model_name: str, shard_id) -> Dict[str, object]:
+    p = os.path.join(shard_path, "metadata.json")
+    if os.path.exists(p):
+        return json.load(open(p))
+    return default_metadata(model_name, shard_id)

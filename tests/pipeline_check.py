@@ -1,0 +1,59 @@
+"""torchrun entry: N pipeline stages over NCCL == one full-range engine, token for token.
+Launched by tests/test_pipeline_gpu.py (needs >= 2 GPUs)."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from golden_util import load_case, spec_kwargs  # noqa: E402
+
+from dli_b200.engine import ModelSpec, ShardEngine  # noqa: E402
+from dli_b200.pipeline import EngineStage, PipelineRunner, build_stage_engine, init_distributed  # noqa: E402
+from oracle import decoder_ref as R  # noqa: E402
+
+
+def main():
+    rank, world, local = init_distributed()
+    c = load_case("llama_tiny")
+    spec = ModelSpec.from_hf_config(spec_kwargs(c["config"]))
+    sd = R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"])
+    B, T = c["prompts"].shape
+    rounds, M, b = 6, B, 1  # one sequence per micro-batch slot
+    eng = build_stage_engine(spec, rank, world, local, max_batch=M * b, max_seq_len=128)
+    eng.load_state_dict(sd)
+    stage = EngineStage(eng, b, T, T + rounds + 2, M)
+    if stage.is_first:
+        for mb in range(M):
+            stage.prompt_ids[mb] = c["prompts"][mb].to("cuda", torch.int32).contiguous()
+    runner = PipelineRunner(stage, rank, world, M)
+    runner.run("prefill")
+    first = None
+    if stage.is_last:
+        first = torch.stack([eng._state(b, mb)["tokens"].clone() for mb in range(M)])  # [M, b]
+    runner.run("decode", rounds)
+    torch.cuda.synchronize()
+    ok = True
+    if stage.is_last:
+        logs = torch.stack([eng._state(b, mb)["token_log"][:rounds, 0] for mb in range(M)])  # [M, rounds]
+        got = torch.cat((first[:, :1], logs), dim=1).cpu().long()  # [M, 1 + rounds]
+        full = ShardEngine(spec, device=f"cuda:{local}", max_batch=B, max_seq_len=128)
+        full.load_state_dict(sd)
+        want = full.generate(c["prompts"], T + 1 + rounds)[:, T:]
+        ok = torch.equal(got, want)
+        print("pipeline tokens", got.tolist(), "single-engine tokens", want.tolist(), flush=True)
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("PIPELINE_OK" if flag.item() == 1 else "PIPELINE_MISMATCH", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if flag.item() == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()

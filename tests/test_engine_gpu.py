@@ -119,7 +119,7 @@ def test_engine_matches_oracle_live(cuda, name):
     assert torch.equal(tok.cpu().long(), full[:, T])
     # two decode steps through the 2-stage chain == single engine
     for i in range(2):
-        s0._dec[B]["tokens"].copy_(tok)
+        s0._state(B)["tokens"].copy_(tok)
         h = s0.decode_step(B)
         tok = s1.decode_step(B, hidden_in=h).clone()
         assert torch.equal(tok.cpu().long(), full[:, T + 1 + i])

@@ -1,0 +1,127 @@
+"""Pipeline schedule + neighbour exchange on CPU: world_size 2 and 3 over gloo, with a
+toy integer stage standing in for the CUDA ShardEngine (host logic only)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from dli_b200.pipeline import PipelineRunner, StageBase, tick_work, total_ticks
+from dli_b200.sharding import shard_ranges
+
+
+class ToyStage(StageBase):
+    """hidden' = hidden * 3 + (stage + 1) + step ; last stage: token = hidden.sum % 1000.
+    Stage 0 turns tokens into hidden = token (+ prompt sum at prefill)."""
+
+    def __init__(self, rank, world, n_micro, b, d):
+        self.rank, self.is_first, self.is_last = rank, rank == 0, rank == world - 1
+        self.b, self.d = b, d
+        self.tokens = [torch.zeros(b, dtype=torch.int32) for _ in range(n_micro)]
+        self.hidden = [torch.zeros(b, d, dtype=torch.float32) for _ in range(n_micro)]
+        self.pf_in = torch.zeros(b, d, dtype=torch.float32)
+        self.steps = [0] * n_micro
+        self.log = [[] for _ in range(n_micro)]
+        self.prompts = [torch.arange(b, dtype=torch.float32) + 10 * mb for mb in range(n_micro)]
+
+    def recv_buffer(self, kind, mb):
+        if self.is_first:
+            return self.tokens[mb]
+        return self.pf_in if kind == "prefill" else self.hidden[mb]
+
+    def compute(self, kind, mb):
+        if self.is_first:
+            src = self.prompts[mb] if kind == "prefill" else self.tokens[mb].float()
+            h = src[:, None].expand(self.b, self.d).clone()
+        else:
+            h = (self.pf_in if kind == "prefill" else self.hidden[mb]).clone()
+        h = h * 3 + (self.rank + 1) + self.steps[mb]
+        self.steps[mb] += 1
+        if self.is_last:
+            tok = (h.sum(dim=1).long() % 1000).int()
+            self.log[mb].append(tok.clone())
+            self.out = tok
+            return self.out
+        self.hidden[mb].copy_(h)
+        return self.hidden[mb]
+
+
+def sequential(world, n_micro, b, d, rounds):
+    """Same toy model without any pipeline: the expected token log per slot."""
+    logs = []
+    for mb in range(n_micro):
+        log, src = [], torch.arange(b, dtype=torch.float32) + 10 * mb
+        for step in range(rounds + 1):
+            h = src[:, None].expand(b, d).clone()
+            for s in range(world):
+                h = h * 3 + (s + 1) + step
+            tok = (h.sum(dim=1).long() % 1000).int()
+            log.append(tok)
+            src = tok.float()
+        logs.append(torch.stack(log))
+    return logs
+
+
+def _worker(rank, world, port, n_micro, rounds, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    stage = ToyStage(rank, world, n_micro, b=2, d=4)
+    runner = PipelineRunner(stage, rank, world, n_micro)
+    runner.run("prefill")
+    runner.run("decode", rounds)
+    if rank == world - 1:
+        q.put([torch.stack(l).tolist() for l in stage.log])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("world,n_micro,rounds", [(2, 2, 3), (2, 1, 2), (3, 4, 2), (2, 3, 4)])
+def test_pipeline_matches_sequential_over_gloo(world, n_micro, rounds):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_micro, rounds, q)) for r in range(world)]
+    [p.start() for p in procs]
+    got = q.get(timeout=120)
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    want = sequential(world, n_micro, 2, 4, rounds)
+    for mb in range(n_micro):
+        assert got[mb] == want[mb].tolist(), (mb, got[mb], want[mb].tolist())
+
+
+def test_tick_schedule_properties():
+    for N, M, R in [(2, 2, 3), (4, 4, 5), (8, 8, 2), (3, 5, 2), (4, 2, 3), (2, 1, 4)]:
+        P = max(N, M)
+        seen = {}
+        for t in range(total_ticks(N, M, R)):
+            for s in range(N):
+                w = tick_work(t, s, N, M, R)
+                if w is not None:
+                    seen.setdefault(w, []).append((t, s))
+        assert len(seen) == M * R  # every (round, slot) is processed ...
+        for (r, mb), visits in seen.items():
+            assert [s for _, s in visits] == list(range(N))  # ... by every stage in order, one tick apart
+            assert [t for t, _ in visits] == list(range(visits[0][0], visits[0][0] + N))
+            if r > 0:  # the token of round r-1 has left the last stage before stage 0 needs it
+                assert seen[(r - 1, mb)][-1][0] < visits[0][0]
+        assert tick_work(total_ticks(N, M, R), 0, N, M, R) is None
+
+
+def test_stage_layer_ranges_follow_reference_formula():
+    assert shard_ranges(32, 4) == [(0, 7), (8, 15), (16, 23), (24, 31)]
+    assert shard_ranges(22, 2) == [(0, 10), (11, 21)]
+    assert shard_ranges(80, 8)[-1] == (70, 79)
+    assert shard_ranges(6, 4) == [(0, 0), (1, 1), (2, 2), (3, 5)]  # remainder on the last shard
+    with pytest.raises(ValueError):
+        shard_ranges(2, 3)

@@ -1,0 +1,21 @@
+"""Multi-GPU: N NCCL pipeline stages reproduce the single-GPU tokens (needs >= 2 GPUs;
+skipped on a 1-GPU box — the schedule itself is covered on CPU by test_pipeline_cpu.py)."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_nccl_pipeline_equals_single_engine(cuda, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs, have {torch.cuda.device_count()}")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29500 + world), os.path.join(ROOT, "tests", "pipeline_check.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0 and "PIPELINE_OK" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
