@@ -320,7 +320,8 @@ class ShardEngine:
                 ops.attn_prefill(qkv, attn, prefill_shape[0], prefill_shape[1], H, KV, hd, self.scale,
                                  window=s.sliding_window)
             else:
-                ops.paged_attn_decode(qkv, qkv.shape[1], self.kv.k[li], self.kv.v[li], self.kv.page_table, seq_lens,
+                # the kernel indexes page-table rows by batch row: pass the slot's rows
+                ops.paged_attn_decode(qkv, qkv.shape[1], self.kv.k[li], self.kv.v[li], st["page_rows"], seq_lens,
                                       attn, H, KV, hd, self.scale, num_splits=st["splits"], scratch=st["scratch"],
                                       window=s.sliding_window)
             if s.arch == "llama":
@@ -374,6 +375,7 @@ class ShardEngine:
                 "positions": torch.zeros(B, dtype=torch.int32, device=dev),
                 "seq_lens": torch.zeros(B, dtype=torch.int32, device=dev),
                 "seq_ids": torch.arange(mb * B, (mb + 1) * B, dtype=torch.int32, device=dev),
+                "page_rows": self.kv.page_table[mb * B:(mb + 1) * B],  # view: rows of this slot's sequences
                 "tokens": torch.zeros(B, dtype=torch.int32, device=dev),
                 "step": torch.zeros(1, dtype=torch.int32, device=dev),
                 # residual stream of the slot's decode step: stage input (recv target) and output (send source)
