@@ -13,6 +13,7 @@ arithmetic goes through the C-ABI kernels (ops.py -> include/dli.h).
 from __future__ import annotations
 
 import math
+import time
 from dataclasses import dataclass
 from typing import Dict, List, Optional
 
@@ -488,7 +489,7 @@ class ShardEngine:
     # ------------------------------------------------------------------ public API
     @torch.no_grad()
     def generate(self, input_ids: torch.Tensor, max_length: int, return_logits: bool = False,
-                 forced: Optional[torch.Tensor] = None):
+                 forced: Optional[torch.Tensor] = None, deadline: Optional[float] = None):
         """Greedy generate (the parity mode of worker/app.py:297-305: the reference
         samples, see SURVEY.md §0 F3).  input_ids: int [B, T] on any device;
         `max_length` is the TOTAL length like the reference's.  Returns int64
@@ -517,6 +518,12 @@ class ShardEngine:
             self.use_cuda_graph = False
         try:
             for i in range(n_new - 1):
+                if deadline is not None and (i & 7) == 0:
+                    # the reference can only check its timeout around generate() (worker/app.py:293,:311);
+                    # here it is checked between decode steps
+                    torch.cuda.current_stream().synchronize()
+                    if time.time() > deadline:
+                        raise TimeoutError("Inference generation timed out")
                 if forced is not None:
                     st["tokens"].copy_(forced[:, i])
                 self.decode_step(B)
@@ -536,3 +543,48 @@ class ShardEngine:
     @property
     def last_logits(self):
         return None if not self._dec else next(iter(self._dec.values()))["logits"]
+
+
+class LocalChain:
+    """Several ShardEngines resident in ONE process, run back to back on one GPU:
+    the in-process form of the shard pipeline, used by the worker when the
+    `shard_ids` of an /inference request (worker/app.py:260,:274) are all loaded
+    here.  The stages must cover layers 0..L-1 without gaps."""
+
+    def __init__(self, engines: List[ShardEngine]):
+        engines = sorted(engines, key=lambda e: e.start)
+        L = engines[0].spec.n_layers
+        if engines[0].start != 0 or engines[-1].end != L - 1 or any(
+                a.end + 1 != b.start for a, b in zip(engines, engines[1:])):
+            have = [(e.start, e.end) for e in engines]
+            raise ValueError(f"shards resident on this worker cover layers {have}, not all of 0..{L - 1}")
+        self.engines = engines
+
+    @torch.no_grad()
+    def generate(self, input_ids: torch.Tensor, max_length: int, deadline: Optional[float] = None) -> torch.Tensor:
+        if len(self.engines) == 1:
+            return self.engines[0].generate(input_ids, max_length, deadline=deadline)
+        B, T = input_ids.shape
+        n_new = max_length - T
+        if n_new <= 0:
+            return input_ids.cpu().long()[:, :max_length]
+        first, last = self.engines[0], self.engines[-1]
+        for e in self.engines:
+            e.start_batch(B, T, max_length)
+        x = input_ids.to(device=first.device, dtype=torch.int32).reshape(-1).contiguous()
+        x = first.prefill(B, T, ids=x)
+        for e in self.engines[1:]:
+            x = e.prefill(B, T, hidden=x)
+        toks = [x.clone()]
+        for i in range(n_new - 1):
+            if deadline is not None and (i & 7) == 0:
+                torch.cuda.current_stream().synchronize()
+                if time.time() > deadline:
+                    raise TimeoutError("Inference generation timed out")
+            first._state(B)["tokens"].copy_(toks[-1])
+            x = first.decode_step(B)
+            for e in self.engines[1:]:
+                x = e.decode_step(B, hidden_in=x)
+            toks.append(x.clone())
+        new = torch.stack(toks, dim=1)
+        return torch.cat((input_ids.cpu().long(), new.cpu().long()), dim=1)

@@ -1,0 +1,251 @@
+"""Drop-in for the reference worker service (reference worker/app.py).
+
+Same routes, methods, JSON keys, status codes and environment variables as the
+Flask app the master talks to (worker/app.py:49-330; contract table SURVEY.md
+§A.1; behaviour recorded from the reference itself in
+tests/golden/worker_contract.json):
+
+    GET  /health          worker/app.py:49-92
+    POST /load_model      worker/app.py:94-137
+    POST /load_shard      worker/app.py:139-206
+    POST /unload_model    worker/app.py:208-250
+    POST /inference       worker/app.py:252-330  (+ run_shard_inference :332-372)
+
+`/ssh_setup` (:374-413, a paramiko login test) is out of scope.  Behind the routes
+the model object is a ShardEngine on the B200 instead of a transformers model on
+the CPU.  Built on werkzeug (Flask is not installed; werkzeug is what Flask wraps).
+
+Deliberate deviations from the reference, each a fixed defect:
+  Q1  `shard_id: 0` is accepted (the reference's `all([...])` rejects falsy ids);
+  Q2  every shard id of the request is used (the reference silently uses only the
+      first), as an in-process layer-range chain; the shards must cover all layers;
+  Q3  greedy decoding (the parity mode); the reference samples with no seed;
+  Q6  the timeout is checked between decode steps, not only around generate();
+  Q7  /unload_model also frees the lazily created per-shard engines;
+  USE_GPU defaults to 1: this worker has no CPU path (the reference defaults to 0).
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+from typing import Dict
+
+import psutil
+import torch
+from werkzeug.wrappers import Request, Response
+
+from .sharding import load_hf_state_dict, read_metadata
+
+
+class IdTokenizer:
+    """Used when no tokenizer files exist (the hub is unreachable): prompts are
+    whitespace-separated token ids."""
+
+    def __call__(self, prompt, return_tensors="pt"):
+        ids = torch.tensor([[int(t) for t in str(prompt).split()]], dtype=torch.int64)
+        return {"input_ids": ids, "attention_mask": torch.ones_like(ids)}
+
+    def decode(self, ids, skip_special_tokens=True):
+        return " ".join(str(int(i)) for i in ids)
+
+
+def _load_tokenizer(path: str):
+    names = ("tokenizer.json", "tokenizer.model", "vocab.json", "tokenizer_config.json")
+    if path and os.path.isdir(path) and any(os.path.exists(os.path.join(path, n)) for n in names):
+        from transformers import AutoTokenizer
+
+        return AutoTokenizer.from_pretrained(path)
+    return IdTokenizer()
+
+
+class Worker:
+    """State + handlers; one instance per process (the reference keeps the same
+    three dicts as module globals, worker/app.py:14-16)."""
+
+    def __init__(self, env=None):
+        env = os.environ if env is None else env
+        self.loaded_models: Dict[str, object] = {}
+        self.loaded_tokenizers: Dict[str, object] = {}
+        self.loaded_shards: Dict[str, Dict[object, dict]] = {}
+        self.model_cache_dir = env.get("MODEL_CACHE_DIR", "/app/model_cache")
+        self.use_gpu = env.get("USE_GPU", "1") == "1"
+        self.device = "cuda" if torch.cuda.is_available() and self.use_gpu else "cpu"
+        self.auth_enabled = env.get("AUTH_ENABLED", "0") == "1"
+        self.auth_key = env.get("AUTH_KEY", "")
+        self.max_seq_len = int(env.get("DLI_MAX_SEQ_LEN", "4096"))
+        self.routes = {("GET", "/health"): self.health, ("POST", "/load_model"): self.load_model,
+                       ("POST", "/load_shard"): self.load_shard, ("POST", "/unload_model"): self.unload_model,
+                       ("POST", "/inference"): self.inference}
+
+    # ------------------------------------------------------------------ helpers
+    def _resolve_model_dir(self, model_name: str) -> str:
+        for cand in (model_name, os.path.join(self.model_cache_dir, model_name.replace("/", "_")),
+                     os.path.join(self.model_cache_dir, model_name)):
+            if os.path.isdir(cand) and os.path.exists(os.path.join(cand, "config.json")):
+                return cand
+        raise FileNotFoundError(f"{model_name} is not a local model directory and the Hugging Face hub is not "
+                                f"reachable (looked in {self.model_cache_dir})")
+
+    def _engine(self, path: str, start=0, end=None):
+        from .engine import ModelSpec, ShardEngine
+
+        if self.device != "cuda":
+            raise RuntimeError("this worker has no CPU path: it needs a CUDA device and USE_GPU=1")
+        cfg = json.load(open(os.path.join(path, "config.json")))
+        spec = ModelSpec.from_hf_config(cfg)
+        eng = ShardEngine(spec, start, end, device="cuda:0", max_batch=1,
+                          max_seq_len=min(self.max_seq_len, spec.max_pos))
+        eng.load_state_dict(load_hf_state_dict(path, eng.start, eng.end, spec.n_layers))
+        return eng
+
+    # ------------------------------------------------------------------ routes
+    def health(self, _data):
+        gpu = 0.0
+        if torch.cuda.is_available() and self.use_gpu:
+            mx = torch.cuda.max_memory_allocated()
+            gpu = torch.cuda.memory_allocated() / mx if mx > 0 else 0.0
+        shard_info = [{"model_name": m, "shard_id": sid, "path": d["path"], "metadata": d["metadata"]}
+                      for m, shards in self.loaded_shards.items() for sid, d in shards.items()]
+        return {"status": "healthy",
+                "resources": {"cpu": psutil.cpu_percent() / 100.0, "memory": psutil.virtual_memory().percent / 100.0,
+                              "gpu": gpu, "gpu_available": torch.cuda.is_available() and self.use_gpu,
+                              "device": self.device},
+                "loaded_models": list(self.loaded_models.keys()),
+                "loaded_tokenizers": list(self.loaded_tokenizers.keys()),
+                "loaded_shards": shard_info}, 200
+
+    def load_model(self, data):
+        model_name = (data or {}).get("model_name")
+        if not model_name:
+            return {"status": "error", "message": "Model name is required"}, 400
+        try:
+            if model_name in self.loaded_models:
+                return {"status": "success", "message": f"Model {model_name} is already loaded"}, 200
+            path = self._resolve_model_dir(model_name)
+            if model_name not in self.loaded_tokenizers:
+                self.loaded_tokenizers[model_name] = _load_tokenizer(path)
+            self.loaded_models[model_name] = self._engine(path)
+            return {"status": "success", "message": f"Model {model_name} loaded successfully on {self.device}"}, 200
+        except Exception as e:  # noqa: BLE001 — the reference maps every failure to 500
+            return {"status": "error", "message": f"Failed to load model: {str(e)}"}, 500
+
+    def load_shard(self, data):
+        data = data or {}
+        model_name, shard_id, shard_path = data.get("model_name"), data.get("shard_id"), data.get("shard_path")
+        if not model_name or shard_id is None or shard_id == "" or not shard_path:  # Q1: 0 is a valid id
+            return {"status": "error", "message": "Model name, shard ID, and shard path are required"}, 400
+        try:
+            shards = self.loaded_shards.setdefault(model_name, {})
+            if shard_id in shards:
+                return {"status": "success", "message": f"Shard {shard_id} of model {model_name} is already loaded"}, 200
+            if model_name not in self.loaded_tokenizers:
+                self.loaded_tokenizers[model_name] = _load_tokenizer(os.path.join(os.path.dirname(shard_path), "tokenizer"))
+            shards[shard_id] = {"path": shard_path, "metadata": read_metadata(shard_path, model_name, shard_id)}
+            return {"status": "success", "message": f"Shard {shard_id} of model {model_name} loaded successfully"}, 200
+        except Exception as e:  # noqa: BLE001
+            return {"status": "error", "message": f"Failed to load shard: {str(e)}"}, 500
+
+    def unload_model(self, data):
+        model_name = (data or {}).get("model_name")
+        if not model_name:
+            return {"status": "error", "message": "Model name is required"}, 400
+        try:
+            for key in [k for k in self.loaded_models if k == model_name or k.startswith(f"{model_name}_")]:
+                eng = self.loaded_models.pop(key)  # Q7: per-shard engines too
+                if hasattr(eng, "unload"):
+                    eng.unload()
+            self.loaded_tokenizers.pop(model_name, None)
+            self.loaded_shards.pop(model_name, None)
+            if self.device == "cuda":
+                torch.cuda.empty_cache()
+            return {"status": "success", "message": f"Model {model_name} unloaded successfully"}, 200
+        except Exception as e:  # noqa: BLE001
+            return {"status": "error", "message": f"Failed to unload model: {str(e)}"}, 500
+
+    def inference(self, data):
+        data = data or {}
+        model_name, prompt = data.get("model_name"), data.get("prompt")
+        max_length = data.get("max_length", 100)
+        shard_ids = data.get("shard_ids")
+        timeout = data.get("timeout", 60)
+        if not model_name or not prompt:
+            return {"status": "error", "message": "Model name and prompt are required"}, 400
+        try:
+            start_time = time.time()
+            deadline = start_time + timeout
+            if shard_ids:
+                result = self.run_shard_inference(model_name, prompt, shard_ids, max_length, deadline)
+            else:
+                if model_name not in self.loaded_models:
+                    resp, code = self.load_model({"model_name": model_name})
+                    if code == 500:
+                        return resp, code
+                model, tokenizer = self.loaded_models[model_name], self.loaded_tokenizers[model_name]
+                ids = tokenizer(prompt, return_tensors="pt")["input_ids"]
+                if (time.time() - start_time) > timeout:
+                    raise TimeoutError("Inference preparation timed out")
+                outputs = model.generate(ids, max_length=max_length, deadline=deadline)
+                result = tokenizer.decode(outputs[0], skip_special_tokens=True)
+                if (time.time() - start_time) > timeout:
+                    raise TimeoutError("Inference generation timed out")
+            return {"status": "success", "result": result, "execution_time": time.time() - start_time}, 200
+        except TimeoutError as e:
+            return {"status": "error", "message": str(e)}, 408
+        except Exception as e:  # noqa: BLE001
+            return {"status": "error", "message": f"Inference failed: {str(e)}"}, 500
+
+    def run_shard_inference(self, model_name, prompt, shard_ids, max_length, deadline=None):
+        """worker/app.py:332-372, with the intended semantics: the listed shards are
+        layer ranges run in order on hidden states (lazy weight load on first use)."""
+        from .engine import LocalChain
+
+        engines = []
+        for shard_id in shard_ids:
+            if shard_id not in self.loaded_shards.get(model_name, {}):
+                raise ValueError(f"Shard {shard_id} of model {model_name} is not loaded")
+            info = self.loaded_shards[model_name][shard_id]
+            key = f"{model_name}_{shard_id}"
+            if key not in self.loaded_models:
+                md = info["metadata"]
+                self.loaded_models[key] = self._engine(info["path"], md["start_layer"], md["end_layer"])
+            engines.append(self.loaded_models[key])
+        tokenizer = self.loaded_tokenizers[model_name]
+        ids = tokenizer(prompt, return_tensors="pt")["input_ids"]
+        outputs = LocalChain(engines).generate(ids, max_length=max_length, deadline=deadline)
+        return tokenizer.decode(outputs[0], skip_special_tokens=True)
+
+    # ------------------------------------------------------------------ WSGI
+    def dispatch(self, method: str, path: str, data, headers):
+        if self.auth_enabled:  # worker/app.py:32-47
+            if headers.get("Authorization") != f"Bearer {self.auth_key}":
+                return {"status": "error", "message": "Unauthorized access"}, 401
+        fn = self.routes.get((method, path))
+        if fn is None:
+            known = {p for _, p in self.routes}
+            return {"status": "error", "message": "Method not allowed" if path in known else "Not found"}, \
+                (405 if path in known else 404)
+        return fn(data)
+
+    def __call__(self, environ, start_response):
+        req = Request(environ)
+        data = req.get_json(silent=True) if req.method == "POST" else None
+        body, code = self.dispatch(req.method, req.path, data, req.headers)
+        return Response(json.dumps(body), status=code, mimetype="application/json")(environ, start_response)
+
+
+def main(argv=None):
+    import argparse
+
+    from werkzeug.serving import run_simple
+
+    ap = argparse.ArgumentParser(description="B200 drop-in for the reference worker (port 5000 like worker/app.py:416)")
+    ap.add_argument("--host", default="0.0.0.0")
+    ap.add_argument("--port", type=int, default=5000)
+    a = ap.parse_args(argv)
+    # one request at a time, like the reference's single sync gunicorn worker (worker/Dockerfile:45)
+    run_simple(a.host, a.port, Worker(), threaded=False)
+
+
+if __name__ == "__main__":
+    main()
