@@ -15,6 +15,8 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+void set_pdl(bool on);
+
 int fail(int code, const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -22,6 +24,10 @@ int fail(int code, const char* fmt, ...) {
   va_end(ap);
   return code;
 }
+
+static bool g_pdl = false;
+bool pdl_enabled() { return g_pdl; }
+void set_pdl(bool on) { g_pdl = on; }
 
 int sm_count_cached() {
   static int cached[64] = {0};
@@ -41,7 +47,13 @@ extern "C" {
 
 const char* dli_last_error(void) { return dli::g_err; }
 
-int dli_version(void) { return 1000; }
+int dli_version(void) { return 1001; }
+
+int dli_set_pdl(int enable) {
+  const int before = dli::pdl_enabled() ? 1 : 0;
+  dli::set_pdl(enable != 0);
+  return before;
+}
 
 int dli_sm_count(void) {
   int n = dli::sm_count_cached();

@@ -12,6 +12,12 @@
 // writes an un-normalised partial (O, max, sum) to scratch and a second tiny
 // kernel merges the splits.
 //
+// Fused variant (cos/sin/new-token pointers given): q is read from the packed qkv row
+// of the new token and rotated in shared memory; the CTA that owns the sequence's
+// last KV tile also rotates the new token's k, writes k and v into their cache page
+// and patches them into its staged tile, so the separate RoPE/append kernel
+// disappears from the decode step (bit-identical rounding to rope_kv.cu).
+//
 // Algorithmic bytes per launch: sum_b min(S_b, window) * KV * hd * 2 (K and V)
 // * 2 bytes; q/out/scratch are negligible.
 #include "mma_utils.cuh"
@@ -36,7 +42,9 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
                          const int32_t* __restrict__ page_table, int max_pages,
                          const int32_t* __restrict__ seq_lens, bf16* __restrict__ out,
                          float* __restrict__ part_o, float* __restrict__ part_ml, int H, int KV,
-                         int page_shift, int num_splits, float scale_log2, int window) {
+                         int page_shift, int num_splits, float scale_log2, int window,
+                         int fused, const bf16* __restrict__ cos_t, const bf16* __restrict__ sin_t,
+                         bf16* k_cache_w, bf16* v_cache_w, int pdl_early) {
   using L = DecodeSmem<HD>;
   constexpr int RB = L::kRowBytes;
   constexpr int CH = HD / 8;  // 16-byte chunks per row
@@ -48,6 +56,8 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
   const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int G = H / KV;
+  pdl_wait();  // seq_lens, q and the cache pages come from earlier kernels of the stream
+  if (pdl_early) pdl_trigger();
   const int seq_len = seq_lens[b];
   const int first_tok = (window > 0 && seq_len > window) ? seq_len - window : 0;
   const int tile_lo = first_tok / kAttnTile;
@@ -104,14 +114,58 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
       cp_async_wait<0>();
     }
     __syncthreads();
+    const uint32_t cK = sK + stage * L::kTileBytes, cV = sV + stage * L::kTileBytes;
+    if (fused && tile == tile_hi - 1) {
+      // this CTA owns the tile of the new token (position seq_len-1): rotate its k, store
+      // k and v to the cache page and patch them into the staged tile
+      const int pos = seq_len - 1, row = pos - tile * kAttnTile, half = HD / 2;
+      const int page = pt[pos >> page_shift];
+      const size_t coff = ((((size_t)page * KV + kvh) << page_shift) + (pos & page_mask)) * HD;
+      const bf16* knew = q + (size_t)b * q_stride + (size_t)(H + kvh) * HD;
+      const bf16* vnew = q + (size_t)b * q_stride + (size_t)(H + KV + kvh) * HD;
+      if (tid < half) {
+        const int i = tid;
+        float x1 = __bfloat162float(knew[i]), x2 = __bfloat162float(knew[i + half]);
+        if (cos_t) {
+          const float c = __bfloat162float(cos_t[(size_t)pos * half + i]), sn = __bfloat162float(sin_t[(size_t)pos * half + i]);
+          const float o1 = round_bf16(x1 * c) + round_bf16(-x2 * sn);
+          const float o2 = round_bf16(x2 * c) + round_bf16(x1 * sn);
+          x1 = o1; x2 = o2;
+        }
+        const bf16 b1 = __float2bfloat16_rn(x1), b2 = __float2bfloat16_rn(x2);
+        k_cache_w[coff + i] = b1;
+        k_cache_w[coff + i + half] = b2;
+        *reinterpret_cast<bf16*>(smem + (cK - sQ) + swz<RB>(row, i >> 3) + (i & 7) * 2) = b1;
+        *reinterpret_cast<bf16*>(smem + (cK - sQ) + swz<RB>(row, (i + half) >> 3) + (i & 7) * 2) = b2;
+      } else if (tid < half + CH) {
+        const int c = tid - half;
+        const uint4 u = ld_16B(vnew + c * 8);
+        st_16B(v_cache_w + coff + c * 8, u);
+        *reinterpret_cast<uint4*>(smem + (cV - sQ) + swz<RB>(row, c)) = u;
+      }
+      __syncthreads();
+    }
     if (tile == t_begin) {
+      if (fused && cos_t) {
+        // rotate the G query rows in shared memory (rotate-half, bf16 op by op)
+        const int pos = seq_len - 1, half = HD / 2;
+        for (int idx = tid; idx < G * half; idx += kAttnThreads) {
+          const int g = idx / half, i = idx - g * half;
+          bf16* p1 = reinterpret_cast<bf16*>(smem + swz<RB>(g, i >> 3) + (i & 7) * 2);
+          bf16* p2 = reinterpret_cast<bf16*>(smem + swz<RB>(g, (i + half) >> 3) + (i & 7) * 2);
+          const float x1 = __bfloat162float(*p1), x2 = __bfloat162float(*p2);
+          const float c = __bfloat162float(cos_t[(size_t)pos * half + i]), sn = __bfloat162float(sin_t[(size_t)pos * half + i]);
+          *p1 = __float2bfloat16_rn(round_bf16(x1 * c) + round_bf16(-x2 * sn));
+          *p2 = __float2bfloat16_rn(round_bf16(x2 * c) + round_bf16(x1 * sn));
+        }
+        __syncthreads();
+      }
 #pragma unroll
       for (int kk = 0; kk < HD / 16; ++kk) {
         const int mi = lane >> 3;
         ldmatrix_x4(qf[kk], sQ + swz<RB>((mi & 1) * 8 + (lane & 7), kk * 2 + (mi >> 1)));
       }
     }
-    const uint32_t cK = sK + stage * L::kTileBytes, cV = sV + stage * L::kTileBytes;
 
     // ---- S = Q K^T for this warp's 16 tokens ---------------------------------------
     float s[2][4];
@@ -225,62 +279,90 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
   }
 }
 
-// Merge the per-split partials: one warp per (sequence, head).
+// Merge the per-split partials: one warp per (sequence, head).  Lanes first take one
+// split each (max / weights / denominator by shuffles), then every lane accumulates its
+// HD/32 output columns over the splits with independent, unrolled loads.
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads)
 attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
                         bf16* __restrict__ out, int n_bh, int num_splits, float scale_log2) {
+  constexpr int VEC = HD / 32;
   const int bh = blockIdx.x * (kAttnThreads / 32) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
+  pdl_wait();
+  pdl_trigger();
   if (bh >= n_bh) return;
   const float* ml = part_ml + (size_t)bh * num_splits * 2;
-  float mmax = -INFINITY;
-  for (int s = 0; s < num_splits; ++s) mmax = fmaxf(mmax, ml[s * 2]);
-  float acc[HD / 32];
-#pragma unroll
-  for (int i = 0; i < HD / 32; ++i) acc[i] = 0.f;
-  float lsum = 0.f;
+  // up to 64 splits: lane owns splits lane and lane + 32
+  float m0 = -INFINITY, l0 = 0.f, m1 = -INFINITY, l1 = 0.f;
+  if (lane < num_splits) { m0 = ml[lane * 2]; l0 = ml[lane * 2 + 1]; }
+  if (lane + 32 < num_splits) { m1 = ml[(lane + 32) * 2]; l1 = ml[(lane + 32) * 2 + 1]; }
+  const float mmax = warp_max(fmaxf(m0, m1));
+  float f0 = 0.f, f1 = 0.f;
   if (mmax != -INFINITY) {
-    for (int s = 0; s < num_splits; ++s) {
-      const float f = exp2f((ml[s * 2] - mmax) * scale_log2);
-      lsum += f * ml[s * 2 + 1];
-      const float* po = part_o + ((size_t)bh * num_splits + s) * HD;
+    f0 = exp2f((m0 - mmax) * scale_log2);
+    f1 = exp2f((m1 - mmax) * scale_log2);
+  }
+  const float lsum = warp_sum(f0 * l0 + f1 * l1);
+  float acc[VEC];
 #pragma unroll
-      for (int i = 0; i < HD / 32; ++i) acc[i] += f * po[lane + 32 * i];
+  for (int i = 0; i < VEC; ++i) acc[i] = 0.f;
+  const float* po = part_o + (size_t)bh * num_splits * HD + lane * VEC;
+#pragma unroll 8
+  for (int s = 0; s < num_splits; ++s) {
+    const float f = __shfl_sync(0xffffffffu, s < 32 ? f0 : f1, s & 31);
+    float v[VEC];
+    if (VEC == 4) {
+      const float4 t = *reinterpret_cast<const float4*>(po + (size_t)s * HD);
+      v[0] = t.x; v[1] = t.y; v[2] = t.z; v[VEC - 1] = t.w;
+    } else {
+      const float2 t = *reinterpret_cast<const float2*>(po + (size_t)s * HD);
+      v[0] = t.x; v[VEC - 1] = t.y;
     }
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) acc[i] += f * v[i];
   }
   const float inv = lsum > 0.f ? 1.f / lsum : 0.f;
+  bf16* o = out + (size_t)bh * HD + lane * VEC;
 #pragma unroll
-  for (int i = 0; i < HD / 32; ++i)
-    out[(size_t)bh * HD + lane + 32 * i] = __float2bfloat16_rn(acc[i] * inv);
+  for (int i = 0; i < VEC; i += 2)
+    *reinterpret_cast<uint32_t*>(o + i) = pack_bf16(acc[i] * inv, acc[i + 1] * inv);
 }
 
 template <int HD>
 static int launch_decode(const void* q, int q_stride, const void* k_cache, const void* v_cache,
                          const int32_t* page_table, int max_pages, const int32_t* seq_lens,
                          void* out, void* scratch, int B, int H, int KV, int page_shift,
-                         int num_splits, float scale, int window, cudaStream_t s) {
+                         int num_splits, float scale, int window, cudaStream_t s, int fused = 0,
+                         const void* cos_t = nullptr, const void* sin_t = nullptr) {
   using L = DecodeSmem<HD>;
   static bool attr_set = false;
+  static int occ = 1;
   if (!attr_set) {
     DLI_CUDA_CALL(cudaFuncSetAttribute(paged_attn_decode_kernel<HD>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    int o = 0;
+    DLI_CUDA_CALL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, paged_attn_decode_kernel<HD>, kAttnThreads,
+                                                                L::kTotal));
+    occ = o > 0 ? o : 1;
     attr_set = true;
   }
   const float scale_log2 = scale * 1.4426950408889634f;
   float* part_o = reinterpret_cast<float*>(scratch);
   float* part_ml = part_o ? part_o + (size_t)B * H * num_splits * HD : nullptr;
   dim3 grid(num_splits, KV, B);
-  paged_attn_decode_kernel<HD><<<grid, kAttnThreads, L::kTotal, s>>>(
-      (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table, max_pages,
-      seq_lens, (bf16*)out, part_o, part_ml, H, KV, page_shift, num_splits, scale_log2, window);
-  DLI_CUDA_LAUNCH_CHECK("paged_attn_decode_kernel");
+  // dependents may be released early only when every CTA of this grid is resident at once
+  const int pdl_early = (size_t)num_splits * KV * B <= (size_t)sm_count_cached() * occ ? 1 : 0;
+  DLI_LAUNCH("paged_attn_decode_kernel", paged_attn_decode_kernel<HD>, grid, dim3(kAttnThreads), (size_t)L::kTotal, s,
+             (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table, max_pages, seq_lens,
+             (bf16*)out, part_o, part_ml, H, KV, page_shift, num_splits, scale_log2, window, fused,
+             (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, pdl_early);
   if (num_splits > 1) {
     const int n_bh = B * H;
     const int per_cta = kAttnThreads / 32;
-    attn_split_merge_kernel<HD><<<(n_bh + per_cta - 1) / per_cta, kAttnThreads, 0, s>>>(
-        part_o, part_ml, (bf16*)out, n_bh, num_splits, scale_log2);
-    DLI_CUDA_LAUNCH_CHECK("attn_split_merge_kernel");
+    DLI_LAUNCH("attn_split_merge_kernel", attn_split_merge_kernel<HD>, dim3((n_bh + per_cta - 1) / per_cta),
+               dim3(kAttnThreads), (size_t)0, s, (const float*)part_o, (const float*)part_ml, (bf16*)out, n_bh,
+               num_splits, scale_log2);
   }
   return DLI_OK;
 }
@@ -307,8 +389,8 @@ int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
                 "dli_paged_attn_decode_bf16: need H %% KV == 0 and H/KV <= 16 (got H=%d KV=%d)", H, KV);
   DLI_CHECK_ARG(page_size >= 8 && (page_size & (page_size - 1)) == 0,
                 "dli_paged_attn_decode_bf16: page_size must be a power of two >= 8 (got %d)", page_size);
-  DLI_CHECK_ARG(num_splits >= 1 && num_splits <= 65535 && KV <= 65535 && B <= 65535,
-                "dli_paged_attn_decode_bf16: num_splits/KV/B out of grid range");
+  DLI_CHECK_ARG(num_splits >= 1 && num_splits <= 64 && KV <= 65535 && B <= 65535,
+                "dli_paged_attn_decode_bf16: num_splits must be 1..64 (got %d)", num_splits);
   DLI_CHECK_ARG(q_stride >= H * hd && q_stride % 8 == 0 && max_pages > 0 && window >= 0,
                 "dli_paged_attn_decode_bf16: bad q_stride/max_pages/window");
   DLI_CHECK_ARG(aligned16(q) && aligned16(k_cache) && aligned16(v_cache) && aligned16(scratch),
@@ -330,6 +412,43 @@ int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
 }
 
 }  // extern "C"
+
+extern "C" int dli_paged_attn_decode_fused_bf16(void* qkv, int row_stride, const void* cos, const void* sin,
+                                                void* k_cache, void* v_cache, const int32_t* page_table,
+                                                int max_pages, const int32_t* seq_lens, void* out, void* scratch,
+                                                size_t scratch_bytes, int B, int H, int KV, int hd, int page_size,
+                                                int num_splits, float scale, int window, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(qkv && k_cache && v_cache && page_table && seq_lens && out,
+                "dli_paged_attn_decode_fused_bf16: null pointer");
+  DLI_CHECK_ARG((cos == nullptr) == (sin == nullptr), "dli_paged_attn_decode_fused_bf16: cos and sin go together");
+  DLI_CHECK_ARG(hd == 64 || hd == 128, "dli_paged_attn_decode_fused_bf16: hd must be 64 or 128 (got %d)", hd);
+  DLI_CHECK_ARG(B >= 0 && H > 0 && KV > 0 && H % KV == 0 && H / KV <= 16,
+                "dli_paged_attn_decode_fused_bf16: need H %% KV == 0 and H/KV <= 16 (got H=%d KV=%d)", H, KV);
+  DLI_CHECK_ARG(page_size >= 8 && (page_size & (page_size - 1)) == 0,
+                "dli_paged_attn_decode_fused_bf16: page_size must be a power of two >= 8 (got %d)", page_size);
+  DLI_CHECK_ARG(num_splits >= 1 && num_splits <= 64 && KV <= 65535 && B <= 65535,
+                "dli_paged_attn_decode_fused_bf16: num_splits must be 1..64");
+  DLI_CHECK_ARG(row_stride >= (H + 2 * KV) * hd && row_stride % 8 == 0 && max_pages > 0 && window >= 0,
+                "dli_paged_attn_decode_fused_bf16: bad row_stride/max_pages/window");
+  DLI_CHECK_ARG(aligned16(qkv) && aligned16(k_cache) && aligned16(v_cache) && aligned16(scratch) &&
+                    aligned16(cos) && aligned16(sin),
+                "dli_paged_attn_decode_fused_bf16: pointers must be 16-byte aligned");
+  if (num_splits > 1) {
+    const size_t need = dli_paged_attn_decode_scratch_bytes(B, H, hd, num_splits);
+    DLI_CHECK_ARG(scratch && scratch_bytes >= need,
+                  "dli_paged_attn_decode_fused_bf16: scratch too small (%zu < %zu bytes)", scratch_bytes, need);
+  }
+  if (B == 0) return DLI_OK;
+  int shift = 0;
+  while ((1 << shift) < page_size) ++shift;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (hd == 128)
+    return launch_decode<128>(qkv, row_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B,
+                              H, KV, shift, num_splits, scale, window, s, 1, cos, sin);
+  return launch_decode<64>(qkv, row_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B, H,
+                           KV, shift, num_splits, scale, window, s, 1, cos, sin);
+}
 
 // ---------------------------------------------------------------------------------------
 // Split-KV decode attention for callers that cannot allocate device memory.

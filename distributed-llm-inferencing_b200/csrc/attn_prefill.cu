@@ -26,6 +26,7 @@ attn_prefill_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int T,
   const uint32_t sK = sQ + kTileBytes;
   const uint32_t sV = sK + 2 * kTileBytes;
 
+  pdl_wait();
   const int qtile = gridDim.x - 1 - blockIdx.x;
   const int h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / (H / KV);
@@ -183,9 +184,8 @@ static int launch_prefill(const void* qkv, void* out, int B, int T, int H, int K
     attr_set = true;
   }
   dim3 grid((T + kPfTile - 1) / kPfTile, H, B);
-  attn_prefill_kernel<HD><<<grid, kPfThreads, kSmem, s>>>((const bf16*)qkv, (bf16*)out, T, H, KV,
-                                                          scale * 1.4426950408889634f, window);
-  DLI_CUDA_LAUNCH_CHECK("attn_prefill_kernel");
+  DLI_LAUNCH("attn_prefill_kernel", attn_prefill_kernel<HD>, grid, dim3(kPfThreads), (size_t)kSmem, s, (const bf16*)qkv,
+             (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window);
   return DLI_OK;
 }
 

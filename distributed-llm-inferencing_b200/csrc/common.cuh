@@ -34,6 +34,34 @@ int fail(int code, const char* fmt, ...);
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 int sm_count_cached();
+bool pdl_enabled();  // abi.cu: programmatic dependent launch on/off (dli_set_pdl)
+
+// Every kernel of the library is launched through this helper.  With PDL enabled the
+// launch carries cudaLaunchAttributeProgrammaticStreamSerialization, so the kernel may
+// start while its predecessor in the stream is still draining; each kernel therefore
+// calls pdl_wait() before it touches anything a predecessor may have written.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+#define DLI_LAUNCH(what, ...)                                                        \
+  do {                                                                               \
+    cudaError_t e__ = ::dli::launch_kernel(__VA_ARGS__);                             \
+    if (e__ != cudaSuccess)                                                          \
+      return ::dli::fail(DLI_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e__));    \
+  } while (0)
 
 // ---- device helpers ----------------------------------------------------------
 typedef __nv_bfloat16 bf16;
@@ -42,6 +70,12 @@ typedef __nv_bfloat162 bf162;
 struct __align__(16) bf16x8 {
   bf162 v[4];
 };
+
+// Programmatic dependent launch: block until the preceding kernel of the stream has
+// completed and its writes are visible (no-op when launched without the attribute) ...
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// ... and allow the next kernel of the stream to start launching.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

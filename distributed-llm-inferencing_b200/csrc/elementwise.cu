@@ -10,6 +10,8 @@ embedding_kernel(const int32_t* __restrict__ ids, const int32_t* __restrict__ po
                  const bf16* __restrict__ table, const bf16* __restrict__ pos_table,
                  bf16* __restrict__ out, int d, int vocab) {
   const size_t row = blockIdx.x;
+  pdl_wait();
+  pdl_trigger();
   int id = ids[row];
   id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
   const uint4* src = reinterpret_cast<const uint4*>(table + (size_t)id * d);
@@ -41,6 +43,8 @@ __global__ void __launch_bounds__(kArgmaxThreads)
 argmax_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out, int V) {
   __shared__ float sv[kArgmaxThreads / 32];
   __shared__ int si[kArgmaxThreads / 32];
+  pdl_wait();
+  pdl_trigger();
   const bf16* row = logits + (size_t)blockIdx.x * ld;
   float best = -INFINITY;
   int besti = 0x7fffffff;
@@ -88,6 +92,8 @@ argmax_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out
 __global__ void decode_advance_kernel(const int32_t* __restrict__ tokens, int32_t* __restrict__ token_log,
                                       int32_t* __restrict__ positions, int32_t* __restrict__ seq_lens,
                                       int32_t* __restrict__ step, int B, int log_capacity) {
+  pdl_wait();
+  pdl_trigger();
   const int s = *step;
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
     if (token_log && s < log_capacity) token_log[(size_t)s * B + b] = tokens[b];
@@ -107,9 +113,8 @@ int dli_decode_advance(const int32_t* tokens, int32_t* token_log, int32_t* posit
   using namespace dli;
   DLI_CHECK_ARG(step && (tokens || !token_log), "dli_decode_advance: null pointer");
   DLI_CHECK_ARG(B >= 0 && log_capacity >= 0, "dli_decode_advance: bad sizes B=%d cap=%d", B, log_capacity);
-  decode_advance_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(tokens, token_log, positions, seq_lens,
-                                                                         step, B, log_capacity);
-  DLI_CUDA_LAUNCH_CHECK("dli_decode_advance");
+  DLI_LAUNCH("dli_decode_advance", decode_advance_kernel, dim3(1), dim3(256), (size_t)0, static_cast<cudaStream_t>(stream),
+             tokens, token_log, positions, seq_lens, step, B, log_capacity);
   return DLI_OK;
 }
 
@@ -125,9 +130,8 @@ int dli_embedding_bf16(const int32_t* ids, const int32_t* positions, const void*
   DLI_CHECK_ARG(aligned16(table) && aligned16(pos_table) && aligned16(out),
                 "dli_embedding_bf16: pointers must be 16-byte aligned");
   if (rows == 0) return DLI_OK;
-  embedding_kernel<<<rows, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      ids, positions, (const bf16*)table, (const bf16*)pos_table, (bf16*)out, d, vocab);
-  DLI_CUDA_LAUNCH_CHECK("dli_embedding_bf16");
+  DLI_LAUNCH("dli_embedding_bf16", embedding_kernel, dim3(rows), dim3(128), (size_t)0, static_cast<cudaStream_t>(stream),
+             ids, positions, (const bf16*)table, (const bf16*)pos_table, (bf16*)out, d, vocab);
   return DLI_OK;
 }
 
@@ -136,8 +140,8 @@ int dli_argmax_bf16(const void* logits, int ld, int32_t* out, int B, int V, dli_
   DLI_CHECK_ARG(logits && out, "dli_argmax_bf16: null pointer");
   DLI_CHECK_ARG(B >= 0 && V > 0 && ld >= V, "dli_argmax_bf16: bad sizes B=%d V=%d ld=%d", B, V, ld);
   if (B == 0) return DLI_OK;
-  argmax_kernel<<<B, kArgmaxThreads, 0, static_cast<cudaStream_t>(stream)>>>((const bf16*)logits, ld, out, V);
-  DLI_CUDA_LAUNCH_CHECK("dli_argmax_bf16");
+  DLI_LAUNCH("dli_argmax_bf16", argmax_kernel, dim3(B), dim3(kArgmaxThreads), (size_t)0, static_cast<cudaStream_t>(stream),
+             (const bf16*)logits, ld, out, V);
   return DLI_OK;
 }
 

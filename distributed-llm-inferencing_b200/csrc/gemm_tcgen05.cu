@@ -213,6 +213,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(smem_addr(tmem_ptr_smem), Cfg::kTmemCols);
+  pdl_wait();  // barrier init / TMEM allocation above overlap the previous kernel's tail
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -411,9 +412,8 @@ static int launch_gemm(const void* x, const void* w, const void* bias, const voi
     if ((rc = make_tmap(&tmB, x, M, K, BN)) != DLI_OK) return rc;
     grid = dim3((M + BN - 1) / BN, (N + Cfg::kARows - 1) / Cfg::kARows);
   }
-  gemm_tcgen05_kernel<BN, kSwap, kGated><<<grid, kGemmThreads, Cfg::kSmemBytes, s>>>(
-      tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue);
-  DLI_CUDA_LAUNCH_CHECK("gemm_tcgen05_kernel");
+  DLI_LAUNCH("gemm_tcgen05_kernel", gemm_tcgen05_kernel<BN, kSwap, kGated>, grid, dim3(kGemmThreads),
+             (size_t)Cfg::kSmemBytes, s, tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue);
   return DLI_OK;
 }
 

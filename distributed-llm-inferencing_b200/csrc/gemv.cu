@@ -1,6 +1,9 @@
 // Weight-streaming GEMV for decode (M <= 4 rows of x per pass), CUDA cores.
 //
-// y[m, n] = epi( sum_k x[m,k] * w[n,k] ),  w in the HF Linear layout [N, K].
+// y[m, n] = epi( sum_k xn[m,k] * w[n,k] ),  w in the HF Linear layout [N, K],
+// xn = x, or (kNorm) xn = ln_w * bf16(x * rsqrt(mean(x^2) + eps)): the RMSNorm of
+// the residual stream computed in the kernel prologue with HF's rounding points,
+// so the decode step needs no separate norm kernel.
 //
 // HBM-bound by design: every weight byte is read exactly once per pass with
 // 128-bit streaming loads (ld.global.nc.L1::no_allocate); algorithmic bytes per
@@ -10,6 +13,10 @@
 // then partial sums are combined through shared memory (one warp per output).
 // Tasks (row groups) are dealt round-robin to a grid sized as a multiple of the
 // SM count, so every SM streams the same number of bytes.
+//
+// Programmatic dependent launch: the weights do not depend on the previous
+// kernel, so a CTA issues the loads of its first weight chunk BEFORE it waits for
+// the previous kernel (pdl_wait); HBM keeps streaming across kernel boundaries.
 #include "common.cuh"
 
 namespace dli {
@@ -24,24 +31,24 @@ __device__ __forceinline__ size_t gated_row(int n, int is_up) {
   return (size_t)(n >> 7) * 256 + (n & 127) + (is_up ? 128 : 0);
 }
 
-template <int M, bool kGated>
-__global__ void __launch_bounds__(kGemvThreads)
-gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
-            const bf16* __restrict__ bias, const bf16* residual, bf16* y, int N, int K,
-            int epilogue, int ntasks) {
+template <int M, bool kGated, bool kNorm>
+__global__ void __launch_bounds__(kGemvThreads, M <= 2 ? 3 : 2)
+gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* __restrict__ bias,
+            const bf16* residual, bf16* y, int N, int K, int epilogue, int ntasks,
+            const bf16* __restrict__ ln_w, float eps) {
   // partial sums: [parity][value][thread]; value = row * M + m
   __shared__ float part[2][kGemvRows * M][kGemvThreads];
+  __shared__ float red[kGemvWarps][M];
+  extern __shared__ __align__(16) uint8_t xnorm_raw[];  // kNorm: normalised x, [M][K] bf16
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int kvec = K >> 3;
   const int iters = (kvec + kGemvThreads - 1) / kGemvThreads;
   // gated: a task is 2 output columns (2 gate rows + their 2 up rows)
   constexpr int kOutPerTask = kGated ? kGemvRows / 2 : kGemvRows;
-  const uint4* xv = reinterpret_cast<const uint4*>(x);
+  const uint4 zero = make_uint4(0, 0, 0, 0);
 
-  int parity = 0;
-  for (int task = blockIdx.x; task < ntasks; task += gridDim.x, parity ^= 1) {
+  auto row_ptrs = [&](int task, const uint4* (&wrow)[kGemvRows]) {
     const int n0 = task * kOutPerTask;
-    const uint4* wrow[kGemvRows];
 #pragma unroll
     for (int r = 0; r < kGemvRows; ++r) {
       size_t row;
@@ -53,6 +60,73 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
       }
       wrow[r] = reinterpret_cast<const uint4*>(w + row * (size_t)K);
     }
+  };
+
+  // ---- first weight chunk in flight before waiting for the previous kernel -----------------
+  const uint4* wrow[kGemvRows];
+  uint4 pre0[kGemvRows];
+  const bool has_task = (int)blockIdx.x < ntasks;
+  if (has_task) {
+    row_ptrs(blockIdx.x, wrow);
+#pragma unroll
+    for (int r = 0; r < kGemvRows; ++r) pre0[r] = tid < kvec ? ld_stream_16B(wrow[r] + tid) : zero;
+  }
+  pdl_wait();
+  pdl_trigger();  // the grid is resident at once (grid <= SMs x occupancy): successors may queue behind us
+
+  const uint4* xv = reinterpret_cast<const uint4*>(x);
+  if (kNorm) {
+    // RMSNorm prologue (TF:models/llama/modeling_llama.py:62-67): fp32 mean of squares over
+    // the row, hn = bf16(x * rstd), xn = bf16(ln_w * hn); result parked in shared memory.
+    float ss[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) ss[m] = 0.f;
+    for (int i = tid; i < kvec; i += kGemvThreads) {
+#pragma unroll
+      for (int m = 0; m < M; ++m) {
+        float f[8];
+        unpack8(ld_16B(xv + (size_t)m * kvec + i), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss[m] += f[e] * f[e];
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      ss[m] = warp_sum(ss[m]);
+      if (lane == 0) red[warp][m] = ss[m];
+    }
+    __syncthreads();
+    float rstd[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      float t = 0.f;
+#pragma unroll
+      for (int ww = 0; ww < kGemvWarps; ++ww) t += red[ww][m];
+      rstd[m] = rsqrtf(t / (float)K + eps);
+    }
+    uint4* xs = reinterpret_cast<uint4*>(xnorm_raw);
+    const uint4* lw = reinterpret_cast<const uint4*>(ln_w);
+    for (int i = tid; i < kvec; i += kGemvThreads) {
+      float g[8];
+      unpack8(ld_16B(lw + i), g);
+#pragma unroll
+      for (int m = 0; m < M; ++m) {
+        float f[8];
+        unpack8(ld_16B(xv + (size_t)m * kvec + i), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = g[e] * round_bf16(f[e] * rstd[m]);
+        xs[(size_t)m * kvec + i] = pack8(f);
+      }
+    }
+    __syncthreads();
+    xv = xs;  // generic pointer into shared memory
+  }
+
+  int parity = 0;
+  bool first = true;
+  for (int task = blockIdx.x; task < ntasks; task += gridDim.x, parity ^= 1) {
+    const int n0 = task * kOutPerTask;
+    if (!first) row_ptrs(task, wrow);
     float acc[kGemvRows][M];
 #pragma unroll
     for (int r = 0; r < kGemvRows; ++r)
@@ -63,11 +137,11 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
       const int i0 = tid + j * kGemvThreads, i1 = i0 + kGemvThreads;
       const bool p0 = i0 < kvec, p1 = i1 < kvec;
       uint4 wv0[kGemvRows], wv1[kGemvRows];
-      const uint4 zero = make_uint4(0, 0, 0, 0);
+      const bool use_pre = first && j == 0;
 #pragma unroll
       for (int r = 0; r < kGemvRows; ++r) {
-        wv0[r] = p0 ? ld_stream_16B(wrow[r] + i0) : zero;
         wv1[r] = p1 ? ld_stream_16B(wrow[r] + i1) : zero;
+        wv0[r] = use_pre ? pre0[r] : (p0 ? ld_stream_16B(wrow[r] + i0) : zero);
       }
       uint4 xa[M], xb[M];
 #pragma unroll
@@ -91,6 +165,7 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
         }
       }
     }
+    first = false;
 
 #pragma unroll
     for (int r = 0; r < kGemvRows; ++r)
@@ -128,29 +203,35 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
   }
 }
 
-template <int M, bool kGated>
-static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf16* residual,
-                       bf16* y, int N, int K, int epilogue, cudaStream_t s) {
+template <int M, bool kGated, bool kNorm>
+static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf16* residual, bf16* y, int N, int K,
+                       int epilogue, const bf16* ln_w, float eps, cudaStream_t s) {
   constexpr int kOutPerTask = kGated ? kGemvRows / 2 : kGemvRows;
   const int ntasks = (N + kOutPerTask - 1) / kOutPerTask;
   const int sms = sm_count_cached();
   if (sms <= 0) return fail(DLI_ERR_CUDA, "gemv: no CUDA device");
+  const size_t dyn = kNorm ? (size_t)M * K * 2 : 0;
   static int occ = 0;  // resident CTAs per SM for this instantiation
-  if (occ == 0) {
+  static size_t occ_dyn = 0;
+  if (occ == 0 || dyn > occ_dyn) {
+    if (dyn > 0) {
+      DLI_CUDA_CALL(cudaFuncSetAttribute(gemv_kernel<M, kGated, kNorm>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(dyn > 98304 ? dyn : 98304)));
+    }
     int o = 0;
-    DLI_CUDA_CALL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, gemv_kernel<M, kGated>,
-                                                                kGemvThreads, 0));
+    DLI_CUDA_CALL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, gemv_kernel<M, kGated, kNorm>, kGemvThreads, dyn));
     occ = o > 0 ? o : 1;
+    occ_dyn = dyn;
   }
   const int grid = ntasks < sms * occ ? ntasks : sms * occ;
-  gemv_kernel<M, kGated><<<grid, kGemvThreads, 0, s>>>(x, w, bias, residual, y, N, K, epilogue, ntasks);
-  DLI_CUDA_LAUNCH_CHECK("gemv_kernel");
+  DLI_LAUNCH("gemv_kernel", gemv_kernel<M, kGated, kNorm>, dim3(grid), dim3(kGemvThreads), dyn, s, x, w, bias, residual,
+             y, N, K, epilogue, ntasks, ln_w, eps);
   return DLI_OK;
 }
 
-template <bool kGated>
-static int gemv_dispatch(const void* x, const void* w, const void* bias, const void* residual,
-                         void* y, int M, int N, int K, int epilogue, dli_stream_t stream) {
+template <bool kGated, bool kNorm>
+static int gemv_dispatch(const void* x, const void* w, const void* bias, const void* residual, void* y, int M, int N,
+                         int K, int epilogue, const void* ln_w, float eps, dli_stream_t stream) {
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // M > 4 is served in passes of <= 4 rows (weights re-streamed once per pass).
   for (int m0 = 0; m0 < M; m0 += 4) {
@@ -158,15 +239,23 @@ static int gemv_dispatch(const void* x, const void* w, const void* bias, const v
     const bf16* xp = (const bf16*)x + (size_t)m0 * K;
     const bf16* rp = residual ? (const bf16*)residual + (size_t)m0 * N : nullptr;
     bf16* yp = (bf16*)y + (size_t)m0 * N;
+    const bf16 *wp = (const bf16*)w, *bp = (const bf16*)bias, *lp = (const bf16*)ln_w;
     int rc;
     switch (mm) {
-      case 1: rc = launch_gemv<1, kGated>(xp, (const bf16*)w, (const bf16*)bias, rp, yp, N, K, epilogue, s); break;
-      case 2: rc = launch_gemv<2, kGated>(xp, (const bf16*)w, (const bf16*)bias, rp, yp, N, K, epilogue, s); break;
-      case 3: rc = launch_gemv<3, kGated>(xp, (const bf16*)w, (const bf16*)bias, rp, yp, N, K, epilogue, s); break;
-      default: rc = launch_gemv<4, kGated>(xp, (const bf16*)w, (const bf16*)bias, rp, yp, N, K, epilogue, s); break;
+      case 1: rc = launch_gemv<1, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s); break;
+      case 2: rc = launch_gemv<2, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s); break;
+      case 3: rc = launch_gemv<3, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s); break;
+      default: rc = launch_gemv<4, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s); break;
     }
     if (rc != DLI_OK) return rc;
   }
+  return DLI_OK;
+}
+
+static int check_gemv(const char* name, const void* x, const void* w, const void* y, int M, int N, int K) {
+  DLI_CHECK_ARG(x && w && y, "%s: null pointer", name);
+  DLI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && K % 8 == 0, "%s: need K %% 8 == 0 (got M=%d N=%d K=%d)", name, M, N, K);
+  DLI_CHECK_ARG(aligned16(x) && aligned16(w), "%s: x and w must be 16-byte aligned", name);
   return DLI_OK;
 }
 
@@ -177,26 +266,46 @@ extern "C" {
 int dli_gemv_bf16(const void* x, const void* w, const void* bias, const void* residual, void* y,
                   int M, int N, int K, int epilogue, dli_stream_t stream) {
   using namespace dli;
-  DLI_CHECK_ARG(x && w && y, "dli_gemv_bf16: null pointer");
-  DLI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && K % 8 == 0,
-                "dli_gemv_bf16: need K %% 8 == 0 (got M=%d N=%d K=%d)", M, N, K);
+  int rc = check_gemv("dli_gemv_bf16", x, w, y, M, N, K);
+  if (rc != DLI_OK) return rc;
   DLI_CHECK_ARG(!(epilogue & DLI_EPI_BIAS) || bias, "dli_gemv_bf16: DLI_EPI_BIAS without bias");
-  DLI_CHECK_ARG(!(epilogue & DLI_EPI_RESIDUAL) || residual,
-                "dli_gemv_bf16: DLI_EPI_RESIDUAL without residual");
-  DLI_CHECK_ARG(aligned16(x) && aligned16(w), "dli_gemv_bf16: x and w must be 16-byte aligned");
+  DLI_CHECK_ARG(!(epilogue & DLI_EPI_RESIDUAL) || residual, "dli_gemv_bf16: DLI_EPI_RESIDUAL without residual");
   if (M == 0) return DLI_OK;
-  return gemv_dispatch<false>(x, w, bias, residual, y, M, N, K, epilogue, stream);
+  return gemv_dispatch<false, false>(x, w, bias, residual, y, M, N, K, epilogue, nullptr, 0.f, stream);
 }
 
 int dli_gemv_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F, int K,
                              dli_stream_t stream) {
   using namespace dli;
-  DLI_CHECK_ARG(x && w_gu && y, "dli_gemv_gated_silu_bf16: null pointer");
-  DLI_CHECK_ARG(M >= 0 && F > 0 && F % 128 == 0 && K > 0 && K % 8 == 0,
-                "dli_gemv_gated_silu_bf16: need F %% 128 == 0, K %% 8 == 0 (got M=%d F=%d K=%d)", M, F, K);
-  DLI_CHECK_ARG(aligned16(x) && aligned16(w_gu), "dli_gemv_gated_silu_bf16: pointers must be 16-byte aligned");
+  int rc = check_gemv("dli_gemv_gated_silu_bf16", x, w_gu, y, M, F, K);
+  if (rc != DLI_OK) return rc;
+  DLI_CHECK_ARG(F % 128 == 0, "dli_gemv_gated_silu_bf16: need F %% 128 == 0 (got F=%d)", F);
   if (M == 0) return DLI_OK;
-  return gemv_dispatch<true>(x, w_gu, nullptr, nullptr, y, M, F, K, 0, stream);
+  return gemv_dispatch<true, false>(x, w_gu, nullptr, nullptr, y, M, F, K, 0, nullptr, 0.f, stream);
+}
+
+int dli_rmsnorm_gemv_bf16(const void* h, const void* ln_w, float eps, const void* w, const void* bias,
+                          const void* residual, void* y, int M, int N, int K, int epilogue, dli_stream_t stream) {
+  using namespace dli;
+  int rc = check_gemv("dli_rmsnorm_gemv_bf16", h, w, y, M, N, K);
+  if (rc != DLI_OK) return rc;
+  DLI_CHECK_ARG(ln_w && aligned16(ln_w), "dli_rmsnorm_gemv_bf16: ln_w must be a 16-byte aligned pointer");
+  DLI_CHECK_ARG(K <= 16384, "dli_rmsnorm_gemv_bf16: K <= 16384 (the normalised rows live in shared memory)");
+  DLI_CHECK_ARG(!(epilogue & DLI_EPI_BIAS) || bias, "dli_rmsnorm_gemv_bf16: DLI_EPI_BIAS without bias");
+  DLI_CHECK_ARG(!(epilogue & DLI_EPI_RESIDUAL) || residual, "dli_rmsnorm_gemv_bf16: DLI_EPI_RESIDUAL without residual");
+  if (M == 0) return DLI_OK;
+  return gemv_dispatch<false, true>(h, w, bias, residual, y, M, N, K, epilogue, ln_w, eps, stream);
+}
+
+int dli_rmsnorm_gemv_gated_silu_bf16(const void* h, const void* ln_w, float eps, const void* w_gu, void* y, int M,
+                                     int F, int K, dli_stream_t stream) {
+  using namespace dli;
+  int rc = check_gemv("dli_rmsnorm_gemv_gated_silu_bf16", h, w_gu, y, M, F, K);
+  if (rc != DLI_OK) return rc;
+  DLI_CHECK_ARG(ln_w && aligned16(ln_w), "dli_rmsnorm_gemv_gated_silu_bf16: ln_w must be a 16-byte aligned pointer");
+  DLI_CHECK_ARG(F % 128 == 0 && K <= 16384, "dli_rmsnorm_gemv_gated_silu_bf16: need F %% 128 == 0, K <= 16384");
+  if (M == 0) return DLI_OK;
+  return gemv_dispatch<true, true>(h, w_gu, nullptr, nullptr, y, M, F, K, 0, ln_w, eps, stream);
 }
 
 }  // extern "C"

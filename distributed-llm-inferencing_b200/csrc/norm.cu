@@ -30,6 +30,8 @@ add_norm_kernel(const bf16* __restrict__ x, const bf16* __restrict__ residual,
                 const bf16* __restrict__ weight, const bf16* __restrict__ bias,
                 bf16* resid_out, bf16* __restrict__ y, int d, float eps) {
   __shared__ float red[kNormThreads / 32];
+  pdl_wait();
+  pdl_trigger();
   const size_t row = blockIdx.x;
   const int nvec = d >> 3;
   const uint4* xr = reinterpret_cast<const uint4*>(x + row * d);
@@ -119,14 +121,11 @@ static int launch_norm(bool ln, const void* x, const void* residual, const void*
   if (rows == 0) return DLI_OK;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (ln)
-    add_norm_kernel<true><<<rows, kNormThreads, 0, s>>>(
-        (const bf16*)x, (const bf16*)residual, (const bf16*)weight, (const bf16*)bias,
-        (bf16*)resid_out, (bf16*)y, d, eps);
+    DLI_LAUNCH(name, add_norm_kernel<true>, dim3(rows), dim3(kNormThreads), (size_t)0, s, (const bf16*)x,
+               (const bf16*)residual, (const bf16*)weight, (const bf16*)bias, (bf16*)resid_out, (bf16*)y, d, eps);
   else
-    add_norm_kernel<false><<<rows, kNormThreads, 0, s>>>(
-        (const bf16*)x, (const bf16*)residual, (const bf16*)weight, nullptr,
-        (bf16*)resid_out, (bf16*)y, d, eps);
-  DLI_CUDA_LAUNCH_CHECK(name);
+    DLI_LAUNCH(name, add_norm_kernel<false>, dim3(rows), dim3(kNormThreads), (size_t)0, s, (const bf16*)x,
+               (const bf16*)residual, (const bf16*)weight, (const bf16*)nullptr, (bf16*)resid_out, (bf16*)y, d, eps);
   return DLI_OK;
 }
 

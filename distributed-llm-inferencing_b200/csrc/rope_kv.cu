@@ -20,6 +20,8 @@ rope_kv_append_kernel(bf16* __restrict__ qkv, const bf16* __restrict__ cos_t,
                       bf16* __restrict__ k_cache, bf16* __restrict__ v_cache, int H, int KV,
                       int hd, int page_shift) {
   const size_t row = blockIdx.x;
+  pdl_wait();
+  pdl_trigger();
   const int pos = positions[row];
   const int seq = seq_ids[row];
   const int page_size = 1 << page_shift;
@@ -91,9 +93,8 @@ extern "C" int dli_rope_kv_append_bf16(void* qkv, const void* cos, const void* s
   if (rows == 0) return DLI_OK;
   int shift = 0;
   while ((1 << shift) < page_size) ++shift;
-  rope_kv_append_kernel<<<rows, kRopeThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      (bf16*)qkv, (const bf16*)cos, (const bf16*)sin, positions, seq_ids, page_table, max_pages,
-      (bf16*)k_cache, (bf16*)v_cache, H, KV, hd, shift);
-  DLI_CUDA_LAUNCH_CHECK("dli_rope_kv_append_bf16");
+  DLI_LAUNCH("dli_rope_kv_append_bf16", rope_kv_append_kernel, dim3(rows), dim3(kRopeThreads), (size_t)0,
+             static_cast<cudaStream_t>(stream), (bf16*)qkv, (const bf16*)cos, (const bf16*)sin, positions, seq_ids,
+             page_table, max_pages, (bf16*)k_cache, (bf16*)v_cache, H, KV, hd, shift);
   return DLI_OK;
 }

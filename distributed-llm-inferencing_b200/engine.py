@@ -13,6 +13,7 @@ arithmetic goes through the C-ABI kernels (ops.py -> include/dli.h).
 from __future__ import annotations
 
 import math
+import os
 import time
 from dataclasses import dataclass
 from typing import Dict, List, Optional
@@ -160,6 +161,8 @@ class ShardEngine:
         self.use_cuda_graph = use_cuda_graph
         torch.cuda.set_device(self.device)
         self.sms = ops.sm_count()
+        # kernels may start (and prefetch weights) while their predecessor drains
+        ops.set_pdl(os.environ.get("DLI_PDL", "1") == "1")
         self.w: Dict[str, torch.Tensor] = {}
         self.layers: List[Dict[str, torch.Tensor]] = []
         self.kv = PagedKVCache(self.n_local, spec.n_kv_heads, spec.head_dim, page_size, max_batch, max_seq_len,
@@ -308,27 +311,35 @@ class ShardEngine:
         s = self.spec
         x, qkv, attn, act = self._x[:rows], self._qkv[:rows], self._attn[:rows], self._act[:rows]
         H, KV, hd = s.n_heads, s.n_kv_heads, s.head_dim
+        decode = prefill_shape is None
+        fuse_norm = decode and rows <= 4 and s.arch == "llama"  # RMSNorm inside the weight-streaming GEMV
         for li, L in enumerate(self.layers):
-            if s.arch == "llama":
+            if fuse_norm:
+                ops.rmsnorm_linear(h, L["ln1"], s.eps, L["wqkv"], out=qkv)
+            elif s.arch == "llama":
                 ops.add_rmsnorm(h, L["ln1"], s.eps, out=x)
                 ops.linear(x, L["wqkv"], out=qkv)
             else:
                 ops.add_layernorm(h, L["ln1"], L["ln1b"], s.eps, out=x)
                 ops.linear(x, L["wqkv"], bias=L["bqkv"], out=qkv)
-            ops.rope_kv_append(qkv, self.cos, self.sin, positions, seq_ids, self.kv.page_table,
-                               self.kv.k[li], self.kv.v[li], H, KV, hd)
-            if prefill_shape is not None:
+            if decode:
+                # RoPE + KV append of the new token + split-KV attention in one kernel; the
+                # kernel indexes page-table rows by batch row, so it gets the slot's rows
+                ops.paged_attn_decode_fused(qkv, self.cos, self.sin, self.kv.k[li], self.kv.v[li], st["page_rows"],
+                                            seq_lens, attn, H, KV, hd, self.scale, num_splits=st["splits"],
+                                            scratch=st["scratch"], window=s.sliding_window)
+            else:
+                ops.rope_kv_append(qkv, self.cos, self.sin, positions, seq_ids, self.kv.page_table,
+                                   self.kv.k[li], self.kv.v[li], H, KV, hd)
                 ops.attn_prefill(qkv, attn, prefill_shape[0], prefill_shape[1], H, KV, hd, self.scale,
                                  window=s.sliding_window)
-            else:
-                # the kernel indexes page-table rows by batch row: pass the slot's rows
-                ops.paged_attn_decode(qkv, qkv.shape[1], self.kv.k[li], self.kv.v[li], st["page_rows"], seq_lens,
-                                      attn, H, KV, hd, self.scale, num_splits=st["splits"], scratch=st["scratch"],
-                                      window=s.sliding_window)
             if s.arch == "llama":
                 ops.linear(attn, L["wo"], residual=h, out=h)
-                ops.add_rmsnorm(h, L["ln2"], s.eps, out=x)
-                ops.linear_gated_silu(x, L["wgu"], out=act)
+                if fuse_norm:
+                    ops.rmsnorm_linear_gated_silu(h, L["ln2"], s.eps, L["wgu"], out=act)
+                else:
+                    ops.add_rmsnorm(h, L["ln2"], s.eps, out=x)
+                    ops.linear_gated_silu(x, L["wgu"], out=act)
                 ops.linear(act, L["wdown"], residual=h, out=h)
             else:
                 ops.linear(attn, L["wo"], bias=L["bo"], residual=h, out=h)
@@ -342,11 +353,14 @@ class ShardEngine:
         s = self.spec
         B = h_last.shape[0]
         xn = self._x[:B]
-        if s.arch == "llama":
-            ops.add_rmsnorm(h_last, self.w["norm"], s.eps, out=xn)
+        if s.arch == "llama" and B <= 4:
+            ops.rmsnorm_linear(h_last, self.w["norm"], s.eps, self.w["head"], out=logits)
         else:
-            ops.add_layernorm(h_last, self.w["norm"], self.w["normb"], s.eps, out=xn)
-        ops.linear(xn, self.w["head"], out=logits)
+            if s.arch == "llama":
+                ops.add_rmsnorm(h_last, self.w["norm"], s.eps, out=xn)
+            else:
+                ops.add_layernorm(h_last, self.w["norm"], self.w["normb"], s.eps, out=xn)
+            ops.linear(xn, self.w["head"], out=logits)
         ops.argmax(logits, out=tokens)
 
     # ------------------------------------------------------------------ prefill

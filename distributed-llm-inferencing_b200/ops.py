@@ -211,3 +211,53 @@ def decode_advance(tokens, token_log, positions, seq_lens, step):
     _lib.check("dli_decode_advance", _lib.load().dli_decode_advance(
         _p(tokens), _p(token_log), _p(positions), _p(seq_lens), _p(step), B, cap, _stream()))
     launch_count += 1
+
+
+def set_pdl(enable: bool) -> bool:
+    """Programmatic dependent launch for all subsequent kernel launches; returns the old setting."""
+    return bool(_lib.load().dli_set_pdl(1 if enable else 0))
+
+
+def paged_attn_decode_fused(qkv, cos, sin, k_cache, v_cache, page_table, seq_lens, out, H, KV, hd, scale,
+                            num_splits=1, scratch=None, window=0):
+    """RoPE + KV append of the new token + split-KV decode attention in one kernel (+ merge)."""
+    global launch_count
+    _req(qkv), _req(cos), _req(sin), _req(k_cache), _req(v_cache), _req(out)
+    _req(page_table, torch.int32), _req(seq_lens, torch.int32)
+    B = seq_lens.numel()
+    page_size = k_cache.shape[2]
+    sbytes = 0 if scratch is None else scratch.numel() * scratch.element_size()
+    _lib.check("dli_paged_attn_decode_fused_bf16", _lib.load().dli_paged_attn_decode_fused_bf16(
+        _p(qkv), qkv.shape[1], _p(cos), _p(sin), _p(k_cache), _p(v_cache), _p(page_table), page_table.shape[1],
+        _p(seq_lens), _p(out), _p(scratch), sbytes, B, H, KV, hd, page_size, num_splits, float(scale), window,
+        _stream()))
+    launch_count += 2 if num_splits > 1 else 1
+    return out
+
+
+def rmsnorm_linear(h, ln_w, eps, w, bias=None, residual=None, out=None, epilogue=EPI_NONE):
+    """epi(rmsnorm(h) * ln_w @ w.T) in one weight-streaming kernel (decode, M <= 4 per pass)."""
+    global launch_count
+    _req(h), _req(ln_w), _req(w), _req(bias), _req(residual), _req(out)
+    M, K = h.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=h.device)
+    epi = epilogue | (EPI_BIAS if bias is not None else 0) | (EPI_RESIDUAL if residual is not None else 0)
+    _lib.check("dli_rmsnorm_gemv_bf16", _lib.load().dli_rmsnorm_gemv_bf16(
+        _p(h), _p(ln_w), float(eps), _p(w), _p(bias), _p(residual), _p(out), M, N, K, epi, _stream()))
+    launch_count += (M + 3) // 4
+    return out
+
+
+def rmsnorm_linear_gated_silu(h, ln_w, eps, w_gu, out=None):
+    global launch_count
+    _req(h), _req(ln_w), _req(w_gu), _req(out)
+    M, K = h.shape
+    F = w_gu.shape[0] // 2
+    if out is None:
+        out = torch.empty(M, F, dtype=torch.bfloat16, device=h.device)
+    _lib.check("dli_rmsnorm_gemv_gated_silu_bf16", _lib.load().dli_rmsnorm_gemv_gated_silu_bf16(
+        _p(h), _p(ln_w), float(eps), _p(w_gu), _p(out), M, F, K, _stream()))
+    launch_count += (M + 3) // 4
+    return out

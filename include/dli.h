@@ -55,6 +55,14 @@ int dli_version(void);
  * split counts); negative error code without a device. */
 int dli_sm_count(void);
 
+/* Programmatic dependent launch for every kernel the library enqueues from now
+ * on (process-wide; returns the previous setting).  When on, a kernel may begin
+ * (and the weight-streaming kernels prefetch their first weight chunk) while its
+ * predecessor in the stream drains; each kernel waits for the predecessor's
+ * results before reading activations, so results do not change.  Off by
+ * default; the host engine turns it on for the decode step. */
+int dli_set_pdl(int enable);
+
 /* ---- embedding ---------------------------------------------------------
  * out[r,:] = table[ids[r],:] (+ pos_table[positions[r],:] when pos_table != NULL)
  * Replaces: TF:models/llama/modeling_llama.py:389 (embed_tokens) and
@@ -119,6 +127,22 @@ int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
                                void* scratch, size_t scratch_bytes, int B, int H,
                                int KV, int hd, int page_size, int num_splits,
                                float scale, int window, dli_stream_t stream);
+
+/* Decode attention fused with RoPE and the KV-cache append of the new token
+ * (replaces dli_rope_kv_append_bf16 + dli_paged_attn_decode_bf16 in a decode
+ * step; same reference lines, same bf16 rounding points, bit-identical result).
+ * qkv: packed rows [B, row_stride] holding q | k | v of the NEW token of each
+ * sequence, NOT yet rotated; the new token's position is seq_lens[b] - 1.
+ * q is rotated on the fly, the new k is rotated and written with v into the
+ * sequence's cache page (k_cache / v_cache are written), then attended with
+ * the rest of the context.  cos == NULL: no rotation (GPT-2). */
+int dli_paged_attn_decode_fused_bf16(void* qkv, int row_stride, const void* cos,
+                                     const void* sin, void* k_cache, void* v_cache,
+                                     const int32_t* page_table, int max_pages,
+                                     const int32_t* seq_lens, void* out, void* scratch,
+                                     size_t scratch_bytes, int B, int H, int KV, int hd,
+                                     int page_size, int num_splits, float scale,
+                                     int window, dli_stream_t stream);
 
 /* Same computation as dli_paged_attn_decode_bf16 for callers that cannot
  * allocate device memory where they call it: a server that handed all of HBM
@@ -192,6 +216,19 @@ int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, in
                              int K, dli_stream_t stream);
 int dli_linear_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M,
                                int F, int K, dli_stream_t stream);
+
+/* RMSNorm fused into the decode projection (M <= 4 rows per pass):
+ *   y = epi( (ln_w * bf16(h * rsqrt(mean(h^2) + eps))) . w^T )
+ * i.e. LlamaRMSNorm (TF:models/llama/modeling_llama.py:62-67) followed by the
+ * q/k/v or gate/up projection (:262-264, :183) in one kernel; the normalised
+ * row is built in shared memory with HF's rounding points, so the result is
+ * bit-identical to dli_add_rmsnorm_bf16 + dli_gemv_bf16.  K <= 16384. */
+int dli_rmsnorm_gemv_bf16(const void* h, const void* ln_w, float eps, const void* w,
+                          const void* bias, const void* residual, void* y, int M, int N,
+                          int K, int epilogue, dli_stream_t stream);
+int dli_rmsnorm_gemv_gated_silu_bf16(const void* h, const void* ln_w, float eps,
+                                     const void* w_gu, void* y, int M, int F, int K,
+                                     dli_stream_t stream);
 
 /* ---- greedy sampling epilogue ----------------------------------------------
  * out[b] = argmax_v logits[b, v]  (lowest index wins ties, like torch.argmax),

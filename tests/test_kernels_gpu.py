@@ -359,3 +359,88 @@ def test_bad_arguments_raise(cuda):
     assert "K % 8" in str(e.value)
     with pytest.raises(ValueError):
         ops.add_rmsnorm(x.cpu(), w[0].cpu(), 1e-5)
+
+
+# ----------------------------------------------------------------------------- fused decode kernels
+@pytest.mark.parametrize("B,H,KV,hd,page,lens,splits,window,rope",
+                         [(1, 32, 8, 128, 16, [2049], 16, 0, True), (3, 32, 4, 64, 32, [1, 64, 300], 4, 0, True),
+                          (2, 64, 8, 128, 16, [513, 1000], 8, 256, True), (2, 12, 12, 64, 16, [40, 97], 2, 0, False)])
+def test_fused_rope_append_attention_is_bit_identical(cuda, B, H, KV, hd, page, lens, splits, window, rope):
+    """dli_paged_attn_decode_fused == dli_rope_kv_append + dli_paged_attn_decode, bit for bit
+    (outputs AND the cache pages it wrote)."""
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(99 + B)
+    page_table, kc, vc = _paged_cache(B, max(lens), KV, hd, page, cuda, gen)
+    qkv = torch.randn(B, (H + 2 * KV) * hd, device=cuda, generator=gen).to(BF)
+    cos, sin = _hf_rope_tables(hd, 500000.0, max(lens) + 1, cuda) if rope else (None, None)
+    seq_lens = torch.tensor(lens, device=cuda, dtype=torch.int32)
+    positions = (seq_lens - 1).contiguous()
+    seq_ids = torch.arange(B, device=cuda, dtype=torch.int32)
+    nbytes = ops.attn_decode_scratch_bytes(B, H, hd, splits)
+    scratch = torch.empty(max(nbytes, 4) // 4, device=cuda, dtype=torch.float32)
+    scale = hd ** -0.5
+    # reference: two kernels
+    qkv_a, kc_a, vc_a = qkv.clone(), kc.clone(), vc.clone()
+    ops.rope_kv_append(qkv_a, cos, sin, positions, seq_ids, page_table, kc_a, vc_a, H, KV, hd)
+    out_a = torch.empty(B, H * hd, device=cuda, dtype=BF)
+    ops.paged_attn_decode(qkv_a, qkv_a.shape[1], kc_a, vc_a, page_table, seq_lens, out_a, H, KV, hd, scale,
+                          num_splits=splits, scratch=scratch, window=window)
+    # fused
+    qkv_b, kc_b, vc_b = qkv.clone(), kc.clone(), vc.clone()
+    out_b = torch.empty_like(out_a)
+    ops.paged_attn_decode_fused(qkv_b, cos, sin, kc_b, vc_b, page_table, seq_lens, out_b, H, KV, hd, scale,
+                                num_splits=splits, scratch=scratch, window=window)
+    assert torch.equal(kc_a, kc_b) and torch.equal(vc_a, vc_b)
+    assert torch.equal(out_a, out_b)
+    assert torch.equal(qkv_b, qkv)  # the fused kernel leaves the qkv row untouched
+
+
+@pytest.mark.parametrize("M", [1, 2, 4])
+@pytest.mark.parametrize("N,K", [(6144, 4096), (2560, 2048), (128256, 4096), (10240, 8192)])
+def test_rmsnorm_gemv_is_bit_identical_to_two_kernels(cuda, M, N, K):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(M + N)
+    h = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    lnw = (1 + 0.1 * torch.randn(K, device=cuda, generator=gen)).to(BF)
+    w = (torch.randn(N, K, device=cuda, generator=gen) * 0.02).to(BF)
+    res = torch.randn(M, N, device=cuda, generator=gen).to(BF)
+    two = ops.gemv(ops.add_rmsnorm(h, lnw, 1e-5), w, residual=res)
+    one = ops.rmsnorm_linear(h, lnw, 1e-5, w, residual=res)
+    assert torch.equal(one, two)
+
+
+@pytest.mark.parametrize("M,F,K", [(1, 14336, 4096), (3, 5632, 2048)])
+def test_rmsnorm_gemv_gated_is_bit_identical_to_two_kernels(cuda, M, F, K):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(F)
+    h = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    lnw = (1 + 0.1 * torch.randn(K, device=cuda, generator=gen)).to(BF)
+    wgu = ops.pack_gate_up((torch.randn(F, K, device=cuda, generator=gen) * 0.03).to(BF),
+                           (torch.randn(F, K, device=cuda, generator=gen) * 0.03).to(BF))
+    two = ops.gemv_gated_silu(ops.add_rmsnorm(h, lnw, 1e-5), wgu)
+    one = ops.rmsnorm_linear_gated_silu(h, lnw, 1e-5, wgu)
+    assert torch.equal(one, two)
+
+
+def test_pdl_does_not_change_results(cuda):
+    """Programmatic dependent launch only overlaps kernel boundaries: same tokens."""
+    from dli_b200 import ops
+
+    from golden_util import load_case, spec_kwargs
+    from dli_b200.engine import ModelSpec, ShardEngine
+    from oracle import decoder_ref as R
+
+    c = load_case("llama_tiny")
+    spec = ModelSpec.from_hf_config(spec_kwargs(c["config"]))
+    sd = R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"])
+    outs = []
+    for on in (False, True, False):
+        eng = ShardEngine(spec, max_batch=2, max_seq_len=128)
+        ops.set_pdl(on)
+        eng.load_state_dict(sd)
+        outs.append(eng.generate(c["prompts"], c["prompts"].shape[1] + 20))
+    ops.set_pdl(True)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
