@@ -38,7 +38,8 @@ SIGNATURES = {
     ),
     "dli_paged_attn_decode_fused_bf16": (
         _i,
-        [_vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i, _vp],
+        [_vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i,
+         _vp, _sz, _vp, _sz, _vp],
     ),
     "dli_set_pdl": (_i, [_i]),
     "dli_rmsnorm_gemv_bf16": (_i, [_vp, _vp, _f, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),

@@ -1,6 +1,10 @@
 // Library-level entry points: error reporting, version, device query.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
+
+#include <mutex>
+#include <unordered_set>
 
 #include "common.cuh"
 
@@ -24,6 +28,8 @@ int fail(int code, const char* fmt, ...) {
   va_end(ap);
   return code;
 }
+
+void prepare_kernel(const void*) {}  // hook for one-time per-kernel attributes (none needed today)
 
 static bool g_pdl = false;
 bool pdl_enabled() { return g_pdl; }

@@ -27,15 +27,31 @@ namespace dli {
 constexpr int kAttnThreads = 128;
 constexpr int kAttnTile = 64;
 
-template <int HD>
+// cp.async.bulk.prefetch.L2: one instruction moves a whole piece from HBM into L2.
+__device__ __forceinline__ void l2_prefetch_slice(const uint8_t* ptr, size_t bytes, size_t part, size_t nparts) {
+  constexpr size_t kPiece = 4096;
+  if (ptr == nullptr || bytes == 0) return;
+  const size_t per = ((bytes + nparts - 1) / nparts + kPiece - 1) / kPiece * kPiece;
+  const size_t begin = part * per;
+  const size_t end = begin + per < bytes ? begin + per : bytes;
+  for (size_t off = begin + (size_t)threadIdx.x * kPiece; off < end; off += (size_t)blockDim.x * kPiece) {
+    const uint32_t n = (uint32_t)((end - off < kPiece ? end - off : kPiece) & ~(size_t)15);
+    if (n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr + off), "r"(n) : "memory");
+  }
+}
+
+template <int HD, int NS>
 struct DecodeSmem {
   static constexpr int kRowBytes = HD * 2;
   static constexpr int kQBytes = 16 * kRowBytes;
   static constexpr int kTileBytes = kAttnTile * kRowBytes;
-  static constexpr int kTotal = kQBytes + 4 * kTileBytes;  // Q + 2 stages x (K, V)
+  static constexpr int kTotal = kQBytes + 2 * NS * kTileBytes;  // Q + NS stages x (K, V)
 };
 
-template <int HD>
+// NS = cp.async stages.  NS = 2 keeps 3 CTAs per SM for large batches; NS = 4 puts a whole
+// 256-token split in flight at once, which is what a batch-1 step (latency-bound, one CTA
+// per SM at most) needs.
+template <int HD, int NS>
 __global__ void __launch_bounds__(kAttnThreads)
 paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
                          const bf16* __restrict__ k_cache, const bf16* __restrict__ v_cache,
@@ -44,18 +60,27 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
                          float* __restrict__ part_o, float* __restrict__ part_ml, int H, int KV,
                          int page_shift, int num_splits, float scale_log2, int window,
                          int fused, const bf16* __restrict__ cos_t, const bf16* __restrict__ sin_t,
-                         bf16* k_cache_w, bf16* v_cache_w, int pdl_early) {
-  using L = DecodeSmem<HD>;
+                         bf16* k_cache_w, bf16* v_cache_w, int pdl_early, const uint8_t* __restrict__ pf_ptr,
+                         size_t pf_bytes) {
+  using L = DecodeSmem<HD, NS>;
   constexpr int RB = L::kRowBytes;
   constexpr int CH = HD / 8;  // 16-byte chunks per row
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t sQ = smem_u32(smem);
   const uint32_t sK = sQ + L::kQBytes;
-  const uint32_t sV = sK + 2 * L::kTileBytes;
+  const uint32_t sV = sK + NS * L::kTileBytes;
 
   const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int G = H / KV;
+  if (split >= num_splits) {
+    // Prefetch role (extra CTAs on SMs the attention grid leaves idle): pull the weights of
+    // the NEXT projection into L2 while this latency-bound kernel runs, so HBM keeps
+    // streaming.  Weights are constants: no dependency wait needed.
+    l2_prefetch_slice(pf_ptr, pf_bytes, ((size_t)b * KV + kvh) * (gridDim.x - num_splits) + (split - num_splits),
+                      (size_t)(gridDim.x - num_splits) * KV * gridDim.z);
+    return;
+  }
   pdl_wait();  // seq_lens, q and the cache pages come from earlier kernels of the stream
   if (pdl_early) pdl_trigger();
   const int seq_len = seq_lens[b];
@@ -101,18 +126,16 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
   for (int i = 0; i < HD / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
   uint32_t qf[HD / 16][4];
 
-  if (t_begin < t_end) load_tile(t_begin, 0);
-  cp_async_commit();
+  // one commit group per stage (empty groups keep the count uniform)
+#pragma unroll
+  for (int st = 0; st < NS; ++st) {
+    if (t_begin + st < t_end) load_tile(t_begin + st, st);
+    cp_async_commit();
+  }
 
   for (int tile = t_begin; tile < t_end; ++tile) {
-    const int stage = (tile - t_begin) & 1;
-    if (tile + 1 < t_end) {
-      load_tile(tile + 1, stage ^ 1);
-      cp_async_commit();
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
+    const int stage = (tile - t_begin) % NS;
+    cp_async_wait<NS - 1>();  // all but the newest NS-1 groups have landed: this tile is in
     __syncthreads();
     const uint32_t cK = sK + stage * L::kTileBytes, cV = sV + stage * L::kTileBytes;
     if (fused && tile == tile_hi - 1) {
@@ -221,7 +244,9 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
       mma_16816(o[2 * jp], pa, vf[0], vf[1]);
       mma_16816(o[2 * jp + 1], pa, vf[2], vf[3]);
     }
-    __syncthreads();  // stage may be refilled by the next iteration's prefetch
+    __syncthreads();  // every warp is done with this stage: refill it
+    if (tile + NS < t_end) load_tile(tile + NS, stage);
+    cp_async_commit();
   }
   cp_async_wait<0>();
   __syncthreads();
@@ -233,7 +258,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
   }
   float* red_o = reinterpret_cast<float*>(smem + L::kQBytes);                        // [4][16][HD]
-  float* red_ml = reinterpret_cast<float*>(smem + L::kQBytes + 2 * L::kTileBytes);   // [4][16][2]
+  float* red_ml = reinterpret_cast<float*>(smem + L::kQBytes + NS * L::kTileBytes);  // [4][16][2]
   {
     const int g = lane >> 2, t = lane & 3;
 #pragma unroll
@@ -285,8 +310,13 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
 template <int HD>
 __global__ void __launch_bounds__(kAttnThreads)
 attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
-                        bf16* __restrict__ out, int n_bh, int num_splits, float scale_log2) {
+                        bf16* __restrict__ out, int n_bh, int num_splits, float scale_log2, int merge_ctas,
+                        const uint8_t* __restrict__ pf_ptr, size_t pf_bytes) {
   constexpr int VEC = HD / 32;
+  if ((int)blockIdx.x >= merge_ctas) {  // prefetch role, see paged_attn_decode_kernel
+    l2_prefetch_slice(pf_ptr, pf_bytes, blockIdx.x - merge_ctas, gridDim.x - merge_ctas);
+    return;
+  }
   const int bh = blockIdx.x * (kAttnThreads / 32) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   pdl_wait();
@@ -329,42 +359,60 @@ attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restric
     *reinterpret_cast<uint32_t*>(o + i) = pack_bf16(acc[i] * inv, acc[i + 1] * inv);
 }
 
-template <int HD>
-static int launch_decode(const void* q, int q_stride, const void* k_cache, const void* v_cache,
-                         const int32_t* page_table, int max_pages, const int32_t* seq_lens,
-                         void* out, void* scratch, int B, int H, int KV, int page_shift,
-                         int num_splits, float scale, int window, cudaStream_t s, int fused = 0,
-                         const void* cos_t = nullptr, const void* sin_t = nullptr) {
-  using L = DecodeSmem<HD>;
+template <int HD, int NS>
+static int launch_decode_ns(const void* q, int q_stride, const void* k_cache, const void* v_cache,
+                            const int32_t* page_table, int max_pages, const int32_t* seq_lens, void* out,
+                            void* scratch, int B, int H, int KV, int page_shift, int num_splits, float scale,
+                            int window, cudaStream_t s, int fused, const void* cos_t, const void* sin_t,
+                            const void* pf_a, size_t pf_a_bytes, const void* pf_b, size_t pf_b_bytes) {
+  using L = DecodeSmem<HD, NS>;
   static bool attr_set = false;
-  static int occ = 1;
   if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(paged_attn_decode_kernel<HD>,
+    DLI_CUDA_CALL(cudaFuncSetAttribute(paged_attn_decode_kernel<HD, NS>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
-    int o = 0;
-    DLI_CUDA_CALL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, paged_attn_decode_kernel<HD>, kAttnThreads,
-                                                                L::kTotal));
-    occ = o > 0 ? o : 1;
     attr_set = true;
   }
   const float scale_log2 = scale * 1.4426950408889634f;
   float* part_o = reinterpret_cast<float*>(scratch);
   float* part_ml = part_o ? part_o + (size_t)B * H * num_splits * HD : nullptr;
-  dim3 grid(num_splits, KV, B);
-  // dependents may be released early only when every CTA of this grid is resident at once
-  const int pdl_early = (size_t)num_splits * KV * B <= (size_t)sm_count_cached() * occ ? 1 : 0;
-  DLI_LAUNCH("paged_attn_decode_kernel", paged_attn_decode_kernel<HD>, grid, dim3(kAttnThreads), (size_t)L::kTotal, s,
-             (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table, max_pages, seq_lens,
-             (bf16*)out, part_o, part_ml, H, KV, page_shift, num_splits, scale_log2, window, fused,
-             (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, pdl_early);
+  // prefetch CTAs only when the attention grid leaves SMs idle
+  const int sms = sm_count_cached();
+  const int attn_ctas = num_splits * KV * B;
+  int extra = 0;
+  if (pf_a && pf_a_bytes && attn_ctas < sms) extra = (sms - attn_ctas) / (KV * B);
+  dim3 grid(num_splits + extra, KV, B);
+  DLI_LAUNCH("paged_attn_decode_kernel", paged_attn_decode_kernel<HD, NS>, grid, dim3(kAttnThreads),
+             (size_t)L::kTotal, s, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table,
+             max_pages, seq_lens, (bf16*)out, part_o, part_ml, H, KV, page_shift, num_splits, scale_log2, window,
+             fused, (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, 1,
+             (const uint8_t*)(extra ? pf_a : nullptr), extra ? pf_a_bytes : (size_t)0);
   if (num_splits > 1) {
     const int n_bh = B * H;
     const int per_cta = kAttnThreads / 32;
-    DLI_LAUNCH("attn_split_merge_kernel", attn_split_merge_kernel<HD>, dim3((n_bh + per_cta - 1) / per_cta),
-               dim3(kAttnThreads), (size_t)0, s, (const float*)part_o, (const float*)part_ml, (bf16*)out, n_bh,
-               num_splits, scale_log2);
+    const int merge_ctas = (n_bh + per_cta - 1) / per_cta;
+    const int pf_ctas = (pf_b && pf_b_bytes && merge_ctas < sms) ? sms - merge_ctas : 0;
+    DLI_LAUNCH("attn_split_merge_kernel", attn_split_merge_kernel<HD>, dim3(merge_ctas + pf_ctas), dim3(kAttnThreads),
+               (size_t)0, s, (const float*)part_o, (const float*)part_ml, (bf16*)out, n_bh, num_splits, scale_log2,
+               merge_ctas, (const uint8_t*)(pf_ctas ? pf_b : nullptr), pf_ctas ? pf_b_bytes : (size_t)0);
   }
   return DLI_OK;
+}
+
+template <int HD>
+static int launch_decode(const void* q, int q_stride, const void* k_cache, const void* v_cache,
+                         const int32_t* page_table, int max_pages, const int32_t* seq_lens,
+                         void* out, void* scratch, int B, int H, int KV, int page_shift,
+                         int num_splits, float scale, int window, cudaStream_t s, int fused = 0,
+                         const void* cos_t = nullptr, const void* sin_t = nullptr, const void* pf_a = nullptr,
+                         size_t pf_a_bytes = 0, const void* pf_b = nullptr, size_t pf_b_bytes = 0) {
+  // few CTAs (batch-1 style): one CTA per SM with a deep load pipeline; many CTAs: occupancy
+  if ((size_t)num_splits * KV * B <= (size_t)sm_count_cached())
+    return launch_decode_ns<HD, 4>(q, q_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B,
+                                   H, KV, page_shift, num_splits, scale, window, s, fused, cos_t, sin_t, pf_a,
+                                   pf_a_bytes, pf_b, pf_b_bytes);
+  return launch_decode_ns<HD, 2>(q, q_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B, H,
+                                 KV, page_shift, num_splits, scale, window, s, fused, cos_t, sin_t, pf_a, pf_a_bytes,
+                                 pf_b, pf_b_bytes);
 }
 
 }  // namespace dli
@@ -417,10 +465,14 @@ extern "C" int dli_paged_attn_decode_fused_bf16(void* qkv, int row_stride, const
                                                 void* k_cache, void* v_cache, const int32_t* page_table,
                                                 int max_pages, const int32_t* seq_lens, void* out, void* scratch,
                                                 size_t scratch_bytes, int B, int H, int KV, int hd, int page_size,
-                                                int num_splits, float scale, int window, dli_stream_t stream) {
+                                                int num_splits, float scale, int window, const void* l2_prefetch_a,
+                                                size_t l2_prefetch_a_bytes, const void* l2_prefetch_b,
+                                                size_t l2_prefetch_b_bytes, dli_stream_t stream) {
   using namespace dli;
   DLI_CHECK_ARG(qkv && k_cache && v_cache && page_table && seq_lens && out,
                 "dli_paged_attn_decode_fused_bf16: null pointer");
+  DLI_CHECK_ARG(aligned16(l2_prefetch_a) && aligned16(l2_prefetch_b),
+                "dli_paged_attn_decode_fused_bf16: prefetch ranges must be 16-byte aligned");
   DLI_CHECK_ARG((cos == nullptr) == (sin == nullptr), "dli_paged_attn_decode_fused_bf16: cos and sin go together");
   DLI_CHECK_ARG(hd == 64 || hd == 128, "dli_paged_attn_decode_fused_bf16: hd must be 64 or 128 (got %d)", hd);
   DLI_CHECK_ARG(B >= 0 && H > 0 && KV > 0 && H % KV == 0 && H / KV <= 16,
@@ -445,9 +497,11 @@ extern "C" int dli_paged_attn_decode_fused_bf16(void* qkv, int row_stride, const
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (hd == 128)
     return launch_decode<128>(qkv, row_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B,
-                              H, KV, shift, num_splits, scale, window, s, 1, cos, sin);
+                              H, KV, shift, num_splits, scale, window, s, 1, cos, sin, l2_prefetch_a,
+                              l2_prefetch_a_bytes, l2_prefetch_b, l2_prefetch_b_bytes);
   return launch_decode<64>(qkv, row_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B, H,
-                           KV, shift, num_splits, scale, window, s, 1, cos, sin);
+                           KV, shift, num_splits, scale, window, s, 1, cos, sin, l2_prefetch_a, l2_prefetch_a_bytes,
+                           l2_prefetch_b, l2_prefetch_b_bytes);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -40,9 +40,12 @@ bool pdl_enabled();  // abi.cu: programmatic dependent launch on/off (dli_set_pd
 // launch carries cudaLaunchAttributeProgrammaticStreamSerialization, so the kernel may
 // start while its predecessor in the stream is still draining; each kernel therefore
 // calls pdl_wait() before it touches anything a predecessor may have written.
+void prepare_kernel(const void* fn);  // abi.cu: one-time per-kernel attributes
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                                  Args... args) {
+  prepare_kernel(reinterpret_cast<const void*>(kernel));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;

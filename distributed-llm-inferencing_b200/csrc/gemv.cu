@@ -14,9 +14,11 @@
 // Tasks (row groups) are dealt round-robin to a grid sized as a multiple of the
 // SM count, so every SM streams the same number of bytes.
 //
-// Programmatic dependent launch: the weights do not depend on the previous
-// kernel, so a CTA issues the loads of its first weight chunk BEFORE it waits for
-// the previous kernel (pdl_wait); HBM keeps streaming across kernel boundaries.
+// Programmatic dependent launch: a CTA of the next kernel may move in while this
+// kernel drains; it waits (pdl_wait) before reading activations.  Prefetching the
+// first task's weights ahead of that wait (registers, or cp.async into shared
+// memory) was measured and gave nothing: the shared-memory variant costs L1
+// capacity that the streaming loads need (profiles/r1_notes.md).
 #include "common.cuh"
 
 namespace dli {
@@ -62,15 +64,7 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
     }
   };
 
-  // ---- first weight chunk in flight before waiting for the previous kernel -----------------
   const uint4* wrow[kGemvRows];
-  uint4 pre0[kGemvRows];
-  const bool has_task = (int)blockIdx.x < ntasks;
-  if (has_task) {
-    row_ptrs(blockIdx.x, wrow);
-#pragma unroll
-    for (int r = 0; r < kGemvRows; ++r) pre0[r] = tid < kvec ? ld_stream_16B(wrow[r] + tid) : zero;
-  }
   pdl_wait();
   pdl_trigger();  // the grid is resident at once (grid <= SMs x occupancy): successors may queue behind us
 
@@ -123,10 +117,9 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
   }
 
   int parity = 0;
-  bool first = true;
   for (int task = blockIdx.x; task < ntasks; task += gridDim.x, parity ^= 1) {
     const int n0 = task * kOutPerTask;
-    if (!first) row_ptrs(task, wrow);
+    row_ptrs(task, wrow);
     float acc[kGemvRows][M];
 #pragma unroll
     for (int r = 0; r < kGemvRows; ++r)
@@ -137,11 +130,10 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
       const int i0 = tid + j * kGemvThreads, i1 = i0 + kGemvThreads;
       const bool p0 = i0 < kvec, p1 = i1 < kvec;
       uint4 wv0[kGemvRows], wv1[kGemvRows];
-      const bool use_pre = first && j == 0;
 #pragma unroll
       for (int r = 0; r < kGemvRows; ++r) {
+        wv0[r] = p0 ? ld_stream_16B(wrow[r] + i0) : zero;
         wv1[r] = p1 ? ld_stream_16B(wrow[r] + i1) : zero;
-        wv0[r] = use_pre ? pre0[r] : (p0 ? ld_stream_16B(wrow[r] + i0) : zero);
       }
       uint4 xa[M], xb[M];
 #pragma unroll
@@ -165,7 +157,6 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
         }
       }
     }
-    first = false;
 
 #pragma unroll
     for (int r = 0; r < kGemvRows; ++r)
@@ -210,14 +201,13 @@ static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf1
   const int ntasks = (N + kOutPerTask - 1) / kOutPerTask;
   const int sms = sm_count_cached();
   if (sms <= 0) return fail(DLI_ERR_CUDA, "gemv: no CUDA device");
+  // vectors per row prefetched across the kernel boundary: the whole row, or 512 (8 KB)
   const size_t dyn = kNorm ? (size_t)M * K * 2 : 0;
   static int occ = 0;  // resident CTAs per SM for this instantiation
   static size_t occ_dyn = 0;
   if (occ == 0 || dyn > occ_dyn) {
-    if (dyn > 0) {
-      DLI_CUDA_CALL(cudaFuncSetAttribute(gemv_kernel<M, kGated, kNorm>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)(dyn > 98304 ? dyn : 98304)));
-    }
+    DLI_CUDA_CALL(cudaFuncSetAttribute(gemv_kernel<M, kGated, kNorm>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)(dyn > 131072 ? dyn : 131072)));
     int o = 0;
     DLI_CUDA_CALL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, gemv_kernel<M, kGated, kNorm>, kGemvThreads, dyn));
     occ = o > 0 ? o : 1;

@@ -161,6 +161,7 @@ class ShardEngine:
         self.use_cuda_graph = use_cuda_graph
         torch.cuda.set_device(self.device)
         self.sms = ops.sm_count()
+        self.l2_prefetch = os.environ.get("DLI_L2_PREFETCH", "1") == "1"
         # kernels may start (and prefetch weights) while their predecessor drains
         ops.set_pdl(os.environ.get("DLI_PDL", "1") == "1")
         self.w: Dict[str, torch.Tensor] = {}
@@ -230,7 +231,7 @@ class ShardEngine:
                 self.w["norm"] = t("transformer.ln_f.weight")
                 self.w["normb"] = t("transformer.ln_f.bias")
                 self.w["head"] = self.w["embed"] if self.is_first else t("transformer.wte.weight")
-        self._graphs.clear()
+        self._finalize_layers()
 
     def load_random(self, seed: int = 0, std: float = 0.02) -> None:
         """Random-init weights generated directly on the device (synthetic
@@ -262,6 +263,15 @@ class ShardEngine:
         if self.is_last:
             self.w["norm"] = n(d, mean=1.0)
             self.w["head"] = self.w["embed"] if (s.tie_embeddings and self.is_first) else n(s.vocab, d)
+        self._finalize_layers()
+
+    def _finalize_layers(self) -> None:
+        """Views used as L2-prefetch ranges: the first ~24 MB of the gate/up matrix is pulled
+        into L2 while the (latency-bound) split merge of the attention runs."""
+        for L in self.layers:
+            if "wgu" in L:
+                rows = min(L["wgu"].shape[0], (24 << 20) // (2 * L["wgu"].shape[1]))
+                L["wgu_head"] = L["wgu"][:rows]
         self._graphs.clear()
 
     def weight_bytes(self) -> int:
@@ -301,9 +311,14 @@ class ShardEngine:
         self._graphs.clear()  # captured graphs hold the old workspace pointers
 
     def _num_splits(self, B: int) -> int:
+        """KV splits per (sequence, kv head).  Enough CTAs to cover the SMs once, but no
+        finer than 4 tiles (256 tokens) per split: a split's tiles are all in flight at
+        once (4-stage cp.async) and the merge cost grows with the split count."""
+        if os.environ.get("DLI_ATTN_SPLITS"):
+            return int(os.environ["DLI_ATTN_SPLITS"])
         tiles = (self.max_seq_len + 63) // 64
-        want = max(1, (2 * self.sms + B * self.spec.n_kv_heads - 1) // (B * self.spec.n_kv_heads))
-        return max(1, min(tiles, want, 64))
+        want = max(1, self.sms // (B * self.spec.n_kv_heads))
+        return max(1, min((tiles + 3) // 4, want, 64))
 
     # ------------------------------------------------------------------ one layer range
     def _layers_forward(self, h, rows, positions, seq_ids, seq_lens, prefill_shape, st):
@@ -327,7 +342,10 @@ class ShardEngine:
                 # kernel indexes page-table rows by batch row, so it gets the slot's rows
                 ops.paged_attn_decode_fused(qkv, self.cos, self.sin, self.kv.k[li], self.kv.v[li], st["page_rows"],
                                             seq_lens, attn, H, KV, hd, self.scale, num_splits=st["splits"],
-                                            scratch=st["scratch"], window=s.sliding_window)
+                                            scratch=st["scratch"], window=s.sliding_window,
+                                            # spare SMs pull the next projections' weights into L2 meanwhile
+                                            prefetch_a=L["wo"] if self.l2_prefetch else None,
+                                            prefetch_b=L.get("wgu_head") if self.l2_prefetch else None)
             else:
                 ops.rope_kv_append(qkv, self.cos, self.sin, positions, seq_ids, self.kv.page_table,
                                    self.kv.k[li], self.kv.v[li], H, KV, hd)

@@ -218,8 +218,12 @@ def set_pdl(enable: bool) -> bool:
     return bool(_lib.load().dli_set_pdl(1 if enable else 0))
 
 
+def _bytes(t):
+    return 0 if t is None else t.numel() * t.element_size()
+
+
 def paged_attn_decode_fused(qkv, cos, sin, k_cache, v_cache, page_table, seq_lens, out, H, KV, hd, scale,
-                            num_splits=1, scratch=None, window=0):
+                            num_splits=1, scratch=None, window=0, prefetch_a=None, prefetch_b=None):
     """RoPE + KV append of the new token + split-KV decode attention in one kernel (+ merge)."""
     global launch_count
     _req(qkv), _req(cos), _req(sin), _req(k_cache), _req(v_cache), _req(out)
@@ -230,7 +234,7 @@ def paged_attn_decode_fused(qkv, cos, sin, k_cache, v_cache, page_table, seq_len
     _lib.check("dli_paged_attn_decode_fused_bf16", _lib.load().dli_paged_attn_decode_fused_bf16(
         _p(qkv), qkv.shape[1], _p(cos), _p(sin), _p(k_cache), _p(v_cache), _p(page_table), page_table.shape[1],
         _p(seq_lens), _p(out), _p(scratch), sbytes, B, H, KV, hd, page_size, num_splits, float(scale), window,
-        _stream()))
+        _p(prefetch_a), _bytes(prefetch_a), _p(prefetch_b), _bytes(prefetch_b), _stream()))
     launch_count += 2 if num_splits > 1 else 1
     return out
 

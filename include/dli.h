@@ -135,14 +135,22 @@ int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
  * sequence, NOT yet rotated; the new token's position is seq_lens[b] - 1.
  * q is rotated on the fly, the new k is rotated and written with v into the
  * sequence's cache page (k_cache / v_cache are written), then attended with
- * the rest of the context.  cos == NULL: no rotation (GPT-2). */
+ * the rest of the context.  cos == NULL: no rotation (GPT-2).
+ * l2_prefetch_a / _b (optional, may be NULL): device ranges — normally the
+ * weights of the projections that follow — pulled into L2 with
+ * cp.async.bulk.prefetch by spare CTAs while the attention kernel (a) and the
+ * split merge (b) run; at small batch these two kernels are latency-bound and
+ * use few SMs, so HBM would otherwise idle.  Ignored when the grid already
+ * fills the GPU.  They change no result. */
 int dli_paged_attn_decode_fused_bf16(void* qkv, int row_stride, const void* cos,
                                      const void* sin, void* k_cache, void* v_cache,
                                      const int32_t* page_table, int max_pages,
                                      const int32_t* seq_lens, void* out, void* scratch,
                                      size_t scratch_bytes, int B, int H, int KV, int hd,
                                      int page_size, int num_splits, float scale,
-                                     int window, dli_stream_t stream);
+                                     int window, const void* l2_prefetch_a,
+                                     size_t l2_prefetch_a_bytes, const void* l2_prefetch_b,
+                                     size_t l2_prefetch_b_bytes, dli_stream_t stream);
 
 /* Same computation as dli_paged_attn_decode_bf16 for callers that cannot
  * allocate device memory where they call it: a server that handed all of HBM
