@@ -42,6 +42,9 @@ SIGNATURES = {
          _vp, _sz, _vp, _sz, _vp],
     ),
     "dli_set_pdl": (_i, [_i]),
+    "dli_gemm_splitk_scratch_bytes": (_sz, [_i, _i]),
+    "dli_gemm_splitk_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "dli_gemm_splitk_gated_silu_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _sz, _vp]),
     "dli_rmsnorm_gemv_bf16": (_i, [_vp, _vp, _f, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "dli_rmsnorm_gemv_gated_silu_bf16": (_i, [_vp, _vp, _f, _vp, _vp, _i, _i, _i, _vp]),
     "dli_attn_prefill_bf16": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _i, _vp]),

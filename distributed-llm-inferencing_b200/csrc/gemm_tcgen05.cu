@@ -184,7 +184,7 @@ template <int BN, bool kSwap, bool kGated>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const bf16* __restrict__ bias, const bf16* residual, bf16* y, int M, int N, int K,
-                    int epilogue) {
+                    int epilogue, float* splitk_partial, int* splitk_counters) {
   using Cfg = GemmCfg<BN, kSwap, kGated>;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte alignment
@@ -196,7 +196,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_mem + 8 * (2 * Cfg::kStages + 1));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int num_kb = K / kBlockK;
+  // split-K (gridDim.z > 1, swap mode): this CTA reduces k-blocks [kb0, kb0 + num_kb)
+  const int total_kb = K / kBlockK;
+  const int kb_per = (total_kb + gridDim.z - 1) / gridDim.z;
+  const int kb0 = blockIdx.z * kb_per;
+  const int num_kb = min(kb_per, total_kb - kb0);
   // blockIdx.x walks the activation-row tiles fastest so CTAs sharing a weight
   // tile run together and the weight tile is fetched from HBM once.
   const int a_row0 = (kSwap ? blockIdx.y : blockIdx.x) * Cfg::kARows;  // rows of the A-operand matrix
@@ -228,8 +232,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
         const uint32_t sB = sA + Cfg::kABytes;
         mbar_expect_tx(full_bar + 8 * s, Cfg::kStageBytes);
-        tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, a_row0);
-        tma_load_2d(sB, &tmB, full_bar + 8 * s, kb * kBlockK, b_row0);
+        tma_load_2d(sA, &tmA, full_bar + 8 * s, (kb0 + kb) * kBlockK, a_row0);
+        tma_load_2d(sB, &tmB, full_bar + 8 * s, (kb0 + kb) * kBlockK, b_row0);
       }
     }
   } else if (warp == 1) {
@@ -316,35 +320,99 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else {
       // swap: lane = weight row n, columns = activation rows m (only m < M are real)
       constexpr int kOutRows = 128;
-      const int n = blockIdx.y * kOutRows + quad * 32 + lane;
+      const int row = quad * 32 + lane;
+      const int n = blockIdx.y * kOutRows + row;
       const int n_out = kGated ? N / 2 : N;
       const int m_tile0 = blockIdx.x * BN;
+      const int splits = gridDim.z;
+      const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+      bool finish = true;
+      if (splits > 1) {
+        // Deterministic split-K: every split parks its fp32 partial tile in the workspace
+        // ([tile][split][column m][row n], lanes contiguous), the CTA that arrives last at the
+        // tile's counter adds the partials in split order and runs the epilogue, then
+        // re-zeroes the counter for the next launch.
+        float* mine = splitk_partial + ((size_t)tile * splits + blockIdx.z) * Cfg::kAccCols * 128;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 16) {
-        if (m_tile0 + c0 >= M) break;  // warp-uniform
-        uint32_t r[16], r2[16];
-        tmem_ld_32x16(lane_base + c0, r);
-        if (kGated) tmem_ld_32x16(lane_base + BN + c0, r2);
-        tmem_ld_wait();
-        if (n < n_out) {
-          const float bv = (!kGated && (epilogue & DLI_EPI_BIAS)) ? __bfloat162float(bias[n]) : 0.f;
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+          if (m_tile0 + c0 >= M) break;
+          uint32_t r[16], r2[16];
+          tmem_ld_32x16(lane_base + c0, r);
+          if (kGated) tmem_ld_32x16(lane_base + BN + c0, r2);
+          tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const int m = m_tile0 + c0 + j;
-            if (m < M) {
-              float v;
-              if (kGated) {
-                const float gte = round_bf16(__uint_as_float(r[j])), up = round_bf16(__uint_as_float(r2[j]));
-                v = round_bf16(silu_f(gte)) * up;
-              } else {
-                v = round_bf16(__uint_as_float(r[j]) + bv);
-                if (epilogue & DLI_EPI_GELU_NEW) v = round_bf16(gelu_new_f(v));
-                if (epilogue & DLI_EPI_RESIDUAL) v += __bfloat162float(residual[(size_t)m * n_out + n]);
-              }
-              y[(size_t)m * n_out + n] = __float2bfloat16_rn(v);
+            if (m_tile0 + c0 + j < M) {
+              mine[(size_t)(c0 + j) * 128 + row] = __uint_as_float(r[j]);
+              if (kGated) mine[(size_t)(BN + c0 + j) * 128 + row] = __uint_as_float(r2[j]);
             }
           }
         }
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // the 4 epilogue warps
+        volatile uint32_t* flag = tmem_ptr_smem + 2;
+        if (warp == 2 && lane == 0) *flag = (atomicAdd(splitk_counters + tile, 1) == splits - 1) ? 1u : 0u;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        finish = *flag != 0;
+        if (finish) __threadfence();
+      }
+      if (finish) {
+        const float* all = splitk_partial + (size_t)tile * splits * Cfg::kAccCols * 128;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+          if (m_tile0 + c0 >= M) break;  // warp-uniform
+          float a1[16], a2[16];
+          if (splits == 1) {
+            uint32_t r[16], r2[16];
+            tmem_ld_32x16(lane_base + c0, r);
+            if (kGated) tmem_ld_32x16(lane_base + BN + c0, r2);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { a1[j] = __uint_as_float(r[j]); a2[j] = kGated ? __uint_as_float(r2[j]) : 0.f; }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { a1[j] = 0.f; a2[j] = 0.f; }
+            for (int sp = 0; sp < splits; ++sp) {
+              const float* src = all + (size_t)sp * Cfg::kAccCols * 128;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                if (m_tile0 + c0 + j < M) {
+                  a1[j] += __ldcg(src + (size_t)(c0 + j) * 128 + row);
+                  if (kGated) a2[j] += __ldcg(src + (size_t)(BN + c0 + j) * 128 + row);
+                }
+              }
+            }
+          }
+          if (n < n_out) {
+            const float bv = (!kGated && (epilogue & DLI_EPI_BIAS)) ? __bfloat162float(bias[n]) : 0.f;
+            // y may alias residual: read all residual values of the chunk before the first store,
+            // otherwise every load would have to wait for the previous store
+            float rr[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int m = m_tile0 + c0 + j;
+              rr[j] = (!kGated && (epilogue & DLI_EPI_RESIDUAL) && m < M)
+                          ? __bfloat162float(residual[(size_t)m * n_out + n]) : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int m = m_tile0 + c0 + j;
+              if (m < M) {
+                float v;
+                if (kGated) {
+                  const float gte = round_bf16(a1[j]), up = round_bf16(a2[j]);
+                  v = round_bf16(silu_f(gte)) * up;
+                } else {
+                  v = round_bf16(a1[j] + bv);
+                  if (epilogue & DLI_EPI_GELU_NEW) v = round_bf16(gelu_new_f(v));
+                  v += rr[j];
+                }
+                y[(size_t)m * n_out + n] = __float2bfloat16_rn(v);
+              }
+            }
+          }
+        }
+        if (splits > 1 && warp == 2 && lane == 0) splitk_counters[tile] = 0;
       }
     }
     tcgen05_fence_before();
@@ -392,7 +460,8 @@ static int make_tmap(CUtensorMap* tm, const void* base, int rows, int K, int box
 
 template <int BN, bool kSwap, bool kGated>
 static int launch_gemm(const void* x, const void* w, const void* bias, const void* residual, void* y, int M,
-                       int N /* rows of w */, int K, int epilogue, cudaStream_t s) {
+                       int N /* rows of w */, int K, int epilogue, cudaStream_t s, void* scratch = nullptr,
+                       size_t scratch_bytes = 0) {
   using Cfg = GemmCfg<BN, kSwap, kGated>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -412,8 +481,30 @@ static int launch_gemm(const void* x, const void* w, const void* bias, const voi
     if ((rc = make_tmap(&tmB, x, M, K, BN)) != DLI_OK) return rc;
     grid = dim3((M + BN - 1) / BN, (N + Cfg::kARows - 1) / Cfg::kARows);
   }
+  float* partial = nullptr;
+  int* counters = nullptr;
+  if (kSwap && scratch) {
+    // split K so that about one CTA per SM streams weights (each needs ~200 KB of smem)
+    const int tiles = grid.x * grid.y, total_kb = K / kBlockK;
+    int splits = sm_count_cached() / tiles;
+    if (splits > total_kb) splits = total_kb;
+    if (splits > 1) {
+      const int kb_per = (total_kb + splits - 1) / splits;
+      splits = (total_kb + kb_per - 1) / kb_per;  // no empty split
+    }
+    if (splits > 1) {
+      const size_t cbytes = (((size_t)tiles * sizeof(int)) + 255) & ~(size_t)255;
+      const size_t need = cbytes + (size_t)tiles * splits * Cfg::kAccCols * 128 * sizeof(float);
+      if (need <= scratch_bytes) {
+        counters = reinterpret_cast<int*>(scratch);
+        partial = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + cbytes);
+        grid.z = splits;
+      }
+    }
+  }
   DLI_LAUNCH("gemm_tcgen05_kernel", gemm_tcgen05_kernel<BN, kSwap, kGated>, grid, dim3(kGemmThreads),
-             (size_t)Cfg::kSmemBytes, s, tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue);
+             (size_t)Cfg::kSmemBytes, s, tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue,
+             partial, counters);
   return DLI_OK;
 }
 
@@ -458,6 +549,52 @@ int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, in
   if (M <= 64) return launch_gemm<64, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
   if (M <= 128) return launch_gemm<128, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
   return launch_gemm<256, false, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
+}
+
+size_t dli_gemm_splitk_scratch_bytes(int M, int N) {
+  // one int32 counter per 128-row weight tile + at most one fp32 partial tile per SM
+  // (<= 256 CTAs) of 2 accumulators x BN columns x 128 rows, BN = M rounded up to 16/32/64/128
+  if (M <= 0 || N <= 0 || M > 128) return 0;
+  const size_t bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
+  const size_t tiles = ((size_t)N + 127) / 128;
+  return ((tiles * sizeof(int) + 255) & ~(size_t)255) + (size_t)256 * 2 * bn * 128 * sizeof(float);
+}
+
+int dli_gemm_splitk_bf16(const void* x, const void* w, const void* bias, const void* residual, void* y, int M, int N,
+                         int K, int epilogue, void* scratch, size_t scratch_bytes, dli_stream_t stream) {
+  using namespace dli;
+  if (M > 128 || scratch == nullptr) return dli_gemm_bf16(x, w, bias, residual, y, M, N, K, epilogue, stream);
+  DLI_CHECK_ARG(x && w && y, "dli_gemm_splitk_bf16: null pointer");
+  DLI_CHECK_ARG(M >= 0 && N > 0 && K > 0 && K % 64 == 0 && N % 16 == 0,
+                "dli_gemm_splitk_bf16: need K %% 64 == 0 and N %% 16 == 0 (got M=%d N=%d K=%d)", M, N, K);
+  DLI_CHECK_ARG(!(epilogue & DLI_EPI_BIAS) || bias, "dli_gemm_splitk_bf16: DLI_EPI_BIAS without bias");
+  DLI_CHECK_ARG(!(epilogue & DLI_EPI_RESIDUAL) || residual, "dli_gemm_splitk_bf16: DLI_EPI_RESIDUAL without residual");
+  DLI_CHECK_ARG(aligned16(x) && aligned16(w) && aligned16(y) && aligned16(residual) && aligned16(scratch),
+                "dli_gemm_splitk_bf16: pointers must be 16-byte aligned");
+  if (M == 0) return DLI_OK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (M <= 16) return launch_gemm<16, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s, scratch, scratch_bytes);
+  if (M <= 32) return launch_gemm<32, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s, scratch, scratch_bytes);
+  if (M <= 64) return launch_gemm<64, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s, scratch, scratch_bytes);
+  return launch_gemm<128, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s, scratch, scratch_bytes);
+}
+
+int dli_gemm_splitk_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F, int K, void* scratch,
+                                    size_t scratch_bytes, dli_stream_t stream) {
+  using namespace dli;
+  if (M > 128 || scratch == nullptr) return dli_gemm_gated_silu_bf16(x, w_gu, y, M, F, K, stream);
+  DLI_CHECK_ARG(x && w_gu && y, "dli_gemm_splitk_gated_silu_bf16: null pointer");
+  DLI_CHECK_ARG(M >= 0 && F > 0 && F % 128 == 0 && K > 0 && K % 64 == 0,
+                "dli_gemm_splitk_gated_silu_bf16: need F %% 128 == 0, K %% 64 == 0 (got M=%d F=%d K=%d)", M, F, K);
+  DLI_CHECK_ARG(aligned16(x) && aligned16(w_gu) && aligned16(y) && aligned16(scratch),
+                "dli_gemm_splitk_gated_silu_bf16: pointers must be 16-byte aligned");
+  if (M == 0) return DLI_OK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int N2 = 2 * F;
+  if (M <= 16) return launch_gemm<16, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s, scratch, scratch_bytes);
+  if (M <= 32) return launch_gemm<32, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s, scratch, scratch_bytes);
+  if (M <= 64) return launch_gemm<64, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s, scratch, scratch_bytes);
+  return launch_gemm<128, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s, scratch, scratch_bytes);
 }
 
 int dli_linear_bf16(const void* x, const void* w, const void* bias, const void* residual, void* y, int M, int N,

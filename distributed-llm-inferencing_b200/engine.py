@@ -161,7 +161,7 @@ class ShardEngine:
         self.use_cuda_graph = use_cuda_graph
         torch.cuda.set_device(self.device)
         self.sms = ops.sm_count()
-        self.l2_prefetch = os.environ.get("DLI_L2_PREFETCH", "1") == "1"
+        self.l2_prefetch = os.environ.get("DLI_L2_PREFETCH", "0") == "1"
         # kernels may start (and prefetch weights) while their predecessor drains
         ops.set_pdl(os.environ.get("DLI_PDL", "1") == "1")
         self.w: Dict[str, torch.Tensor] = {}
@@ -174,6 +174,7 @@ class ShardEngine:
             self.cos = self.sin = None
         self.scale = spec.head_dim ** -0.5
         self._ws_rows = 0
+        self._sk = None  # split-K workspace of the batched-decode projections (zeroed once, self-resetting)
         self._graphs: Dict[tuple, tuple] = {}
         self._dec: Dict[tuple, dict] = {}
 
@@ -328,15 +329,28 @@ class ShardEngine:
         H, KV, hd = s.n_heads, s.n_kv_heads, s.head_dim
         decode = prefill_shape is None
         fuse_norm = decode and rows <= 4 and s.arch == "llama"  # RMSNorm inside the weight-streaming GEMV
+        split_k = decode and 4 < rows <= 128  # batched decode: split-K tcgen05 weight stream on every SM
+        if split_k and self._sk is None:
+            n_max = max(s.vocab, 2 * s.d_ff, (H + 2 * KV) * hd, s.d_model)
+            self._sk = torch.zeros(ops.gemm_splitk_scratch_bytes(128, n_max), dtype=torch.uint8, device=self.device)
+
+        def lin(x_, w_, **kw):
+            return ops.linear_splitk(x_, w_, self._sk, **kw) if split_k else ops.linear(x_, w_, **kw)
+
+        def gated(x_, w_, out):
+            if split_k:
+                return ops.linear_splitk_gated_silu(x_, w_, self._sk, out=out)
+            return ops.linear_gated_silu(x_, w_, out=out)
+
         for li, L in enumerate(self.layers):
             if fuse_norm:
                 ops.rmsnorm_linear(h, L["ln1"], s.eps, L["wqkv"], out=qkv)
             elif s.arch == "llama":
                 ops.add_rmsnorm(h, L["ln1"], s.eps, out=x)
-                ops.linear(x, L["wqkv"], out=qkv)
+                lin(x, L["wqkv"], out=qkv)
             else:
                 ops.add_layernorm(h, L["ln1"], L["ln1b"], s.eps, out=x)
-                ops.linear(x, L["wqkv"], bias=L["bqkv"], out=qkv)
+                lin(x, L["wqkv"], bias=L["bqkv"], out=qkv)
             if decode:
                 # RoPE + KV append of the new token + split-KV attention in one kernel; the
                 # kernel indexes page-table rows by batch row, so it gets the slot's rows
@@ -352,18 +366,18 @@ class ShardEngine:
                 ops.attn_prefill(qkv, attn, prefill_shape[0], prefill_shape[1], H, KV, hd, self.scale,
                                  window=s.sliding_window)
             if s.arch == "llama":
-                ops.linear(attn, L["wo"], residual=h, out=h)
+                lin(attn, L["wo"], residual=h, out=h)
                 if fuse_norm:
                     ops.rmsnorm_linear_gated_silu(h, L["ln2"], s.eps, L["wgu"], out=act)
                 else:
                     ops.add_rmsnorm(h, L["ln2"], s.eps, out=x)
-                    ops.linear_gated_silu(x, L["wgu"], out=act)
-                ops.linear(act, L["wdown"], residual=h, out=h)
+                    gated(x, L["wgu"], act)
+                lin(act, L["wdown"], residual=h, out=h)
             else:
-                ops.linear(attn, L["wo"], bias=L["bo"], residual=h, out=h)
+                lin(attn, L["wo"], bias=L["bo"], residual=h, out=h)
                 ops.add_layernorm(h, L["ln2"], L["ln2b"], s.eps, out=x)
-                ops.linear(x, L["wfc"], bias=L["bfc"], out=act, epilogue=ops.EPI_GELU_NEW)
-                ops.linear(act, L["wdown"], bias=L["bdown"], residual=h, out=h)
+                lin(x, L["wfc"], bias=L["bfc"], out=act, epilogue=ops.EPI_GELU_NEW)
+                lin(act, L["wdown"], bias=L["bdown"], residual=h, out=h)
         return h
 
     def _head(self, h_last, logits, tokens):

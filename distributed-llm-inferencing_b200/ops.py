@@ -265,3 +265,36 @@ def rmsnorm_linear_gated_silu(h, ln_w, eps, w_gu, out=None):
         _p(h), _p(ln_w), float(eps), _p(w_gu), _p(out), M, F, K, _stream()))
     launch_count += (M + 3) // 4
     return out
+
+
+def gemm_splitk_scratch_bytes(M, N) -> int:
+    return int(_lib.load().dli_gemm_splitk_scratch_bytes(M, N))
+
+
+def linear_splitk(x, w, scratch, bias=None, residual=None, out=None, epilogue=EPI_NONE):
+    """Batched-decode projection (4 < M <= 128): split-K tcgen05 weight stream.  `scratch` is a
+    zero-initialised uint8/float tensor of gemm_splitk_scratch_bytes(M, N) bytes."""
+    global launch_count
+    _req(x), _req(w), _req(bias), _req(residual), _req(out)
+    M, K = x.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+    epi = epilogue | (EPI_BIAS if bias is not None else 0) | (EPI_RESIDUAL if residual is not None else 0)
+    _lib.check("dli_gemm_splitk_bf16", _lib.load().dli_gemm_splitk_bf16(
+        _p(x), _p(w), _p(bias), _p(residual), _p(out), M, N, K, epi, _p(scratch), _bytes(scratch), _stream()))
+    launch_count += 1
+    return out
+
+
+def linear_splitk_gated_silu(x, w_gu, scratch, out=None):
+    global launch_count
+    _req(x), _req(w_gu), _req(out)
+    M, K = x.shape
+    F = w_gu.shape[0] // 2
+    if out is None:
+        out = torch.empty(M, F, dtype=torch.bfloat16, device=x.device)
+    _lib.check("dli_gemm_splitk_gated_silu_bf16", _lib.load().dli_gemm_splitk_gated_silu_bf16(
+        _p(x), _p(w_gu), _p(out), M, F, K, _p(scratch), _bytes(scratch), _stream()))
+    launch_count += 1
+    return out

@@ -225,6 +225,24 @@ int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, in
 int dli_linear_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M,
                                int F, int K, dli_stream_t stream);
 
+/* Split-K variants of the tensor-core GEMM for batched decode (4 < M <= 128),
+ * where the kernel is a weight stream and a matrix with few 128-row tiles would
+ * leave most SMs (and most of HBM's bandwidth) idle: K is split over about
+ * SMs/tiles CTAs per tile, each parks its fp32 partial in `scratch`, and the CTA
+ * that finishes a tile last adds the partials in split order (deterministic) and
+ * runs the epilogue.  scratch: dli_gemm_splitk_scratch_bytes(M, N) bytes (N = rows
+ * of w; 2F for the gated form), ZERO-FILLED before its first use; every call
+ * leaves its counters zero again.  Calls sharing a scratch buffer must be ordered
+ * on one stream.  M > 128 or scratch == NULL falls through to dli_gemm_bf16. */
+size_t dli_gemm_splitk_scratch_bytes(int M, int N);
+int dli_gemm_splitk_bf16(const void* x, const void* w, const void* bias,
+                         const void* residual, void* y, int M, int N, int K,
+                         int epilogue, void* scratch, size_t scratch_bytes,
+                         dli_stream_t stream);
+int dli_gemm_splitk_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M,
+                                    int F, int K, void* scratch, size_t scratch_bytes,
+                                    dli_stream_t stream);
+
 /* RMSNorm fused into the decode projection (M <= 4 rows per pass):
  *   y = epi( (ln_w * bf16(h * rsqrt(mean(h^2) + eps))) . w^T )
  * i.e. LlamaRMSNorm (TF:models/llama/modeling_llama.py:62-67) followed by the
