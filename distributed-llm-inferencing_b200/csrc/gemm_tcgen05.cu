@@ -217,7 +217,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(smem_addr(tmem_ptr_smem), Cfg::kTmemCols);
-  pdl_wait();  // barrier init / TMEM allocation above overlap the previous kernel's tail
+  // barrier init / TMEM allocation overlap the previous kernel's tail; the warps that touch
+  // data written by the previous kernel call pdl_wait() themselves (producer: after the
+  // first ring of WEIGHT loads is in flight; epilogue: before reading residual / scratch)
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -225,12 +227,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (warp == 0) {
     if (lane == 0) {
+      // the operand that holds WEIGHTS (A in swap mode, B otherwise) does not depend on the
+      // previous kernel: its first ring of loads goes out before the dependency wait
+      const int pre = min((int)Cfg::kStages, num_kb);
+      for (int kb = 0; kb < pre; ++kb) {
+        const uint32_t sA = smem_addr(smem + kb * Cfg::kStageBytes);
+        mbar_expect_tx(full_bar + 8 * kb, Cfg::kStageBytes);
+        if (kSwap) tma_load_2d(sA, &tmA, full_bar + 8 * kb, (kb0 + kb) * kBlockK, a_row0);
+        else tma_load_2d(sA + Cfg::kABytes, &tmB, full_bar + 8 * kb, (kb0 + kb) * kBlockK, b_row0);
+      }
+      pdl_wait();
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % Cfg::kStages;
         const uint32_t ph = (kb / Cfg::kStages) & 1;
-        mbar_wait(empty_bar + 8 * s, ph ^ 1);
         const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
         const uint32_t sB = sA + Cfg::kABytes;
+        if (kb < pre) {  // weights in flight, expect_tx armed: only the activation tile is missing
+          if (kSwap) tma_load_2d(sB, &tmB, full_bar + 8 * s, (kb0 + kb) * kBlockK, b_row0);
+          else tma_load_2d(sA, &tmA, full_bar + 8 * s, (kb0 + kb) * kBlockK, a_row0);
+          continue;
+        }
+        mbar_wait(empty_bar + 8 * s, ph ^ 1);
         mbar_expect_tx(full_bar + 8 * s, Cfg::kStageBytes);
         tma_load_2d(sA, &tmA, full_bar + 8 * s, (kb0 + kb) * kBlockK, a_row0);
         tma_load_2d(sB, &tmB, full_bar + 8 * s, (kb0 + kb) * kBlockK, b_row0);
@@ -265,6 +282,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else {
     // ---- epilogue warps 2..5: TMEM lane quadrant = warp % 4 -----------------------------
     const int quad = warp & 3;
+    pdl_wait();
     mbar_wait(tmem_full_bar, 0);
     tcgen05_fence_after();
     const uint32_t lane_base = tmem_base + ((uint32_t)(quad * 32) << 16);
@@ -424,6 +442,194 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 }
 
+
+// ======================================================================================
+// Persistent prefill GEMM (M > 128): one CTA per SM walks the output tiles, the accumulator
+// is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i overlaps the MMAs
+// of tile i+1, and the TMA -> MMA ring keeps running across tile boundaries.
+//   A = x tile [128 m, 64 k], B = w tile [BN n, 64 k]; TMEM lane = m, column = n.
+//   warp 0: TMA producer   warp 1: MMA issuer + TMEM owner   warps 2-5: epilogue
+// Weight tiles do not depend on the previous kernel: the producer issues the first ring
+// of weight loads before it waits for the previous kernel (programmatic dependent launch).
+// ======================================================================================
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+template <int BN, bool kGated>
+struct PrefillCfg {
+  static constexpr int kABytes = 128 * kBlockK * 2;
+  static constexpr int kBBytes = BN * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagesRaw = (216 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kTmemCols = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
+  static constexpr int kOutCols = kGated ? 128 : BN;  // output columns per tile
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
+  static_assert(!kGated || BN == 256, "gated tile is gate128|up128");
+};
+
+template <int BN, bool kGated>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const bf16* __restrict__ bias, const bf16* residual, bf16* y, int M, int N, int K,
+                    int epilogue, int m_tiles, int num_tiles) {
+  using Cfg = PrefillCfg<BN, kGated>;
+  constexpr int S = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* bar_mem = smem + S * Cfg::kStageBytes;
+  const uint32_t full_bar = smem_addr(bar_mem);
+  const uint32_t empty_bar = full_bar + 8 * S;
+  const uint32_t tfull_bar = empty_bar + 8 * S;   // 2 accumulator stages
+  const uint32_t tempty_bar = tfull_bar + 16;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_mem + 8 * (2 * S + 4));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_kb = K / kBlockK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < S; ++s) {
+      mbar_init(full_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar + 8 * a, 1);
+      mbar_init(tempty_bar + 8 * a, 4);  // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(smem_addr(tmem_ptr_smem), Cfg::kTmemCols);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ring of weight (B) loads for the first tile goes out before the dependency wait
+      const int first = blockIdx.x;
+      const int pre = (first < num_tiles) ? min(S, num_kb) : 0;
+      for (int kb = 0; kb < pre; ++kb) {
+        const uint32_t sA = smem_addr(smem + kb * Cfg::kStageBytes);
+        mbar_expect_tx(full_bar + 8 * kb, Cfg::kStageBytes);
+        tma_load_2d(sA + Cfg::kABytes, &tmB, full_bar + 8 * kb, kb * kBlockK, (first / m_tiles) * BN);
+      }
+      pdl_wait();
+      uint32_t kc = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile % m_tiles, n_blk = tile / m_tiles;
+        for (int kb = 0; kb < num_kb; ++kb, ++kc) {
+          const int s = kc % S;
+          const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
+          if ((int)kc < pre) {  // B already in flight, expect_tx already armed
+            tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, m_blk * 128);
+            continue;
+          }
+          mbar_wait(empty_bar + 8 * s, ((kc / S) & 1) ^ 1);
+          mbar_expect_tx(full_bar + 8 * s, Cfg::kStageBytes);
+          tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, m_blk * 128);
+          tma_load_2d(sA + Cfg::kABytes, &tmB, full_bar + 8 * s, kb * kBlockK, n_blk * BN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BN);
+      uint32_t kc = 0, tl = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+        const uint32_t as = tl & 1;
+        mbar_wait(tempty_bar + 8 * as, ((tl >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+        tcgen05_fence_after();
+        const uint32_t tacc = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb, ++kc) {
+          const int s = kc % S;
+          mbar_wait(full_bar + 8 * s, (kc / S) & 1);
+          tcgen05_fence_after();
+          const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
+          const uint64_t adesc = make_smem_desc(sA);
+          const uint64_t bdesc = make_smem_desc(sA + Cfg::kABytes);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k)
+            umma_bf16(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar + 8 * s);
+        }
+        umma_commit(tfull_bar + 8 * as);
+      }
+    }
+  } else {
+    const int quad = warp & 3;
+    pdl_wait();  // residual / bias may come from the previous kernel
+    uint32_t tl = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+      const int m_blk = tile % m_tiles, n_blk = tile / m_tiles;
+      const uint32_t as = tl & 1;
+      mbar_wait(tfull_bar + 8 * as, (tl >> 1) & 1);
+      tcgen05_fence_after();
+      const uint32_t lane_base = tmem_base + as * BN + ((uint32_t)(quad * 32) << 16);
+      const int m = m_blk * 128 + quad * 32 + lane;
+      const int n_tile0 = n_blk * Cfg::kOutCols;
+      const int n_out = kGated ? N / 2 : N;
+#pragma unroll 1
+      for (int c0 = 0; c0 < Cfg::kOutCols; c0 += 16) {
+        uint32_t r[16], r2[16];
+        tmem_ld_32x16(lane_base + c0, r);
+        if (kGated) tmem_ld_32x16(lane_base + 128 + c0, r2);
+        tmem_ld_wait();
+        const int n0 = n_tile0 + c0;
+        if (m < M && n0 < n_out) {
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+          if (kGated) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float gte = round_bf16(v[j]), up = round_bf16(__uint_as_float(r2[j]));
+              v[j] = round_bf16(silu_f(gte)) * up;
+            }
+          } else {
+            if (epilogue & DLI_EPI_BIAS) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] += (n0 + j < N) ? __bfloat162float(bias[n0 + j]) : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = round_bf16(v[j]);
+            if (epilogue & DLI_EPI_GELU_NEW) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = round_bf16(gelu_new_f(v[j]));
+            }
+          }
+          bf16* dst = y + (size_t)m * n_out + n0;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            if (n0 + h * 8 < n_out) {
+              if (!kGated && (epilogue & DLI_EPI_RESIDUAL)) {
+                float rr[8];
+                unpack8(ld_16B(residual + (size_t)m * n_out + n0 + h * 8), rr);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[h * 8 + j] += rr[j];
+              }
+              st_16B(dst + h * 8, pack8(v + h * 8));
+            }
+          }
+        }
+      }
+      // this warp is done reading the accumulator stage: hand it back to the MMA warp
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar + 8 * as);
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
 // ---- host side ---------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
@@ -458,10 +664,35 @@ static int make_tmap(CUtensorMap* tm, const void* base, int rows, int K, int box
   return DLI_OK;
 }
 
+template <int BN, bool kGated>
+static int launch_prefill_gemm(const void* x, const void* w, const void* bias, const void* residual, void* y, int M,
+                               int N /* rows of w */, int K, int epilogue, cudaStream_t s) {
+  using Cfg = PrefillCfg<BN, kGated>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  CUtensorMap tmA, tmB;
+  int rc;
+  if ((rc = make_tmap(&tmA, x, M, K, 128)) != DLI_OK) return rc;
+  if ((rc = make_tmap(&tmB, w, N, K, BN)) != DLI_OK) return rc;
+  const int m_tiles = (M + 127) / 128, n_tiles = (N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  const int sms = sm_count_cached();
+  const int grid = num_tiles < sms ? num_tiles : sms;
+  DLI_LAUNCH("gemm_prefill_kernel", gemm_prefill_kernel<BN, kGated>, dim3(grid), dim3(kGemmThreads),
+             (size_t)Cfg::kSmemBytes, s, tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue,
+             m_tiles, num_tiles);
+  return DLI_OK;
+}
+
 template <int BN, bool kSwap, bool kGated>
 static int launch_gemm(const void* x, const void* w, const void* bias, const void* residual, void* y, int M,
                        int N /* rows of w */, int K, int epilogue, cudaStream_t s, void* scratch = nullptr,
                        size_t scratch_bytes = 0) {
+  if constexpr (!kSwap) return launch_prefill_gemm<BN, kGated>(x, w, bias, residual, y, M, N, K, epilogue, s);
   using Cfg = GemmCfg<BN, kSwap, kGated>;
   static bool attr_set = false;
   if (!attr_set) {
