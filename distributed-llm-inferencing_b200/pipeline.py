@@ -174,6 +174,9 @@ def run_pipeline_bench(args, spec, peaks):
         dist.barrier()
         return t.item()
 
+    runner.run("prefill")  # warm-up: lazy module loads, function attributes, NCCL connections
+    for mb in range(M):
+        eng.start_batch(b, ctx, max_len, mb=mb)
     pf_ms = timed(lambda: runner.run("prefill"))
     runner.run("decode", W)  # warm-up rounds (captures the per-slot CUDA graphs)
     n0 = ops.launch_count
