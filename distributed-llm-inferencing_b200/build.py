@@ -26,6 +26,7 @@ SOURCES = [
     "gemv.cu",
     "gemm_tcgen05.cu",
     "elementwise.cu",
+    "sample.cu",
 ]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

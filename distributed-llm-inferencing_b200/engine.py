@@ -174,6 +174,7 @@ class ShardEngine:
             self.cos = self.sin = None
         self.scale = spec.head_dim ** -0.5
         self._ws_rows = 0
+        self.sampling = None  # None = greedy; else dict(temperature=, top_k=, top_p=) for ops.sample
         self._sk = None  # split-K workspace of the batched-decode projections (zeroed once, self-resetting)
         self._graphs: Dict[tuple, tuple] = {}
         self._dec: Dict[tuple, dict] = {}
@@ -380,8 +381,9 @@ class ShardEngine:
                 lin(act, L["wdown"], bias=L["bdown"], residual=h, out=h)
         return h
 
-    def _head(self, h_last, logits, tokens):
-        """final norm + lm_head + greedy argmax on [B, d]."""
+    def _head(self, h_last, logits, tokens, st=None):
+        """final norm + lm_head + token choice on [B, d]: greedy argmax, or (self.sampling)
+        the reference's temperature/top-k/top-p multinomial with the slot's seed and step."""
         s = self.spec
         B = h_last.shape[0]
         xn = self._x[:B]
@@ -393,7 +395,10 @@ class ShardEngine:
             else:
                 ops.add_layernorm(h_last, self.w["norm"], self.w["normb"], s.eps, out=xn)
             ops.linear(xn, self.w["head"], out=logits)
-        ops.argmax(logits, out=tokens)
+        if self.sampling is None:
+            ops.argmax(logits, out=tokens)
+        else:
+            ops.sample(logits, out=tokens, seed=st["seed"], step=st["step"], **self.sampling)
 
     # ------------------------------------------------------------------ prefill
     def _state(self, B: int, mb: int = 0) -> dict:
@@ -425,6 +430,7 @@ class ShardEngine:
                 "page_rows": self.kv.page_table[mb * B:(mb + 1) * B],  # view: rows of this slot's sequences
                 "tokens": torch.zeros(B, dtype=torch.int32, device=dev),
                 "step": torch.zeros(1, dtype=torch.int32, device=dev),
+                "seed": torch.zeros(1, dtype=torch.int64, device=dev),
                 # residual stream of the slot's decode step: stage input (recv target) and output (send source)
                 "h": torch.empty(B, self.spec.d_model, dtype=BF, device=dev),
                 "logits": torch.empty(B, self.spec.vocab, dtype=BF, device=dev) if self.is_last else None,
@@ -461,7 +467,7 @@ class ShardEngine:
             return h
         last_rows = (torch.arange(B, dtype=torch.int32, device=dev) + 1) * T - 1
         h_last = ops.embedding(last_rows, h, out=st["h"])  # row gather of the last positions
-        self._head(h_last, st["logits"], st["tokens"])
+        self._head(h_last, st["logits"], st["tokens"], st)
         return st["tokens"]
 
     # ------------------------------------------------------------------ decode
@@ -478,7 +484,7 @@ class ShardEngine:
                 ops.embedding(st["tokens"], self.w["embed"], out=h)
         self._layers_forward(h, B, st["positions"], st["seq_ids"], st["seq_lens"], None, st)
         if self.is_last:
-            self._head(h, st["logits"], st["tokens"])
+            self._head(h, st["logits"], st["tokens"], st)
         ops.decode_advance(st["tokens"], st["token_log"] if self.is_last else None, st["positions"], st["seq_lens"],
                            st["step"])
         return st["tokens"] if self.is_last else h
@@ -535,7 +541,9 @@ class ShardEngine:
     # ------------------------------------------------------------------ public API
     @torch.no_grad()
     def generate(self, input_ids: torch.Tensor, max_length: int, return_logits: bool = False,
-                 forced: Optional[torch.Tensor] = None, deadline: Optional[float] = None):
+                 forced: Optional[torch.Tensor] = None, deadline: Optional[float] = None,
+                 do_sample: bool = False, temperature: float = 0.8, top_k: int = 50, top_p: float = 0.95,
+                 seed: int = 0):
         """Greedy generate (the parity mode of worker/app.py:297-305: the reference
         samples, see SURVEY.md §0 F3).  input_ids: int [B, T] on any device;
         `max_length` is the TOTAL length like the reference's.  Returns int64
@@ -551,12 +559,21 @@ class ShardEngine:
             return input_ids.cpu().long()[:, :max_length]
         self.start_batch(B, T, max_length)
         st = self._dec[(B, 0)]
+        # greedy is the parity mode; do_sample=True is the reference's default call
+        # (worker/app.py:297-305).  The mode is part of the captured graph.
+        mode = dict(temperature=float(temperature), top_k=int(top_k), top_p=float(top_p)) if do_sample else None
+        if mode != self.sampling:
+            self.sampling = mode
+            self._graphs.clear()
+        st["seed"].fill_(int(seed))
+        st["step"].fill_(-1)  # prefill draws with step -1, decode steps with 0, 1, ...
         ids = input_ids.to(device=self.device, dtype=torch.int32, non_blocking=True).reshape(-1).contiguous()
         eager = return_logits or forced is not None
         if forced is not None:
             forced = forced.to(device=self.device, dtype=torch.int32)
         logits_out, toks = [], []
         toks.append(self.prefill(B, T, ids=ids).clone())
+        st["step"].zero_()
         if return_logits:
             logits_out.append(st["logits"].float().cpu())
         graph = self.use_cuda_graph
@@ -607,9 +624,12 @@ class LocalChain:
         self.engines = engines
 
     @torch.no_grad()
-    def generate(self, input_ids: torch.Tensor, max_length: int, deadline: Optional[float] = None) -> torch.Tensor:
+    def generate(self, input_ids: torch.Tensor, max_length: int, deadline: Optional[float] = None,
+                 do_sample: bool = False, temperature: float = 0.8, top_k: int = 50, top_p: float = 0.95,
+                 seed: int = 0) -> torch.Tensor:
         if len(self.engines) == 1:
-            return self.engines[0].generate(input_ids, max_length, deadline=deadline)
+            return self.engines[0].generate(input_ids, max_length, deadline=deadline, do_sample=do_sample,
+                                            temperature=temperature, top_k=top_k, top_p=top_p, seed=seed)
         B, T = input_ids.shape
         n_new = max_length - T
         if n_new <= 0:
@@ -617,10 +637,18 @@ class LocalChain:
         first, last = self.engines[0], self.engines[-1]
         for e in self.engines:
             e.start_batch(B, T, max_length)
+        mode = dict(temperature=float(temperature), top_k=int(top_k), top_p=float(top_p)) if do_sample else None
+        if mode != last.sampling:  # the token choice lives on the last stage
+            last.sampling = mode
+            last._graphs.clear()
+        lst = last._state(B)
+        lst["seed"].fill_(int(seed))
+        lst["step"].fill_(-1)
         x = input_ids.to(device=first.device, dtype=torch.int32).reshape(-1).contiguous()
         x = first.prefill(B, T, ids=x)
         for e in self.engines[1:]:
             x = e.prefill(B, T, hidden=x)
+        lst["step"].zero_()
         toks = [x.clone()]
         for i in range(n_new - 1):
             if deadline is not None and (i & 7) == 0:

@@ -298,3 +298,25 @@ def linear_splitk_gated_silu(x, w_gu, scratch, out=None):
         _p(x), _p(w_gu), _p(out), M, F, K, _p(scratch), _bytes(scratch), _stream()))
     launch_count += 1
     return out
+
+
+def sample(logits, out=None, temperature=0.8, top_k=50, top_p=0.95, seed=None, step=None, debug_cap=0):
+    """Temperature -> top-k -> top-p -> multinomial on bf16 logits [B, V].
+    seed: int64 device tensor [1]; step: int32 device tensor [1] (both optional).
+    debug_cap > 0 additionally returns (probs [B, cap] fp32, ids [B, cap] int32) of the kept set."""
+    global launch_count
+    if logits.dtype != torch.bfloat16 or not logits.is_cuda or logits.stride(1) != 1:
+        raise ValueError("sample needs a CUDA bf16 tensor with unit inner stride")
+    _req(seed, torch.int64), _req(step, torch.int32)
+    B, V = logits.shape
+    if out is None:
+        out = torch.empty(B, dtype=torch.int32, device=logits.device)
+    probs = ids = None
+    if debug_cap:
+        probs = torch.empty(B, debug_cap, dtype=torch.float32, device=logits.device)
+        ids = torch.empty(B, debug_cap, dtype=torch.int32, device=logits.device)
+    _lib.check("dli_sample_bf16", _lib.load().dli_sample_bf16(
+        _p(logits), logits.stride(0), _p(out), B, V, float(temperature), int(top_k), float(top_p), _p(seed), _p(step),
+        _p(probs), _p(ids), int(debug_cap), _stream()))
+    launch_count += 1
+    return (out, probs, ids) if debug_cap else out

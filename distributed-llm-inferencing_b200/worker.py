@@ -19,7 +19,9 @@ Deliberate deviations from the reference, each a fixed defect:
   Q1  `shard_id: 0` is accepted (the reference's `all([...])` rejects falsy ids);
   Q2  every shard id of the request is used (the reference silently uses only the
       first), as an in-process layer-range chain; the shards must cover all layers;
-  Q3  greedy decoding (the parity mode); the reference samples with no seed;
+  Q3  sampling like the reference by default (do_sample=True, top_k=50, top_p=0.95,
+      temperature=0.8) but reproducible: optional request fields `seed` and
+      `do_sample` (false = greedy, the parity mode);
   Q6  the timeout is checked between decode steps, not only around generate();
   Q7  /unload_model also frees the lazily created per-shard engines;
   USE_GPU defaults to 1: this worker has no CPU path (the reference defaults to 0).
@@ -175,7 +177,8 @@ class Worker:
             start_time = time.time()
             deadline = start_time + timeout
             if shard_ids:
-                result = self.run_shard_inference(model_name, prompt, shard_ids, max_length, deadline)
+                result = self.run_shard_inference(model_name, prompt, shard_ids, max_length, deadline,
+                                                  self._gen_kwargs(data))
             else:
                 if model_name not in self.loaded_models:
                     resp, code = self.load_model({"model_name": model_name})
@@ -185,7 +188,7 @@ class Worker:
                 ids = tokenizer(prompt, return_tensors="pt")["input_ids"]
                 if (time.time() - start_time) > timeout:
                     raise TimeoutError("Inference preparation timed out")
-                outputs = model.generate(ids, max_length=max_length, deadline=deadline)
+                outputs = model.generate(ids, max_length=max_length, deadline=deadline, **self._gen_kwargs(data))
                 result = tokenizer.decode(outputs[0], skip_special_tokens=True)
                 if (time.time() - start_time) > timeout:
                     raise TimeoutError("Inference generation timed out")
@@ -195,7 +198,13 @@ class Worker:
         except Exception as e:  # noqa: BLE001
             return {"status": "error", "message": f"Inference failed: {str(e)}"}, 500
 
-    def run_shard_inference(self, model_name, prompt, shard_ids, max_length, deadline=None):
+    @staticmethod
+    def _gen_kwargs(data):
+        """generate() arguments of worker/app.py:297-305, plus the optional overrides."""
+        return dict(do_sample=bool(data.get("do_sample", True)), temperature=0.8, top_k=50, top_p=0.95,
+                    seed=int(data.get("seed", int(time.time() * 1e6) & 0x7fffffff)))
+
+    def run_shard_inference(self, model_name, prompt, shard_ids, max_length, deadline=None, gen=None):
         """worker/app.py:332-372, with the intended semantics: the listed shards are
         layer ranges run in order on hidden states (lazy weight load on first use)."""
         from .engine import LocalChain
@@ -212,7 +221,7 @@ class Worker:
             engines.append(self.loaded_models[key])
         tokenizer = self.loaded_tokenizers[model_name]
         ids = tokenizer(prompt, return_tensors="pt")["input_ids"]
-        outputs = LocalChain(engines).generate(ids, max_length=max_length, deadline=deadline)
+        outputs = LocalChain(engines).generate(ids, max_length=max_length, deadline=deadline, **(gen or {}))
         return tokenizer.decode(outputs[0], skip_special_tokens=True)
 
     # ------------------------------------------------------------------ WSGI

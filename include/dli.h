@@ -263,6 +263,23 @@ int dli_rmsnorm_gemv_gated_silu_bf16(const void* h, const void* ln_w, float eps,
 int dli_argmax_bf16(const void* logits, int ld, int32_t* out, int B, int V,
                     dli_stream_t stream);
 
+/* The reference's default sampling epilogue (worker/app.py:297-305: do_sample=True,
+ * top_k=50, top_p=0.95, temperature=0.8): TemperatureLogitsWarper -> TopKLogitsWarper
+ * -> TopPLogitsWarper -> softmax -> multinomial (TF:generation/logits_process.py,
+ * TF:generation/utils.py:2762-2793) on fp32 copies of the bf16 logits.  Top-k keeps
+ * ties at the threshold, top-p keeps at least one token, exactly as the HF warpers do.
+ * The draw is an inverse-CDF lookup with a Philox4x32-10 uniform keyed by
+ * (*seed, *step, row): reproducible for a given seed, equal to torch.multinomial in
+ * distribution (not in bit pattern: torch uses another stream and algorithm).
+ * seed/step are DEVICE pointers so a captured graph can be replayed (NULL = 0).
+ * top_k = 0 disables top-k (then V <= 2048); top_k <= 2048.
+ * dbg_probs/dbg_ids [B, dbg_cap] (optional): the kept tokens in descending
+ * probability and their renormalised probabilities, -1/0 padded (parity tests). */
+int dli_sample_bf16(const void* logits, int ld, int32_t* out, int B, int V,
+                    float temperature, int top_k, float top_p, const uint64_t* seed,
+                    const int32_t* step, float* dbg_probs, int32_t* dbg_ids, int dbg_cap,
+                    dli_stream_t stream);
+
 /* Device-side bookkeeping between two decode steps, so a whole step can live in
  * a replayed CUDA graph with no host round trip (the reference syncs the host
  * every token: stopping criteria at TF:generation/utils.py:2804 and the

@@ -143,17 +143,22 @@ def test_inference_sharded_and_unsharded_equal_oracle(cuda, shard_dirs):
     for i, p in enumerate(paths):
         assert _post(c, "/load_shard", {"model_name": "org/tiny", "shard_id": i, "shard_path": p})[0] == 200
     code, body = _post(c, "/inference", {"model_name": "org/tiny", "prompt": prompt, "shard_ids": [0, 1],
-                                         "max_length": T + n_new})
+                                         "max_length": T + n_new, "do_sample": False})
     assert code == 200 and set(body) == {"status", "result", "execution_time"} and body["status"] == "success"
     got = [int(t) for t in body["result"].split()]
     assert got[:T] == ids.tolist() and len(got) == T + n_new
     # unsharded path through /load_model (lazy, like the reference) gives the same tokens
-    code, body2 = _post(c, "/inference", {"model_name": full, "prompt": prompt, "max_length": T + n_new})
+    code, body2 = _post(c, "/inference", {"model_name": full, "prompt": prompt, "max_length": T + n_new,
+                                          "do_sample": False})
     assert code == 200 and body2["result"] == body["result"]
     # against the oracle: identical over the margin-safe prefix of this fixture sequence
     noise = 2.0 * case["hf_err"].max()
     n_safe = int((case["margin"][:, 0] > 2.0 * noise).int().cumprod(0).sum())
     assert got[T:T + min(n_safe, n_new)] == want[0, T:T + min(n_safe, n_new)].tolist()
+    # default request = the reference's sampling call; a seed makes it reproducible
+    req = {"model_name": full, "prompt": prompt, "max_length": T + n_new, "seed": 5}
+    (c1, b1), (c2, b2) = _post(c, "/inference", req), _post(c, "/inference", req)
+    assert c1 == c2 == 200 and b1["result"] == b2["result"] and len(b1["result"].split()) == T + n_new
     # a shard subset that does not cover all layers is refused loudly
     code, body3 = _post(c, "/inference", {"model_name": "org/tiny", "prompt": prompt, "shard_ids": [1]})
     assert code == 500 and "not all of" in body3["message"]
