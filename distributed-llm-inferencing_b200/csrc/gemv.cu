@@ -19,6 +19,8 @@
 // first task's weights ahead of that wait (registers, or cp.async into shared
 // memory) was measured and gave nothing: the shared-memory variant costs L1
 // capacity that the streaming loads need (profiles/r1_notes.md).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace dli {
@@ -37,7 +39,7 @@ template <int M, bool kGated, bool kNorm>
 __global__ void __launch_bounds__(kGemvThreads, M <= 2 ? 3 : 2)
 gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* __restrict__ bias,
             const bf16* residual, bf16* y, int N, int K, int epilogue, int ntasks,
-            const bf16* __restrict__ ln_w, float eps) {
+            const bf16* __restrict__ ln_w, float eps, int pf_l2) {
   // partial sums: [parity][value][thread]; value = row * M + m
   __shared__ float part[2][kGemvRows * M][kGemvThreads];
   __shared__ float red[kGemvWarps][M];
@@ -65,6 +67,14 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
   };
 
   const uint4* wrow[kGemvRows];
+  if (pf_l2 && (int)blockIdx.x < ntasks && tid < kGemvRows) {
+    // Before waiting for the previous kernel: pull the head of this CTA's first weight rows into L2
+    // with one bulk prefetch per row (no registers, shared memory or L1 footprint), so HBM keeps
+    // streaming through the kernel boundary.  Worth ~1.5 us per layer on the 4-GEMV chain.
+    row_ptrs(blockIdx.x, wrow);
+    const uint32_t bytes = (uint32_t)min((size_t)K * 2, (size_t)pf_l2) & ~15u;
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(wrow[tid]), "r"(bytes) : "memory");
+  }
   pdl_wait();
   pdl_trigger();  // the grid is resident at once (grid <= SMs x occupancy): successors may queue behind us
 
@@ -214,8 +224,9 @@ static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf1
     occ_dyn = dyn;
   }
   const int grid = ntasks < sms * occ ? ntasks : sms * occ;
+  static const int pf_l2 = getenv("DLI_GEMV_PF_L2") ? atoi(getenv("DLI_GEMV_PF_L2")) : 8192;
   DLI_LAUNCH("gemv_kernel", gemv_kernel<M, kGated, kNorm>, dim3(grid), dim3(kGemvThreads), dyn, s, x, w, bias, residual,
-             y, N, K, epilogue, ntasks, ln_w, eps);
+             y, N, K, epilogue, ntasks, ln_w, eps, pf_l2);
   return DLI_OK;
 }
 
