@@ -45,8 +45,25 @@ struct DecodeSmem {
   static constexpr int kRowBytes = HD * 2;
   static constexpr int kQBytes = 16 * kRowBytes;
   static constexpr int kTileBytes = kAttnTile * kRowBytes;
-  static constexpr int kTotal = kQBytes + 2 * NS * kTileBytes;  // Q + NS stages x (K, V)
+  static constexpr int kStageTotal = kQBytes + 2 * NS * kTileBytes;  // Q + NS stages x (K, V)
+  // NS == 4 (the few-CTA, batch-1 configuration) also holds this CTA's merged partial
+  // (16 x HD fp32 + max/sum) where the other CTAs of its cluster can read it (DSMEM)
+  static constexpr int kClusterBytes = NS == 4 ? 16 * HD * 4 + 128 : 0;
+  static constexpr int kTotal = kStageTotal + kClusterBytes;
 };
+
+// ---- thread-block cluster helpers (distributed shared memory) ------------------------------------
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t local_smem_addr, uint32_t cta_rank) {
+  uint32_t remote;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_smem_addr), "r"(cta_rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+  return v;
+}
 
 // NS = cp.async stages.  NS = 2 keeps 3 CTAs per SM for large batches; NS = 4 puts a whole
 // 256-token split in flight at once, which is what a batch-1 step (latency-bound, one CTA
@@ -60,7 +77,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
                          float* __restrict__ part_o, float* __restrict__ part_ml, int H, int KV,
                          int page_shift, int num_splits, float scale_log2, int window,
                          int fused, const bf16* __restrict__ cos_t, const bf16* __restrict__ sin_t,
-                         bf16* k_cache_w, bf16* v_cache_w, int pdl_early, const uint8_t* __restrict__ pf_ptr,
+                         bf16* k_cache_w, bf16* v_cache_w, int cluster_merge, const uint8_t* __restrict__ pf_ptr,
                          size_t pf_bytes) {
   using L = DecodeSmem<HD, NS>;
   constexpr int RB = L::kRowBytes;
@@ -82,7 +99,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     return;
   }
   pdl_wait();  // seq_lens, q and the cache pages come from earlier kernels of the stream
-  if (pdl_early) pdl_trigger();
+  pdl_trigger();
   const int seq_len = seq_lens[b];
   const int first_tok = (window > 0 && seq_len > window) ? seq_len - window : 0;
   const int tile_lo = first_tok / kAttnTile;
@@ -293,6 +310,13 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     const int h = kvh * G + row;
     if (num_splits == 1) {
       out[((size_t)b * H + h) * HD + col] = __float2bfloat16_rn(lsum > 0.f ? acc / lsum : 0.f);
+    } else if (cluster_merge) {
+      float* cpo = reinterpret_cast<float*>(smem + L::kStageTotal);
+      cpo[idx] = acc;
+      if (col == 0) {
+        cpo[16 * HD + row * 2 + 0] = mmax;
+        cpo[16 * HD + row * 2 + 1] = lsum;
+      }
     } else {
       const size_t slot = ((size_t)b * H + h) * num_splits + split;
       part_o[slot * HD + col] = acc;
@@ -301,6 +325,33 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
         part_ml[slot * 2 + 1] = lsum;
       }
     }
+  }
+  if (num_splits > 1 && cluster_merge) {
+    // The num_splits CTAs of this (sequence, kv head) are one thread-block cluster: after a
+    // cluster barrier each CTA merges its share of the G*HD outputs by reading every CTA's
+    // partial through distributed shared memory, in split order (deterministic) — no scratch
+    // buffer in HBM, no second kernel.
+    cluster_sync_all();
+    const uint32_t cpo_addr = smem_u32(smem + L::kStageTotal);
+    const int total = G * HD;
+    const int per = (total + num_splits - 1) / num_splits;
+    const int lo = split * per, hi = min(lo + per, total);
+    for (int idx = lo + tid; idx < hi; idx += kAttnThreads) {
+      const int row = idx / HD, col = idx - row * HD;
+      float mmax = -INFINITY;
+      for (int sp = 0; sp < num_splits; ++sp)
+        mmax = fmaxf(mmax, ld_dsmem_f32(cpo_addr + (16 * HD + row * 2) * 4, sp));
+      float acc = 0.f, lsum = 0.f;
+      if (mmax != -INFINITY) {
+        for (int sp = 0; sp < num_splits; ++sp) {
+          const float f = exp2f((ld_dsmem_f32(cpo_addr + (16 * HD + row * 2) * 4, sp) - mmax) * scale_log2);
+          acc += f * ld_dsmem_f32(cpo_addr + idx * 4, sp);
+          lsum += f * ld_dsmem_f32(cpo_addr + (16 * HD + row * 2 + 1) * 4, sp);
+        }
+      }
+      out[((size_t)b * H + kvh * G + row) * HD + col] = __float2bfloat16_rn(lsum > 0.f ? acc / lsum : 0.f);
+    }
+    cluster_sync_all();  // nobody leaves while a peer may still read its shared memory
   }
 }
 
@@ -375,16 +426,28 @@ static int launch_decode_ns(const void* q, int q_stride, const void* k_cache, co
   const float scale_log2 = scale * 1.4426950408889634f;
   float* part_o = reinterpret_cast<float*>(scratch);
   float* part_ml = part_o ? part_o + (size_t)B * H * num_splits * HD : nullptr;
-  // prefetch CTAs only when the attention grid leaves SMs idle
   const int sms = sm_count_cached();
   const int attn_ctas = num_splits * KV * B;
+  if (NS == 4 && num_splits > 1 && num_splits <= 8 && scratch == nullptr) {
+    // no scratch given: the splits of a (sequence, kv head) run as one thread-block cluster and
+    // merge through distributed shared memory inside the kernel
+    cudaError_t e = launch_kernel_cluster(
+        paged_attn_decode_kernel<HD, NS>, dim3(num_splits, KV, B), dim3(kAttnThreads), (size_t)L::kTotal, s,
+        (unsigned)num_splits, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table,
+        max_pages, seq_lens, (bf16*)out, (float*)nullptr, (float*)nullptr, H, KV, page_shift, num_splits, scale_log2,
+        window, fused, (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, 1,
+        (const uint8_t*)nullptr, (size_t)0);
+    if (e != cudaSuccess) return fail(DLI_ERR_CUDA, "paged_attn_decode_kernel (cluster): %s", cudaGetErrorString(e));
+    return DLI_OK;
+  }
+  // prefetch CTAs only when the attention grid leaves SMs idle
   int extra = 0;
   if (pf_a && pf_a_bytes && attn_ctas < sms) extra = (sms - attn_ctas) / (KV * B);
   dim3 grid(num_splits + extra, KV, B);
   DLI_LAUNCH("paged_attn_decode_kernel", paged_attn_decode_kernel<HD, NS>, grid, dim3(kAttnThreads),
              (size_t)L::kTotal, s, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table,
              max_pages, seq_lens, (bf16*)out, part_o, part_ml, H, KV, page_shift, num_splits, scale_log2, window,
-             fused, (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, 1,
+             fused, (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, 0,
              (const uint8_t*)(extra ? pf_a : nullptr), extra ? pf_a_bytes : (size_t)0);
   if (num_splits > 1) {
     const int n_bh = B * H;
@@ -443,10 +506,13 @@ int dli_paged_attn_decode_bf16(const void* q, int q_stride, const void* k_cache,
                 "dli_paged_attn_decode_bf16: bad q_stride/max_pages/window");
   DLI_CHECK_ARG(aligned16(q) && aligned16(k_cache) && aligned16(v_cache) && aligned16(scratch),
                 "dli_paged_attn_decode_bf16: pointers must be 16-byte aligned");
+
   if (num_splits > 1) {
     const size_t need = dli_paged_attn_decode_scratch_bytes(B, H, hd, num_splits);
-    DLI_CHECK_ARG(scratch && scratch_bytes >= need,
-                  "dli_paged_attn_decode_bf16: scratch too small (%zu < %zu bytes)", scratch_bytes, need);
+    const bool cluster_ok = scratch == nullptr && num_splits <= 8 && num_splits * KV * B <= sm_count_cached();
+    DLI_CHECK_ARG(cluster_ok || (scratch && scratch_bytes >= need),
+                  "dli_paged_attn_decode_bf16: scratch too small (%zu < %zu bytes); scratch may only be NULL for <= 8 splits and "
+                  "num_splits*KV*B <= number of SMs (cluster merge)", scratch_bytes, need);
   }
   if (B == 0) return DLI_OK;
   int shift = 0;
@@ -486,10 +552,13 @@ extern "C" int dli_paged_attn_decode_fused_bf16(void* qkv, int row_stride, const
   DLI_CHECK_ARG(aligned16(qkv) && aligned16(k_cache) && aligned16(v_cache) && aligned16(scratch) &&
                     aligned16(cos) && aligned16(sin),
                 "dli_paged_attn_decode_fused_bf16: pointers must be 16-byte aligned");
+
   if (num_splits > 1) {
     const size_t need = dli_paged_attn_decode_scratch_bytes(B, H, hd, num_splits);
-    DLI_CHECK_ARG(scratch && scratch_bytes >= need,
-                  "dli_paged_attn_decode_fused_bf16: scratch too small (%zu < %zu bytes)", scratch_bytes, need);
+    const bool cluster_ok = scratch == nullptr && num_splits <= 8 && num_splits * KV * B <= sm_count_cached();
+    DLI_CHECK_ARG(cluster_ok || (scratch && scratch_bytes >= need),
+                  "dli_paged_attn_decode_fused_bf16: scratch too small (%zu < %zu bytes); scratch may only be NULL for <= 8 splits and "
+                  "num_splits*KV*B <= number of SMs (cluster merge)", scratch_bytes, need);
   }
   if (B == 0) return DLI_OK;
   int shift = 0;

@@ -420,10 +420,16 @@ class ShardEngine:
         dev = self.device
         if (B, mb) not in self._dec:
             splits = self._num_splits(B)
+            # few CTAs (small batch): the splits of a (sequence, kv head) form a thread-block cluster
+            # and merge through distributed shared memory — no scratch buffer, no merge kernel
+            cluster = (os.environ.get("DLI_ATTN_CLUSTER", "0") == "1" and splits > 1
+                       and min(splits, 8) * self.spec.n_kv_heads * B <= self.sms)
+            if cluster:
+                splits = min(splits, 8)
             nbytes = ops.attn_decode_scratch_bytes(B, self.spec.n_heads, self.spec.head_dim, splits)
             self._dec[(B, mb)] = {
                 "splits": splits,
-                "scratch": torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=dev),
+                "scratch": None if cluster else torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=dev),
                 "positions": torch.zeros(B, dtype=torch.int32, device=dev),
                 "seq_lens": torch.zeros(B, dtype=torch.int32, device=dev),
                 "seq_ids": torch.arange(mb * B, (mb + 1) * B, dtype=torch.int32, device=dev),

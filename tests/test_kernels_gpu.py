@@ -502,3 +502,33 @@ def test_batched_decode_uses_splitk_and_matches_small_batch(cuda):
     for b in range(2):
         n_safe = int((c["margin"][:, b] > 2.0 * noise).int().cumprod(0).sum())
         assert torch.equal(out[b, T:T + n_safe], c["tokens"][b, :n_safe])
+
+
+@pytest.mark.parametrize("B,H,KV,hd,page,lens,splits,window",
+                         [(1, 32, 8, 128, 16, [2049], 8, 0), (2, 32, 8, 128, 16, [700, 64], 4, 0),
+                          (1, 32, 4, 64, 32, [300], 3, 0), (1, 64, 8, 128, 16, [1500], 8, 512)])
+def test_cluster_dsmem_merge_matches_scratch_merge(cuda, B, H, KV, hd, page, lens, splits, window):
+    """scratch == NULL: the splits run as one thread-block cluster and merge through distributed
+    shared memory; same result as partials-in-HBM + merge kernel up to the order of one fp32 sum."""
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(31 + H)
+    page_table, kc, vc = _paged_cache(B, max(lens), KV, hd, page, cuda, gen)
+    qkv = torch.randn(B, (H + 2 * KV) * hd, device=cuda, generator=gen).to(BF)
+    cos, sin = _hf_rope_tables(hd, 10000.0, max(lens) + 1, cuda)
+    seq_lens = torch.tensor(lens, device=cuda, dtype=torch.int32)
+    scratch = torch.empty(max(ops.attn_decode_scratch_bytes(B, H, hd, splits), 4) // 4, device=cuda, dtype=torch.float32)
+    outs = []
+    for sc in (scratch, None):
+        kc2, vc2 = kc.clone(), vc.clone()
+        out = torch.empty(B, H * hd, device=cuda, dtype=BF)
+        ops.paged_attn_decode_fused(qkv.clone(), cos, sin, kc2, vc2, page_table, seq_lens, out, H, KV, hd, hd ** -0.5,
+                                    num_splits=splits, scratch=sc, window=window)
+        outs.append(out)
+    _ulp_close(outs[1], outs[0], max_ulp=1, min_exact=0.99)
+    # too many splits for a cluster and no scratch: refused with a clear message
+    from dli_b200 import _lib
+    with pytest.raises(_lib.DliError, match="cluster merge"):
+        ops.paged_attn_decode_fused(qkv.clone(), cos, sin, kc.clone(), vc.clone(), page_table, seq_lens,
+                                    torch.empty(B, H * hd, device=cuda, dtype=BF), H, KV, hd, hd ** -0.5,
+                                    num_splits=9, scratch=None)
