@@ -40,7 +40,8 @@ __device__ __forceinline__ void argmax_combine(float& v, int& i, float ov, int o
 }
 
 __global__ void __launch_bounds__(kArgmaxThreads)
-argmax_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out, int V) {
+argmax_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out, int V,
+              float* __restrict__ cand, int idx_offset) {
   __shared__ float sv[kArgmaxThreads / 32];
   __shared__ int si[kArgmaxThreads / 32];
   pdl_wait();
@@ -82,7 +83,15 @@ argmax_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out
       const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
       argmax_combine(best, besti, ov, oi);
     }
-    if (lane == 0) out[blockIdx.x] = besti == 0x7fffffff ? 0 : besti;
+    if (lane == 0) {
+      const int idx = besti == 0x7fffffff ? 0 : besti;
+      if (cand) {  // vocabulary-parallel head: (best logit, global token id) of this slice
+        cand[blockIdx.x * 2] = best;
+        reinterpret_cast<int32_t*>(cand)[blockIdx.x * 2 + 1] = idx + idx_offset;
+      } else {
+        out[blockIdx.x] = idx;
+      }
+    }
   }
 }
 
@@ -104,9 +113,46 @@ __global__ void decode_advance_kernel(const int32_t* __restrict__ tokens, int32_
   if (threadIdx.x == 0) *step = s + 1;
 }
 
+// Global argmax from per-slice candidates [n][B][2] = (best logit, token id bits): highest logit,
+// lowest token id on ties — the same winner a single argmax over the whole row picks.
+__global__ void argmax_merge_kernel(const float* __restrict__ cands, int n, int B, int32_t* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float best = -INFINITY;
+    int besti = 0x7fffffff;
+    for (int s = 0; s < n; ++s) {
+      const float v = cands[((size_t)s * B + b) * 2];
+      const int i = reinterpret_cast<const int32_t*>(cands)[((size_t)s * B + b) * 2 + 1];
+      if (v > best || (v == best && i < besti)) { best = v; besti = i; }
+    }
+    out[b] = besti == 0x7fffffff ? 0 : besti;
+  }
+}
+
 }  // namespace dli
 
 extern "C" {
+
+int dli_argmax_candidate_bf16(const void* logits, int ld, int idx_offset, float* cand, int B, int V,
+                              dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(logits && cand, "dli_argmax_candidate_bf16: null pointer");
+  DLI_CHECK_ARG(B >= 0 && V > 0 && ld >= V && idx_offset >= 0, "dli_argmax_candidate_bf16: bad sizes B=%d V=%d ld=%d", B, V, ld);
+  if (B == 0) return DLI_OK;
+  DLI_LAUNCH("dli_argmax_candidate_bf16", argmax_kernel, dim3(B), dim3(kArgmaxThreads), (size_t)0,
+             static_cast<cudaStream_t>(stream), (const bf16*)logits, ld, (int32_t*)nullptr, V, cand, idx_offset);
+  return DLI_OK;
+}
+
+int dli_argmax_merge(const float* cands, int n, int B, int32_t* out, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(cands && out && n > 0 && B >= 0, "dli_argmax_merge: bad arguments");
+  if (B == 0) return DLI_OK;
+  DLI_LAUNCH("dli_argmax_merge", argmax_merge_kernel, dim3(1), dim3(256), (size_t)0, static_cast<cudaStream_t>(stream),
+             cands, n, B, out);
+  return DLI_OK;
+}
 
 int dli_decode_advance(const int32_t* tokens, int32_t* token_log, int32_t* positions, int32_t* seq_lens,
                        int32_t* step, int B, int log_capacity, dli_stream_t stream) {
@@ -141,7 +187,7 @@ int dli_argmax_bf16(const void* logits, int ld, int32_t* out, int B, int V, dli_
   DLI_CHECK_ARG(B >= 0 && V > 0 && ld >= V, "dli_argmax_bf16: bad sizes B=%d V=%d ld=%d", B, V, ld);
   if (B == 0) return DLI_OK;
   DLI_LAUNCH("dli_argmax_bf16", argmax_kernel, dim3(B), dim3(kArgmaxThreads), (size_t)0, static_cast<cudaStream_t>(stream),
-             (const bf16*)logits, ld, out, V);
+             (const bf16*)logits, ld, out, V, (float*)nullptr, 0);
   return DLI_OK;
 }
 

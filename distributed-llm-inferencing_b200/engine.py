@@ -145,7 +145,11 @@ class PagedKVCache:
 class ShardEngine:
     def __init__(self, spec: ModelSpec, start_layer: int = 0, end_layer: Optional[int] = None,
                  device: str = "cuda:0", max_batch: int = 1, max_seq_len: int = 2048, page_size: int = 16,
-                 use_cuda_graph: bool = True):
+                 use_cuda_graph: bool = True, head_shard: Optional[tuple] = None):
+        """head_shard=(rank, world): vocabulary-parallel lm_head for a pipeline — every stage holds
+        rows [rank*ceil(V/world), ...) of the head (the reference's sharder copies the head into
+        every shard anyway, shard_model.py:76-78), so the last stage does not carry the whole
+        [V, d] matrix on top of its layers; see pipeline.py."""
         if not torch.cuda.is_available():
             raise RuntimeError("ShardEngine needs a CUDA device: this package has no CPU path")
         self.spec = spec
@@ -155,6 +159,12 @@ class ShardEngine:
             raise ValueError(f"bad layer range [{self.start}, {self.end}] for {spec.n_layers} layers")
         self.is_first = self.start == 0
         self.is_last = self.end == spec.n_layers - 1
+        self.head_shard = head_shard
+        if head_shard is not None:
+            r, w = head_shard
+            per = (spec.vocab + w - 1) // w
+            self.v0, self.v1 = min(r * per, spec.vocab), min((r + 1) * per, spec.vocab)
+        self.has_head = self.is_last and head_shard is None  # whole head + token choice on this stage
         self.n_local = self.end - self.start + 1
         self.device = torch.device(device)
         self.max_batch, self.max_seq_len = max_batch, max_seq_len
@@ -208,7 +218,12 @@ class ShardEngine:
                     "wgu": ops.pack_gate_up(sd[p + "mlp.gate_proj.weight"].to(BF), sd[p + "mlp.up_proj.weight"].to(BF)).to(dev),
                     "wdown": t(p + "mlp.down_proj.weight"),
                 })
-            if self.is_last:
+            if self.head_shard is not None:
+                full = sd["lm_head.weight"] if ("lm_head.weight" in sd and not s.tie_embeddings) \
+                    else sd["model.embed_tokens.weight"]
+                self.w["norm"] = t("model.norm.weight")
+                self.w["head"] = full[self.v0:self.v1].to(BF).contiguous().to(dev)
+            elif self.is_last:
                 self.w["norm"] = t("model.norm.weight")
                 if "lm_head.weight" in sd and not s.tie_embeddings:
                     self.w["head"] = t("lm_head.weight")
@@ -262,7 +277,10 @@ class ShardEngine:
                 "ln1": n(d, mean=1.0), "wqkv": n((s.n_heads + 2 * s.n_kv_heads) * hd, d), "wo": n(d, s.n_heads * hd),
                 "ln2": n(d, mean=1.0), "wgu": n(2 * ff, d), "wdown": n(d, ff),
             })
-        if self.is_last:
+        if self.head_shard is not None:
+            self.w["norm"] = n(d, mean=1.0)
+            self.w["head"] = n(self.v1 - self.v0, d)
+        elif self.is_last:
             self.w["norm"] = n(d, mean=1.0)
             self.w["head"] = self.w["embed"] if (s.tie_embeddings and self.is_first) else n(s.vocab, d)
         self._finalize_layers()
@@ -439,10 +457,19 @@ class ShardEngine:
                 "seed": torch.zeros(1, dtype=torch.int64, device=dev),
                 # residual stream of the slot's decode step: stage input (recv target) and output (send source)
                 "h": torch.empty(B, self.spec.d_model, dtype=BF, device=dev),
-                "logits": torch.empty(B, self.spec.vocab, dtype=BF, device=dev) if self.is_last else None,
+                "logits": torch.empty(B, self.spec.vocab, dtype=BF, device=dev) if self.has_head else None,
                 # persistent: its address is baked into the captured decode graph
-                "token_log": torch.zeros(self.max_seq_len, B, dtype=torch.int32, device=dev) if self.is_last else None,
+                "token_log": torch.zeros(self.max_seq_len, B, dtype=torch.int32, device=dev)
+                if (self.has_head or (self.head_shard is not None and self.is_first)) else None,
             }
+            if self.head_shard is not None:
+                st, w = self._dec[(B, mb)], self.head_shard[1]
+                st["hf"] = torch.empty(B, self.spec.d_model, dtype=BF, device=dev)  # final hidden of the slot
+                st["logits"] = torch.empty(B, self.v1 - self.v0, dtype=BF, device=dev)
+                st["cand"] = torch.zeros(B, 2, dtype=torch.float32, device=dev)  # (best logit, global index bits)
+                if self.is_first:
+                    st["cands"] = torch.zeros(w, B, 2, dtype=torch.float32, device=dev)  # one row per stage
+                    st["cand"] = st["cands"][0]  # stage 0 writes its own candidate in place
         st = self._dec[(B, mb)]
         st["positions"].fill_(prompt_len)
         st["seq_lens"].fill_(prompt_len + 1)
@@ -472,6 +499,8 @@ class ShardEngine:
         if not self.is_last:
             return h
         last_rows = (torch.arange(B, dtype=torch.int32, device=dev) + 1) * T - 1
+        if self.head_shard is not None:
+            return ops.embedding(last_rows, h, out=st["hf"])  # final hidden of the last positions -> all stages
         h_last = ops.embedding(last_rows, h, out=st["h"])  # row gather of the last positions
         self._head(h_last, st["logits"], st["tokens"], st)
         return st["tokens"]
@@ -489,11 +518,12 @@ class ShardEngine:
             else:
                 ops.embedding(st["tokens"], self.w["embed"], out=h)
         self._layers_forward(h, B, st["positions"], st["seq_ids"], st["seq_lens"], None, st)
-        if self.is_last:
+        if self.has_head:
             self._head(h, st["logits"], st["tokens"], st)
-        ops.decode_advance(st["tokens"], st["token_log"] if self.is_last else None, st["positions"], st["seq_lens"],
-                           st["step"])
-        return st["tokens"] if self.is_last else h
+        # head-shard mode: stage 0 logs the token it just consumed (the previous step's choice)
+        log = st["token_log"] if (self.has_head or (self.head_shard is not None and self.is_first)) else None
+        ops.decode_advance(st["tokens"], log, st["positions"], st["seq_lens"], st["step"])
+        return st["tokens"] if self.has_head else h
 
     def decode_step(self, B: int, hidden_in: Optional[torch.Tensor] = None, mb: int = 0):
         """One token for each of the B sequences of slot `mb`.  The stage's whole step
@@ -530,7 +560,54 @@ class ShardEngine:
         g, launches = self._graphs[key]
         g.replay()
         ops.launch_count += launches
-        return st["tokens"] if self.is_last else st["h"]
+        return st["tokens"] if self.has_head else st["h"]
+
+    # ------------------------------------------------------------------ vocabulary-parallel head
+    def head_slice_step(self, B: int, mb: int = 0):
+        """This stage's share of the lm_head for slot mb: final norm + the rows [v0, v1) of the head on
+        st["hf"], then the slice's best (logit, global token id) into st["cand"].  Graph-captured."""
+        st = self._dec[(B, mb)]
+        key = (B, mb, "head")
+
+        def body():
+            s = self.spec
+            if B <= 4 and s.arch == "llama":
+                ops.rmsnorm_linear(st["hf"], self.w["norm"], s.eps, self.w["head"], out=st["logits"])
+            else:
+                xn = self._x[:B]
+                if s.arch == "llama":
+                    ops.add_rmsnorm(st["hf"], self.w["norm"], s.eps, out=xn)
+                else:
+                    ops.add_layernorm(st["hf"], self.w["norm"], self.w["normb"], s.eps, out=xn)
+                ops.linear(xn, self.w["head"], out=st["logits"])
+            ops.argmax_candidate(st["logits"], self.v0, st["cand"])
+
+        self._workspace(B)
+        if not self.use_cuda_graph:
+            body()
+            return st["cand"]
+        if key not in self._graphs:
+            side = torch.cuda.Stream(device=self.device)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                body()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            n0 = ops.launch_count
+            with torch.cuda.graph(g):
+                body()
+            self._graphs[key] = (g, ops.launch_count - n0)
+        g, launches = self._graphs[key]
+        g.replay()
+        ops.launch_count += launches
+        return st["cand"]
+
+    def combine_candidates(self, B: int, mb: int = 0):
+        """Stage 0: global argmax over the stages' candidates -> st["tokens"] (lowest id wins ties)."""
+        st = self._dec[(B, mb)]
+        ops.argmax_merge(st["cands"], st["tokens"])
+        return st["tokens"]
 
     def decode_step_host(self, tokens_in: torch.Tensor, tokens_out: torch.Tensor) -> torch.Tensor:
         """One decode step with HOST buffers, the per-token call a streaming client

@@ -320,3 +320,24 @@ def sample(logits, out=None, temperature=0.8, top_k=50, top_p=0.95, seed=None, s
         _p(probs), _p(ids), int(debug_cap), _stream()))
     launch_count += 1
     return (out, probs, ids) if debug_cap else out
+
+
+def argmax_candidate(logits, idx_offset, cand):
+    """Best (logit, idx_offset + index) of each row of a logits slice -> cand [B, 2] float32."""
+    global launch_count
+    _req(cand, torch.float32)
+    B, V = logits.shape
+    _lib.check("dli_argmax_candidate_bf16", _lib.load().dli_argmax_candidate_bf16(
+        _p(logits), logits.stride(0), int(idx_offset), _p(cand), B, V, _stream()))
+    launch_count += 1
+    return cand
+
+
+def argmax_merge(cands, out):
+    """cands [n, B, 2] float32 (per-slice candidates) -> out int32 [B]: the global greedy token."""
+    global launch_count
+    _req(cands, torch.float32), _req(out, torch.int32)
+    n, B = cands.shape[0], cands.shape[1]
+    _lib.check("dli_argmax_merge", _lib.load().dli_argmax_merge(_p(cands), n, B, _p(out), _stream()))
+    launch_count += 1
+    return out

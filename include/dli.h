@@ -263,6 +263,15 @@ int dli_rmsnorm_gemv_gated_silu_bf16(const void* h, const void* ln_w, float eps,
 int dli_argmax_bf16(const void* logits, int ld, int32_t* out, int B, int V,
                     dli_stream_t stream);
 
+/* Vocabulary-parallel greedy head (pipeline stages each hold a row slice of lm_head):
+ * dli_argmax_candidate_bf16 writes, per row b, cand[b] = (best logit as fp32, idx_offset +
+ * its index, stored as int32 bits in the second float) for a logits SLICE [B, V_slice];
+ * dli_argmax_merge picks, from n such candidate arrays [n, B, 2], the highest logit with
+ * the lowest token id on ties — exactly what dli_argmax_bf16 returns on the whole row. */
+int dli_argmax_candidate_bf16(const void* logits, int ld, int idx_offset, float* cand, int B,
+                              int V, dli_stream_t stream);
+int dli_argmax_merge(const float* cands, int n, int B, int32_t* out, dli_stream_t stream);
+
 /* The reference's default sampling epilogue (worker/app.py:297-305: do_sample=True,
  * top_k=50, top_p=0.95, temperature=0.8): TemperatureLogitsWarper -> TopKLogitsWarper
  * -> TopPLogitsWarper -> softmax -> multinomial (TF:generation/logits_process.py,

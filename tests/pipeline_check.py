@@ -13,7 +13,8 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 from golden_util import load_case, spec_kwargs  # noqa: E402
 
 from dli_b200.engine import ModelSpec, ShardEngine  # noqa: E402
-from dli_b200.pipeline import EngineStage, PipelineRunner, build_stage_engine, init_distributed  # noqa: E402
+from dli_b200.pipeline import (EngineStage, PipelineRunner, VocabParallelRunner, build_stage_engine,  # noqa: E402
+                               init_distributed)
 from oracle import decoder_ref as R  # noqa: E402
 
 
@@ -24,23 +25,29 @@ def main():
     sd = R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"])
     B, T = c["prompts"].shape
     rounds, M, b = 6, B, 1  # one sequence per micro-batch slot
-    eng = build_stage_engine(spec, rank, world, local, max_batch=M * b, max_seq_len=128)
+    vp = os.environ.get("DLI_PIPE_VP", "0") == "1"  # vocabulary-parallel head
+    eng = build_stage_engine(spec, rank, world, local, max_batch=M * b, max_seq_len=128, vocab_parallel=vp)
     eng.load_state_dict(sd)
     stage = EngineStage(eng, b, T, T + rounds + 2, M)
     if stage.is_first:
         for mb in range(M):
             stage.prompt_ids[mb] = c["prompts"][mb].to("cuda", torch.int32).contiguous()
-    runner = PipelineRunner(stage, rank, world, M)
+    runner = (VocabParallelRunner if vp else PipelineRunner)(stage, rank, world, M)
     runner.run("prefill")
     first = None
-    if stage.is_last:
+    if stage.is_last and not vp:
         first = torch.stack([eng._state(b, mb)["tokens"].clone() for mb in range(M)])  # [M, b]
     runner.run("decode", rounds)
     torch.cuda.synchronize()
     ok = True
-    if stage.is_last:
+    holder = stage.is_first if vp else stage.is_last  # who ends up with the tokens
+    if holder:
         logs = torch.stack([eng._state(b, mb)["token_log"][:rounds, 0] for mb in range(M)])  # [M, rounds]
-        got = torch.cat((first[:, :1], logs), dim=1).cpu().long()  # [M, 1 + rounds]
+        if vp:  # stage 0 logged the token it consumed at each step; the last choice is still in `tokens`
+            final = torch.stack([eng._state(b, mb)["tokens"].clone() for mb in range(M)])
+            got = torch.cat((logs, final[:, :1]), dim=1).cpu().long()
+        else:
+            got = torch.cat((first[:, :1], logs), dim=1).cpu().long()  # [M, 1 + rounds]
         full = ShardEngine(spec, device=f"cuda:{local}", max_batch=B, max_seq_len=128)
         full.load_state_dict(sd)
         want = full.generate(c["prompts"], T + 1 + rounds)[:, T:]

@@ -125,3 +125,104 @@ def test_stage_layer_ranges_follow_reference_formula():
     assert shard_ranges(6, 4) == [(0, 0), (1, 1), (2, 2), (3, 5)]  # remainder on the last shard
     with pytest.raises(ValueError):
         shard_ranges(2, 3)
+
+
+# ------------------------------------------------------------------ vocabulary-parallel head schedule
+class ToyVPStage(ToyStage):
+    """ToyStage whose 'head' is split over the stages: stage s proposes
+    (value = (sum(hf) * (s + 3)) % 17, id = 100 * s + sum(hf) % 7); the global token is the id of
+    the highest value (lowest id on ties)."""
+
+    def __init__(self, rank, world, n_micro, b, d):
+        super().__init__(rank, world, n_micro, b, d)
+        self.world = world
+        self.hf = [torch.zeros(b, d, dtype=torch.float32) for _ in range(n_micro)]
+        self.cand = [torch.zeros(b, 2, dtype=torch.float32) for _ in range(n_micro)]
+        self.cands = [torch.zeros(world, b, 2, dtype=torch.float32) for _ in range(n_micro)]
+        self.final = [[] for _ in range(n_micro)]
+
+    def compute(self, kind, mb):
+        if self.is_first:
+            src = self.prompts[mb] if kind == "prefill" else self.tokens[mb].float()
+            h = src[:, None].expand(self.b, self.d).clone()
+        else:
+            h = (self.pf_in if kind == "prefill" else self.hidden[mb]).clone()
+        h = h * 3 + (self.rank + 1) + self.steps[mb]
+        self.steps[mb] += 1
+        if self.is_last:
+            self.hf[mb].copy_(h)
+            return self.hf[mb]
+        self.hidden[mb].copy_(h)
+        return self.hidden[mb]
+
+    def hf_buffer(self, mb):
+        return self.hf[mb]
+
+    @staticmethod
+    def propose(hf, s):
+        tot = hf.sum(dim=1).long()
+        return ((tot * (s + 3)) % 17).float(), (100 * s + tot % 7).float()
+
+    def head_slice(self, mb):
+        val, idx = self.propose(self.hf[mb], self.rank)
+        tgt = self.cands[mb][0] if self.is_first else self.cand[mb]
+        tgt[:, 0], tgt[:, 1] = val, idx
+        return tgt
+
+    def cand_buffer(self, src, mb):
+        return self.cands[mb][src]
+
+    def combine(self, mb):
+        c = self.cands[mb]  # [world, b, 2]
+        key = c[:, :, 0] * 10000 - c[:, :, 1]  # highest value, then lowest id
+        win = key.argmax(dim=0)
+        tok = c[win, torch.arange(self.b), 1].int()
+        self.tokens[mb].copy_(tok)
+        self.final[mb].append(tok.clone())
+
+
+def sequential_vp(world, n_micro, b, d, rounds):
+    logs = []
+    for mb in range(n_micro):
+        log, src = [], torch.arange(b, dtype=torch.float32) + 10 * mb
+        for step in range(rounds + 1):
+            h = src[:, None].expand(b, d).clone()
+            for s in range(world):
+                h = h * 3 + (s + 1) + step
+            vals, ids = zip(*(ToyVPStage.propose(h, s) for s in range(world)))
+            key = torch.stack(vals) * 10000 - torch.stack(ids)
+            tok = torch.stack(ids)[key.argmax(dim=0), torch.arange(b)].int()
+            log.append(tok)
+            src = tok.float()
+        logs.append(torch.stack(log))
+    return logs
+
+
+def _vp_worker(rank, world, port, n_micro, rounds, q):
+    from dli_b200.pipeline import VocabParallelRunner
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    stage = ToyVPStage(rank, world, n_micro, b=2, d=4)
+    runner = VocabParallelRunner(stage, rank, world, n_micro)
+    runner.run("prefill")
+    runner.run("decode", rounds)
+    if rank == 0:
+        q.put([torch.stack(l).tolist() for l in stage.final])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_micro,rounds", [(2, 3, 3), (2, 1, 2), (3, 4, 2), (3, 2, 3)])
+def test_vocab_parallel_pipeline_matches_sequential_over_gloo(world, n_micro, rounds):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_vp_worker, args=(r, world, port, n_micro, rounds, q)) for r in range(world)]
+    [p.start() for p in procs]
+    got = q.get(timeout=120)
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    want = sequential_vp(world, n_micro, 2, 4, rounds)
+    for mb in range(n_micro):
+        assert got[mb] == want[mb].tolist(), (mb, got[mb], want[mb].tolist())

@@ -11,11 +11,14 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+@pytest.mark.parametrize("vp", [0, 1])
 @pytest.mark.parametrize("world", [2, 4])
-def test_nccl_pipeline_equals_single_engine(cuda, world):
+def test_nccl_pipeline_equals_single_engine(cuda, world, vp):
+    """vp=1: lm_head split by vocabulary rows over the stages (VocabParallelRunner)."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs, have {torch.cuda.device_count()}")
+    os.environ["DLI_PIPE_VP"] = str(vp)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-           "--master-addr", "127.0.0.1", "--master-port", str(29500 + world), os.path.join(ROOT, "tests", "pipeline_check.py")]
+           "--master-addr", "127.0.0.1", "--master-port", str(29500 + world + 10 * vp), os.path.join(ROOT, "tests", "pipeline_check.py")]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert p.returncode == 0 and "PIPELINE_OK" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
