@@ -23,6 +23,7 @@ import torch
 from . import ops
 
 BF = torch.bfloat16
+_EXP_SKIP = os.environ.get("DLI_EXP_SKIP", "")  # measurement knob only, see profiles/r1_notes.md
 
 
 @dataclass
@@ -370,7 +371,9 @@ class ShardEngine:
             else:
                 ops.add_layernorm(h, L["ln1"], L["ln1b"], s.eps, out=x)
                 lin(x, L["wqkv"], bias=L["bqkv"], out=qkv)
-            if decode:
+            if decode and _EXP_SKIP == "attn":
+                pass  # experiment knob (DLI_EXP_SKIP=attn): measure the step without attention
+            elif decode:
                 # RoPE + KV append of the new token + split-KV attention in one kernel; the
                 # kernel indexes page-table rows by batch row, so it gets the slot's rows
                 ops.paged_attn_decode_fused(qkv, self.cos, self.sin, self.kv.k[li], self.kv.v[li], st["page_rows"],

@@ -235,7 +235,7 @@ def paged_attn_decode_fused(qkv, cos, sin, k_cache, v_cache, page_table, seq_len
         _p(qkv), qkv.shape[1], _p(cos), _p(sin), _p(k_cache), _p(v_cache), _p(page_table), page_table.shape[1],
         _p(seq_lens), _p(out), _p(scratch), sbytes, B, H, KV, hd, page_size, num_splits, float(scale), window,
         _p(prefetch_a), _bytes(prefetch_a), _p(prefetch_b), _bytes(prefetch_b), _stream()))
-    launch_count += 2 if num_splits > 1 else 1
+    launch_count += 2 if (num_splits > 1 and scratch is not None) else 1  # cluster merge: one kernel
     return out
 
 
