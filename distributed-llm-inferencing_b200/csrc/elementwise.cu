@@ -106,8 +106,10 @@ __global__ void decode_advance_kernel(const int32_t* __restrict__ tokens, int32_
   const int s = *step;
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
     if (token_log && s < log_capacity) token_log[(size_t)s * B + b] = tokens[b];
-    if (positions) positions[b] += 1;
-    if (seq_lens) seq_lens[b] += 1;
+    // a row with seq_lens == 0 is an idle slot of a continuously batched step: it stays idle
+    const bool active = !seq_lens || seq_lens[b] > 0;
+    if (positions && active) positions[b] += 1;
+    if (seq_lens && active) seq_lens[b] += 1;
   }
   __syncthreads();
   if (threadIdx.x == 0) *step = s + 1;

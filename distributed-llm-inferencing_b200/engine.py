@@ -438,6 +438,14 @@ class ShardEngine:
             self.kv.release(b)
             self.kv.reserve(b, max_total_len)
         self.kv.commit()
+        self._make_state(B, mb)
+        st = self._dec[(B, mb)]
+        st["positions"].fill_(prompt_len)
+        st["seq_lens"].fill_(prompt_len + 1)
+        st["step"].zero_()
+
+    def _make_state(self, B: int, mb: int = 0) -> dict:
+        """Allocate (once) the decode state of slot (B, mb); does not touch KV reservations."""
         dev = self.device
         if (B, mb) not in self._dec:
             splits = self._num_splits(B)
@@ -473,10 +481,7 @@ class ShardEngine:
                 if self.is_first:
                     st["cands"] = torch.zeros(w, B, 2, dtype=torch.float32, device=dev)  # one row per stage
                     st["cand"] = st["cands"][0]  # stage 0 writes its own candidate in place
-        st = self._dec[(B, mb)]
-        st["positions"].fill_(prompt_len)
-        st["seq_lens"].fill_(prompt_len + 1)
-        st["step"].zero_()
+        return self._dec[(B, mb)]
 
     def prefill(self, B: int, T: int, ids: Optional[torch.Tensor] = None, hidden: Optional[torch.Tensor] = None,
                 mb: int = 0):

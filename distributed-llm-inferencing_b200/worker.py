@@ -76,6 +76,11 @@ class Worker:
         self.auth_enabled = env.get("AUTH_ENABLED", "0") == "1"
         self.auth_key = env.get("AUTH_KEY", "")
         self.max_seq_len = int(env.get("DLI_MAX_SEQ_LEN", "4096"))
+        # DLI_BATCHING=1: concurrent /inference requests on an unsharded model share decode steps
+        # (continuous batching, greedy); the reference serialises requests (worker/Dockerfile:45)
+        self.batching = env.get("DLI_BATCHING", "0") == "1"
+        self.max_batch = int(env.get("DLI_MAX_BATCH", "8")) if self.batching else 1
+        self.batchers: Dict[str, object] = {}
         self.routes = {("GET", "/health"): self.health, ("POST", "/load_model"): self.load_model,
                        ("POST", "/load_shard"): self.load_shard, ("POST", "/unload_model"): self.unload_model,
                        ("POST", "/inference"): self.inference}
@@ -96,7 +101,7 @@ class Worker:
             raise RuntimeError("this worker has no CPU path: it needs a CUDA device and USE_GPU=1")
         cfg = json.load(open(os.path.join(path, "config.json")))
         spec = ModelSpec.from_hf_config(cfg)
-        eng = ShardEngine(spec, start, end, device="cuda:0", max_batch=1,
+        eng = ShardEngine(spec, start, end, device="cuda:0", max_batch=self.max_batch if end is None else 1,
                           max_seq_len=min(self.max_seq_len, spec.max_pos))
         eng.load_state_dict(load_hf_state_dict(path, eng.start, eng.end, spec.n_layers))
         return eng
@@ -128,6 +133,10 @@ class Worker:
             if model_name not in self.loaded_tokenizers:
                 self.loaded_tokenizers[model_name] = _load_tokenizer(path)
             self.loaded_models[model_name] = self._engine(path)
+            if self.batching:
+                from .batching import ContinuousBatcher
+
+                self.batchers[model_name] = ContinuousBatcher(self.loaded_models[model_name]).start()
             return {"status": "success", "message": f"Model {model_name} loaded successfully on {self.device}"}, 200
         except Exception as e:  # noqa: BLE001 — the reference maps every failure to 500
             return {"status": "error", "message": f"Failed to load model: {str(e)}"}, 500
@@ -153,6 +162,8 @@ class Worker:
         if not model_name:
             return {"status": "error", "message": "Model name is required"}, 400
         try:
+            if model_name in self.batchers:
+                self.batchers.pop(model_name).stop()
             for key in [k for k in self.loaded_models if k == model_name or k.startswith(f"{model_name}_")]:
                 eng = self.loaded_models.pop(key)  # Q7: per-shard engines too
                 if hasattr(eng, "unload"):
@@ -188,7 +199,10 @@ class Worker:
                 ids = tokenizer(prompt, return_tensors="pt")["input_ids"]
                 if (time.time() - start_time) > timeout:
                     raise TimeoutError("Inference preparation timed out")
-                outputs = model.generate(ids, max_length=max_length, deadline=deadline, **self._gen_kwargs(data))
+                if model_name in self.batchers:  # joins the running batch; greedy
+                    outputs = self.batchers[model_name].submit(ids[0], max_length, timeout).result()[None]
+                else:
+                    outputs = model.generate(ids, max_length=max_length, deadline=deadline, **self._gen_kwargs(data))
                 result = tokenizer.decode(outputs[0], skip_special_tokens=True)
                 if (time.time() - start_time) > timeout:
                     raise TimeoutError("Inference generation timed out")
@@ -253,7 +267,8 @@ def main(argv=None):
     ap.add_argument("--port", type=int, default=5000)
     a = ap.parse_args(argv)
     # one request at a time, like the reference's single sync gunicorn worker (worker/Dockerfile:45)
-    run_simple(a.host, a.port, Worker(), threaded=False)
+    w = Worker()
+    run_simple(a.host, a.port, w, threaded=w.batching)
 
 
 if __name__ == "__main__":

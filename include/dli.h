@@ -294,7 +294,8 @@ int dli_sample_bf16(const void* logits, int ld, int32_t* out, int B, int V,
  * every token: stopping criteria at TF:generation/utils.py:2804 and the
  * torch.cat of input_ids at :2800): token_log[step*B + b] = tokens[b] (when
  * token_log != NULL and step < log_capacity), positions[b] += 1, seq_lens[b] += 1
- * (each optional), then *step += 1.  All int32. */
+ * (each optional; rows whose seq_lens is 0 are idle batch slots and are left alone),
+ * then *step += 1.  All int32. */
 int dli_decode_advance(const int32_t* tokens, int32_t* token_log, int32_t* positions,
                        int32_t* seq_lens, int32_t* step, int B, int log_capacity,
                        dli_stream_t stream);

@@ -1,0 +1,82 @@
+"""Continuous batching: concurrent requests of different prompt and output lengths share decode
+steps and each gets exactly the tokens it gets when it is the only request in the batcher."""
+import threading
+
+import pytest
+import torch
+
+from golden_util import load_case, spec_kwargs
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(max_batch):
+    from dli_b200.engine import ModelSpec, ShardEngine
+    from oracle import decoder_ref as R
+
+    c = load_case("llama_tiny")
+    spec = ModelSpec.from_hf_config(spec_kwargs(c["config"]))
+    sd = R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"])
+    eng = ShardEngine(spec, max_batch=max_batch, max_seq_len=128)
+    eng.load_state_dict(sd)
+    return eng, spec, c
+
+
+def test_requests_join_and_leave_without_changing_each_other(cuda):
+    from dli_b200.batching import ContinuousBatcher
+
+    eng, spec, c = _engine(4)
+    g = torch.Generator().manual_seed(3)
+    reqs = [(torch.randint(0, spec.vocab, (T,), generator=g), T + n) for T, n in
+            [(5, 9), (17, 20), (9, 1), (30, 12), (3, 25), (12, 7), (21, 16)]]
+    # alone: one request at a time through the same batcher (same kernels, same batch width)
+    b = ContinuousBatcher(eng, max_batch=4)
+    alone = []
+    for ids, ml in reqs:
+        f = b.submit(ids, ml)
+        while not f.done():
+            b.step()
+        alone.append(f.result())
+    # together: all submitted at once; 7 requests over 4 slots, so slots are reused mid-flight
+    futs = [b.submit(ids, ml) for ids, ml in reqs]
+    steps0 = b.steps
+    while not all(f.done() for f in futs):
+        b.step()
+    for (ids, ml), a, f in zip(reqs, alone, futs):
+        out = f.result()
+        assert out.shape == (ml,) and torch.equal(out[: len(ids)], ids)
+        assert torch.equal(out, a)
+    # sharing steps: far fewer decode steps than the sum of the requests' lengths
+    assert b.steps - steps0 < sum(ml - len(ids) for ids, ml in reqs) * 0.6
+    # and the first fixture prompt matches the plain engine over its margin-safe prefix
+    T = c["prompts"].shape[1]
+    f = b.submit(c["prompts"][0], T + 12)
+    while not f.done():
+        b.step()
+    noise = 2.0 * c["hf_err"].max()
+    n_safe = min(12, int((c["margin"][:, 0] > 2.0 * noise).int().cumprod(0).sum()))
+    assert torch.equal(f.result()[T:T + n_safe], c["tokens"][0, :n_safe])
+    assert len(eng.kv.free) == eng.kv.num_pages  # every sequence's pages were returned
+
+
+def test_background_thread_serves_concurrent_submitters(cuda):
+    from dli_b200.batching import ContinuousBatcher
+
+    eng, spec, _ = _engine(4)
+    b = ContinuousBatcher(eng).start()
+    g = torch.Generator().manual_seed(4)
+    prompts = [torch.randint(0, spec.vocab, (6 + i,), generator=g) for i in range(6)]
+    results = [None] * 6
+
+    def client(i):
+        results[i] = b.submit(prompts[i], len(prompts[i]) + 10 + i).result(timeout=60)
+
+    threads = [threading.Thread(target=client, args=(i,)) for i in range(6)]
+    [t.start() for t in threads]
+    [t.join(timeout=90) for t in threads]
+    b.stop()
+    for i, r in enumerate(results):
+        assert r is not None and r.shape == (len(prompts[i]) + 10 + i,) and torch.equal(r[: len(prompts[i])], prompts[i])
+    assert b.submit(prompts[0], 3).result().tolist() == prompts[0][:3].tolist()  # nothing to generate
+    with pytest.raises(ValueError):
+        b.submit(prompts[0], 1000).result()
