@@ -1,0 +1,70 @@
+"""Client-side dispatch of an inference request to worker nodes — the caller of the worker
+boundary (reference master/dashboard/views.py:305-455 `process_inference_request`), without
+Django: plain functions over a `post(url, json, headers, timeout)` callable (requests.post by
+default).  SURVEY.md §8f rank 2.  Kept semantics: shards known -> /inference with `shard_ids`
+(max_length 100, timeout 60, HTTP timeout 120, views.py:345-355); no shards -> /load_model
+(HTTP timeout 300) then /inference on the first active node (views.py:391-421); a non-200
+answer or `status != success` is a failure with the worker's message.
+Fixed relative to the reference: shard ids are ordered and sent to the node that holds them
+all (the reference takes "the first node that has shards", views.py:337-340); shards that
+are registered with the master but not yet on the worker are (re)announced with /load_shard
+first (no reference view ever calls it); the Authorization header is sent when a key is
+configured (the reference master never sends it, so AUTH_ENABLED=1 breaks it).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional
+
+
+@dataclass
+class Node:
+    url: str  # e.g. http://10.0.0.5:5000
+    is_active: bool = True
+    # shard_id -> shard_path of the shards this node holds for a model: {model: {id: path}}
+    shards: Dict[str, Dict[object, str]] = field(default_factory=dict)
+
+
+class DispatchError(RuntimeError):
+    pass
+
+
+def _default_post(url, json=None, headers=None, timeout=None):
+    import requests
+
+    return requests.post(url, json=json, headers=headers, timeout=timeout)
+
+
+def _check(resp, what):
+    if resp.status_code != 200:
+        raise DispatchError(f"{what}: node returned status code {resp.status_code}: {resp.text}")
+    data = resp.json()
+    if data.get("status") != "success":
+        raise DispatchError(f"{what}: {data.get('message', 'Unknown error')}")
+    return data
+
+
+def dispatch_inference(nodes: List[Node], model_name: str, prompt: str, max_length: int = 100, timeout: int = 60,
+                       auth_key: Optional[str] = None, post: Callable = _default_post, extra: Optional[dict] = None) -> str:
+    """Returns the generated text, or raises DispatchError with the failure message the
+    reference would store in InferenceRequest.error."""
+    headers = {"Authorization": f"Bearer {auth_key}"} if auth_key else {}
+    active = [n for n in nodes if n.is_active]
+    holders = [n for n in active if n.shards.get(model_name)]
+    body = {"model_name": model_name, "prompt": prompt, "max_length": max_length, "timeout": timeout, **(extra or {})}
+    if holders:
+        # the node that holds the most shards of the model runs the (in-process) layer-range chain
+        node = max(holders, key=lambda n: len(n.shards[model_name]))
+        ids = sorted(node.shards[model_name], key=lambda i: (str(type(i)), i))
+        for sid in ids:
+            _check(post(f"{node.url}/load_shard", json={"model_name": model_name, "shard_id": sid,
+                                                        "shard_path": node.shards[model_name][sid]},
+                        headers=headers, timeout=300), f"load_shard {sid}")
+        return _check(post(f"{node.url}/inference", json={**body, "shard_ids": ids}, headers=headers, timeout=120),
+                      "inference")["result"]
+    if not active:
+        raise DispatchError("No active worker nodes available")
+    node = active[0]
+    _check(post(f"{node.url}/load_model", json={"model_name": model_name}, headers=headers, timeout=300),
+           "Failed to load model")
+    return _check(post(f"{node.url}/inference", json=body, headers=headers, timeout=120), "inference")["result"]

@@ -144,3 +144,26 @@ def test_unload_frees_memory(cuda):
     eng.unload()
     assert torch.cuda.memory_allocated() < before
     assert len(eng.kv.free) == eng.kv.num_pages
+
+
+def test_gpt2_small_shape_against_oracle(cuda):
+    """BASELINE configs[0] shape (GPT-2 small: L12 d768 H12 V50257, tied head, learned positions,
+    LayerNorm, Conv1D biases, gelu_new) through the CUDA path vs the oracle on the same seeded
+    weights: last-position logits within 2x the oracle's own bf16-vs-fp32 error."""
+    from dli_b200.engine import NAMED_SPECS, ShardEngine
+    from oracle import decoder_ref as R
+
+    spec = NAMED_SPECS["gpt2"]
+    rspec = R.ModelSpec(**spec.__dict__)
+    sd = R.seeded_state_dict(rspec, seed=5, std=0.04)
+    ids = R.seeded_prompts(spec.vocab, 1, 32, seed=6)
+    ref16 = R.forward(ids, sd, rspec).float()
+    ref32 = R.forward(ids, {k: v.float() for k, v in sd.items()}, rspec)
+    eng = ShardEngine(spec, max_batch=1, max_seq_len=128)
+    eng.load_state_dict(sd)
+    out, logits = eng.generate(ids, 32 + 8, return_logits=True)
+    err_ours = (logits[0] - ref32).abs().max().item()
+    err_oracle = (ref16 - ref32).abs().max().item()
+    print(f"gpt2-small: |ours-fp32| {err_ours:.4f}  |oracle_bf16-fp32| {err_oracle:.4f}  scale {ref32.abs().max():.2f}")
+    assert err_ours <= 2.0 * err_oracle + 0.02
+    assert out.shape == (1, 40) and torch.equal(eng.generate(ids, 40), out)  # graph == eager
