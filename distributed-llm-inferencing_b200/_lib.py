@@ -48,6 +48,7 @@ SIGNATURES = {
     "dli_rmsnorm_gemv_bf16": (_i, [_vp, _vp, _f, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "dli_rmsnorm_gemv_gated_silu_bf16": (_i, [_vp, _vp, _f, _vp, _vp, _i, _i, _i, _vp]),
     "dli_attn_prefill_bf16": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "dli_attn_prefill_tc_bf16": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "dli_gemv_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "dli_gemm_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "dli_linear_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),

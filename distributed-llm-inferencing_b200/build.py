@@ -23,6 +23,7 @@ SOURCES = [
     "rope_kv.cu",
     "attn_decode.cu",
     "attn_prefill.cu",
+    "attn_prefill_tc.cu",
     "gemv.cu",
     "gemm_tcgen05.cu",
     "elementwise.cu",

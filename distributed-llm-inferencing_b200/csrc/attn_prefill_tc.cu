@@ -1,0 +1,303 @@
+// Causal prefill attention on the 5th-generation tensor cores (head_dim 128).
+//
+// One CTA = 128 query rows of one head; KV tiles of 128 tokens.  Both GEMMs of
+// flash attention are tcgen05.mma with fp32 accumulators in TMEM:
+//   S = Q K^T   : A = Q tile, B = K tile, both K-major (hd contiguous), SWIZZLE_128B, via TMA
+//   O += P V    : A = P (bf16, written to shared memory by the softmax warps in the same
+//                 K-major swizzled layout), B = V tile as an MN-major operand (hd contiguous,
+//                 tokens along K), exactly as TMA lands the [tokens, hd] rows
+// TMEM: S0 | S1 (two score buffers, 128 columns each) | O (128 columns).
+// Roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 =
+// softmax + epilogue, one query row per thread (TMEM lane), fp32 online softmax.
+// The MMA warp issues S(j+1) before it waits for the softmax of tile j, so the tensor pipe
+// works on the next scores while the SFUs exponentiate the current ones; P/V of tile j are
+// multiplied as soon as P(j) is in shared memory and O has been rescaled.
+// The T x T score matrix never leaves the SM.  FLOPs per head: 4 * T^2/2 * hd (causal).
+#include "tcgen05_utils.cuh"
+
+namespace dli {
+
+constexpr int kTcThreads = 192;
+constexpr int kTcTile = 128;      // query rows per CTA and tokens per KV tile
+constexpr int kTcHd = 128;
+constexpr int kSpanBytes = 128 * 64 * 2;  // one [128 rows x 64 elements] swizzled sub-tile: 16 KB
+constexpr int kTileBytes2 = 2 * kSpanBytes;  // a [128 x 128] bf16 operand tile: 32 KB
+
+// smem: Q | K0 K1 | V0 V1 | P | barriers
+constexpr int kTcSmem = 6 * kTileBytes2 + 1024 + 256;
+
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+      "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// MN-major SWIZZLE_128B operand (V as B: N = hd contiguous, K = tokens): 64-element MN groups are
+// LBO apart (the two hd halves = two TMA boxes, 16 KB), 8-row K groups are SBO = 1024 B apart.
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3ffffu) >> 4);
+  d |= (uint64_t)(kSpanBytes >> 4) << 16;  // leading (MN) byte offset
+  d |= (uint64_t)64 << 32;                 // stride (K) byte offset = 1024 B
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// D=f32, A=bf16 K-major, B=bf16 (K-major or MN-major), M=128, N=128
+__host__ __device__ constexpr uint32_t make_idesc_attn(bool b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(128 >> 3) << 17) |
+         ((uint32_t)(128 >> 4) << 24);
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, int T, int H, int KV,
+                       float scale_log2, int window) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const uint32_t sQ = smem_addr(smem);
+  const uint32_t sK = sQ + kTileBytes2;          // 2 stages
+  const uint32_t sV = sK + 2 * kTileBytes2;      // 2 stages
+  const uint32_t sP = sV + 2 * kTileBytes2;
+  uint8_t* bar_mem = smem + 6 * kTileBytes2;
+  const uint32_t bars = smem_addr(bar_mem);
+  // barrier slots (8 B each)
+  const uint32_t q_full = bars, k_full = bars + 8, k_empty = bars + 24, v_full = bars + 40, v_empty = bars + 56,
+                 s_full = bars + 72, s_empty = bars + 88, p_full = bars + 104, pv_done = bars + 112;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_mem + 128);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qtile = gridDim.x - 1 - blockIdx.x;  // heavier (later) query tiles first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int kvh = h / (H / KV);
+  const int q0 = qtile * kTcTile;
+  int t_begin = 0;
+  if (window > 0 && q0 - window + 1 > 0) t_begin = (q0 - window + 1) / kTcTile;
+  const int t_end = qtile + 1;  // diagonal tile last
+  const int row_base = b * T;   // row of token 0 of this sequence in the packed qkv matrix
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(k_full + 8 * i, 1);
+      mbar_init(k_empty + 8 * i, 1);
+      mbar_init(v_full + 8 * i, 1);
+      mbar_init(v_empty + 8 * i, 1);
+      mbar_init(s_full + 8 * i, 1);
+      mbar_init(s_empty + 8 * i, 4);  // one arrive per softmax warp
+    }
+    mbar_init(p_full, 4);
+    mbar_init(pv_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(smem_addr(tmem_ptr_smem), 512);
+  pdl_wait();
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t tS = tmem_base, tO = tmem_base + 256;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---------------- TMA producer ----------------
+      mbar_expect_tx(q_full, kTileBytes2);
+      tma_load_2d(sQ, &tm, q_full, h * kTcHd, row_base + q0);
+      tma_load_2d(sQ + kSpanBytes, &tm, q_full, h * kTcHd + 64, row_base + q0);
+      int it = 0;
+      for (int j = t_begin; j < t_end; ++j, ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        const int krow = row_base + j * kTcTile;
+        mbar_wait(k_empty + 8 * st, ph ^ 1);
+        mbar_expect_tx(k_full + 8 * st, kTileBytes2);
+        tma_load_2d(sK + st * kTileBytes2, &tm, k_full + 8 * st, (H + kvh) * kTcHd, krow);
+        tma_load_2d(sK + st * kTileBytes2 + kSpanBytes, &tm, k_full + 8 * st, (H + kvh) * kTcHd + 64, krow);
+        mbar_wait(v_empty + 8 * st, ph ^ 1);
+        mbar_expect_tx(v_full + 8 * st, kTileBytes2);
+        tma_load_2d(sV + st * kTileBytes2, &tm, v_full + 8 * st, (H + KV + kvh) * kTcHd, krow);
+        tma_load_2d(sV + st * kTileBytes2 + kSpanBytes, &tm, v_full + 8 * st, (H + KV + kvh) * kTcHd + 64, krow);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ---------------- MMA issuer ----------------
+      constexpr uint32_t idesc_s = make_idesc_attn(false), idesc_o = make_idesc_attn(true);
+      const int n = t_end - t_begin;
+      auto issue_s = [&](int it) {  // S(it) = Q K^T into score buffer it & 1
+        const int st = it & 1;
+        mbar_wait(k_full + 8 * st, (it >> 1) & 1);
+        mbar_wait(s_empty + 8 * st, ((it >> 1) & 1) ^ 1);  // softmax of tile it-2 has read this buffer
+        tcgen05_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < kTcHd / kUmmaK; ++kk) {
+          const uint32_t off = (kk >> 2) * kSpanBytes + (kk & 3) * 32;
+          umma_bf16(tS + st * 128, make_smem_desc(sQ + off), make_smem_desc(sK + st * kTileBytes2 + off), idesc_s,
+                    kk > 0 ? 1u : 0u);
+        }
+        umma_commit(s_full + 8 * st);
+        umma_commit(k_empty + 8 * st);
+      };
+      mbar_wait(q_full, 0);
+      issue_s(0);
+      for (int it = 0; it < n; ++it) {
+        if (it + 1 < n) issue_s(it + 1);
+        const int st = it & 1;
+        mbar_wait(p_full, it & 1);                 // P(it) in shared memory, O rescaled
+        mbar_wait(v_full + 8 * st, (it >> 1) & 1);
+        tcgen05_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < kTcTile / kUmmaK; ++kk) {
+          // A = P: K-major, k-step = 16 tokens; B = V: MN-major, 16 tokens = two 8-row groups (2048 B)
+          const uint64_t adesc = make_smem_desc(sP + (kk >> 2) * kSpanBytes + (kk & 3) * 32);
+          const uint64_t bdesc = make_smem_desc_mn(sV + st * kTileBytes2 + kk * 2048);
+          umma_bf16(tO, adesc, bdesc, idesc_o, (it > 0 || kk > 0) ? 1u : 0u);
+        }
+        umma_commit(pv_done);
+        umma_commit(v_empty + 8 * st);
+      }
+    }
+  } else {
+    // ---------------- softmax + epilogue: thread = query row ----------------
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;           // TMEM lane
+    const int qrow = q0 + row;                  // position in the sequence
+    const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+    float m_run = -INFINITY, l_run = 0.f;
+    int it = 0;
+    for (int j = t_begin; j < t_end; ++j, ++it) {
+      const int st = it & 1;
+      mbar_wait(s_full + 8 * st, (it >> 1) & 1);
+      tcgen05_fence_after();
+      float s[128];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tS + st * 128 + lane_off + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(r[i]);
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_empty + 8 * st);  // score buffer may be overwritten by S(it+2)
+      const bool need_mask = (j == qtile) || (window > 0 && j * kTcTile < q0 + kTcTile - window + 1);
+      if (need_mask) {
+#pragma unroll
+        for (int i = 0; i < 128; ++i) {
+          const int tok = j * kTcTile + i;
+          if (tok > qrow || (window > 0 && tok <= qrow - window)) s[i] = -INFINITY;
+        }
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < 128; ++i) mx = fmaxf(mx, s[i]);
+      const float m_new = fmaxf(m_run, mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float corr = exp2f((m_run - m_use) * scale_log2);
+      m_run = m_new;
+      float rs = 0.f;
+#pragma unroll
+      for (int i = 0; i < 128; ++i) {
+        s[i] = exp2f((s[i] - m_use) * scale_log2);
+        rs += s[i];
+      }
+      l_run = l_run * corr + rs;
+      // previous P.V must have finished before P is overwritten and O is rescaled
+      if (it > 0) {
+        mbar_wait(pv_done, (it - 1) & 1);
+        tcgen05_fence_after();
+      }
+      // P (bf16) -> shared memory, K-major SWIZZLE_128B: [2 spans of 64 tokens][128 rows][128 B]
+      uint8_t* prow = smem + (sP - sQ) + row * 128;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {  // 16 chunks of 8 tokens (16 B)
+        uint4 u;
+        u.x = pack_bf16(s[c * 8 + 0], s[c * 8 + 1]);
+        u.y = pack_bf16(s[c * 8 + 2], s[c * 8 + 3]);
+        u.z = pack_bf16(s[c * 8 + 4], s[c * 8 + 5]);
+        u.w = pack_bf16(s[c * 8 + 6], s[c * 8 + 7]);
+        const int span = c >> 3, chunk = c & 7;
+        *reinterpret_cast<uint4*>(prow + span * kSpanBytes + ((chunk ^ (row & 7)) << 4)) = u;
+      }
+      if (it > 0) {
+        // O *= corr (rows whose running maximum moved); TMEM -> registers -> TMEM
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tO + lane_off + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * corr);
+          tmem_st_32x32(tO + lane_off + c * 32, r);
+        }
+        tmem_st_wait();
+      }
+      fence_proxy_async();       // P visible to the tensor core's (async proxy) shared-memory reads
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
+    }
+    // ---- epilogue: O / l -> bf16 ----
+    mbar_wait(pv_done, (it - 1) & 1);
+    tcgen05_fence_after();
+    const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+    bf16* dst = out + ((size_t)(row_base + qrow)) * ((size_t)H * kTcHd) + (size_t)h * kTcHd;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tO + lane_off + c * 32, r);
+      tmem_ld_wait();
+      if (qrow < T) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[g * 8 + i]) * inv;
+          st_16B(dst + c * 32 + g * 8, pack8(v));
+        }
+      }
+    }
+    tcgen05_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace dli
+
+extern "C" int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T, int H, int KV, int hd, float scale,
+                                        int window, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(qkv && out, "dli_attn_prefill_tc_bf16: null pointer");
+  DLI_CHECK_ARG(hd == 128, "dli_attn_prefill_tc_bf16: head_dim must be 128 (got %d); use dli_attn_prefill_bf16", hd);
+  DLI_CHECK_ARG(B >= 0 && T >= 0 && H > 0 && KV > 0 && H % KV == 0 && window >= 0,
+                "dli_attn_prefill_tc_bf16: bad sizes B=%d T=%d H=%d KV=%d", B, T, H, KV);
+  DLI_CHECK_ARG(H <= 65535 && B <= 65535, "dli_attn_prefill_tc_bf16: H/B out of grid range");
+  DLI_CHECK_ARG(aligned16(qkv) && aligned16(out), "dli_attn_prefill_tc_bf16: pointers must be 16-byte aligned");
+  if (B == 0 || T == 0) return DLI_OK;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
+    attr_set = true;
+  }
+  CUtensorMap tm;
+  const int cols = (H + 2 * KV) * hd;
+  // the packed qkv matrix [B*T, cols]; box = 128 rows x 64 columns (one swizzle span)
+  int rc = make_tmap(&tm, qkv, B * T, cols, 128);
+  if (rc != DLI_OK) return rc;
+  dim3 grid((T + kTcTile - 1) / kTcTile, H, B);
+  DLI_LAUNCH("attn_prefill_tc_kernel", attn_prefill_tc_kernel, grid, dim3(kTcThreads), (size_t)kTcSmem,
+             static_cast<cudaStream_t>(stream), tm, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window);
+  return DLI_OK;
+}

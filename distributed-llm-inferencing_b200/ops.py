@@ -6,6 +6,8 @@ stream.  Tensors must be CUDA, contiguous where noted, bf16 unless stated.
 """
 from __future__ import annotations
 
+import os as _os
+
 import torch
 
 from . import _lib
@@ -113,9 +115,18 @@ def paged_attn_decode(q, q_stride, k_cache, v_cache, page_table, seq_lens, out, 
     return out
 
 
-def attn_prefill(qkv, out, B, T, H, KV, hd, scale, window=0):
+def attn_prefill(qkv, out, B, T, H, KV, hd, scale, window=0, tensor_core=None):
+    """Causal prefill attention.  head_dim 128 runs on tcgen05 (dli_attn_prefill_tc_bf16) unless
+    tensor_core=False or DLI_PREFILL_ATTN=mma; head_dim 64 uses the mma.sync kernel."""
     global launch_count
     _req(qkv), _req(out)
+    if tensor_core is None:
+        tensor_core = hd == 128 and _os.environ.get("DLI_PREFILL_ATTN", "tc") != "mma"
+    if tensor_core:
+        _lib.check("dli_attn_prefill_tc_bf16", _lib.load().dli_attn_prefill_tc_bf16(
+            _p(qkv), _p(out), B, T, H, KV, hd, float(scale), window, _stream()))
+        launch_count += 1
+        return out
     _lib.check("dli_attn_prefill_bf16", _lib.load().dli_attn_prefill_bf16(
         _p(qkv), _p(out), B, T, H, KV, hd, float(scale), window, _stream()))
     launch_count += 1

@@ -191,6 +191,12 @@ int dli_paged_attn_decode_static_bf16(const void* q, int q_stride, const void* k
 int dli_attn_prefill_bf16(const void* qkv, void* out, int B, int T, int H, int KV,
                           int hd, float scale, int window, dli_stream_t stream);
 
+/* Same computation on the tensor cores (head_dim 128 only): both GEMMs of flash attention are
+ * tcgen05.mma with TMEM accumulators (S = Q K^T, O += P V with V as an MN-major operand), Q/K/V
+ * tiles of 128 rows arrive by TMA, the softmax runs one query row per thread out of TMEM. */
+int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T, int H, int KV, int hd,
+                             float scale, int window, dli_stream_t stream);
+
 /* ---- projections -----------------------------------------------------------
  * y[M,N] = epi(x[M,K] . w[N,K]^T)   — w is the HF nn.Linear layout [out,in].
  * Replaces q/k/v/o_proj TF:models/llama/modeling_llama.py:262-264,:288, the

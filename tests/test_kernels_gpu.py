@@ -227,16 +227,19 @@ def test_paged_attn_decode(cuda, B, H, KV, hd, page, lens, splits, window):
 @pytest.mark.parametrize(
     "B,T,H,KV,hd,window",
     [(1, 2048, 32, 8, 128, 0), (2, 100, 32, 4, 64, 0), (1, 1, 4, 4, 64, 0), (1, 300, 8, 2, 128, 128),
-     (3, 65, 12, 12, 64, 0)],
+     (3, 65, 12, 12, 64, 0), (2, 129, 8, 8, 128, 0), (1, 1, 4, 2, 128, 0), (2, 700, 16, 4, 128, 200)],
 )
-def test_attn_prefill(cuda, B, T, H, KV, hd, window):
+@pytest.mark.parametrize("tensor_core", [False, True])
+def test_attn_prefill(cuda, B, T, H, KV, hd, window, tensor_core):
     from dli_b200 import ops
 
+    if tensor_core and hd != 128:
+        pytest.skip("the tcgen05 kernel covers head_dim 128")
     gen = torch.Generator(device="cuda").manual_seed(7 + T)
     qkv = torch.randn(B * T, (H + 2 * KV) * hd, device=cuda, generator=gen).to(BF)
     out = torch.empty(B * T, H * hd, device=cuda, dtype=BF)
     scale = hd ** -0.5
-    ops.attn_prefill(qkv, out, B, T, H, KV, hd, scale, window=window)
+    ops.attn_prefill(qkv, out, B, T, H, KV, hd, scale, window=window, tensor_core=tensor_core)
     G = H // KV
     x = qkv.float().reshape(B, T, H + 2 * KV, hd)
     q = x[:, :, :H].permute(0, 2, 1, 3)  # [B,H,T,hd]
