@@ -262,15 +262,25 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j) { a1[j] = 0.f; a2[j] = 0.f; }
-            for (int sp = 0; sp < splits; ++sp) {
-              const float* src = all + (size_t)sp * Cfg::kAccCols * 128;
+            // four splits' worth of loads in flight at a time (one L2 round trip instead of four);
+            // the additions stay in split order, so the result does not depend on arrival order
+            for (int sp0 = 0; sp0 < splits; sp0 += 4) {
+              float v1[4][16], v2[4][16];
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                if (m_tile0 + c0 + j < M) {
-                  a1[j] += __ldcg(src + (size_t)(c0 + j) * 128 + row);
-                  if (kGated) a2[j] += __ldcg(src + (size_t)(BN + c0 + j) * 128 + row);
+              for (int q = 0; q < 4; ++q) {
+                const bool on = sp0 + q < splits;
+                const float* src = all + (size_t)(on ? sp0 + q : sp0) * Cfg::kAccCols * 128;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const bool ld = on && (m_tile0 + c0 + j < M);
+                  v1[q][j] = ld ? __ldcg(src + (size_t)(c0 + j) * 128 + row) : 0.f;
+                  v2[q][j] = (kGated && ld) ? __ldcg(src + (size_t)(BN + c0 + j) * 128 + row) : 0.f;
                 }
               }
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int j = 0; j < 16; ++j) { a1[j] += v1[q][j]; a2[j] += v2[q][j]; }
             }
           }
           if (n < n_out) {
