@@ -7,8 +7,8 @@
 //                 K-major swizzled layout), B = V tile as an MN-major operand (hd contiguous,
 //                 tokens along K), exactly as TMA lands the [tokens, hd] rows
 // TMEM: S0 | S1 (two score buffers, 128 columns each) | O (128 columns).
-// Roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-5 =
-// softmax + epilogue, one query row per thread (TMEM lane), fp32 online softmax.
+// Roles (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-9 =
+// softmax + epilogue: two threads per query row (TMEM lane), 64 columns each, fp32 online softmax.
 // The MMA warp issues S(j+1) before it waits for the softmax of tile j, so the tensor pipe
 // works on the next scores while the SFUs exponentiate the current ones; P/V of tile j are
 // multiplied as soon as P(j) is in shared memory and O has been rescaled.
@@ -17,14 +17,14 @@
 
 namespace dli {
 
-constexpr int kTcThreads = 192;
+constexpr int kTcThreads = 320;  // TMA warp + MMA warp + 8 softmax warps
 constexpr int kTcTile = 128;      // query rows per CTA and tokens per KV tile
 constexpr int kTcHd = 128;
 constexpr int kSpanBytes = 128 * 64 * 2;  // one [128 rows x 64 elements] swizzled sub-tile: 16 KB
 constexpr int kTileBytes2 = 2 * kSpanBytes;  // a [128 x 128] bf16 operand tile: 32 KB
 
 // smem: Q | K0 K1 | V0 V1 | P | barriers
-constexpr int kTcSmem = 6 * kTileBytes2 + 1024 + 256;
+constexpr int kTcSmem = 6 * kTileBytes2 + 1024 + 256 + 2048;  // + row max / sum exchange
 
 __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32]) {
   asm volatile(
@@ -91,9 +91,9 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
       mbar_init(v_full + 8 * i, 1);
       mbar_init(v_empty + 8 * i, 1);
       mbar_init(s_full + 8 * i, 1);
-      mbar_init(s_empty + 8 * i, 4);  // one arrive per softmax warp
+      mbar_init(s_empty + 8 * i, 8);  // one arrive per softmax warp
     }
-    mbar_init(p_full, 4);
+    mbar_init(p_full, 8);
     mbar_init(pv_done, 1);
     fence_barrier_init();
   }
@@ -165,22 +165,28 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
       }
     }
   } else {
-    // ---------------- softmax + epilogue: thread = query row ----------------
-    const int quad = warp & 3;
+    // ---------------- softmax + epilogue: 8 warps; a query row is shared by two threads ----------------
+    // warps w and w+4 own the same TMEM lane quadrant; `half` 0 takes score/output columns 0-63,
+    // half 1 columns 64-127.  Only the row maximum has to be exchanged per tile (shared memory + one
+    // named barrier); each thread keeps the running sum of its own columns until the epilogue.
+    const int sw = warp - 2;
+    const int quad = warp & 3, half = sw >> 2;
     const int row = quad * 32 + lane;           // TMEM lane
     const int qrow = q0 + row;                  // position in the sequence
     const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+    const uint32_t col0 = half * 64;
+    float* xch = reinterpret_cast<float*>(bar_mem + 256);  // [2 parities][2 halves][128 rows]
     float m_run = -INFINITY, l_run = 0.f;
     int it = 0;
     for (int j = t_begin; j < t_end; ++j, ++it) {
       const int st = it & 1;
       mbar_wait(s_full + 8 * st, (it >> 1) & 1);
       tcgen05_fence_after();
-      float s[128];
+      float s[64];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32(tS + st * 128 + lane_off + c * 32, r);
+        tmem_ld_32x32(tS + st * 128 + lane_off + col0 + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(r[i]);
@@ -191,21 +197,24 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
       const bool need_mask = (j == qtile) || (window > 0 && j * kTcTile < q0 + kTcTile - window + 1);
       if (need_mask) {
 #pragma unroll
-        for (int i = 0; i < 128; ++i) {
-          const int tok = j * kTcTile + i;
+        for (int i = 0; i < 64; ++i) {
+          const int tok = j * kTcTile + (int)col0 + i;
           if (tok > qrow || (window > 0 && tok <= qrow - window)) s[i] = -INFINITY;
         }
       }
       float mx = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 128; ++i) mx = fmaxf(mx, s[i]);
+      for (int i = 0; i < 64; ++i) mx = fmaxf(mx, s[i]);
+      xch[(it & 1) * 256 + half * 128 + row] = mx;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mx = fmaxf(mx, xch[(it & 1) * 256 + (half ^ 1) * 128 + row]);
       const float m_new = fmaxf(m_run, mx);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
       const float corr = exp2f((m_run - m_use) * scale_log2);
       m_run = m_new;
       float rs = 0.f;
 #pragma unroll
-      for (int i = 0; i < 128; ++i) {
+      for (int i = 0; i < 64; ++i) {
         s[i] = exp2f((s[i] - m_use) * scale_log2);
         rs += s[i];
       }
@@ -215,28 +224,27 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
         mbar_wait(pv_done, (it - 1) & 1);
         tcgen05_fence_after();
       }
-      // P (bf16) -> shared memory, K-major SWIZZLE_128B: [2 spans of 64 tokens][128 rows][128 B]
-      uint8_t* prow = smem + (sP - sQ) + row * 128;
+      // P (bf16) -> shared memory, K-major SWIZZLE_128B: span `half` = this thread's 64 tokens
+      uint8_t* prow = smem + (sP - sQ) + half * kSpanBytes + row * 128;
 #pragma unroll
-      for (int c = 0; c < 16; ++c) {  // 16 chunks of 8 tokens (16 B)
+      for (int c = 0; c < 8; ++c) {  // 8 chunks of 8 tokens (16 B)
         uint4 u;
         u.x = pack_bf16(s[c * 8 + 0], s[c * 8 + 1]);
         u.y = pack_bf16(s[c * 8 + 2], s[c * 8 + 3]);
         u.z = pack_bf16(s[c * 8 + 4], s[c * 8 + 5]);
         u.w = pack_bf16(s[c * 8 + 6], s[c * 8 + 7]);
-        const int span = c >> 3, chunk = c & 7;
-        *reinterpret_cast<uint4*>(prow + span * kSpanBytes + ((chunk ^ (row & 7)) << 4)) = u;
+        *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = u;
       }
       if (it > 0) {
-        // O *= corr (rows whose running maximum moved); TMEM -> registers -> TMEM
+        // O *= corr on this thread's 64 output columns; TMEM -> registers -> TMEM
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           uint32_t r[32];
-          tmem_ld_32x32(tO + lane_off + c * 32, r);
+          tmem_ld_32x32(tO + lane_off + col0 + c * 32, r);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * corr);
-          tmem_st_32x32(tO + lane_off + c * 32, r);
+          tmem_st_32x32(tO + lane_off + col0 + c * 32, r);
         }
         tmem_st_wait();
       }
@@ -245,15 +253,18 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
     }
-    // ---- epilogue: O / l -> bf16 ----
+    // ---- epilogue: O / l -> bf16 (the two halves of a row add their partial sums) ----
+    xch[(it & 1) * 256 + half * 128 + row] = l_run;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    l_run += xch[(it & 1) * 256 + (half ^ 1) * 128 + row];
     mbar_wait(pv_done, (it - 1) & 1);
     tcgen05_fence_after();
     const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-    bf16* dst = out + ((size_t)(row_base + qrow)) * ((size_t)H * kTcHd) + (size_t)h * kTcHd;
+    bf16* dst = out + ((size_t)(row_base + qrow)) * ((size_t)H * kTcHd) + (size_t)h * kTcHd + col0;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < 2; ++c) {
       uint32_t r[32];
-      tmem_ld_32x32(tO + lane_off + c * 32, r);
+      tmem_ld_32x32(tO + lane_off + col0 + c * 32, r);
       tmem_ld_wait();
       if (qrow < T) {
 #pragma unroll

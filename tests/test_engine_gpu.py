@@ -167,3 +167,30 @@ def test_gpt2_small_shape_against_oracle(cuda):
     print(f"gpt2-small: |ours-fp32| {err_ours:.4f}  |oracle_bf16-fp32| {err_oracle:.4f}  scale {ref32.abs().max():.2f}")
     assert err_ours <= 2.0 * err_oracle + 0.02
     assert out.shape == (1, 40) and torch.equal(eng.generate(ids, 40), out)  # graph == eager
+
+
+@pytest.mark.parametrize("name", ["gpt2_tiny", "mistral_tiny"])
+def test_batched_decode_other_families(cuda, name):
+    """Batch 8 (tcgen05 split-K projections; GPT-2: bias + gelu_new epilogues, Mistral: sliding
+    window) gives every row the tokens transformers gives it, over the margin-safe prefix."""
+    c = load_case(name)
+    eng, spec, _ = _engine(c)
+    eng.unload()
+    from dli_b200.engine import ShardEngine
+    from oracle import decoder_ref as R
+
+    eng = ShardEngine(spec, max_batch=8, max_seq_len=128)
+    eng.load_state_dict(R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"]))
+    B0, T = c["prompts"].shape
+    N = c["tokens"].shape[1]
+    reps = 8 // B0
+    out = eng.generate(c["prompts"].repeat(reps, 1), T + N)
+    for r in range(1, reps):
+        assert torch.equal(out[:B0], out[r * B0:(r + 1) * B0])
+    noise = 2.0 * c["hf_err"].max()
+    checked = 0
+    for b in range(B0):
+        n_safe = int((c["margin"][:, b] > 2.0 * noise).int().cumprod(0).sum())
+        checked += n_safe
+        assert torch.equal(out[b, T:T + n_safe], c["tokens"][b, :n_safe]), (name, b, n_safe)
+    assert checked > 0
