@@ -261,9 +261,19 @@ def batch_decode_extra(spec, B, ctx, K, peaks, page_size, old_eng):
 
 
 # ---------------------------------------------------------------------------------- CPU baseline
+def _use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 for multi-process launches; the CPU arm is meant to use
+    every host core this process may run on."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    if os.environ.get("OMP_NUM_THREADS") and torch.get_num_threads() < n:
+        torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
 def cpu_baseline(spec, args, new_tokens=4, prompt_len=16):
     from oracle import ref_worker_port as P
 
+    _use_all_host_threads()
     t0 = time.time()
     r = P.time_cpu_decode(spec, prompt_len, new_tokens, greedy=True, warmup_tokens=0)
     return {"value": r["decode_tok_s"], "unit": UNIT, "cores": r["threads"], "kind": "port",
@@ -277,6 +287,7 @@ def run_reference(args, spec):
     all host threads, each step = one decoded token at a short context (bounded sample)."""
     from oracle import ref_worker_port as P
 
+    _use_all_host_threads()
     model = P.build_cpu_model(spec)
     tok = P.IdTokenizer()
     prompt_len = 16
