@@ -246,42 +246,105 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         finish = *flag != 0;
         if (finish) __threadfence();
       }
-      if (finish) {
+      if (finish && splits > 1) {
+        // Reduction by the last-arriving CTA of the tile.  The partials are in global memory now, so
+        // the work is re-dealt for memory parallelism: an item is 8 consecutive weight rows n of one
+        // activation row m (two float4 per split, one 16-byte residual load, one 16-byte store), 16
+        // consecutive threads cover the 128 rows of a y row, and a thread requests everything its
+        // batch of items needs before it touches any of it (one L2 round trip per batch instead of
+        // one per 16-column chunk).  Splits are still added in split order: deterministic.
         const float* all = splitk_partial + (size_t)tile * splits * Cfg::kAccCols * 128;
+        constexpr int kItems = kGated ? 2 : 4;  // items per batch (register budget)
+        const int et = (int)threadIdx.x - 64;   // 0..127 over the epilogue warps
+        const int m_real = min(BN, M - m_tile0);
+        const int items = m_real * 16;
+        const int n_tile0 = blockIdx.y * kOutRows;
+        for (int it0 = 0; it0 < items; it0 += 128 * kItems) {
+          float acc1[kItems][8], acc2[kItems][8];
+          uint4 resv[kItems];
+#pragma unroll
+          for (int q = 0; q < kItems; ++q) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { acc1[q][e] = 0.f; acc2[q][e] = 0.f; }
+            const int id = it0 + q * 128 + et;
+            const int mc = id >> 4, ng = id & 15;
+            const int nn = n_tile0 + ng * 8;
+            const bool on = id < items && nn < n_out;
+            resv[q] = make_uint4(0u, 0u, 0u, 0u);
+            if (!kGated && on && (epilogue & DLI_EPI_RESIDUAL))
+              resv[q] = ld_16B(residual + (size_t)(m_tile0 + mc) * n_out + nn);
+          }
+          for (int sp0 = 0; sp0 < splits; sp0 += 4) {
+            float4 v[kItems][4][kGated ? 4 : 2];
+#pragma unroll
+            for (int q = 0; q < kItems; ++q) {
+              const int id = it0 + q * 128 + et;
+              const int mc = id >> 4, ng = id & 15;
+              const bool on = id < items;
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                const bool ld = on && sp0 + u < splits;
+                const float* src = all + ((size_t)(ld ? sp0 + u : 0) * Cfg::kAccCols + (ld ? mc : 0)) * 128 + ng * 8;
+                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                v[q][u][0] = ld ? __ldcg(reinterpret_cast<const float4*>(src)) : z;
+                v[q][u][1] = ld ? __ldcg(reinterpret_cast<const float4*>(src) + 1) : z;
+                if (kGated) {
+                  v[q][u][2] = ld ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)BN * 128)) : z;
+                  v[q][u][3] = ld ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)BN * 128) + 1) : z;
+                }
+              }
+            }
+#pragma unroll
+            for (int q = 0; q < kItems; ++q)
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                acc1[q][0] += v[q][u][0].x; acc1[q][1] += v[q][u][0].y; acc1[q][2] += v[q][u][0].z; acc1[q][3] += v[q][u][0].w;
+                acc1[q][4] += v[q][u][1].x; acc1[q][5] += v[q][u][1].y; acc1[q][6] += v[q][u][1].z; acc1[q][7] += v[q][u][1].w;
+                if (kGated) {
+                  acc2[q][0] += v[q][u][2].x; acc2[q][1] += v[q][u][2].y; acc2[q][2] += v[q][u][2].z; acc2[q][3] += v[q][u][2].w;
+                  acc2[q][4] += v[q][u][3].x; acc2[q][5] += v[q][u][3].y; acc2[q][6] += v[q][u][3].z; acc2[q][7] += v[q][u][3].w;
+                }
+              }
+          }
+#pragma unroll
+          for (int q = 0; q < kItems; ++q) {
+            const int id = it0 + q * 128 + et;
+            const int mc = id >> 4, ng = id & 15;
+            const int nn = n_tile0 + ng * 8;
+            if (id < items && nn < n_out) {
+              float o[8], rr[8];
+              unpack8(resv[q], rr);
+              float bvv[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) bvv[e] = 0.f;
+              if (!kGated && (epilogue & DLI_EPI_BIAS)) unpack8(ld_16B(bias + nn), bvv);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                if (kGated) {
+                  const float gte = round_bf16(acc1[q][e]), up = round_bf16(acc2[q][e]);
+                  o[e] = round_bf16(silu_f(gte)) * up;
+                } else {
+                  float vv = round_bf16(acc1[q][e] + bvv[e]);
+                  if (epilogue & DLI_EPI_GELU_NEW) vv = round_bf16(gelu_new_f(vv));
+                  o[e] = vv + rr[e];
+                }
+              }
+              st_16B(y + (size_t)(m_tile0 + mc) * n_out + nn, pack8(o));
+            }
+          }
+        }
+      } else if (finish) {
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += 16) {
           if (m_tile0 + c0 >= M) break;  // warp-uniform
           float a1[16], a2[16];
-          if (splits == 1) {
+          {
             uint32_t r[16], r2[16];
             tmem_ld_32x16(lane_base + c0, r);
             if (kGated) tmem_ld_32x16(lane_base + BN + c0, r2);
             tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 16; ++j) { a1[j] = __uint_as_float(r[j]); a2[j] = kGated ? __uint_as_float(r2[j]) : 0.f; }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) { a1[j] = 0.f; a2[j] = 0.f; }
-            // four splits' worth of loads in flight at a time (one L2 round trip instead of four);
-            // the additions stay in split order, so the result does not depend on arrival order
-            for (int sp0 = 0; sp0 < splits; sp0 += 4) {
-              float v1[4][16], v2[4][16];
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const bool on = sp0 + q < splits;
-                const float* src = all + (size_t)(on ? sp0 + q : sp0) * Cfg::kAccCols * 128;
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                  const bool ld = on && (m_tile0 + c0 + j < M);
-                  v1[q][j] = ld ? __ldcg(src + (size_t)(c0 + j) * 128 + row) : 0.f;
-                  v2[q][j] = (kGated && ld) ? __ldcg(src + (size_t)(BN + c0 + j) * 128 + row) : 0.f;
-                }
-              }
-#pragma unroll
-              for (int q = 0; q < 4; ++q)
-#pragma unroll
-                for (int j = 0; j < 16; ++j) { a1[j] += v1[q][j]; a2[j] += v2[q][j]; }
-            }
           }
           if (n < n_out) {
             const float bv = (!kGated && (epilogue & DLI_EPI_BIAS)) ? __bfloat162float(bias[n]) : 0.f;
@@ -312,6 +375,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           }
         }
+      }
+      if (finish) {
         if (splits > 1 && warp == 2 && lane == 0) splitk_counters[tile] = 0;
       }
     }
