@@ -413,6 +413,22 @@ struct PrefillCfg {
   static_assert(!kGated || BN == 256, "gated tile is gate128|up128");
 };
 
+// Tile walk of the persistent kernel: m-tiles in groups of 16, inside a group m fastest, then n.  The
+// 148 tiles in flight at any time then cover ~16 activation tiles x ~9 weight tiles, so both operands are
+// re-used out of L2 (m fastest over ALL m-tiles would re-stream the whole activation matrix from HBM
+// once per weight tile when M is tens of thousands of rows).  M <= 2048 is a single group.
+__device__ __forceinline__ void prefill_tile_coords(int tile, int m_tiles, int num_tiles, int& m_blk, int& n_blk) {
+  constexpr int kGroup = 16;
+  const int n_tiles = num_tiles / m_tiles;
+  const int per_group = kGroup * n_tiles;
+  const int grp = tile / per_group;
+  const int m0 = grp * kGroup;
+  const int gsize = min(kGroup, m_tiles - m0);
+  const int r = tile - grp * per_group;
+  n_blk = r / gsize;
+  m_blk = m0 + r - n_blk * gsize;
+}
+
 template <int BN, bool kGated>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -456,15 +472,18 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // ring of weight (B) loads for the first tile goes out before the dependency wait
       const int first = blockIdx.x;
       const int pre = (first < num_tiles) ? min(S, num_kb) : 0;
+      int first_m = 0, first_n = 0;
+      if (pre) prefill_tile_coords(first, m_tiles, num_tiles, first_m, first_n);
       for (int kb = 0; kb < pre; ++kb) {
         const uint32_t sA = smem_addr(smem + kb * Cfg::kStageBytes);
         mbar_expect_tx(full_bar + 8 * kb, Cfg::kStageBytes);
-        tma_load_2d(sA + Cfg::kABytes, &tmB, full_bar + 8 * kb, kb * kBlockK, (first / m_tiles) * BN);
+        tma_load_2d(sA + Cfg::kABytes, &tmB, full_bar + 8 * kb, kb * kBlockK, first_n * BN);
       }
       pdl_wait();
       uint32_t kc = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_blk = tile % m_tiles, n_blk = tile / m_tiles;
+        int m_blk, n_blk;
+        prefill_tile_coords(tile, m_tiles, num_tiles, m_blk, n_blk);
         for (int kb = 0; kb < num_kb; ++kb, ++kc) {
           const int s = kc % S;
           const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
@@ -508,7 +527,8 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     pdl_wait();  // residual / bias may come from the previous kernel
     uint32_t tl = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
-      const int m_blk = tile % m_tiles, n_blk = tile / m_tiles;
+      int m_blk, n_blk;
+      prefill_tile_coords(tile, m_tiles, num_tiles, m_blk, n_blk);
       const uint32_t as = tl & 1;
       mbar_wait(tfull_bar + 8 * as, (tl >> 1) & 1);
       tcgen05_fence_after();
