@@ -332,13 +332,15 @@ class ShardEngine:
         self._graphs.clear()  # captured graphs hold the old workspace pointers
 
     def _num_splits(self, B: int) -> int:
-        """KV splits per (sequence, kv head).  Enough CTAs to cover the SMs once, but no
-        finer than 4 tiles (256 tokens) per split: a split's tiles are all in flight at
-        once (4-stage cp.async) and the merge cost grows with the split count."""
+        """KV splits per (sequence, kv head).  About two CTAs per SM (measured sweet spot of the
+        3-stage kernel: B = 4 / 8 / 16 at 2k context are 21 / 15 / 21 % faster with 8 / 4 / 2 splits
+        than with one CTA per SM; 32+ sequences need no split), but no finer than 4 tiles (256
+        tokens) per split: the merge cost grows with the split count, and at batch 1 the 9 splits
+        of a 2k context (72 CTAs, whole split in flight) measured best in the full step."""
         if os.environ.get("DLI_ATTN_SPLITS"):
             return int(os.environ["DLI_ATTN_SPLITS"])
         tiles = (self.max_seq_len + 63) // 64
-        want = max(1, self.sms // (B * self.spec.n_kv_heads))
+        want = max(1, 2 * self.sms // (B * self.spec.n_kv_heads))
         return max(1, min((tiles + 3) // 4, want, 64))
 
     # ------------------------------------------------------------------ one layer range
