@@ -193,6 +193,10 @@ def _gather_kv(cache, page_table, b, S):
         (2, 64, 8, 128, 16, [1000, 513], 8, 0),
         (2, 32, 8, 128, 16, [900, 200], 4, 256),
         (2, 12, 12, 64, 16, [40, 97], 2, 0),
+        (1, 64, 8, 128, 16, [8195], 33, 0),        # 70B heads at an 8k context (BASELINE configs[4])
+        (4, 64, 8, 128, 16, [8192, 4097, 1, 6000], 9, 0),
+        (2, 32, 8, 128, 16, [5000, 4097], 8, 4096),  # Mistral window once the context exceeds it
+        (40, 32, 8, 128, 16, [2048 - 7 * i for i in range(40)], 1, 0),  # many sequences: the 3-stage path
     ],
 )
 def test_paged_attn_decode(cuda, B, H, KV, hd, page, lens, splits, window):
