@@ -30,6 +30,7 @@ from __future__ import annotations
 
 import json
 import os
+import threading
 import time
 from typing import Dict
 
@@ -81,6 +82,9 @@ class Worker:
         self.batching = env.get("DLI_BATCHING", "0") == "1"
         self.max_batch = int(env.get("DLI_MAX_BATCH", "8")) if self.batching else 1
         self.batchers: Dict[str, object] = {}
+        # With batching the WSGI server is threaded: everything that touches the dicts above or runs an
+        # engine directly holds this lock; only the wait on a batcher's future happens outside it.
+        self._lock = threading.RLock()
         self.routes = {("GET", "/health"): self.health, ("POST", "/load_model"): self.load_model,
                        ("POST", "/load_shard"): self.load_shard, ("POST", "/unload_model"): self.unload_model,
                        ("POST", "/inference"): self.inference}
@@ -188,21 +192,25 @@ class Worker:
             start_time = time.time()
             deadline = start_time + timeout
             if shard_ids:
-                result = self.run_shard_inference(model_name, prompt, shard_ids, max_length, deadline,
-                                                  self._gen_kwargs(data))
+                with self._lock:
+                    result = self.run_shard_inference(model_name, prompt, shard_ids, max_length, deadline,
+                                                      self._gen_kwargs(data))
             else:
-                if model_name not in self.loaded_models:
-                    resp, code = self.load_model({"model_name": model_name})
-                    if code == 500:
-                        return resp, code
-                model, tokenizer = self.loaded_models[model_name], self.loaded_tokenizers[model_name]
-                ids = tokenizer(prompt, return_tensors="pt")["input_ids"]
-                if (time.time() - start_time) > timeout:
-                    raise TimeoutError("Inference preparation timed out")
-                if model_name in self.batchers:  # joins the running batch; greedy
-                    outputs = self.batchers[model_name].submit(ids[0], max_length, timeout).result()[None]
-                else:
-                    outputs = model.generate(ids, max_length=max_length, deadline=deadline, **self._gen_kwargs(data))
+                with self._lock:
+                    if model_name not in self.loaded_models:
+                        resp, code = self.load_model({"model_name": model_name})
+                        if code == 500:
+                            return resp, code
+                    model, tokenizer = self.loaded_models[model_name], self.loaded_tokenizers[model_name]
+                    batcher = self.batchers.get(model_name)
+                    ids = tokenizer(prompt, return_tensors="pt")["input_ids"]
+                    if (time.time() - start_time) > timeout:
+                        raise TimeoutError("Inference preparation timed out")
+                    if batcher is None:
+                        outputs = model.generate(ids, max_length=max_length, deadline=deadline,
+                                                 **self._gen_kwargs(data))
+                if batcher is not None:  # joins the running batch (greedy); the wait is outside the lock
+                    outputs = batcher.submit(ids[0], max_length, timeout).result()[None]
                 result = tokenizer.decode(outputs[0], skip_special_tokens=True)
                 if (time.time() - start_time) > timeout:
                     raise TimeoutError("Inference generation timed out")
@@ -248,7 +256,10 @@ class Worker:
             known = {p for _, p in self.routes}
             return {"status": "error", "message": "Method not allowed" if path in known else "Not found"}, \
                 (405 if path in known else 404)
-        return fn(data)
+        if fn == self.inference:  # takes the lock itself, around everything but a batcher wait
+            return fn(data)
+        with self._lock:
+            return fn(data)
 
     def __call__(self, environ, start_response):
         req = Request(environ)
