@@ -761,13 +761,15 @@ int dli_gemm_splitk_gated_silu_bf16(const void* x, const void* w_gu, void* y, in
 
 int dli_linear_bf16(const void* x, const void* w, const void* bias, const void* residual, void* y, int M, int N,
                     int K, int epilogue, dli_stream_t stream) {
-  if (M <= 4 || K % 64 != 0 || N % 16 != 0)
+  // measured on B200 (profiles/r1_notes.md): the CUDA-core GEMV streams at 6.0-7.3 TB/s for M <= 2 but
+  // drops to 4.1-5.0 TB/s at M = 3-4 (FMA issue bound); the swap-AB tensor-core stream holds 5.7-6.4
+  if (M <= 2 || K % 64 != 0 || N % 16 != 0)
     return dli_gemv_bf16(x, w, bias, residual, y, M, N, K, epilogue, stream);
   return dli_gemm_bf16(x, w, bias, residual, y, M, N, K, epilogue, stream);
 }
 
 int dli_linear_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F, int K, dli_stream_t stream) {
-  if (M <= 4 || K % 64 != 0) return dli_gemv_gated_silu_bf16(x, w_gu, y, M, F, K, stream);
+  if (M <= 2 || K % 64 != 0) return dli_gemv_gated_silu_bf16(x, w_gu, y, M, F, K, stream);
   return dli_gemm_gated_silu_bf16(x, w_gu, y, M, F, K, stream);
 }
 

@@ -23,6 +23,7 @@ import torch
 from . import ops
 
 BF = torch.bfloat16
+_GEMV_MAX_ROWS = int(os.environ.get("DLI_GEMV_MAX_ROWS", "2"))  # rows served by the CUDA-core GEMV (<= 4)
 _EXP_SKIP = os.environ.get("DLI_EXP_SKIP", "")  # measurement knob only, see profiles/r1_notes.md
 
 
@@ -350,8 +351,10 @@ class ShardEngine:
         x, qkv, attn, act = self._x[:rows], self._qkv[:rows], self._attn[:rows], self._act[:rows]
         H, KV, hd = s.n_heads, s.n_kv_heads, s.head_dim
         decode = prefill_shape is None
-        fuse_norm = decode and rows <= 4 and s.arch == "llama"  # RMSNorm inside the weight-streaming GEMV
-        split_k = decode and 4 < rows <= 128  # batched decode: split-K tcgen05 weight stream on every SM
+        # rows <= 2: CUDA-core GEMV with the RMSNorm fused in (6.0-7.3 TB/s); 3..128 rows: split-K tcgen05
+        # weight stream on every SM (the GEMV's FMA work grows with the rows: 4.1-5.0 TB/s at 3-4 rows)
+        fuse_norm = decode and rows <= _GEMV_MAX_ROWS and s.arch == "llama"
+        split_k = decode and _GEMV_MAX_ROWS < rows <= 128
         if split_k and self._sk is None:
             n_max = max(s.vocab, 2 * s.d_ff, (H + 2 * KV) * hd, s.d_model)
             self._sk = torch.zeros(ops.gemm_splitk_scratch_bytes(128, n_max), dtype=torch.uint8, device=self.device)
@@ -410,7 +413,7 @@ class ShardEngine:
         s = self.spec
         B = h_last.shape[0]
         xn = self._x[:B]
-        if s.arch == "llama" and B <= 4:
+        if s.arch == "llama" and B <= _GEMV_MAX_ROWS:
             ops.rmsnorm_linear(h_last, self.w["norm"], s.eps, self.w["head"], out=logits)
         else:
             if s.arch == "llama":
@@ -581,7 +584,7 @@ class ShardEngine:
 
         def body():
             s = self.spec
-            if B <= 4 and s.arch == "llama":
+            if B <= _GEMV_MAX_ROWS and s.arch == "llama":
                 ops.rmsnorm_linear(st["hf"], self.w["norm"], s.eps, self.w["head"], out=st["logits"])
             else:
                 xn = self._x[:B]

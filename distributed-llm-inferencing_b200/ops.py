@@ -150,7 +150,7 @@ def _linear(fn_name, x, w, bias, residual, out, epilogue):
 
 
 def linear(x, w, bias=None, residual=None, out=None, epilogue=EPI_NONE):
-    """y = epi(x @ w.T); GEMV for M <= 4, tcgen05 GEMM otherwise."""
+    """y = epi(x @ w.T); CUDA-core GEMV for M <= 2, tcgen05 GEMM otherwise."""
     return _linear("dli_linear_bf16", x, w, bias, residual, out, epilogue)
 
 
