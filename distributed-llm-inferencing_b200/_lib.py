@@ -53,6 +53,8 @@ SIGNATURES = {
     "dli_gemm_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "dli_linear_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "dli_gemv_gated_silu_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "dli_gemv_mma_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "dli_gemv_mma_gated_silu_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "dli_gemm_gated_silu_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "dli_linear_gated_silu_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "dli_argmax_bf16": (_i, [_vp, _i, _vp, _i, _i, _vp]),

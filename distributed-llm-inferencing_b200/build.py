@@ -25,6 +25,7 @@ SOURCES = [
     "attn_prefill.cu",
     "attn_prefill_tc.cu",
     "gemv.cu",
+    "gemv_mma.cu",
     "gemm_tcgen05.cu",
     "elementwise.cu",
     "sample.cu",

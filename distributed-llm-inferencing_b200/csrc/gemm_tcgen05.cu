@@ -765,6 +765,9 @@ int dli_linear_bf16(const void* x, const void* w, const void* bias, const void* 
   // drops to 4.1-5.0 TB/s at M = 3-4 (FMA issue bound); the swap-AB tensor-core stream holds 5.7-6.4
   if (M <= 2 || K % 64 != 0 || N % 16 != 0)
     return dli_gemv_bf16(x, w, bias, residual, y, M, N, K, epilogue, stream);
+  // no split-K scratch here: a matrix of few 128-row tiles would leave most SMs idle in the swap-AB
+  // kernel (1.8 TB/s on 4096 x 14336), the mma.sync stream holds 4-5 TB/s on those
+  if (M <= 8 && N < 8192) return dli_gemv_mma_bf16(x, w, bias, residual, y, M, N, K, epilogue, stream);
   return dli_gemm_bf16(x, w, bias, residual, y, M, N, K, epilogue, stream);
 }
 

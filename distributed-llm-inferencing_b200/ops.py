@@ -158,6 +158,11 @@ def gemv(x, w, bias=None, residual=None, out=None, epilogue=EPI_NONE):
     return _linear("dli_gemv_bf16", x, w, bias, residual, out, epilogue)
 
 
+def gemv_mma(x, w, bias=None, residual=None, out=None, epilogue=EPI_NONE):
+    """Weight stream with mma.sync for 3..16 rows (dli_gemv_mma_bf16)."""
+    return _linear("dli_gemv_mma_bf16", x, w, bias, residual, out, epilogue)
+
+
 def gemm(x, w, bias=None, residual=None, out=None, epilogue=EPI_NONE):
     return _linear("dli_gemm_bf16", x, w, bias, residual, out, epilogue)
 
@@ -182,6 +187,10 @@ def linear_gated_silu(x, w_gu, out=None):
 
 def gemv_gated_silu(x, w_gu, out=None):
     return _gated("dli_gemv_gated_silu_bf16", x, w_gu, out)
+
+
+def gemv_mma_gated_silu(x, w_gu, out=None):
+    return _gated("dli_gemv_mma_gated_silu_bf16", x, w_gu, out)
 
 
 def gemm_gated_silu(x, w_gu, out=None):

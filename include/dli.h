@@ -226,6 +226,19 @@ int dli_linear_bf16(const void* x, const void* w, const void* bias,
  * (the host packs this once at load).  F % 128 == 0, K % 64 == 0. */
 int dli_gemv_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F,
                              int K, dli_stream_t stream);
+
+/* The same projections for 3..16 activation rows: the weight-streaming loop of
+ * the GEMV with its multiply-adds on mma.sync.m16n8k16 (x = A operand, 8 weight
+ * rows = B operand, both loaded straight from global memory into fragments), so
+ * the kernel stays an HBM stream where the CUDA-core GEMV turns FMA-issue bound.
+ * Same reference lines, layouts, epilogues and rounding points as dli_gemv_bf16 /
+ * dli_gemv_gated_silu_bf16; M <= 16, K % 8 == 0 (gated: F % 128 == 0).  The
+ * summation order differs from the GEMV's (fixed, deterministic). */
+int dli_gemv_mma_bf16(const void* x, const void* w, const void* bias,
+                      const void* residual, void* y, int M, int N, int K,
+                      int epilogue, dli_stream_t stream);
+int dli_gemv_mma_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M,
+                                 int F, int K, dli_stream_t stream);
 int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F,
                              int K, dli_stream_t stream);
 int dli_linear_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M,

@@ -27,4 +27,17 @@ for name, (N, K, gated) in shapes.items():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
         us = e0.elapsed_time(e1) / 12 * 1000
-        print(f'{name:12s} M={M:2d}: {us:7.1f} us  {N * K * 2 / us / 1e6:5.2f} TB/s')
+        line = f'{name:12s} M={M:2d}: {us:7.1f} us  {N * K * 2 / us / 1e6:5.2f} TB/s'
+        if M >= 2:
+            def run2():
+                for w in ws:
+                    (ops.gemv_mma_gated_silu(x, w, out=out) if gated else ops.gemv_mma(x, w, out=out))
+            run2(); torch.cuda.synchronize()
+            g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2):
+                for _ in range(4): run2()
+            g2.replay(); torch.cuda.synchronize()
+            e0.record(); g2.replay(); e1.record(); torch.cuda.synchronize()
+            us2 = e0.elapsed_time(e1) / 12 * 1000
+            line += f'   | mma stream {us2:7.1f} us  {N * K * 2 / us2 / 1e6:5.2f} TB/s'
+        print(line)

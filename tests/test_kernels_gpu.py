@@ -352,6 +352,41 @@ def test_gemm_gated_silu_tcgen05(cuda, M, F, K):
     torch.testing.assert_close(y.float(), _gated_ref(x, wg, wu).float(), rtol=3.2e-2, atol=2e-2 * math.sqrt(K / 4096))
 
 
+@pytest.mark.parametrize("M", [1, 3, 4, 8, 9, 13, 16])
+@pytest.mark.parametrize("N,K", [(6144, 4096), (4096, 14336), (2560, 2048), (1000, 264), (50257, 768)])
+def test_gemv_mma(cuda, M, N, K):
+    """mma.sync weight stream (3..16 rows): same contract as the GEMV, incl. ragged N and K."""
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(M * 7 + N + K)
+    x = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    w = (torch.randn(N, K, device=cuda, generator=gen) * 0.02).to(BF)
+    bias = torch.randn(N, device=cuda, generator=gen).to(BF)
+    res = torch.randn(M, N, device=cuda, generator=gen).to(BF)
+    _check_linear(ops.gemv_mma(x, w), _lin_ref(x, w), K)
+    _check_linear(ops.gemv_mma(x, w, bias=bias, residual=res), _lin_ref(x, w, bias, res), K, operand_ulp=2.0 ** -5)
+    _check_linear(ops.gemv_mma(x, w, bias=bias, epilogue=ops.EPI_GELU_NEW), _lin_ref(x, w, bias, gelu=True), K,
+                  operand_ulp=2.0 ** -5)
+    # in-place residual (y aliases residual), as the engine uses it
+    h = res.clone()
+    ops.gemv_mma(x, w, residual=h, out=h)
+    _check_linear(h, _lin_ref(x, w, None, res), K, operand_ulp=2.0 ** -5)
+    # deterministic
+    assert torch.equal(ops.gemv_mma(x, w), ops.gemv_mma(x, w))
+
+
+@pytest.mark.parametrize("M,F,K", [(3, 14336, 4096), (8, 5632, 2048), (16, 256, 128), (11, 28672, 8192)])
+def test_gemv_mma_gated_silu(cuda, M, F, K):
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(F + M)
+    x = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    wg = (torch.randn(F, K, device=cuda, generator=gen) * 0.03).to(BF)
+    wu = (torch.randn(F, K, device=cuda, generator=gen) * 0.03).to(BF)
+    y = ops.gemv_mma_gated_silu(x, ops.pack_gate_up(wg, wu))
+    torch.testing.assert_close(y.float(), _gated_ref(x, wg, wu).float(), rtol=3.2e-2, atol=2e-2 * math.sqrt(K / 4096))
+
+
 def test_gemv_matches_gemm_closely(cuda):
     """The two projection paths agree to bf16 rounding on the same inputs."""
     from dli_b200 import ops
