@@ -202,9 +202,15 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
           if (tok > qrow || (window > 0 && tok <= qrow - window)) s[i] = -INFINITY;
         }
       }
-      float mx = -INFINITY;
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the 64-long one is latency-bound
 #pragma unroll
-      for (int i = 0; i < 64; ++i) mx = fmaxf(mx, s[i]);
+      for (int i = 0; i < 64; i += 4) {
+        mx4[0] = fmaxf(mx4[0], s[i]);
+        mx4[1] = fmaxf(mx4[1], s[i + 1]);
+        mx4[2] = fmaxf(mx4[2], s[i + 2]);
+        mx4[3] = fmaxf(mx4[3], s[i + 3]);
+      }
+      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       xch[(it & 1) * 256 + half * 128 + row] = mx;
       asm volatile("bar.sync 1, 256;" ::: "memory");
       mx = fmaxf(mx, xch[(it & 1) * 256 + (half ^ 1) * 128 + row]);
@@ -212,12 +218,18 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
       const float corr = exp2f((m_run - m_use) * scale_log2);
       m_run = m_new;
-      float rs = 0.f;
+      // p = 2^(s*scale - m*scale): one FFMA feeds each exp2; four partial sums
+      const float ms = m_use * scale_log2;
+      float rs4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int i = 0; i < 64; ++i) {
-        s[i] = exp2f((s[i] - m_use) * scale_log2);
-        rs += s[i];
+      for (int i = 0; i < 64; i += 4) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          s[i + u] = exp2f(fmaf(s[i + u], scale_log2, -ms));
+          rs4[u] += s[i + u];
+        }
       }
+      const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
       l_run = l_run * corr + rs;
       // previous P.V must have finished before P is overwritten and O is rescaled
       if (it > 0) {
@@ -235,7 +247,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
         u.w = pack_bf16(s[c * 8 + 6], s[c * 8 + 7]);
         *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = u;
       }
-      if (it > 0) {
+      // (skipped when no row of this warp moved its maximum: corr == 1 exactly, nothing to do)
+      if (it > 0 && !__all_sync(0xffffffffu, corr == 1.f)) {
         // O *= corr on this thread's 64 output columns; TMEM -> registers -> TMEM
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
