@@ -4,7 +4,7 @@ sys.path.insert(0, '.')
 from dli_b200 import ops
 torch.cuda.set_device(0)
 H, KV, hd, page = 32, 8, 128, 16
-for B, S in [(2, 2048), (4, 2048), (8, 2048), (16, 2048), (32, 2048), (8, 8192)]:
+for B, S in [(8, 2048), (16, 2048), (32, 2048), (64, 2048), (8, 8192)]:
     max_pages = (S + page - 1) // page
     n_pages = B * max_pages
     pt = torch.randperm(n_pages, device='cuda').int().reshape(B, max_pages).contiguous()
@@ -14,7 +14,7 @@ for B, S in [(2, 2048), (4, 2048), (8, 2048), (16, 2048), (32, 2048), (8, 8192)]
     out = torch.empty(B, H * hd, device='cuda', dtype=torch.bfloat16)
     seq = torch.full((B,), S, device='cuda', dtype=torch.int32)
     mb = B * S * KV * hd * 2 * 2 / 1e6
-    for splits in (1, 2, 3, 4, 6, 8, 12, 16, 32):
+    for splits in (1, 2, 4):
         nb = ops.attn_decode_scratch_bytes(B, H, hd, splits)
         scratch = torch.empty(max(nb // 4, 1), device='cuda', dtype=torch.float32)
         def run():
