@@ -7,6 +7,11 @@
 // scheduled first.  Tensor-bound in principle (4*T^2/2*hd FLOPs per head) but
 // only ~4 % of prefill FLOPs at T=2048; K/V re-reads by the
 // G query heads of a KV head are served by L2.
+//
+// kPaged (chunked prefill): the T rows are a CHUNK of each prompt at positions prefix .. prefix+T-1.
+// Queries still come from the packed qkv buffer of the chunk, keys and values of the WHOLE context
+// (the earlier chunks and this one, appended by dli_rope_kv_append_bf16 just before) come from the
+// paged KV cache, page by page like the decode kernel does it.  Same arithmetic otherwise.
 #include "mma_utils.cuh"
 
 namespace dli {
@@ -14,10 +19,12 @@ namespace dli {
 constexpr int kPfThreads = 128;
 constexpr int kPfTile = 64;
 
-template <int HD>
+template <int HD, bool kPaged>
 __global__ void __launch_bounds__(kPfThreads)
 attn_prefill_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int T, int H, int KV,
-                    float scale_log2, int window) {
+                    float scale_log2, int window, const bf16* __restrict__ k_cache,
+                    const bf16* __restrict__ v_cache, const int32_t* __restrict__ page_table, int max_pages,
+                    int page_shift, int prefix) {
   constexpr int RB = HD * 2;
   constexpr int CH = HD / 8;
   constexpr int kTileBytes = kPfTile * RB;
@@ -47,17 +54,31 @@ attn_prefill_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int T,
     for (int i = 0; i < kPfTile * CH / kPfThreads; ++i) {
       const int id = tid + i * kPfThreads;
       const int row = id / CH, c = id - row * CH;
-      const int tok = tile * kPfTile + row;
-      const bool valid = tok < T;
-      const bf16* src = base + (size_t)(valid ? tok : 0) * ld + (size_t)(H + kvh) * HD + c * 8;
-      cp_async_16B(dK + swz<RB>(row, c), src, valid ? 16 : 0);
-      cp_async_16B(dV + swz<RB>(row, c), src + (size_t)KV * HD, valid ? 16 : 0);
+      const int tok = tile * kPfTile + row;  // kPaged: absolute position in the sequence
+      if (kPaged) {
+        const bool valid = tok < prefix + T;
+        size_t off = 0;
+        if (valid) {
+          const int page = page_table[(size_t)b * max_pages + (tok >> page_shift)];
+          off = ((((size_t)page * KV + kvh) << page_shift) + (tok & ((1 << page_shift) - 1))) * HD + c * 8;
+        }
+        cp_async_16B(dK + swz<RB>(row, c), k_cache + off, valid ? 16 : 0);
+        cp_async_16B(dV + swz<RB>(row, c), v_cache + off, valid ? 16 : 0);
+      } else {
+        const bool valid = tok < T;
+        const bf16* src = base + (size_t)(valid ? tok : 0) * ld + (size_t)(H + kvh) * HD + c * 8;
+        cp_async_16B(dK + swz<RB>(row, c), src, valid ? 16 : 0);
+        cp_async_16B(dV + swz<RB>(row, c), src + (size_t)KV * HD, valid ? 16 : 0);
+      }
     }
   };
 
+  // absolute position of the tile's first query row (prefix == 0 when not paged)
+  const int qpos0 = (kPaged ? prefix : 0) + q0;
   int t_begin = 0;
-  if (window > 0 && q0 - window + 1 > 0) t_begin = (q0 - window + 1) / kPfTile;
-  const int t_end = qtile + 1;  // the diagonal tile is the last one
+  if (window > 0 && qpos0 - window + 1 > 0) t_begin = (qpos0 - window + 1) / kPfTile;
+  // last key tile: the one holding the last query row's own position (the diagonal tile when prefix == 0)
+  const int t_end = kPaged ? min((prefix + T + kPfTile - 1) / kPfTile, (qpos0 + kPfTile - 1) / kPfTile + 1) : qtile + 1;
 
   float m_run[2] = {-INFINITY, -INFINITY};
   float l_run[2] = {0.f, 0.f};
@@ -69,7 +90,8 @@ attn_prefill_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int T,
   load_tile(t_begin, 0);
   cp_async_commit();
   const int g = lane >> 2, t4 = lane & 3;
-  const int qrow0 = q0 + warp * 16 + g;  // this thread's rows: qrow0 and qrow0 + 8
+  const int qrow0 = q0 + warp * 16 + g;  // this thread's rows (chunk-relative): qrow0 and qrow0 + 8
+  const int qabs0 = qpos0 + warp * 16 + g;  // ... and their absolute positions
 
   for (int tile = t_begin; tile < t_end; ++tile) {
     const int stage = (tile - t_begin) & 1;
@@ -105,14 +127,15 @@ attn_prefill_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int T,
       }
     }
     // causal (+ sliding window) mask; only tiles that touch a boundary need it
-    const bool need_mask = (tile == qtile) || (window > 0 && tile * kPfTile < q0 + kPfTile - window + 1);
+    const bool need_mask = (tile * kPfTile + kPfTile - 1 > qpos0) ||
+                           (window > 0 && tile * kPfTile < qpos0 + kPfTile - window + 1);
     if (need_mask) {
 #pragma unroll
       for (int j = 0; j < 8; ++j)
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int tok = tile * kPfTile + j * 8 + 2 * t4 + (e & 1);
-          const int qr = qrow0 + (e >> 1) * 8;
+          const int qr = qabs0 + (e >> 1) * 8;
           if (tok > qr || (window > 0 && tok <= qr - window)) s[j][e] = -INFINITY;
         }
     }
@@ -173,19 +196,21 @@ attn_prefill_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int T,
   }
 }
 
-template <int HD>
-static int launch_prefill(const void* qkv, void* out, int B, int T, int H, int KV, float scale,
-                          int window, cudaStream_t s) {
+template <int HD, bool kPaged>
+static int launch_prefill(const void* qkv, void* out, int B, int T, int H, int KV, float scale, int window,
+                          cudaStream_t s, const void* k_cache = nullptr, const void* v_cache = nullptr,
+                          const int32_t* page_table = nullptr, int max_pages = 0, int page_shift = 0, int prefix = 0) {
   constexpr int kSmem = 5 * kPfTile * HD * 2;
   static bool attr_set = false;
   if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_kernel<HD>,
+    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_kernel<HD, kPaged>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     attr_set = true;
   }
   dim3 grid((T + kPfTile - 1) / kPfTile, H, B);
-  DLI_LAUNCH("attn_prefill_kernel", attn_prefill_kernel<HD>, grid, dim3(kPfThreads), (size_t)kSmem, s, (const bf16*)qkv,
-             (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window);
+  DLI_LAUNCH("attn_prefill_kernel", (attn_prefill_kernel<HD, kPaged>), grid, dim3(kPfThreads), (size_t)kSmem, s,
+             (const bf16*)qkv, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window, (const bf16*)k_cache,
+             (const bf16*)v_cache, page_table, max_pages, page_shift, prefix);
   return DLI_OK;
 }
 
@@ -202,6 +227,34 @@ extern "C" int dli_attn_prefill_bf16(const void* qkv, void* out, int B, int T, i
   DLI_CHECK_ARG(aligned16(qkv) && aligned16(out), "dli_attn_prefill_bf16: pointers must be 16-byte aligned");
   if (B == 0 || T == 0) return DLI_OK;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (hd == 128) return launch_prefill<128>(qkv, out, B, T, H, KV, scale, window, s);
-  return launch_prefill<64>(qkv, out, B, T, H, KV, scale, window, s);
+  if (hd == 128) return launch_prefill<128, false>(qkv, out, B, T, H, KV, scale, window, s);
+  return launch_prefill<64, false>(qkv, out, B, T, H, KV, scale, window, s);
+}
+
+extern "C" int dli_attn_prefill_paged_bf16(const void* qkv, void* out, const void* k_cache, const void* v_cache,
+                                           const int32_t* page_table, int max_pages, int B, int T, int prefix, int H,
+                                           int KV, int hd, int page_size, float scale, int window,
+                                           dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(qkv && out && k_cache && v_cache && page_table, "dli_attn_prefill_paged_bf16: null pointer");
+  DLI_CHECK_ARG(hd == 64 || hd == 128, "dli_attn_prefill_paged_bf16: hd must be 64 or 128 (got %d)", hd);
+  DLI_CHECK_ARG(B >= 0 && T >= 0 && prefix >= 0 && H > 0 && KV > 0 && H % KV == 0 && window >= 0 && max_pages > 0,
+                "dli_attn_prefill_paged_bf16: bad sizes B=%d T=%d prefix=%d H=%d KV=%d", B, T, prefix, H, KV);
+  DLI_CHECK_ARG(page_size >= 8 && (page_size & (page_size - 1)) == 0,
+                "dli_attn_prefill_paged_bf16: page_size must be a power of two >= 8 (got %d)", page_size);
+  DLI_CHECK_ARG((long long)prefix + T <= (long long)max_pages * page_size,
+                "dli_attn_prefill_paged_bf16: prefix + T = %d exceeds the page table (%d pages of %d)", prefix + T,
+                max_pages, page_size);
+  DLI_CHECK_ARG(H <= 65535 && B <= 65535, "dli_attn_prefill_paged_bf16: H/B out of grid range");
+  DLI_CHECK_ARG(aligned16(qkv) && aligned16(out) && aligned16(k_cache) && aligned16(v_cache),
+                "dli_attn_prefill_paged_bf16: pointers must be 16-byte aligned");
+  if (B == 0 || T == 0) return DLI_OK;
+  int shift = 0;
+  while ((1 << shift) < page_size) ++shift;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (hd == 128)
+    return launch_prefill<128, true>(qkv, out, B, T, H, KV, scale, window, s, k_cache, v_cache, page_table, max_pages,
+                                     shift, prefix);
+  return launch_prefill<64, true>(qkv, out, B, T, H, KV, scale, window, s, k_cache, v_cache, page_table, max_pages,
+                                  shift, prefix);
 }

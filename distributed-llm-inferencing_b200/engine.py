@@ -390,8 +390,13 @@ class ShardEngine:
             else:
                 ops.rope_kv_append(qkv, self.cos, self.sin, positions, seq_ids, self.kv.page_table,
                                    self.kv.k[li], self.kv.v[li], H, KV, hd)
-                ops.attn_prefill(qkv, attn, prefill_shape[0], prefill_shape[1], H, KV, hd, self.scale,
-                                 window=s.sliding_window)
+                if len(prefill_shape) > 2:  # a chunk at positions prefix..: keys/values from the paged cache
+                    ops.attn_prefill_paged(qkv, attn, self.kv.k[li], self.kv.v[li], st["page_rows"], prefill_shape[0],
+                                           prefill_shape[1], prefill_shape[2], H, KV, hd, self.scale,
+                                           window=s.sliding_window)
+                else:
+                    ops.attn_prefill(qkv, attn, prefill_shape[0], prefill_shape[1], H, KV, hd, self.scale,
+                                     window=s.sliding_window)
             if s.arch == "llama":
                 lin(attn, L["wo"], residual=h, out=h)
                 if fuse_norm:
@@ -489,16 +494,20 @@ class ShardEngine:
         return self._dec[(B, mb)]
 
     def prefill(self, B: int, T: int, ids: Optional[torch.Tensor] = None, hidden: Optional[torch.Tensor] = None,
-                mb: int = 0):
+                mb: int = 0, prefix: Optional[int] = None, final: bool = True):
         """Run the stage over B prompts of T tokens.
         Stage 0 takes `ids` (int32 [B*T] on device), later stages `hidden` [B*T, d].
         Returns hidden [B*T, d] (a view of the workspace), or on the last stage the
-        int32 next tokens [B] (logits stay in the slot's state)."""
+        int32 next tokens [B] (logits stay in the slot's state).
+        Chunked prefill: `prefix` (not None) says the T tokens are a chunk at positions
+        prefix..prefix+T-1 of prompts whose earlier chunks already went through this stage
+        (attention then reads keys/values from the paged cache); `final=False` on every chunk
+        but the last skips the head and returns the hidden states."""
         rows = B * T
         self._workspace(max(rows, B))
         st = self._dec[(B, mb)]
         dev = self.device
-        positions = torch.arange(T, dtype=torch.int32, device=dev).repeat(B)
+        positions = (torch.arange(T, dtype=torch.int32, device=dev) + (prefix or 0)).repeat(B)
         seq_ids = st["seq_ids"].repeat_interleave(T)
         h = self._h[:rows]
         if self.is_first:
@@ -508,8 +517,8 @@ class ShardEngine:
                 ops.embedding(ids, self.w["embed"], out=h)
         elif hidden.data_ptr() != h.data_ptr():
             h.copy_(hidden)
-        self._layers_forward(h, rows, positions, seq_ids, None, (B, T), st)
-        if not self.is_last:
+        self._layers_forward(h, rows, positions, seq_ids, None, (B, T) if prefix is None else (B, T, prefix), st)
+        if not self.is_last or not final:
             return h
         last_rows = (torch.arange(B, dtype=torch.int32, device=dev) + 1) * T - 1
         if self.head_shard is not None:
@@ -517,6 +526,22 @@ class ShardEngine:
         h_last = ops.embedding(last_rows, h, out=st["h"])  # row gather of the last positions
         self._head(h_last, st["logits"], st["tokens"], st)
         return st["tokens"]
+
+    def prefill_chunked(self, B: int, T: int, chunk: int, ids: Optional[torch.Tensor] = None,
+                        hidden: Optional[torch.Tensor] = None, mb: int = 0):
+        """prefill() fed `chunk` tokens of every prompt at a time (bounded activation memory; in a
+        pipeline the stages work on different chunks at once).  ids / hidden are laid out like
+        prefill()'s: [B*T(, d)], sequence-major.  Returns what prefill() returns, except that a
+        non-last stage returns the hidden states of the LAST chunk only."""
+        out = None
+        src = ids if self.is_first else hidden
+        view = src.view(B, T, *src.shape[1:])
+        for c0 in range(0, T, chunk):
+            tc = min(chunk, T - c0)
+            part = view[:, c0:c0 + tc].reshape(B * tc, *src.shape[1:]).contiguous()
+            kw = {"ids": part} if self.is_first else {"hidden": part}
+            out = self.prefill(B, tc, mb=mb, prefix=c0, final=c0 + tc >= T, **kw)
+        return out
 
     # ------------------------------------------------------------------ decode
     def _decode_body(self, B: int, mb: int):

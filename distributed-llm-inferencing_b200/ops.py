@@ -133,6 +133,18 @@ def attn_prefill(qkv, out, B, T, H, KV, hd, scale, window=0, tensor_core=None):
     return out
 
 
+def attn_prefill_paged(qkv, out, k_cache, v_cache, page_table, B, T, prefix, H, KV, hd, scale, window=0):
+    """Causal attention of a prompt chunk (positions prefix..prefix+T-1) against the paged cache
+    (chunked prefill); page_table holds the rows of the B sequences of this call."""
+    global launch_count
+    _req(qkv), _req(out), _req(k_cache), _req(v_cache), _req(page_table, torch.int32)
+    _lib.check("dli_attn_prefill_paged_bf16", _lib.load().dli_attn_prefill_paged_bf16(
+        _p(qkv), _p(out), _p(k_cache), _p(v_cache), _p(page_table), page_table.shape[1], B, T, prefix, H, KV, hd,
+        k_cache.shape[2], float(scale), window, _stream()))
+    launch_count += 1
+    return out
+
+
 def _linear(fn_name, x, w, bias, residual, out, epilogue):
     global launch_count
     _req(x), _req(w), _req(bias), _req(residual), _req(out)

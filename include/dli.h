@@ -197,6 +197,21 @@ int dli_attn_prefill_bf16(const void* qkv, void* out, int B, int T, int H, int K
 int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T, int H, int KV, int hd,
                              float scale, int window, dli_stream_t stream);
 
+/* Causal attention of a CHUNK of each prompt against the whole context so far
+ * (chunked prefill: the prompt is fed T tokens at a time so that pipeline
+ * stages can work on different chunks at once).  Same reference
+ * lines and arithmetic as dli_attn_prefill_bf16.  qkv holds the chunk's rows
+ * (already rotated) at positions prefix .. prefix+T-1 of each sequence; keys
+ * and values of positions 0 .. prefix+T-1 are read from the paged cache, so
+ * dli_rope_kv_append_bf16 must have appended the chunk first.  page_table:
+ * int32 [B, max_pages], row b = sequence b of this call.  prefix == 0 gives
+ * the result of dli_attn_prefill_bf16. */
+int dli_attn_prefill_paged_bf16(const void* qkv, void* out, const void* k_cache,
+                                const void* v_cache, const int32_t* page_table,
+                                int max_pages, int B, int T, int prefix, int H, int KV,
+                                int hd, int page_size, float scale, int window,
+                                dli_stream_t stream);
+
 /* ---- projections -----------------------------------------------------------
  * y[M,N] = epi(x[M,K] . w[N,K]^T)   — w is the HF nn.Linear layout [out,in].
  * Replaces q/k/v/o_proj TF:models/llama/modeling_llama.py:262-264,:288, the

@@ -259,6 +259,39 @@ def test_attn_prefill(cuda, B, T, H, KV, hd, window, tensor_core):
     torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
 
 
+@pytest.mark.parametrize(
+    "B,T,prefix,H,KV,hd,page,window",
+    [(1, 512, 1536, 32, 8, 128, 16, 0), (2, 100, 37, 32, 4, 64, 16, 0), (3, 5, 0, 12, 12, 64, 8, 0),
+     (2, 64, 64, 8, 2, 128, 32, 0), (1, 300, 500, 8, 8, 128, 16, 256), (2, 1, 130, 4, 4, 64, 16, 0)],
+)
+def test_attn_prefill_paged_chunk(cuda, B, T, prefix, H, KV, hd, page, window):
+    """A chunk of T query rows at positions prefix..prefix+T-1 against the paged cache == the rows
+    prefix.. of a full causal attention over prefix+T tokens."""
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(11 + T + prefix)
+    S = prefix + T
+    page_table, kc, vc = _paged_cache(B, S, KV, hd, page, cuda, gen)
+    qkv = torch.randn(B * T, (H + 2 * KV) * hd, device=cuda, generator=gen).to(BF)
+    out = torch.empty(B * T, H * hd, device=cuda, dtype=BF)
+    scale = hd ** -0.5
+    ops.attn_prefill_paged(qkv, out, kc, vc, page_table, B, T, prefix, H, KV, hd, scale, window=window)
+    G = H // KV
+    q = qkv.float().reshape(B, T, H + 2 * KV, hd)[:, :, :H].permute(0, 2, 1, 3)  # [B,H,T,hd]
+    for b in range(B):
+        k = _gather_kv(kc, page_table, b, S).float().repeat_interleave(G, dim=0)  # [H,S,hd]
+        v = _gather_kv(vc, page_table, b, S).float().repeat_interleave(G, dim=0)
+        s = torch.einsum("htd,hsd->hts", q[b], k) * scale
+        qpos = prefix + torch.arange(T, device=cuda)
+        kpos = torch.arange(S, device=cuda)
+        mask = kpos[None, :] > qpos[:, None]
+        if window:
+            mask = mask | (kpos[None, :] <= qpos[:, None] - window)
+        s = s.masked_fill(mask, float("-inf"))
+        ref = torch.einsum("hts,hsd->htd", torch.softmax(s, -1), v).permute(1, 0, 2).reshape(T, H * hd)
+        torch.testing.assert_close(out[b * T:(b + 1) * T].float(), ref, rtol=2e-2, atol=2e-2)
+
+
 # ----------------------------------------------------------------------------- projections
 def _lin_ref(x, w, bias=None, residual=None, gelu=False):
     acc = x.float() @ w.float().t()
