@@ -97,6 +97,34 @@ class PipelineRunner:
             self._exchange(t, kind, n_rounds, mine, out, token_return)
 
 
+def run_chunked_prefill(stage, rank: int, world: int, n_micro: int, n_chunks: int, group=None) -> None:
+    """Chunked prefill ("chunk the prefill to pipeline it").  A prompt pass through N
+    stages keeps only one stage busy at a time; cut into C chunks of tokens, stage s can work on chunk
+    c+1 while stage s+1 works on chunk c (attention reads the earlier chunks' keys/values from the paged
+    cache).  This runs chunks 0 .. C-2 of every slot — unit u = slot*(C-1) + chunk, stage s works on unit
+    t - s at tick t, one grouped send/receive per tick; the LAST chunk of every slot then goes through
+    the runner's ordinary "prefill" pass, which ends with the head and the first token.
+    stage.compute_chunk(slot, chunk) -> hidden states to pass on; stage.chunk_buffer() -> where the
+    next unit's input lands."""
+    units = n_micro * (n_chunks - 1)
+    if units <= 0:
+        return
+    for t in range(units + world - 1):
+        u = t - rank
+        out = None
+        if 0 <= u < units:
+            mb, c = divmod(u, n_chunks - 1)
+            out = stage.compute_chunk(mb, c)
+        ops: List[dist.P2POp] = []
+        if out is not None and rank < world - 1:
+            ops.append(dist.P2POp(dist.isend, out, rank + 1, group))
+        if rank > 0 and 0 <= t - (rank - 1) < units:
+            ops.append(dist.P2POp(dist.irecv, stage.chunk_buffer(), rank - 1, group))
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+
+
 # ------------------------------------------------------------------------------ vocabulary-parallel head
 class VocabParallelRunner:
     """Same pipeline, but the lm_head is split by vocabulary rows over ALL stages.
@@ -176,24 +204,45 @@ class VocabParallelRunner:
 class EngineStage(StageBase):
     """A ShardEngine as one pipeline stage: slot mb <-> the engine's micro-batch state."""
 
-    def __init__(self, engine, b: int, prompt_len: int, max_total_len: int, n_micro: int):
+    def __init__(self, engine, b: int, prompt_len: int, max_total_len: int, n_micro: int, prefill_chunks: int = 1):
         self.eng, self.b, self.T = engine, b, prompt_len
         self.is_first, self.is_last = engine.is_first, engine.is_last
         self.prompt_ids = {}  # stage 0: slot -> int32 [b*T] device tensor
         for mb in range(n_micro):
             engine.start_batch(b, prompt_len, max_total_len, mb=mb)
         dev = engine.device
-        self._pf_in = None if self.is_first else torch.empty(b * prompt_len, engine.spec.d_model,
+        # chunked prefill: chunks 0..C-2 hold Tc tokens of every prompt, the last one the rest
+        self.chunks = max(1, min(prefill_chunks, prompt_len))
+        self.Tc = (prompt_len + self.chunks - 1) // self.chunks
+        self.chunks = (prompt_len + self.Tc - 1) // self.Tc
+        self.T_last = prompt_len - (self.chunks - 1) * self.Tc
+        self._pf_in = None if self.is_first else torch.empty(b * self.Tc, engine.spec.d_model,
                                                              dtype=torch.bfloat16, device=dev)
 
     def recv_buffer(self, kind, mb):
         st = self.eng._state(self.b, mb)
         if self.is_first:
             return st["tokens"]
-        return self._pf_in if kind == "prefill" else st["h"]
+        return self._pf_in[:self.b * self.T_last] if kind == "prefill" else st["h"]
+
+    def _chunk_ids(self, mb, c0, n):
+        return self.prompt_ids[mb].view(self.b, self.T)[:, c0:c0 + n].reshape(-1).contiguous()
+
+    def chunk_buffer(self):
+        return self._pf_in
+
+    def compute_chunk(self, mb, c):
+        """Chunk c < chunks-1 of slot mb (run_chunked_prefill); returns the hidden states to pass on."""
+        kw = {"ids": self._chunk_ids(mb, c * self.Tc, self.Tc)} if self.is_first else {"hidden": self._pf_in}
+        return self.eng.prefill(self.b, self.Tc, mb=mb, prefix=c * self.Tc, final=False, **kw)
 
     def compute(self, kind, mb):
         if kind == "prefill":
+            if self.chunks > 1:  # the last chunk: ends with the head like an unchunked prefill
+                p0 = (self.chunks - 1) * self.Tc
+                kw = ({"ids": self._chunk_ids(mb, p0, self.T_last)} if self.is_first
+                      else {"hidden": self._pf_in[:self.b * self.T_last]})
+                return self.eng.prefill(self.b, self.T_last, mb=mb, prefix=p0, **kw)
             if self.is_first:
                 return self.eng.prefill(self.b, self.T, ids=self.prompt_ids[mb], mb=mb)
             return self.eng.prefill(self.b, self.T, hidden=self._pf_in, mb=mb)
@@ -249,7 +298,11 @@ def run_pipeline_bench(args, spec, peaks):
     max_len = ctx + 2 * (K + W) + 16
     eng = build_stage_engine(spec, rank, world, local, M * b, max_len, args.page_size, vocab_parallel=vp)
     eng.load_random(seed=0)
-    stage = EngineStage(eng, b, ctx, max_len, M)
+    # chunked prefill (DLI_PREFILL_CHUNKS=C): stages work on different chunks of a prompt at once.  Off by
+    # default: at 2k-token prompts the smaller GEMMs and the mma.sync paged attention cost more than the
+    # pipelining returns (2 stages, 8B: 50 -> 74 ms); it is for long prompts on many stages.
+    chunks = int(os.environ.get("DLI_PREFILL_CHUNKS", "1"))
+    stage = EngineStage(eng, b, ctx, max_len, M, prefill_chunks=chunks)
     if stage.is_first:
         g = torch.Generator().manual_seed(1)
         for mb in range(M):
@@ -269,10 +322,14 @@ def run_pipeline_bench(args, spec, peaks):
         dist.barrier()
         return t.item()
 
-    runner.run("prefill")  # warm-up: lazy module loads, function attributes, NCCL connections
+    def prefill_all():
+        run_chunked_prefill(stage, rank, world, M, stage.chunks)  # chunks 0..C-2 of every slot (nothing if C == 1)
+        runner.run("prefill")  # last chunk + head + first token
+
+    prefill_all()  # warm-up: lazy module loads, function attributes, NCCL connections
     for mb in range(M):
         eng.start_batch(b, ctx, max_len, mb=mb)
-    pf_ms = timed(lambda: runner.run("prefill"))
+    pf_ms = timed(prefill_all)
     runner.run("decode", W)  # warm-up rounds (captures the per-slot CUDA graphs)
     n0 = ops.launch_count
     from bench import ClockSampler, decode_step_bytes
@@ -326,7 +383,8 @@ def run_pipeline_bench(args, spec, peaks):
             "e2e": {"value": M * b * K / (e2e_ms / 1e3), "unit": "tokens/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 4 * M * b, "ms_per_step": e2e_ms / K},
             "roofline": roof,
-            "extra": {"prefill_tokens_per_s": M * b * ctx / (pf_ms / 1e3), "prefill_ms": pf_ms, "tick_ms": tick_ms,
+            "extra": {"prefill_tokens_per_s": M * b * ctx / (pf_ms / 1e3), "prefill_ms": pf_ms,
+                      "prefill_chunks": stage.chunks, "tick_ms": tick_ms,
                       "peaks": peaks["source"]},
             "config": {"workload": f"{args.model} bf16 random-init, {world} pipeline stages (contiguous layer ranges, "
                                    f"reference sharder formula) on {world} GPUs, {M} micro-batches x batch {b} greedy "

@@ -14,7 +14,7 @@ from golden_util import load_case, spec_kwargs  # noqa: E402
 
 from dli_b200.engine import ModelSpec, ShardEngine  # noqa: E402
 from dli_b200.pipeline import (EngineStage, PipelineRunner, VocabParallelRunner, build_stage_engine,  # noqa: E402
-                               init_distributed)
+                               init_distributed, run_chunked_prefill)
 from oracle import decoder_ref as R  # noqa: E402
 
 
@@ -28,11 +28,13 @@ def main():
     vp = os.environ.get("DLI_PIPE_VP", "0") == "1"  # vocabulary-parallel head
     eng = build_stage_engine(spec, rank, world, local, max_batch=M * b, max_seq_len=128, vocab_parallel=vp)
     eng.load_state_dict(sd)
-    stage = EngineStage(eng, b, T, T + rounds + 2, M)
+    chunks = int(os.environ.get("DLI_CHECK_CHUNKS", "1"))  # > 1: chunked, pipelined prefill
+    stage = EngineStage(eng, b, T, T + rounds + 2, M, prefill_chunks=chunks)
     if stage.is_first:
         for mb in range(M):
             stage.prompt_ids[mb] = c["prompts"][mb].to("cuda", torch.int32).contiguous()
     runner = (VocabParallelRunner if vp else PipelineRunner)(stage, rank, world, M)
+    run_chunked_prefill(stage, rank, world, M, stage.chunks)
     runner.run("prefill")
     first = None
     if stage.is_last and not vp:
@@ -50,7 +52,19 @@ def main():
             got = torch.cat((first[:, :1], logs), dim=1).cpu().long()  # [M, 1 + rounds]
         full = ShardEngine(spec, device=f"cuda:{local}", max_batch=B, max_seq_len=128)
         full.load_state_dict(sd)
-        want = full.generate(c["prompts"], T + 1 + rounds)[:, T:]
+        if stage.chunks > 1:
+            # same chunking and the same rows per call on the single engine (one sequence at a time, like a
+            # slot): the projections pick their kernel by row count, so only then are the bits identical
+            rows = []
+            for mb in range(M):
+                full.start_batch(1, T, T + rounds + 2)
+                toks = [full.prefill_chunked(1, T, stage.Tc, ids=c["prompts"][mb].to("cuda", torch.int32)).clone()]
+                for _ in range(rounds):
+                    toks.append(full.decode_step(1).clone())
+                rows.append(torch.cat(toks))
+            want = torch.stack(rows).cpu().long()
+        else:
+            want = full.generate(c["prompts"], T + 1 + rounds)[:, T:]
         ok = torch.equal(got, want)
         print("pipeline tokens", got.tolist(), "single-engine tokens", want.tolist(), flush=True)
     flag = torch.tensor([1 if ok else 0], device="cuda")

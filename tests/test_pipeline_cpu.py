@@ -226,3 +226,57 @@ def test_vocab_parallel_pipeline_matches_sequential_over_gloo(world, n_micro, ro
     want = sequential_vp(world, n_micro, 2, 4, rounds)
     for mb in range(n_micro):
         assert got[mb] == want[mb].tolist(), (mb, got[mb], want[mb].tolist())
+
+
+# ------------------------------------------------------------------------------ chunked prefill
+class ToyChunkStage:
+    """Chunk c of slot mb carries the value 100*mb + c; every stage adds 1000*(stage+1) and remembers
+    (per slot) the order in which chunks arrived — what a KV cache needs: chunk c after chunks < c."""
+
+    def __init__(self, rank, world, n_micro, d=3):
+        self.rank, self.is_first, self.is_last = rank, rank == 0, rank == world - 1
+        self.buf = torch.zeros(d)
+        self.d = d
+        self.seen = [[] for _ in range(n_micro)]
+
+    def chunk_buffer(self):
+        return self.buf
+
+    def compute_chunk(self, mb, c):
+        h = torch.full((self.d,), float(100 * mb + c)) if self.is_first else self.buf.clone()
+        h = h + 1000 * (self.rank + 1)
+        self.seen[mb].append((c, h.tolist()))
+        self.out = h
+        return self.out
+
+
+def _chunk_worker(rank, world, port, n_micro, n_chunks, q):
+    from dli_b200.pipeline import run_chunked_prefill
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    stage = ToyChunkStage(rank, world, n_micro)
+    run_chunked_prefill(stage, rank, world, n_micro, n_chunks)
+    q.put((rank, stage.seen))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_micro,n_chunks", [(2, 3, 4), (3, 2, 3), (2, 1, 1), (3, 4, 2)])
+def test_chunked_prefill_schedule_over_gloo(world, n_micro, n_chunks):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_chunk_worker, args=(r, world, port, n_micro, n_chunks, q)) for r in range(world)]
+    [p.start() for p in procs]
+    got = dict(q.get(timeout=120) for _ in range(world))
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    for rank in range(world):
+        for mb in range(n_micro):
+            seen = got[rank][mb]
+            # chunks 0 .. C-2 of every slot, in order, each carrying what the stages before added
+            assert [c for c, _ in seen] == list(range(n_chunks - 1))
+            for c, h in seen:
+                want = 100 * mb + c + sum(1000 * (s + 1) for s in range(rank + 1))
+                assert h == [float(want)] * 3
