@@ -298,10 +298,11 @@ def run_pipeline_bench(args, spec, peaks):
     max_len = ctx + 2 * (K + W) + 16
     eng = build_stage_engine(spec, rank, world, local, M * b, max_len, args.page_size, vocab_parallel=vp)
     eng.load_random(seed=0)
-    # chunked prefill (DLI_PREFILL_CHUNKS=C): stages work on different chunks of a prompt at once.  Off by
-    # default: at 2k-token prompts the smaller GEMMs and the mma.sync paged attention cost more than the
-    # pipelining returns (2 stages, 8B: 50 -> 74 ms); it is for long prompts on many stages.
-    chunks = int(os.environ.get("DLI_PREFILL_CHUNKS", "1"))
+    # chunked prefill (DLI_PREFILL_CHUNKS=C): stages work on different chunks of a prompt at once.  It is for
+    # long prompts on many stages (70B, 8 stages, 8k tokens, 8 chunks: 8.8 -> 7.0 s for 36 prompts); at 2k-token
+    # prompts the smaller GEMMs and the mma.sync paged attention cost more than the pipelining returns
+    # (8B, 2 stages: 50 -> 74 ms), so the default only turns it on for >= 4 stages and >= 4k tokens.
+    chunks = int(os.environ.get("DLI_PREFILL_CHUNKS", "8" if (world >= 4 and ctx >= 4096) else "1"))
     stage = EngineStage(eng, b, ctx, max_len, M, prefill_chunks=chunks)
     if stage.is_first:
         g = torch.Generator().manual_seed(1)
