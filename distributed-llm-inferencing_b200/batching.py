@@ -91,7 +91,8 @@ class ContinuousBatcher:
 
     def _finish_if_done(self, i: int) -> None:
         req = self.slots[i]
-        done = len(req.ids) + len(req.out) >= req.max_length
+        # max_length reached, or the sequence produced an EOS id (transformers' stopping rule)
+        done = len(req.ids) + len(req.out) >= req.max_length or (req.out and req.out[-1] in self.eng.eos_token_ids)
         expired = req.deadline is not None and time.time() > req.deadline
         if not (done or expired):
             return

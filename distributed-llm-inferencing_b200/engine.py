@@ -187,6 +187,10 @@ class ShardEngine:
         self.scale = spec.head_dim ** -0.5
         self._ws_rows = 0
         self.sampling = None  # None = greedy; else dict(temperature=, top_k=, top_p=) for ops.sample
+        # stopping rule of generate(): ids that end a sequence and the filler fed after them (set by the worker
+        # from config.json / generation_config.json; empty = run to max_length, what the benchmarks do)
+        self.eos_token_ids: tuple = ()
+        self.pad_token_id: Optional[int] = None
         self._sk = None  # split-K workspace of the batched-decode projections (zeroed once, self-resetting)
         self._graphs: Dict[tuple, tuple] = {}
         self._dec: Dict[tuple, dict] = {}
@@ -700,14 +704,20 @@ class ShardEngine:
         graph = self.use_cuda_graph
         if eager:
             self.use_cuda_graph = False
+        eos = tuple(self.eos_token_ids) if forced is None else ()
         try:
             for i in range(n_new - 1):
-                if deadline is not None and (i & 7) == 0:
+                if (deadline is not None or eos) and (i & 7) == 0:
                     # the reference can only check its timeout around generate() (worker/app.py:293,:311);
-                    # here it is checked between decode steps
+                    # here it is checked between decode steps, together with the EOS rule
                     torch.cuda.current_stream().synchronize()
-                    if time.time() > deadline:
+                    if deadline is not None and time.time() > deadline:
                         raise TimeoutError("Inference generation timed out")
+                    if eos:
+                        seen = torch.stack(toks) if eager else torch.cat((toks[0][None], st["token_log"][:i]), dim=0)
+                        if all_finished(seen, eos):
+                            n_new = i + 1  # tokens produced so far: the prefill's + i decode steps
+                            break
                 if forced is not None:
                     st["tokens"].copy_(forced[:, i])
                 self.decode_step(B)
@@ -721,12 +731,42 @@ class ShardEngine:
             new = torch.stack(toks, dim=1)
         else:
             new = torch.cat((toks[0][None], st["token_log"][: n_new - 1]), dim=0).t()  # [B, n_new]
-        out = torch.cat((input_ids.cpu().long(), new.cpu().long()), dim=1)
+        new = apply_eos(new.cpu().long()[:, :n_new], eos, self.pad_token_id)
+        out = torch.cat((input_ids.cpu().long(), new), dim=1)
         return (out, logits_out) if return_logits else out
 
     @property
     def last_logits(self):
         return None if not self._dec else next(iter(self._dec.values()))["logits"]
+
+
+def apply_eos(new: torch.Tensor, eos_ids, pad_id: Optional[int]) -> torch.Tensor:
+    """transformers' stopping rule on the NEW tokens [B, n] (host, int64), as generate() applies it
+    (TF:generation/utils.py:2789-2811 with EosTokenCriteria): a sequence is finished once it has produced an
+    EOS id; from then on it is fed pad_token_id (eos if no pad id is configured); generation ends when every
+    sequence is finished, so the result is cut after the LAST sequence's EOS."""
+    if not eos_ids or new.numel() == 0:
+        return new
+    is_eos = torch.zeros_like(new, dtype=torch.bool)
+    for e in eos_ids:
+        is_eos |= new == int(e)
+    B, n = new.shape
+    first = torch.where(is_eos.any(dim=1), is_eos.float().argmax(dim=1), torch.full((B,), n, dtype=torch.long))
+    pad = int(eos_ids[0]) if pad_id is None else int(pad_id)
+    cols = torch.arange(n)[None, :]
+    new = torch.where(cols > first[:, None], torch.full_like(new, pad), new)
+    keep = n if bool((first >= n).any()) else int(first.max().item()) + 1
+    return new[:, :keep]
+
+
+def all_finished(tokens_so_far: torch.Tensor, eos_ids) -> bool:
+    """tokens_so_far: [steps, B] (any device).  True when every sequence has produced an EOS id."""
+    if not eos_ids or tokens_so_far.numel() == 0:
+        return False
+    hit = torch.zeros_like(tokens_so_far, dtype=torch.bool)
+    for e in eos_ids:
+        hit |= tokens_so_far == int(e)
+    return bool(hit.any(dim=0).all().item())
 
 
 class LocalChain:
@@ -771,15 +811,18 @@ class LocalChain:
             x = e.prefill(B, T, hidden=x)
         lst["step"].zero_()
         toks = [x.clone()]
+        eos = tuple(last.eos_token_ids)
         for i in range(n_new - 1):
-            if deadline is not None and (i & 7) == 0:
+            if (deadline is not None or eos) and (i & 7) == 0:
                 torch.cuda.current_stream().synchronize()
-                if time.time() > deadline:
+                if deadline is not None and time.time() > deadline:
                     raise TimeoutError("Inference generation timed out")
+                if eos and all_finished(torch.stack(toks), eos):
+                    break
             first._state(B)["tokens"].copy_(toks[-1])
             x = first.decode_step(B)
             for e in self.engines[1:]:
                 x = e.decode_step(B, hidden_in=x)
             toks.append(x.clone())
-        new = torch.stack(toks, dim=1)
-        return torch.cat((input_ids.cpu().long(), new.cpu().long()), dim=1)
+        new = apply_eos(torch.stack(toks, dim=1).cpu().long(), eos, last.pad_token_id)
+        return torch.cat((input_ids.cpu().long(), new), dim=1)

@@ -62,6 +62,23 @@ def _load_tokenizer(path: str):
     return IdTokenizer()
 
 
+def _stop_tokens(path: str, cfg: dict):
+    """(eos ids, pad id) generate() stops on: generation_config.json wins over config.json, as in
+    transformers (the reference calls model.generate with the checkpoint's generation config)."""
+    gen = {}
+    gp = os.path.join(path, "generation_config.json")
+    if os.path.exists(gp):
+        with open(gp) as f:
+            gen = json.load(f)
+    eos = gen.get("eos_token_id", cfg.get("eos_token_id"))
+    pad = gen.get("pad_token_id", cfg.get("pad_token_id"))
+    if eos is None:
+        eos = ()
+    elif isinstance(eos, int):
+        eos = (eos,)
+    return tuple(int(e) for e in eos), (None if pad is None else int(pad))
+
+
 class Worker:
     """State + handlers; one instance per process (the reference keeps the same
     three dicts as module globals, worker/app.py:14-16)."""
@@ -108,6 +125,7 @@ class Worker:
         eng = ShardEngine(spec, start, end, device="cuda:0", max_batch=self.max_batch if end is None else 1,
                           max_seq_len=min(self.max_seq_len, spec.max_pos))
         eng.load_state_dict(load_hf_state_dict(path, eng.start, eng.end, spec.n_layers))
+        eng.eos_token_ids, eng.pad_token_id = _stop_tokens(path, cfg)
         return eng
 
     # ------------------------------------------------------------------ routes

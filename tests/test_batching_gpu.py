@@ -80,3 +80,30 @@ def test_background_thread_serves_concurrent_submitters(cuda):
     assert b.submit(prompts[0], 3).result().tolist() == prompts[0][:3].tolist()  # nothing to generate
     with pytest.raises(ValueError):
         b.submit(prompts[0], 1000).result()
+
+
+def test_request_ends_at_its_eos(cuda):
+    """A request leaves the batch right after it produced an EOS id (the EOS is part of the result, as in
+    transformers), the others keep going."""
+    from dli_b200.batching import ContinuousBatcher
+
+    eng, spec, c = _engine(4)
+    g = torch.Generator().manual_seed(8)
+    reqs = [(torch.randint(0, spec.vocab, (T,), generator=g), T + 30) for T in (6, 11, 19)]
+    b = ContinuousBatcher(eng, max_batch=4)
+    futs = [b.submit(ids, ml) for ids, ml in reqs]
+    while not all(f.done() for f in futs):
+        b.step()
+    free = [f.result() for f in futs]
+    eos = int(free[0][6 + 7])  # the 8th new token of request 0
+    eng.eos_token_ids = (eos,)
+    futs = [b.submit(ids, ml) for ids, ml in reqs]
+    while not all(f.done() for f in futs):
+        b.step()
+    for (ids, ml), fr, f in zip(reqs, free, futs):
+        new = fr[len(ids):]
+        hits = (new == eos).nonzero()
+        cut = len(ids) + (int(hits[0]) + 1 if len(hits) else len(new))
+        assert torch.equal(f.result(), fr[:cut])
+    assert len(futs[0].result()) <= 6 + 8
+    assert len(eng.kv.free) == eng.kv.num_pages

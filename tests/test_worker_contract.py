@@ -169,3 +169,17 @@ def test_inference_sharded_and_unsharded_equal_oracle(cuda, shard_dirs):
     # unload frees the lazily created per-shard engines too (Q7)
     assert _post(c, "/unload_model", {"model_name": "org/tiny"})[0] == 200
     assert not [k for k in w.loaded_models if k.startswith("org/tiny_")]
+
+
+def test_stop_tokens_come_from_generation_config_first(tmp_path):
+    """transformers takes eos/pad from generation_config.json when the checkpoint has one, else from
+    config.json; an int or a list are both legal."""
+    import json
+
+    from dli_b200.worker import _stop_tokens
+
+    cfg = {"eos_token_id": 2, "pad_token_id": None}
+    assert _stop_tokens(str(tmp_path), cfg) == ((2,), None)
+    assert _stop_tokens(str(tmp_path), {}) == ((), None)
+    (tmp_path / "generation_config.json").write_text(json.dumps({"eos_token_id": [128001, 128009], "pad_token_id": 0}))
+    assert _stop_tokens(str(tmp_path), cfg) == ((128001, 128009), 0)
