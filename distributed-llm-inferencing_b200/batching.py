@@ -23,6 +23,8 @@ from typing import List, Optional
 
 import torch
 
+from .engine import check_max_length
+
 
 @dataclass
 class _Request:
@@ -59,8 +61,11 @@ class ContinuousBatcher:
             req.future.set_exception(ValueError("empty prompt"))
         elif req.max_length > self.eng.max_seq_len:
             req.future.set_exception(ValueError(f"max_length {req.max_length} > engine max_seq_len {self.eng.max_seq_len}"))
-        elif req.max_length <= len(ids):
-            req.future.set_result(ids[: req.max_length].clone())  # nothing to generate (HF returns the prompt)
+        elif req.max_length <= len(ids):  # transformers raises here; the worker answers 500 like the reference
+            try:
+                check_max_length(len(ids), req.max_length)
+            except ValueError as e:
+                req.future.set_exception(e)
         else:
             self.pending.put(req)
         return req.future

@@ -679,9 +679,8 @@ class ShardEngine:
         if not (self.is_first and self.is_last):
             raise RuntimeError("generate() needs the full layer range; use PipelineEngine for shards")
         B, T = input_ids.shape
+        check_max_length(T, max_length)
         n_new = max_length - T
-        if n_new <= 0:
-            return input_ids.cpu().long()[:, :max_length]
         self.start_batch(B, T, max_length)
         st = self._dec[(B, 0)]
         # greedy is the parity mode; do_sample=True is the reference's default call
@@ -740,6 +739,16 @@ class ShardEngine:
         return None if not self._dec else next(iter(self._dec.values()))["logits"]
 
 
+def check_max_length(prompt_len: int, max_length: int) -> None:
+    """transformers refuses to generate when the prompt already fills max_length
+    (TF:generation/utils.py, _validate_generated_length); the reference worker turns that into a 500
+    "Inference failed: Input length of input_ids is ..." — same exception type and message here."""
+    if prompt_len >= max_length:
+        raise ValueError(f"Input length of input_ids is {prompt_len}, but `max_length` is set to {max_length}. "
+                         "This can lead to unexpected behavior. You should consider increasing `max_length` or, "
+                         "better yet, setting `max_new_tokens`.")
+
+
 def apply_eos(new: torch.Tensor, eos_ids, pad_id: Optional[int]) -> torch.Tensor:
     """transformers' stopping rule on the NEW tokens [B, n] (host, int64), as generate() applies it
     (TF:generation/utils.py:2789-2811 with EosTokenCriteria): a sequence is finished once it has produced an
@@ -792,9 +801,8 @@ class LocalChain:
             return self.engines[0].generate(input_ids, max_length, deadline=deadline, do_sample=do_sample,
                                             temperature=temperature, top_k=top_k, top_p=top_p, seed=seed)
         B, T = input_ids.shape
+        check_max_length(T, max_length)
         n_new = max_length - T
-        if n_new <= 0:
-            return input_ids.cpu().long()[:, :max_length]
         first, last = self.engines[0], self.engines[-1]
         for e in self.engines:
             e.start_batch(B, T, max_length)

@@ -77,7 +77,8 @@ def test_background_thread_serves_concurrent_submitters(cuda):
     b.stop()
     for i, r in enumerate(results):
         assert r is not None and r.shape == (len(prompts[i]) + 10 + i,) and torch.equal(r[: len(prompts[i])], prompts[i])
-    assert b.submit(prompts[0], 3).result().tolist() == prompts[0][:3].tolist()  # nothing to generate
+    with pytest.raises(ValueError, match="Input length of input_ids is"):  # transformers' own refusal
+        b.submit(prompts[0], 3).result()
     with pytest.raises(ValueError):
         b.submit(prompts[0], 1000).result()
 

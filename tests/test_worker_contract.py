@@ -166,6 +166,12 @@ def test_inference_sharded_and_unsharded_equal_oracle(cuda, shard_dirs):
     g = _golden("/inference", "timeout -> 408")
     code, body4 = _post(c, "/inference", {"model_name": full, "prompt": prompt, "max_length": T + 4, "timeout": -1})
     assert (code, body4) == (g["status"], g["response"])
+    # a prompt that already fills max_length: transformers refuses, the reference answers 500 with its message
+    for req in ({"model_name": full, "prompt": prompt, "max_length": T},
+                {"model_name": "org/tiny", "prompt": prompt, "shard_ids": [0, 1], "max_length": T - 2}):
+        code, body5 = _post(c, "/inference", req)
+        assert code == 500 and body5["status"] == "error"
+        assert body5["message"].startswith(f"Inference failed: Input length of input_ids is {T}, but `max_length` is set to")
     # unload frees the lazily created per-shard engines too (Q7)
     assert _post(c, "/unload_model", {"model_name": "org/tiny"})[0] == 200
     assert not [k for k in w.loaded_models if k.startswith("org/tiny_")]
