@@ -41,7 +41,7 @@ SIGNATURES = {
         [_vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _sz, _i, _i, _i, _i, _i, _i, _f, _i,
          _vp, _sz, _vp, _sz, _vp],
     ),
-    "dli_attn_prefill_paged_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "dli_attn_prefill_paged_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     "dli_set_pdl": (_i, [_i]),
     "dli_gemm_splitk_scratch_bytes": (_sz, [_i, _i]),
     "dli_gemm_splitk_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _sz, _vp]),

@@ -12,6 +12,8 @@
 // Queries still come from the packed qkv buffer of the chunk, keys and values of the WHOLE context
 // (the earlier chunks and this one, appended by dli_rope_kv_append_bf16 just before) come from the
 // paged KV cache, page by page like the decode kernel does it.  Same arithmetic otherwise.
+#include <stdlib.h>
+
 #include "mma_utils.cuh"
 
 namespace dli {
@@ -231,9 +233,15 @@ extern "C" int dli_attn_prefill_bf16(const void* qkv, void* out, int B, int T, i
   return launch_prefill<64, false>(qkv, out, B, T, H, KV, scale, window, s);
 }
 
+namespace dli {
+int launch_attn_prefill_tc_paged(const void* qkv, void* out, const void* k_cache, const void* v_cache,
+                                 const int32_t* page_table, int max_pages, int num_pages, int B, int T, int prefix,
+                                 int H, int KV, int page_size, float scale, int window, cudaStream_t s);
+}
+
 extern "C" int dli_attn_prefill_paged_bf16(const void* qkv, void* out, const void* k_cache, const void* v_cache,
-                                           const int32_t* page_table, int max_pages, int B, int T, int prefix, int H,
-                                           int KV, int hd, int page_size, float scale, int window,
+                                           const int32_t* page_table, int max_pages, int num_pages, int B, int T,
+                                           int prefix, int H, int KV, int hd, int page_size, float scale, int window,
                                            dli_stream_t stream) {
   using namespace dli;
   DLI_CHECK_ARG(qkv && out && k_cache && v_cache && page_table, "dli_attn_prefill_paged_bf16: null pointer");
@@ -252,6 +260,12 @@ extern "C" int dli_attn_prefill_paged_bf16(const void* qkv, void* out, const voi
   int shift = 0;
   while ((1 << shift) < page_size) ++shift;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // head_dim 128: both attention GEMMs on tcgen05, K/V pages brought in by TMA (num_pages > 0 says how large the
+  // pools are); DLI_PREFILL_ATTN=mma keeps the mma.sync kernel
+  static const bool use_tc = !(getenv("DLI_PREFILL_ATTN") && getenv("DLI_PREFILL_ATTN")[0] == 'm');
+  if (hd == 128 && use_tc && num_pages > 0 && page_size <= 128)
+    return launch_attn_prefill_tc_paged(qkv, out, k_cache, v_cache, page_table, max_pages, num_pages, B, T, prefix, H,
+                                        KV, page_size, scale, window, s);
   if (hd == 128)
     return launch_prefill<128, true>(qkv, out, B, T, H, KV, scale, window, s, k_cache, v_cache, page_table, max_pages,
                                      shift, prefix);

@@ -56,9 +56,16 @@ __host__ __device__ constexpr uint32_t make_idesc_attn(bool b_mn_major) {
          ((uint32_t)(128 >> 4) << 24);
 }
 
+// kPaged (chunked prefill): the T query rows are a chunk at positions prefix .. prefix+T-1; K and V tiles come
+// from the paged cache through two more tensor maps (the cache seen as [pages*KV*page_size, hd] rows, box = one
+// page x 64 columns): the 32 lanes of the producer warp each issue one page-sized box of a 128-token tile.
+// A box whose first token lies beyond the context is requested out of bounds, i.e. zero-filled.
+template <bool kPaged>
 __global__ void __launch_bounds__(kTcThreads, 1)
-attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, int T, int H, int KV,
-                       float scale_log2, int window) {
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUtensorMap tmK,
+                       const __grid_constant__ CUtensorMap tmV, bf16* __restrict__ out, int T, int H, int KV,
+                       float scale_log2, int window, const int32_t* __restrict__ page_table, int max_pages,
+                       int page_shift, int prefix, int cache_rows) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const uint32_t sQ = smem_addr(smem);
@@ -77,9 +84,11 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
   const int h = blockIdx.y, b = blockIdx.z;
   const int kvh = h / (H / KV);
   const int q0 = qtile * kTcTile;
+  const int qpos0 = (kPaged ? prefix : 0) + q0;  // absolute position of the tile's first query row
   int t_begin = 0;
-  if (window > 0 && q0 - window + 1 > 0) t_begin = (q0 - window + 1) / kTcTile;
-  const int t_end = qtile + 1;  // diagonal tile last
+  if (window > 0 && qpos0 - window + 1 > 0) t_begin = (qpos0 - window + 1) / kTcTile;
+  // last key tile: the one holding the last query row's own position (the diagonal tile when prefix == 0)
+  const int t_end = kPaged ? min((prefix + T + kTcTile - 1) / kTcTile, (qpos0 + kTcTile - 1) / kTcTile + 1) : qtile + 1;
   const int row_base = b * T;   // row of token 0 of this sequence in the packed qkv matrix
 
   if (warp == 0 && lane == 0) {
@@ -105,7 +114,42 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
   const uint32_t tmem_base = *tmem_ptr_smem;
   const uint32_t tS = tmem_base, tO = tmem_base + 256;
 
-  if (warp == 0) {
+  if (warp == 0 && kPaged) {
+    // ---------------- TMA producer, paged K/V: one page-sized box per lane ----------------
+    if (lane == 0) {
+      tma_prefetch_desc(&tmK);
+      tma_prefetch_desc(&tmV);
+      mbar_expect_tx(q_full, kTileBytes2);
+      tma_load_2d(sQ, &tm, q_full, h * kTcHd, row_base + q0);
+      tma_load_2d(sQ + kSpanBytes, &tm, q_full, h * kTcHd + 64, row_base + q0);
+    }
+    const int page_size = 1 << page_shift;
+    const int nb = kTcTile >> page_shift;  // boxes per 64-column half of a tile (<= 16)
+    const int half = lane / nb, bi = lane - half * nb;
+    const int total = prefix + T;
+    int it = 0;
+    for (int j = t_begin; j < t_end; ++j, ++it) {
+      const int st = it & 1;
+      const uint32_t ph = (it >> 1) & 1;
+      const int tok0 = j * kTcTile + bi * page_size;
+      int row = cache_rows;  // out of bounds: the box is zero-filled
+      if (lane < 2 * nb && tok0 < total)
+        row = (page_table[(size_t)b * max_pages + (tok0 >> page_shift)] * KV + kvh) << page_shift;
+      const uint32_t dst = (uint32_t)(st * kTileBytes2 + half * kSpanBytes + bi * page_size * 128);
+      if (lane == 0) {
+        mbar_wait(k_empty + 8 * st, ph ^ 1);
+        mbar_expect_tx(k_full + 8 * st, kTileBytes2);
+      }
+      __syncwarp();
+      if (lane < 2 * nb) tma_load_2d(sK + dst, &tmK, k_full + 8 * st, half * 64, row);
+      if (lane == 0) {
+        mbar_wait(v_empty + 8 * st, ph ^ 1);
+        mbar_expect_tx(v_full + 8 * st, kTileBytes2);
+      }
+      __syncwarp();
+      if (lane < 2 * nb) tma_load_2d(sV + dst, &tmV, v_full + 8 * st, half * 64, row);
+    }
+  } else if (warp == 0) {
     if (lane == 0) {
       // ---------------- TMA producer ----------------
       mbar_expect_tx(q_full, kTileBytes2);
@@ -172,7 +216,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
     const int sw = warp - 2;
     const int quad = warp & 3, half = sw >> 2;
     const int row = quad * 32 + lane;           // TMEM lane
-    const int qrow = q0 + row;                  // position in the sequence
+    const int qrel = q0 + row;                  // row of the chunk / prompt
+    const int qrow = qpos0 + row;               // absolute position in the sequence
     const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
     const uint32_t col0 = half * 64;
     float* xch = reinterpret_cast<float*>(bar_mem + 256);  // [2 parities][2 halves][128 rows]
@@ -194,7 +239,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(s_empty + 8 * st);  // score buffer may be overwritten by S(it+2)
-      const bool need_mask = (j == qtile) || (window > 0 && j * kTcTile < q0 + kTcTile - window + 1);
+      const bool need_mask = (j * kTcTile + kTcTile - 1 > qpos0) ||
+                             (window > 0 && j * kTcTile < qpos0 + kTcTile - window + 1);
       if (need_mask) {
 #pragma unroll
         for (int i = 0; i < 64; ++i) {
@@ -273,13 +319,13 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict_
     mbar_wait(pv_done, (it - 1) & 1);
     tcgen05_fence_after();
     const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-    bf16* dst = out + ((size_t)(row_base + qrow)) * ((size_t)H * kTcHd) + (size_t)h * kTcHd + col0;
+    bf16* dst = out + ((size_t)(row_base + qrel)) * ((size_t)H * kTcHd) + (size_t)h * kTcHd + col0;
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
       uint32_t r[32];
       tmem_ld_32x32(tO + lane_off + col0 + c * 32, r);
       tmem_ld_wait();
-      if (qrow < T) {
+      if (qrel < T) {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           float v[8];
@@ -312,7 +358,7 @@ extern "C" int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T
   if (B == 0 || T == 0) return DLI_OK;
   static bool attr_set = false;
   if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
+    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
     attr_set = true;
   }
   CUtensorMap tm;
@@ -321,7 +367,41 @@ extern "C" int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T
   int rc = make_tmap(&tm, qkv, B * T, cols, 128);
   if (rc != DLI_OK) return rc;
   dim3 grid((T + kTcTile - 1) / kTcTile, H, B);
-  DLI_LAUNCH("attn_prefill_tc_kernel", attn_prefill_tc_kernel, grid, dim3(kTcThreads), (size_t)kTcSmem,
-             static_cast<cudaStream_t>(stream), tm, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window);
+  DLI_LAUNCH("attn_prefill_tc_kernel", attn_prefill_tc_kernel<false>, grid, dim3(kTcThreads), (size_t)kTcSmem,
+             static_cast<cudaStream_t>(stream), tm, tm, tm, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window,
+             (const int32_t*)nullptr, 0, 0, 0, 0);
   return DLI_OK;
 }
+
+namespace dli {
+
+// tcgen05 form of dli_attn_prefill_paged_bf16 (head_dim 128, 8 <= page_size <= 128); called from attn_prefill.cu.
+int launch_attn_prefill_tc_paged(const void* qkv, void* out, const void* k_cache, const void* v_cache,
+                                 const int32_t* page_table, int max_pages, int num_pages, int B, int T, int prefix,
+                                 int H, int KV, int page_size, float scale, int window, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
+    attr_set = true;
+  }
+  CUtensorMap tm, tmK, tmV;
+  const int cols = (H + 2 * KV) * kTcHd;
+  int rc = make_tmap(&tm, qkv, B * T, cols, 128);
+  if (rc != DLI_OK) return rc;
+  // the cache pools as [num_pages * KV * page_size, 128] rows; box = one page x 64 columns
+  const long long rows = (long long)num_pages * KV * page_size;
+  if (rows <= 0 || rows > 0x7fffffffLL) return fail(DLI_ERR_INVALID, "dli_attn_prefill_paged_bf16: cache too large for one tensor map");
+  rc = make_tmap(&tmK, k_cache, (int)rows, kTcHd, page_size);
+  if (rc != DLI_OK) return rc;
+  rc = make_tmap(&tmV, v_cache, (int)rows, kTcHd, page_size);
+  if (rc != DLI_OK) return rc;
+  int shift = 0;
+  while ((1 << shift) < page_size) ++shift;
+  dim3 grid((T + kTcTile - 1) / kTcTile, H, B);
+  DLI_LAUNCH("attn_prefill_tc_kernel", attn_prefill_tc_kernel<true>, grid, dim3(kTcThreads), (size_t)kTcSmem, s, tm,
+             tmK, tmV, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window, page_table, max_pages, shift, prefix,
+             (int)rows);
+  return DLI_OK;
+}
+
+}  // namespace dli

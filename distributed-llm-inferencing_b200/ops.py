@@ -139,8 +139,8 @@ def attn_prefill_paged(qkv, out, k_cache, v_cache, page_table, B, T, prefix, H, 
     global launch_count
     _req(qkv), _req(out), _req(k_cache), _req(v_cache), _req(page_table, torch.int32)
     _lib.check("dli_attn_prefill_paged_bf16", _lib.load().dli_attn_prefill_paged_bf16(
-        _p(qkv), _p(out), _p(k_cache), _p(v_cache), _p(page_table), page_table.shape[1], B, T, prefix, H, KV, hd,
-        k_cache.shape[2], float(scale), window, _stream()))
+        _p(qkv), _p(out), _p(k_cache), _p(v_cache), _p(page_table), page_table.shape[1], k_cache.shape[0], B, T, prefix,
+        H, KV, hd, k_cache.shape[2], float(scale), window, _stream()))
     launch_count += 1
     return out
 

@@ -205,12 +205,16 @@ int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T, int H, in
  * and values of positions 0 .. prefix+T-1 are read from the paged cache, so
  * dli_rope_kv_append_bf16 must have appended the chunk first.  page_table:
  * int32 [B, max_pages], row b = sequence b of this call.  prefix == 0 gives
- * the result of dli_attn_prefill_bf16. */
+ * the result of dli_attn_prefill_bf16.  num_pages = pages in the k_cache /
+ * v_cache pools: with head_dim 128 the tcgen05 kernel reads whole pages by TMA
+ * and needs the pool extent (0 = use the mma.sync kernel); cache rows beyond a
+ * sequence's end inside its last page must hold finite values (a pool that was
+ * zero-filled once is fine: they are multiplied by a probability of exactly 0). */
 int dli_attn_prefill_paged_bf16(const void* qkv, void* out, const void* k_cache,
                                 const void* v_cache, const int32_t* page_table,
-                                int max_pages, int B, int T, int prefix, int H, int KV,
-                                int hd, int page_size, float scale, int window,
-                                dli_stream_t stream);
+                                int max_pages, int num_pages, int B, int T, int prefix,
+                                int H, int KV, int hd, int page_size, float scale,
+                                int window, dli_stream_t stream);
 
 /* ---- projections -----------------------------------------------------------
  * y[M,N] = epi(x[M,K] . w[N,K]^T)   — w is the HF nn.Linear layout [out,in].

@@ -262,7 +262,8 @@ def test_attn_prefill(cuda, B, T, H, KV, hd, window, tensor_core):
 @pytest.mark.parametrize(
     "B,T,prefix,H,KV,hd,page,window",
     [(1, 512, 1536, 32, 8, 128, 16, 0), (2, 100, 37, 32, 4, 64, 16, 0), (3, 5, 0, 12, 12, 64, 8, 0),
-     (2, 64, 64, 8, 2, 128, 32, 0), (1, 300, 500, 8, 8, 128, 16, 256), (2, 1, 130, 4, 4, 64, 16, 0)],
+     (2, 64, 64, 8, 2, 128, 32, 0), (1, 300, 500, 8, 8, 128, 16, 256), (2, 1, 130, 4, 4, 64, 16, 0),
+     (2, 200, 77, 16, 4, 128, 8, 0), (1, 130, 1000, 8, 8, 128, 128, 0), (3, 129, 0, 8, 2, 128, 16, 0)],
 )
 def test_attn_prefill_paged_chunk(cuda, B, T, prefix, H, KV, hd, page, window):
     """A chunk of T query rows at positions prefix..prefix+T-1 against the paged cache == the rows
