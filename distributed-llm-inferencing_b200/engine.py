@@ -191,6 +191,9 @@ class ShardEngine:
         # from config.json / generation_config.json; empty = run to max_length, what the benchmarks do)
         self.eos_token_ids: tuple = ()
         self.pad_token_id: Optional[int] = None
+        # generate(): prompts longer than this are prefilled in chunks of this many tokens (bounded activation
+        # workspace; None = whole prompt at once)
+        self.prefill_chunk: Optional[int] = None
         self._sk = None  # split-K workspace of the batched-decode projections (zeroed once, self-resetting)
         self._graphs: Dict[tuple, tuple] = {}
         self._dec: Dict[tuple, dict] = {}
@@ -696,7 +699,10 @@ class ShardEngine:
         if forced is not None:
             forced = forced.to(device=self.device, dtype=torch.int32)
         logits_out, toks = [], []
-        toks.append(self.prefill(B, T, ids=ids).clone())
+        if self.prefill_chunk and T > self.prefill_chunk:
+            toks.append(self.prefill_chunked(B, T, self.prefill_chunk, ids=ids).clone())
+        else:
+            toks.append(self.prefill(B, T, ids=ids).clone())
         st["step"].zero_()
         if return_logits:
             logits_out.append(st["logits"].float().cpu())

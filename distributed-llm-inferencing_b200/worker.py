@@ -94,6 +94,8 @@ class Worker:
         self.auth_enabled = env.get("AUTH_ENABLED", "0") == "1"
         self.auth_key = env.get("AUTH_KEY", "")
         self.max_seq_len = int(env.get("DLI_MAX_SEQ_LEN", "4096"))
+        # prompts longer than this many tokens are prefilled in chunks (0 = whole prompt at once)
+        self.prefill_chunk = int(env.get("DLI_PREFILL_CHUNK", "0")) or None
         # DLI_BATCHING=1: concurrent /inference requests on an unsharded model share decode steps
         # (continuous batching, greedy); the reference serialises requests (worker/Dockerfile:45)
         self.batching = env.get("DLI_BATCHING", "0") == "1"
@@ -126,6 +128,7 @@ class Worker:
                           max_seq_len=min(self.max_seq_len, spec.max_pos))
         eng.load_state_dict(load_hf_state_dict(path, eng.start, eng.end, spec.n_layers))
         eng.eos_token_ids, eng.pad_token_id = _stop_tokens(path, cfg)
+        eng.prefill_chunk = self.prefill_chunk
         return eng
 
     # ------------------------------------------------------------------ routes

@@ -98,6 +98,17 @@ def test_chunked_prefill_matches_whole_prompt_prefill(cuda, name, chunk):
     assert agree >= 0.8, agree
 
 
+def test_generate_with_prefill_chunk_setting(cuda):
+    """engine.prefill_chunk: generate() feeds long prompts in chunks; tokens stay those of the whole-prompt
+    prefill on the head_dim-128 case (same tcgen05 attention arithmetic either way)."""
+    c = load_case("llama_hd128")
+    eng, spec, _ = _engine(c)
+    T = c["prompts"].shape[1]
+    whole = eng.generate(c["prompts"], T + 8)
+    eng.prefill_chunk = 4
+    assert torch.equal(eng.generate(c["prompts"], T + 8), whole)
+
+
 def test_free_running_exact_match_where_margin_allows(cuda):
     """Greedy token IDs identical to transformers' on the sequences whose every step
     has an fp32 margin above the bf16 noise floor of the case."""
