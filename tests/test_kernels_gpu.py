@@ -529,7 +529,7 @@ def test_pdl_does_not_change_results(cuda):
 
 
 # ----------------------------------------------------------------------------- split-K batched decode
-@pytest.mark.parametrize("M", [5, 16, 32, 64, 100, 128])
+@pytest.mark.parametrize("M", [3, 5, 16, 32, 64, 100, 128])
 def test_gemm_splitk_matches_reference_and_is_deterministic(cuda, M):
     from dli_b200 import ops
 
@@ -545,6 +545,12 @@ def test_gemm_splitk_matches_reference_and_is_deterministic(cuda, M):
         assert torch.equal(y1, y2)
         _check_linear(y1, _lin_ref(x, w, bias, res), K)
         _check_linear(ops.linear_splitk(x, w, scratch), _lin_ref(x, w), K)
+        # GPT-2's fc projection (bias + gelu_new) and the engine's in-place residual (y aliases residual)
+        _check_linear(ops.linear_splitk(x, w, scratch, bias=bias, epilogue=ops.EPI_GELU_NEW),
+                      _lin_ref(x, w, bias, gelu=True), K, operand_ulp=2.0 ** -5)
+        h = res.clone()
+        ops.linear_splitk(x, w, scratch, residual=h, out=h)
+        _check_linear(h, _lin_ref(x, w, None, res), K, operand_ulp=2.0 ** -5)
     ops.linear_splitk(x[:, :64].contiguous(), w[:, :64].contiguous(), scratch)
     n_tiles = (w.shape[0] + 127) // 128
     assert int(scratch[: 4 * n_tiles].view(torch.int32).abs().sum()) == 0  # counters are left at zero
