@@ -42,6 +42,7 @@ SIGNATURES = {
          _vp, _sz, _vp, _sz, _vp],
     ),
     "dli_attn_prefill_paged_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "dli_sample_rows_bf16": (_i, [_vp, _i, _vp, _i, _i, _f, _i, _f, _vp, _vp, _vp, _vp]),
     "dli_set_pdl": (_i, [_i]),
     "dli_gemm_splitk_scratch_bytes": (_sz, [_i, _i]),
     "dli_gemm_splitk_bf16": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp, _sz, _vp]),

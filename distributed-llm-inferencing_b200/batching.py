@@ -33,6 +33,8 @@ class _Request:
     deadline: Optional[float]
     future: Future = field(default_factory=Future)
     out: List[int] = field(default_factory=list)
+    do_sample: bool = False
+    seed: int = 0
 
 
 class ContinuousBatcher:
@@ -52,11 +54,21 @@ class ContinuousBatcher:
         st["seq_lens"].zero_()               # all rows idle
         st["positions"].zero_()
         self._tok_host = torch.zeros(self.B, dtype=torch.int32).pin_memory()
+        # per-row token choice: greedy, or the reference's sampling call (temperature 0.8, top-k 50, top-p 0.95,
+        # worker/app.py:297-305) with the request's own seed; the draw of the token at position p is keyed by
+        # (seed, p), so a request gets the same tokens whichever row it lands in and whoever shares the batch
+        self._params = dict(temperature=0.8, top_k=50, top_p=0.95)
+        dev = engine.device
+        self._rows = {"seeds": torch.zeros(self.B, dtype=torch.int64, device=dev), "steps": st["positions"],
+                      "mask": torch.zeros(self.B, dtype=torch.int32, device=dev), "params": self._params}
+        st["row_sampling"] = self._rows
 
     # ------------------------------------------------------------------ client side
-    def submit(self, input_ids, max_length: int = 100, timeout: Optional[float] = None) -> Future:
+    def submit(self, input_ids, max_length: int = 100, timeout: Optional[float] = None, do_sample: bool = False,
+               seed: int = 0) -> Future:
         ids = torch.as_tensor(input_ids, dtype=torch.int64).reshape(-1).cpu()
-        req = _Request(ids, int(max_length), None if timeout is None else time.time() + timeout)
+        req = _Request(ids, int(max_length), None if timeout is None else time.time() + timeout,
+                       do_sample=bool(do_sample), seed=int(seed))
         if len(ids) == 0:
             req.future.set_exception(ValueError("empty prompt"))
         elif req.max_length > self.eng.max_seq_len:
@@ -85,6 +97,13 @@ class ContinuousBatcher:
             T = len(req.ids)
             eng.start_batch(1, T, req.max_length, mb=i)  # sequence id i: reserves its KV pages
             ids = req.ids.to(device=eng.device, dtype=torch.int32)
+            dev = eng.device
+            eng._state(1, i)["row_sampling"] = {  # the prompt's last position keys the first new token
+                "seeds": torch.tensor([req.seed], dtype=torch.int64, device=dev),
+                "steps": torch.tensor([T - 1], dtype=torch.int32, device=dev),
+                "mask": torch.tensor([int(req.do_sample)], dtype=torch.int32, device=dev), "params": self._params}
+            self._rows["seeds"][i:i + 1].fill_(req.seed)
+            self._rows["mask"][i:i + 1].fill_(int(req.do_sample))
             first = eng.prefill(1, T, ids=ids, mb=i)
             # hand the sequence over to row i of the joint decode state
             joint["tokens"][i:i + 1].copy_(first)

@@ -93,7 +93,8 @@ __device__ uint32_t kth_largest_key(const uint16_t* __restrict__ row, int V, int
 __global__ void __launch_bounds__(kSampleThreads)
 sample_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out, int V, float inv_temperature,
               int top_k, float top_p, const uint64_t* __restrict__ seed, const int32_t* __restrict__ step,
-              float* __restrict__ dbg_probs, int32_t* __restrict__ dbg_ids, int dbg_cap) {
+              float* __restrict__ dbg_probs, int32_t* __restrict__ dbg_ids, int dbg_cap, int per_row,
+              const int32_t* __restrict__ row_mask) {
   __shared__ uint32_t hist[256];
   __shared__ uint32_t sh[2];
   __shared__ float cval[kMaxCand];
@@ -102,6 +103,7 @@ sample_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out
   __shared__ float red[kSampleThreads / 32];
   pdl_wait();
   pdl_trigger();
+  if (row_mask != nullptr && row_mask[blockIdx.x] == 0) return;  // this row keeps the token already in out[]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint16_t* row = reinterpret_cast<const uint16_t*>(logits + (size_t)blockIdx.x * ld);
   const int k = top_k > 0 ? min(top_k, V) : V;
@@ -184,7 +186,11 @@ sample_kernel(const bf16* __restrict__ logits, int ld, int32_t* __restrict__ out
       }
     }
     if (lane == 0) {
-      const float u = philox_uniform(seed ? *seed : 0ull, step ? (uint32_t)*step : 0u, blockIdx.x) * mass;
+      // per_row: every row has its own (seed, step) and the row index stays out of the key, so a sequence's
+      // draws do not depend on the batch row it happens to occupy
+      const int r = per_row ? blockIdx.x : 0;
+      const float u = philox_uniform(seed ? seed[r] : 0ull, step ? (uint32_t)step[r] : 0u,
+                                     per_row ? 0u : blockIdx.x) * mass;
       float acc = 0.f;
       int pick = kept - 1;
       for (int i = 0; i < kept; ++i) {
@@ -211,6 +217,24 @@ extern "C" int dli_sample_bf16(const void* logits, int ld, int32_t* out, int B, 
   DLI_CHECK_ARG((dbg_probs == nullptr) == (dbg_ids == nullptr) && dbg_cap >= 0, "dli_sample_bf16: bad debug buffers");
   if (B == 0) return DLI_OK;
   DLI_LAUNCH("dli_sample_bf16", sample_kernel, dim3(B), dim3(kSampleThreads), (size_t)0, static_cast<cudaStream_t>(stream),
-             (const bf16*)logits, ld, out, V, 1.0f / temperature, top_k, top_p, seed, step, dbg_probs, dbg_ids, dbg_cap);
+             (const bf16*)logits, ld, out, V, 1.0f / temperature, top_k, top_p, seed, step, dbg_probs, dbg_ids, dbg_cap,
+             0, (const int32_t*)nullptr);
+  return DLI_OK;
+}
+
+extern "C" int dli_sample_rows_bf16(const void* logits, int ld, int32_t* out, int B, int V, float temperature,
+                                    int top_k, float top_p, const uint64_t* seeds, const int32_t* steps,
+                                    const int32_t* row_mask, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(logits && out && seeds && steps, "dli_sample_rows_bf16: null pointer");
+  DLI_CHECK_ARG(B >= 0 && V > 0 && ld >= V, "dli_sample_rows_bf16: bad sizes B=%d V=%d ld=%d", B, V, ld);
+  DLI_CHECK_ARG(temperature > 0.f && top_p > 0.f && top_p <= 1.f && top_k >= 0,
+                "dli_sample_rows_bf16: need temperature > 0, 0 < top_p <= 1, top_k >= 0 (0 = off)");
+  DLI_CHECK_ARG((top_k > 0 && top_k <= kMaxCand) || V <= kMaxCand,
+                "dli_sample_rows_bf16: top_k must be 1..%d when the vocabulary is larger than that", kMaxCand);
+  if (B == 0) return DLI_OK;
+  DLI_LAUNCH("dli_sample_rows_bf16", sample_kernel, dim3(B), dim3(kSampleThreads), (size_t)0,
+             static_cast<cudaStream_t>(stream), (const bf16*)logits, ld, out, V, 1.0f / temperature, top_k, top_p, seeds,
+             steps, (float*)nullptr, (int32_t*)nullptr, 0, 1, row_mask);
   return DLI_OK;
 }

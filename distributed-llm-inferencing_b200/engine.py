@@ -433,7 +433,13 @@ class ShardEngine:
             else:
                 ops.add_layernorm(h_last, self.w["norm"], self.w["normb"], s.eps, out=xn)
             ops.linear(xn, self.w["head"], out=logits)
-        if self.sampling is None:
+        rows = st.get("row_sampling") if st is not None else None
+        if rows is not None:
+            # rows of different requests (continuous batching): greedy token for every row, then the rows whose
+            # request samples are overwritten by a draw keyed with the request's own seed and token position
+            ops.argmax(logits, out=tokens)
+            ops.sample_rows(logits, tokens, rows["seeds"], rows["steps"], rows["mask"], **rows["params"])
+        elif self.sampling is None:
             ops.argmax(logits, out=tokens)
         else:
             ops.sample(logits, out=tokens, seed=st["seed"], step=st["step"], **self.sampling)
@@ -686,6 +692,7 @@ class ShardEngine:
         n_new = max_length - T
         self.start_batch(B, T, max_length)
         st = self._dec[(B, 0)]
+        st.pop("row_sampling", None)  # a per-request mode left by a ContinuousBatcher does not apply here
         # greedy is the parity mode; do_sample=True is the reference's default call
         # (worker/app.py:297-305).  The mode is part of the captured graph.
         mode = dict(temperature=float(temperature), top_k=int(top_k), top_p=float(top_p)) if do_sample else None

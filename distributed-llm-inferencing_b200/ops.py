@@ -354,6 +354,21 @@ def sample(logits, out=None, temperature=0.8, top_k=50, top_p=0.95, seed=None, s
     return (out, probs, ids) if debug_cap else out
 
 
+def sample_rows(logits, out, seeds, steps, row_mask=None, temperature=0.8, top_k=50, top_p=0.95):
+    """sample() for rows of different requests: per-row seeds (int64 [B]) and steps (int32 [B]); rows whose
+    row_mask (int32 [B]) is 0 keep the token already in `out`."""
+    global launch_count
+    if logits.dtype != torch.bfloat16 or not logits.is_cuda or logits.stride(1) != 1:
+        raise ValueError("sample_rows needs a CUDA bf16 tensor with unit inner stride")
+    _req(seeds, torch.int64), _req(steps, torch.int32), _req(row_mask, torch.int32), _req(out, torch.int32)
+    B, V = logits.shape
+    _lib.check("dli_sample_rows_bf16", _lib.load().dli_sample_rows_bf16(
+        _p(logits), logits.stride(0), _p(out), B, V, float(temperature), int(top_k), float(top_p), _p(seeds), _p(steps),
+        _p(row_mask), _stream()))
+    launch_count += 1
+    return out
+
+
 def argmax_candidate(logits, idx_offset, cand):
     """Best (logit, idx_offset + index) of each row of a logits slice -> cand [B, 2] float32."""
     global launch_count

@@ -97,7 +97,7 @@ class Worker:
         # prompts longer than this many tokens are prefilled in chunks (0 = whole prompt at once)
         self.prefill_chunk = int(env.get("DLI_PREFILL_CHUNK", "0")) or None
         # DLI_BATCHING=1: concurrent /inference requests on an unsharded model share decode steps
-        # (continuous batching, greedy); the reference serialises requests (worker/Dockerfile:45)
+        # (continuous batching; greedy or the reference's sampling call per request); the reference serialises requests (worker/Dockerfile:45)
         self.batching = env.get("DLI_BATCHING", "0") == "1"
         self.max_batch = int(env.get("DLI_MAX_BATCH", "8")) if self.batching else 1
         self.batchers: Dict[str, object] = {}
@@ -230,8 +230,10 @@ class Worker:
                     if batcher is None:
                         outputs = model.generate(ids, max_length=max_length, deadline=deadline,
                                                  **self._gen_kwargs(data))
-                if batcher is not None:  # joins the running batch (greedy); the wait is outside the lock
-                    outputs = batcher.submit(ids[0], max_length, timeout).result()[None]
+                if batcher is not None:  # joins the running batch; the wait is outside the lock
+                    gen = self._gen_kwargs(data)
+                    outputs = batcher.submit(ids[0], max_length, timeout, do_sample=gen["do_sample"],
+                                             seed=gen["seed"]).result()[None]
                 result = tokenizer.decode(outputs[0], skip_special_tokens=True)
                 if (time.time() - start_time) > timeout:
                     raise TimeoutError("Inference generation timed out")

@@ -327,6 +327,16 @@ int dli_sample_bf16(const void* logits, int ld, int32_t* out, int B, int V,
                     const int32_t* step, float* dbg_probs, int32_t* dbg_ids, int dbg_cap,
                     dli_stream_t stream);
 
+/* The same epilogue for a batch whose rows belong to DIFFERENT requests
+ * (continuous batching): seeds[B] / steps[B] give every row its own key — the
+ * row index stays out of it, so a request's draws do not depend on the batch
+ * row it occupies — and rows with row_mask[b] == 0 (may be NULL = all rows)
+ * are left untouched, so greedy requests keep the argmax token already in out. */
+int dli_sample_rows_bf16(const void* logits, int ld, int32_t* out, int B, int V,
+                         float temperature, int top_k, float top_p,
+                         const uint64_t* seeds, const int32_t* steps,
+                         const int32_t* row_mask, dli_stream_t stream);
+
 /* Device-side bookkeeping between two decode steps, so a whole step can live in
  * a replayed CUDA graph with no host round trip (the reference syncs the host
  * every token: stopping criteria at TF:generation/utils.py:2804 and the

@@ -108,3 +108,29 @@ def test_request_ends_at_its_eos(cuda):
         assert torch.equal(f.result(), fr[:cut])
     assert len(futs[0].result()) <= 6 + 8
     assert len(eng.kv.free) == eng.kv.num_pages
+
+
+def test_sampled_requests_are_reproducible_and_independent_of_the_batch(cuda):
+    """do_sample requests (the reference's default call) draw with their own seed, keyed by token position:
+    the same request gives the same tokens alone or next to other requests, in whichever row; greedy requests
+    in the same batch are unaffected; another seed gives another continuation."""
+    from dli_b200.batching import ContinuousBatcher
+
+    eng, spec, c = _engine(4)
+    g = torch.Generator().manual_seed(21)
+    prompts = [torch.randint(0, spec.vocab, (T,), generator=g) for T in (7, 13, 5, 10)]
+    b = ContinuousBatcher(eng, max_batch=4)
+
+    def run(jobs):
+        futs = [b.submit(p, len(p) + 24, do_sample=ds, seed=sd) for p, ds, sd in jobs]
+        while not all(f.done() for f in futs):
+            b.step()
+        return [f.result() for f in futs]
+
+    alone_s = run([(prompts[0], True, 123)])[0]
+    alone_g = run([(prompts[1], False, 0)])[0]
+    together = run([(prompts[2], True, 9), (prompts[1], False, 0), (prompts[3], True, 77), (prompts[0], True, 123)])
+    assert torch.equal(together[3], alone_s)  # same seed, other row, other neighbours
+    assert torch.equal(together[1], alone_g)  # greedy row untouched by the sampling kernel
+    assert not torch.equal(run([(prompts[0], True, 124)])[0], alone_s)
+    assert not torch.equal(run([(prompts[0], False, 0)])[0], alone_s)  # and it is not just the argmax
