@@ -60,8 +60,12 @@ class StageBase:
 
 
 class PipelineRunner:
-    def __init__(self, stage: StageBase, rank: int, world: int, n_micro: int, group=None):
+    def __init__(self, stage: StageBase, rank: int, world: int, n_micro: int, group=None, return_last: bool = False):
+        """return_last: also send the tokens of the LAST decode round of a run() back to stage 0, so that a
+        generation can be driven as several run("decode", k) calls (a server checking EOS / its deadline
+        between blocks); a single run() does not need them back."""
         self.stage, self.rank, self.world, self.M, self.group = stage, rank, world, n_micro, group
+        self.return_last = return_last
 
     def _exchange(self, t: int, kind: str, n_rounds: int, mine, out: Optional[torch.Tensor], token_return: bool):
         """Grouped send of this tick's result and receive of the next tick's input."""
@@ -71,7 +75,7 @@ class PipelineRunner:
             r, mb = mine
             if not self.stage.is_last:
                 ops.append(dist.P2POp(dist.isend, out, s + 1, self.group))
-            elif token_return and N > 1 and (kind == "prefill" or r + 1 < n_rounds):
+            elif token_return and N > 1 and (kind == "prefill" or r + 1 < n_rounds or self.return_last):
                 ops.append(dist.P2POp(dist.isend, out, 0, self.group))
         if s > 0:
             prev = tick_work(t, s - 1, N, self.M, n_rounds)
@@ -79,7 +83,7 @@ class PipelineRunner:
                 ops.append(dist.P2POp(dist.irecv, self.stage.recv_buffer(kind, prev[1]), s - 1, self.group))
         elif token_return and N > 1:
             last = tick_work(t, N - 1, N, self.M, n_rounds)
-            if last is not None and (kind == "prefill" or last[0] + 1 < n_rounds):
+            if last is not None and (kind == "prefill" or last[0] + 1 < n_rounds or self.return_last):
                 ops.append(dist.P2POp(dist.irecv, self.stage.recv_buffer("decode", last[1]), N - 1, self.group))
         if ops:
             for req in dist.batch_isend_irecv(ops):

@@ -91,6 +91,7 @@ class Worker:
         self.model_cache_dir = env.get("MODEL_CACHE_DIR", "/app/model_cache")
         self.use_gpu = env.get("USE_GPU", "1") == "1"
         self.device = "cuda" if torch.cuda.is_available() and self.use_gpu else "cpu"
+        self.cuda_device = "cuda:0"  # a worker group binds every rank to its own GPU (pipeline_worker.py)
         self.auth_enabled = env.get("AUTH_ENABLED", "0") == "1"
         self.auth_key = env.get("AUTH_KEY", "")
         self.max_seq_len = int(env.get("DLI_MAX_SEQ_LEN", "4096"))
@@ -124,7 +125,7 @@ class Worker:
             raise RuntimeError("this worker has no CPU path: it needs a CUDA device and USE_GPU=1")
         cfg = json.load(open(os.path.join(path, "config.json")))
         spec = ModelSpec.from_hf_config(cfg)
-        eng = ShardEngine(spec, start, end, device="cuda:0", max_batch=self.max_batch if end is None else 1,
+        eng = ShardEngine(spec, start, end, device=self.cuda_device, max_batch=self.max_batch if end is None else 1,
                           max_seq_len=min(self.max_seq_len, spec.max_pos))
         eng.load_state_dict(load_hf_state_dict(path, eng.start, eng.end, spec.n_layers))
         eng.eos_token_ids, eng.pad_token_id = _stop_tokens(path, cfg)

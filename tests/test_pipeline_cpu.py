@@ -280,3 +280,81 @@ def test_chunked_prefill_schedule_over_gloo(world, n_micro, n_chunks):
             for c, h in seen:
                 want = 100 * mb + c + sum(1000 * (s + 1) for s in range(rank + 1))
                 assert h == [float(want)] * 3
+
+
+# ------------------------------------------------------------------------------ worker-group control plane
+def _group_worker(rank, world, port, q):
+    """PipelineGroup over gloo with a toy StageRun: token i of a request is base + i; the stop decision is
+    taken by the last rank and reaches everybody; a rank that cannot serve a request fails it for all."""
+    import time
+
+    from dli_b200.pipeline_worker import PipelineGroup, StageRun
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    ctrl = dist.new_group(backend="gloo")
+
+    class Toy(StageRun):
+        def __init__(self, cmd):
+            if cmd.get("missing_on") == rank:
+                raise ValueError(f"Shard {rank} of model toy is not loaded")
+            self.cmd, self.done, self.flag = cmd, 0, torch.zeros(1, dtype=torch.int32)
+
+        def prefill(self):
+            self.done = 1
+
+        def decode(self, rounds):
+            self.done += rounds
+
+        def agree_stop(self, deadline):
+            if rank == world - 1:
+                toks = [self.cmd["base"] + i for i in range(self.done)]
+                r = 1 if self.cmd.get("eos") in toks else (2 if deadline is not None and time.time() > deadline else 0)
+                self.flag.fill_(r)
+            dist.broadcast(self.flag, src=world - 1)
+            return int(self.flag.item())
+
+        def tokens(self, n):
+            return [self.cmd["base"] + i for i in range(n)]
+
+        def close(self):
+            pass
+
+    g = PipelineGroup(rank, world, ctrl, Toy)
+    if rank == 0:
+        out = {}
+        out["full"] = g.generate({"ids": [1, 2, 3], "max_length": 3 + 21, "base": 100})
+        out["eos"] = g.generate({"ids": [1, 2, 3], "max_length": 3 + 40, "base": 100, "eos": 111})
+        try:
+            g.generate({"ids": [1], "max_length": 9, "base": 0, "missing_on": world - 1})
+        except ValueError as e:
+            out["missing"] = str(e)
+        try:
+            g.generate({"ids": [1], "max_length": 40, "base": 0, "deadline": time.time() - 1})
+        except TimeoutError as e:
+            out["timeout"] = str(e)
+        out["after"] = g.generate({"ids": [7], "max_length": 4, "base": 5})  # the group still serves
+        g.shutdown()
+        q.put(out)
+    else:
+        g.serve_forever()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_worker_group_control_plane_over_gloo(world):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_group_worker, args=(r, world, port, q)) for r in range(world)]
+    [p.start() for p in procs]
+    out = q.get(timeout=120)
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    assert out["full"] == [100 + i for i in range(21)]
+    # EOS (token 111 = the 12th) is noticed at the next block boundary: 1 + 8 + 8 = 17 tokens were produced
+    assert out["eos"] == [100 + i for i in range(17)]
+    assert out["missing"] == f"Shard {world - 1} of model toy is not loaded"
+    assert out["timeout"] == "Inference generation timed out"
+    assert out["after"] == [5, 6, 7]

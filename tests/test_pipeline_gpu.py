@@ -35,3 +35,82 @@ def test_nccl_pipeline_with_chunked_prefill(cuda, world, vp, chunks):
            "--master-addr", "127.0.0.1", "--master-port", str(29560 + world + 10 * vp), os.path.join(ROOT, "tests", "pipeline_check.py")]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert p.returncode == 0 and "PIPELINE_OK" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
+
+
+def test_worker_group_serves_a_sharded_model_over_http(cuda, tmp_path):
+    """The deployment of the north star end to end: two reference-style workers (HTTP, one per GPU) in one
+    process group; /load_shard registers shard i on worker i, /inference on worker 0 runs the NCCL pipeline.
+    Same text as one worker holding both shards."""
+    import json
+    import signal
+    import socket
+    import time
+
+    import requests
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from golden_util import load_case, spec_kwargs
+    from werkzeug.test import Client
+
+    from dli_b200.engine import ModelSpec
+    from dli_b200.sharding import write_shards
+    from dli_b200.worker import Worker
+    from oracle import decoder_ref as R
+
+    c = load_case("llama_tiny")
+    cfg = spec_kwargs(c["config"])
+    spec = ModelSpec.from_hf_config(cfg)
+    sd = R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"])
+    paths = write_shards(sd, cfg, "org/tiny", 2, str(tmp_path))
+    prompt = " ".join(str(int(i)) for i in c["prompts"][0])
+    T = c["prompts"].shape[1]
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    env = dict(os.environ, PYTHONPATH=ROOT, USE_GPU="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29611", "-m", "dli_b200.pipeline_worker", "--host", "127.0.0.1", "--port", str(port)]
+    p = subprocess.Popen(cmd, cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                         start_new_session=True)
+    try:
+        for r in range(2):  # both workers answer /health
+            for _ in range(240):
+                try:
+                    if requests.get(f"http://127.0.0.1:{port + r}/health", timeout=2).status_code == 200:
+                        break
+                except requests.RequestException:
+                    time.sleep(0.5)
+            else:
+                raise AssertionError("worker group did not come up")
+        for r in range(2):
+            resp = requests.post(f"http://127.0.0.1:{port + r}/load_shard",
+                                 json={"model_name": "org/tiny", "shard_id": r, "shard_path": paths[r]}, timeout=60)
+            assert resp.status_code == 200, resp.text
+        req = {"model_name": "org/tiny", "prompt": prompt, "shard_ids": [0, 1], "max_length": T + 20, "do_sample": False}
+        resp = requests.post(f"http://127.0.0.1:{port}/inference", json=req, timeout=300)
+        assert resp.status_code == 200, resp.text
+        got = resp.json()["result"]
+        again = requests.post(f"http://127.0.0.1:{port}/inference", json=req, timeout=300).json()["result"]
+        sampled = [requests.post(f"http://127.0.0.1:{port}/inference", json=dict(req, do_sample=True, seed=4),
+                                 timeout=300).json()["result"] for _ in range(2)]
+        # a shard that is not there fails the request for everybody, and the group keeps serving
+        bad = requests.post(f"http://127.0.0.1:{port}/inference", json=dict(req, model_name="org/none"), timeout=60)
+        assert bad.status_code == 500
+        too_short = requests.post(f"http://127.0.0.1:{port}/inference", json=dict(req, max_length=T), timeout=60)
+        assert too_short.status_code == 500 and "Input length of input_ids" in too_short.json()["message"]
+        assert requests.post(f"http://127.0.0.1:{port}/inference", json=req, timeout=300).json()["result"] == got
+    finally:
+        os.killpg(p.pid, signal.SIGTERM)
+        try:
+            out = p.communicate(timeout=30)[0]
+        except subprocess.TimeoutExpired:
+            os.killpg(p.pid, signal.SIGKILL)
+            out = p.communicate()[0]
+    # one worker holding both shards (LocalChain on one GPU): same kernels, same text
+    w = Worker({"MODEL_CACHE_DIR": str(tmp_path)})
+    cl = Client(w)
+    for r in range(2):
+        assert cl.post("/load_shard", json={"model_name": "org/tiny", "shard_id": r, "shard_path": paths[r]}).status_code == 200
+    want = json.loads(cl.post("/inference", json=req).get_data(as_text=True))["result"]
+    assert got == want and again == got, (got, want, out[-2000:])
+    assert sampled[0] == sampled[1] and len(sampled[0].split()) == T + 20
