@@ -201,13 +201,17 @@ def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None):
             self.cuda_device = f"cuda:{local}"
             self.group = PipelineGroup(rank, world, ctrl_group, lambda cmd: CudaStageRun(self, rank, world, cmd))
 
+        def dispatch(self, method, path, data, headers):
+            if torch.cuda.is_available():
+                torch.cuda.set_device(local)  # HTTP handler threads start on device 0; this worker owns GPU `local`
+            return super().dispatch(method, path, data, headers)
+
         def run_shard_inference(self, model_name, prompt, shard_ids, max_length, deadline=None, gen=None):
             local_shards = self.loaded_shards.get(model_name, {})
             if world == 1 or all(s in local_shards for s in shard_ids):
                 return super().run_shard_inference(model_name, prompt, shard_ids, max_length, deadline, gen)
             if rank != 0:
                 raise ValueError("send /inference for a model sharded over the GPUs to the first worker (rank 0)")
-            torch.cuda.set_device(local)  # the HTTP handler thread has its own current device
             if model_name not in self.loaded_tokenizers:
                 raise ValueError(f"Shard {sorted(shard_ids)[0]} of model {model_name} is not loaded")
             tokenizer = self.loaded_tokenizers[model_name]
