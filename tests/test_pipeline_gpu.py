@@ -64,6 +64,7 @@ def test_worker_group_serves_a_sharded_model_over_http(cuda, tmp_path):
     spec = ModelSpec.from_hf_config(cfg)
     sd = R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"])
     paths = write_shards(sd, cfg, "org/tiny", 2, str(tmp_path))
+    full = write_shards(sd, cfg, "org/tiny-full", 1, str(tmp_path))[0]
     prompt = " ".join(str(int(i)) for i in c["prompts"][0])
     T = c["prompts"].shape[1]
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
@@ -99,6 +100,11 @@ def test_worker_group_serves_a_sharded_model_over_http(cuda, tmp_path):
         too_short = requests.post(f"http://127.0.0.1:{port}/inference", json=dict(req, max_length=T), timeout=60)
         assert too_short.status_code == 500 and "Input length of input_ids" in too_short.json()["message"]
         assert requests.post(f"http://127.0.0.1:{port}/inference", json=req, timeout=300).json()["result"] == got
+        # worker 1 is a complete worker too: an unsharded model on ITS GPU gives the same text
+        solo = requests.post(f"http://127.0.0.1:{port + 1}/inference",
+                             json={"model_name": full, "prompt": prompt, "max_length": T + 20, "do_sample": False},
+                             timeout=300)
+        assert solo.status_code == 200 and solo.json()["result"] == got, solo.text
     finally:
         os.killpg(p.pid, signal.SIGTERM)
         try:
