@@ -21,6 +21,7 @@ that one flag, so all ranks leave the loop together.
 """
 from __future__ import annotations
 
+import sys
 import time
 from typing import Callable, Dict, List, Optional
 
@@ -58,8 +59,9 @@ class PipelineGroup:
                 return
             try:
                 self._run(cmd)
-            except Exception:  # noqa: BLE001 — the error was already reported to rank 0 (see _run)
-                pass
+            except Exception as e:  # noqa: BLE001 — rank 0 raises the same error to the client (see _run)
+                print(f"[dli pipeline worker {self.rank}] request failed: {type(e).__name__}: {e}", file=sys.stderr,
+                      flush=True)
 
     # ------------------------------------------------------------------ every rank
     def _run(self, cmd: dict) -> Optional[List[int]]:
