@@ -358,3 +358,35 @@ def test_worker_group_control_plane_over_gloo(world):
     assert out["missing"] == f"Shard {world - 1} of model toy is not loaded"
     assert out["timeout"] == "Inference generation timed out"
     assert out["after"] == [5, 6, 7]
+
+
+# ------------------------------------------------------------------------------ block-wise decode (return_last)
+def _block_worker(rank, world, port, n_micro, blocks, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    stage = ToyStage(rank, world, n_micro, b=2, d=4)
+    runner = PipelineRunner(stage, rank, world, n_micro, return_last=True)
+    runner.run("prefill")
+    for k in blocks:  # a server drives the generation as several run("decode", k) calls
+        runner.run("decode", k)
+    if rank == world - 1:
+        q.put([torch.stack(l).tolist() for l in stage.log])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_micro,blocks", [(2, 1, [2, 1, 3]), (3, 1, [1, 1, 4]), (2, 2, [3, 2])])
+def test_decode_in_blocks_equals_one_run(world, n_micro, blocks):
+    """return_last=True: the last round's tokens of every run() travel back to stage 0, so consecutive
+    run("decode", k) calls continue the same generation (what pipeline_worker.py relies on)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_block_worker, args=(r, world, port, n_micro, blocks, q)) for r in range(world)]
+    [p.start() for p in procs]
+    got = q.get(timeout=120)
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    want = sequential(world, n_micro, 2, 4, sum(blocks))
+    for mb in range(n_micro):
+        assert got[mb] == want[mb].tolist(), (mb, got[mb], want[mb].tolist())
