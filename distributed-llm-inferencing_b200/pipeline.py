@@ -204,6 +204,15 @@ class VocabParallelRunner:
                     req.wait()
 
 
+def chunk_plan(prompt_len: int, want_chunks: int):
+    """(chunks, tokens per chunk, tokens in the last chunk) for a prompt fed in about `want_chunks` chunks:
+    equal chunks of ceil(T / want) tokens, the last one takes the rest (never empty)."""
+    chunks = max(1, min(int(want_chunks), int(prompt_len)))
+    tc = (prompt_len + chunks - 1) // chunks
+    chunks = (prompt_len + tc - 1) // tc
+    return chunks, tc, prompt_len - (chunks - 1) * tc
+
+
 # ------------------------------------------------------------------------------ CUDA stage
 class EngineStage(StageBase):
     """A ShardEngine as one pipeline stage: slot mb <-> the engine's micro-batch state."""
@@ -216,10 +225,7 @@ class EngineStage(StageBase):
             engine.start_batch(b, prompt_len, max_total_len, mb=mb)
         dev = engine.device
         # chunked prefill: chunks 0..C-2 hold Tc tokens of every prompt, the last one the rest
-        self.chunks = max(1, min(prefill_chunks, prompt_len))
-        self.Tc = (prompt_len + self.chunks - 1) // self.chunks
-        self.chunks = (prompt_len + self.Tc - 1) // self.Tc
-        self.T_last = prompt_len - (self.chunks - 1) * self.Tc
+        self.chunks, self.Tc, self.T_last = chunk_plan(prompt_len, prefill_chunks)
         self._pf_in = None if self.is_first else torch.empty(b * self.Tc, engine.spec.d_model,
                                                              dtype=torch.bfloat16, device=dev)
 

@@ -390,3 +390,16 @@ def test_decode_in_blocks_equals_one_run(world, n_micro, blocks):
     want = sequential(world, n_micro, 2, 4, sum(blocks))
     for mb in range(n_micro):
         assert got[mb] == want[mb].tolist(), (mb, got[mb], want[mb].tolist())
+
+
+def test_chunk_plan_covers_the_prompt_exactly():
+    from dli_b200.pipeline import chunk_plan
+
+    for T in list(range(1, 70)) + [2048, 8192, 8191, 4097]:
+        for want in (1, 2, 3, 4, 8, 100):
+            chunks, tc, last = chunk_plan(T, want)
+            assert 1 <= chunks <= max(1, min(want, T)) and 1 <= last <= tc
+            assert (chunks - 1) * tc + last == T
+    assert chunk_plan(8192, 8) == (8, 1024, 1024)
+    assert chunk_plan(10, 3) == (3, 4, 2)
+    assert chunk_plan(5, 1) == (1, 5, 5)
