@@ -98,13 +98,22 @@ class ContinuousBatcher:
             eng.start_batch(1, T, req.max_length, mb=i)  # sequence id i: reserves its KV pages
             ids = req.ids.to(device=eng.device, dtype=torch.int32)
             dev = eng.device
-            eng._state(1, i)["row_sampling"] = {  # the prompt's last position keys the first new token
+            self._rows["seeds"][i:i + 1].fill_(req.seed)
+            self._rows["mask"][i:i + 1].fill_(int(req.do_sample))
+            pst = eng._state(1, i)
+            prefill_rows = {  # the prompt's last position keys the first new token
                 "seeds": torch.tensor([req.seed], dtype=torch.int64, device=dev),
                 "steps": torch.tensor([T - 1], dtype=torch.int32, device=dev),
                 "mask": torch.tensor([int(req.do_sample)], dtype=torch.int32, device=dev), "params": self._params}
-            self._rows["seeds"][i:i + 1].fill_(req.seed)
-            self._rows["mask"][i:i + 1].fill_(int(req.do_sample))
-            first = eng.prefill(1, T, ids=ids, mb=i)
+            # With max_batch == 1 the prefill state (1, 0) IS the joint decode state: its row_sampling (whose
+            # tensors the captured decode graph reads) is only borrowed for the prefill and put back.
+            keep = pst.get("row_sampling")
+            pst["row_sampling"] = prefill_rows
+            try:
+                first = eng.prefill(1, T, ids=ids, mb=i)
+            finally:
+                if pst is joint:
+                    pst["row_sampling"] = keep
             # hand the sequence over to row i of the joint decode state
             joint["tokens"][i:i + 1].copy_(first)
             joint["positions"][i:i + 1].fill_(T)

@@ -3,6 +3,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 #include <unordered_set>
 
@@ -31,20 +32,35 @@ int fail(int code, const char* fmt, ...) {
 
 void prepare_kernel(const void*) {}  // hook for one-time per-kernel attributes (none needed today)
 
-static bool g_pdl = false;
-bool pdl_enabled() { return g_pdl; }
-void set_pdl(bool on) { g_pdl = on; }
+static std::atomic<bool> g_pdl{false};
+bool pdl_enabled() { return g_pdl.load(std::memory_order_relaxed); }
+void set_pdl(bool on) { g_pdl.store(on, std::memory_order_relaxed); }
+
+int current_device_slot() {
+  int dev = -1;
+  const cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    fail(DLI_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  if (dev < 0 || dev >= kMaxDevices) {
+    fail(DLI_ERR_CUDA, "device ordinal %d is outside the %d devices this library keeps per-device state for", dev,
+         kMaxDevices);
+    return -1;
+  }
+  return dev;
+}
 
 int sm_count_cached() {
-  static int cached[64] = {0};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
-  if (cached[dev] == 0) {
-    int n = 0;
+  static std::atomic<int> cached[kMaxDevices];
+  const int dev = current_device_slot();
+  if (dev < 0) return -1;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
-    cached[dev] = n;
+    cached[dev].store(n, std::memory_order_relaxed);
   }
-  return cached[dev];
+  return n;
 }
 
 }  // namespace dli

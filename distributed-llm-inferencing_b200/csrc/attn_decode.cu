@@ -419,12 +419,10 @@ static int launch_decode_ns(const void* q, int q_stride, const void* k_cache, co
                             int window, cudaStream_t s, int fused, const void* cos_t, const void* sin_t,
                             const void* pf_a, size_t pf_a_bytes, const void* pf_b, size_t pf_b_bytes) {
   using L = DecodeSmem<HD, NS>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(paged_attn_decode_kernel<HD, NS>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(paged_attn_decode_kernel<HD, NS>,
+                                                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                                    L::kTotal)));
   const float scale_log2 = scale * 1.4426950408889634f;
   float* part_o = reinterpret_cast<float*>(scratch);
   float* part_ml = part_o ? part_o + (size_t)B * H * num_splits * HD : nullptr;
@@ -594,16 +592,14 @@ namespace dli {
 // device address, so the address is looked up once per device (with that device current)
 // and cached.  Returns nullptr after recording the error.
 static void* static_scratch_for_current_device() {
-  static void* cached[64] = {nullptr};
-  int dev = -1;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess || dev < 0 || dev >= 64) {
-    fail(DLI_ERR_CUDA, "dli_paged_attn_decode_static_bf16: cudaGetDevice: %s", cudaGetErrorString(e));
-    return nullptr;
-  }
+  static void* cached[kMaxDevices] = {nullptr};
+  static std::mutex mu;
+  const int dev = current_device_slot();  // records its own message (CUDA error, or ordinal out of range)
+  if (dev < 0) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
   if (cached[dev] == nullptr) {
     void* ptr = nullptr;
-    e = cudaGetSymbolAddress(&ptr, g_static_attn_scratch);
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_attn_scratch);
     if (e != cudaSuccess || ptr == nullptr) {
       fail(DLI_ERR_CUDA, "dli_paged_attn_decode_static_bf16: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
       return nullptr;

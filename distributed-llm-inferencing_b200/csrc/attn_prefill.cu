@@ -203,12 +203,9 @@ static int launch_prefill(const void* qkv, void* out, int B, int T, int H, int K
                           cudaStream_t s, const void* k_cache = nullptr, const void* v_cache = nullptr,
                           const int32_t* page_table = nullptr, int max_pages = 0, int page_shift = 0, int prefix = 0) {
   constexpr int kSmem = 5 * kPfTile * HD * 2;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_kernel<HD, kPaged>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(
+                                     attn_prefill_kernel<HD, kPaged>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem)));
   dim3 grid((T + kPfTile - 1) / kPfTile, H, B);
   DLI_LAUNCH("attn_prefill_kernel", (attn_prefill_kernel<HD, kPaged>), grid, dim3(kPfThreads), (size_t)kSmem, s,
              (const bf16*)qkv, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window, (const bf16*)k_cache,

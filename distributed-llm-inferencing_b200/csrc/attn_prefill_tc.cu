@@ -356,11 +356,9 @@ extern "C" int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T
   DLI_CHECK_ARG(H <= 65535 && B <= 65535, "dli_attn_prefill_tc_bf16: H/B out of grid range");
   DLI_CHECK_ARG(aligned16(qkv) && aligned16(out), "dli_attn_prefill_tc_bf16: pointers must be 16-byte aligned");
   if (B == 0 || T == 0) return DLI_OK;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(
+                                     attn_prefill_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem)));
   CUtensorMap tm;
   const int cols = (H + 2 * KV) * hd;
   // the packed qkv matrix [B*T, cols]; box = 128 rows x 64 columns (one swizzle span)
@@ -379,11 +377,9 @@ namespace dli {
 int launch_attn_prefill_tc_paged(const void* qkv, void* out, const void* k_cache, const void* v_cache,
                                  const int32_t* page_table, int max_pages, int num_pages, int B, int T, int prefix,
                                  int H, int KV, int page_size, float scale, int window, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(attn_prefill_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(
+                                     attn_prefill_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem)));
   CUtensorMap tm, tmK, tmV;
   const int cols = (H + 2 * KV) * kTcHd;
   int rc = make_tmap(&tm, qkv, B * T, cols, 128);

@@ -5,6 +5,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <mutex>
+
 #include "../../include/dli.h"
 
 namespace dli {
@@ -34,6 +36,28 @@ int fail(int code, const char* fmt, ...);
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 int sm_count_cached();
+int current_device_slot();  // abi.cu: ordinal of the current device (0..63), or -1 after recording the error
+
+// cudaFuncSetAttribute and occupancy results belong to a (kernel, DEVICE) pair, so a launcher keeps one
+// of these per kernel instantiation and repeats its set-up the first time each device calls it (a host
+// that drives several GPUs from one process would otherwise fail to launch on the second one).
+constexpr int kMaxDevices = 64;
+struct PerDeviceOnce {
+  std::mutex mu;
+  bool done[kMaxDevices] = {};
+  int value[kMaxDevices] = {};      // optional payload (e.g. resident CTAs per SM)
+  size_t bytes[kMaxDevices] = {};   // optional payload (e.g. dynamic shared memory the set-up covered)
+};
+#define DLI_ONCE_PER_DEVICE(state, dev_var, ...)                    \
+  const int dev_var = ::dli::current_device_slot();                 \
+  if (dev_var < 0) return DLI_ERR_CUDA;                             \
+  {                                                                 \
+    std::lock_guard<std::mutex> lock__((state).mu);                 \
+    if (!(state).done[dev_var]) {                                   \
+      __VA_ARGS__;                                                  \
+      (state).done[dev_var] = true;                                 \
+    }                                                               \
+  }
 bool pdl_enabled();  // abi.cu: programmatic dependent launch on/off (dli_set_pdl)
 
 // Every kernel of the library is launched through this helper.  With PDL enabled the

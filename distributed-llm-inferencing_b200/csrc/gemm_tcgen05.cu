@@ -599,12 +599,10 @@ template <int BN, bool kGated>
 static int launch_prefill_gemm(const void* x, const void* w, const void* bias, const void* residual, void* y, int M,
                                int N /* rows of w */, int K, int epilogue, cudaStream_t s) {
   using Cfg = PrefillCfg<BN, kGated>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       Cfg::kSmemBytes));
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated>,
+                                                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                                    Cfg::kSmemBytes)));
   CUtensorMap tmA, tmB;
   int rc;
   if ((rc = make_tmap(&tmA, x, M, K, 128)) != DLI_OK) return rc;
@@ -625,12 +623,10 @@ static int launch_gemm(const void* x, const void* w, const void* bias, const voi
                        size_t scratch_bytes = 0) {
   if constexpr (!kSwap) return launch_prefill_gemm<BN, kGated>(x, w, bias, residual, y, M, N, K, epilogue, s);
   using Cfg = GemmCfg<BN, kSwap, kGated>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kGated>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, kSwap, kGated>,
+                                                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                                    Cfg::kSmemBytes)));
   CUtensorMap tmA, tmB;
   int rc;
   dim3 grid;

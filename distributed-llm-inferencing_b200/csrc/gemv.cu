@@ -213,16 +213,23 @@ static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf1
   if (sms <= 0) return fail(DLI_ERR_CUDA, "gemv: no CUDA device");
   // vectors per row prefetched across the kernel boundary: the whole row, or 512 (8 KB)
   const size_t dyn = kNorm ? (size_t)M * K * 2 : 0;
-  static int occ = 0;  // resident CTAs per SM for this instantiation
-  static size_t occ_dyn = 0;
-  if (occ == 0 || dyn > occ_dyn) {
+  // resident CTAs per SM for this instantiation on this device, redone when a call needs more shared memory
+  static PerDeviceOnce once;
+  {
+    const int d = current_device_slot();
+    if (d < 0) return DLI_ERR_CUDA;
+    std::lock_guard<std::mutex> lock(once.mu);
+    if (dyn > once.bytes[d]) once.done[d] = false;
+  }
+  DLI_ONCE_PER_DEVICE(once, dev, {
     DLI_CUDA_CALL(cudaFuncSetAttribute(gemv_kernel<M, kGated, kNorm>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)(dyn > 131072 ? dyn : 131072)));
     int o = 0;
     DLI_CUDA_CALL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, gemv_kernel<M, kGated, kNorm>, kGemvThreads, dyn));
-    occ = o > 0 ? o : 1;
-    occ_dyn = dyn;
-  }
+    once.value[dev] = o > 0 ? o : 1;
+    once.bytes[dev] = dyn;
+  });
+  const int occ = once.value[dev];
   const int grid = ntasks < sms * occ ? ntasks : sms * occ;
   static const int pf_l2 = getenv("DLI_GEMV_PF_L2") ? atoi(getenv("DLI_GEMV_PF_L2")) : 8192;
   DLI_LAUNCH("gemv_kernel", gemv_kernel<M, kGated, kNorm>, dim3(grid), dim3(kGemvThreads), dyn, s, x, w, bias, residual,

@@ -137,13 +137,14 @@ static int launch_gemv_mma(const bf16* x, const bf16* w, const bf16* bias, const
   const int ntasks = (N + kOutPerTask - 1) / kOutPerTask;
   const int sms = sm_count_cached();
   if (sms <= 0) return fail(DLI_ERR_CUDA, "gemv_mma: no CUDA device");
-  static int occ = 0;
-  if (occ == 0) {
+  static PerDeviceOnce once;
+  DLI_ONCE_PER_DEVICE(once, dev, {
     int o = 0;
     DLI_CUDA_CALL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, gemv_mma_kernel<kGated, kTwoTiles>,
                                                                 kMmaGemvThreads, 0));
-    occ = o > 0 ? o : 1;
-  }
+    once.value[dev] = o > 0 ? o : 1;
+  });
+  const int occ = once.value[dev];
   const int grid = ntasks < sms * occ ? ntasks : sms * occ;
   static const int pf_l2 = getenv("DLI_GEMV_PF_L2") ? atoi(getenv("DLI_GEMV_PF_L2")) : 8192;
   DLI_LAUNCH("gemv_mma_kernel", gemv_mma_kernel<kGated, kTwoTiles>, dim3(grid), dim3(kMmaGemvThreads), (size_t)0, s, x,

@@ -24,7 +24,6 @@ from . import ops
 
 BF = torch.bfloat16
 _GEMV_MAX_ROWS = int(os.environ.get("DLI_GEMV_MAX_ROWS", "2"))  # rows served by the CUDA-core GEMV (<= 4)
-_EXP_SKIP = os.environ.get("DLI_EXP_SKIP", "")  # measurement knob only, see profiles/r1_notes.md
 
 
 @dataclass
@@ -44,6 +43,8 @@ class ModelSpec:
     sliding_window: int = 0
     max_pos: int = 8192
     tie_embeddings: bool = False
+    # None = plain RoPE; else the checkpoint's scaling dict, rope_type "linear" or "llama3" (rope_inv_freq)
+    rope_scaling: Optional[dict] = None
 
     @staticmethod
     def from_hf_config(cfg) -> "ModelSpec":
@@ -56,13 +57,38 @@ class ModelSpec:
                              g("layer_norm_epsilon", 1e-5), 0.0, 0, g("n_positions", 1024), True)
         if mt in ("llama", "mistral"):
             d, h = g("hidden_size"), g("num_attention_heads")
+            # transformers 5 keeps theta and the scaling keys in `rope_parameters`; older checkpoints
+            # (Llama-3.1's config.json) have `rope_theta` + `rope_scaling` with `rope_type` or `type`
             rp = g("rope_parameters") or {}
-            theta = (rp.get("rope_theta") if isinstance(rp, dict) else None) or g("rope_theta", 10000.0)
+            rp = dict(rp) if isinstance(rp, dict) else {}
+            legacy = g("rope_scaling")
+            if isinstance(legacy, dict):
+                rp = {**legacy, **rp}
+            theta = rp.get("rope_theta") or g("rope_theta", 10000.0)
+            kind = rp.get("rope_type") or rp.get("type") or "default"
+            scaling = None
+            if kind != "default":
+                if kind not in ("linear", "llama3"):
+                    # a scaled checkpoint run with plain RoPE generates wrong tokens without any error: refuse
+                    raise ValueError(f"unsupported rope_type {kind!r}: this engine implements default, linear and "
+                                     "llama3 RoPE (TF:modeling_rope_utils.py)")
+                scaling = {k: rp[k] for k in ("factor", "low_freq_factor", "high_freq_factor",
+                                              "original_max_position_embeddings") if k in rp}
+                scaling["rope_type"] = kind
+                if kind == "llama3":
+                    scaling.setdefault("original_max_position_embeddings", g("max_position_embeddings", 8192))
+                    missing = [k for k in ("factor", "low_freq_factor", "high_freq_factor") if k not in scaling]
+                    if missing:
+                        raise ValueError(f"rope_type llama3 needs {missing} in the checkpoint's rope parameters")
+                elif "factor" not in scaling:
+                    raise ValueError("rope_type linear needs `factor` in the checkpoint's rope parameters")
+            if float(rp.get("partial_rotary_factor", 1.0)) != 1.0:
+                raise ValueError("partial_rotary_factor != 1 is not supported")
             win = (g("sliding_window") or 0) if mt == "mistral" else 0
             return ModelSpec("llama", g("num_hidden_layers"), d, h, g("num_key_value_heads") or h,
                              g("head_dim") or d // h, g("intermediate_size"), g("vocab_size"),
                              g("rms_norm_eps", 1e-6), float(theta), int(win), g("max_position_embeddings", 8192),
-                             bool(g("tie_word_embeddings", False)))
+                             bool(g("tie_word_embeddings", False)), scaling)
         raise ValueError(f"unsupported model_type {mt!r} (llama, mistral, gpt2)")
 
     def layer_weight_bytes(self) -> int:
@@ -89,12 +115,38 @@ NAMED_SPECS = {
 }
 
 
+def rope_inv_freq(spec: ModelSpec) -> torch.Tensor:
+    """fp32 inverse frequencies [hd/2] on the host, op for op what transformers computes:
+    default RoPE (TF:models/llama/modeling_llama.py:88-103), `linear` (TF:modeling_rope_utils.py:133-184:
+    every frequency divided by `factor`) and `llama3` (TF:modeling_rope_utils.py:550-626: wavelengths above
+    original_len/low_freq_factor divided by `factor`, those below original_len/high_freq_factor kept, a
+    linear blend between).  None of the three rescales cos/sin (attention_factor 1)."""
+    hd = spec.head_dim
+    inv_freq = 1.0 / (spec.rope_theta ** (torch.arange(0, hd, 2, dtype=torch.int64).to(torch.float32) / hd))
+    sc = spec.rope_scaling
+    if not sc:
+        return inv_freq
+    kind = sc.get("rope_type", "default")
+    if kind == "linear":
+        return inv_freq / sc["factor"]
+    if kind == "llama3":
+        factor, lo, hi = sc["factor"], sc["low_freq_factor"], sc["high_freq_factor"]
+        old_len = sc["original_max_position_embeddings"]
+        lo_wavelen, hi_wavelen = old_len / lo, old_len / hi
+        wavelen = 2 * math.pi / inv_freq
+        scaled = torch.where(wavelen > lo_wavelen, inv_freq / factor, inv_freq)
+        smooth = (old_len / wavelen - lo) / (hi - lo)
+        blended = (1 - smooth) * scaled / factor + smooth * scaled
+        medium = ~(wavelen < hi_wavelen) * ~(wavelen > lo_wavelen)
+        return torch.where(medium, blended, scaled)
+    raise ValueError(f"unsupported rope_type {kind!r}")
+
+
 def rope_tables(spec: ModelSpec, max_pos: int, device) -> tuple:
     """bf16 cos/sin half tables [max_pos, hd/2], computed on the host with the
     exact op sequence of LlamaRotaryEmbedding (TF:models/llama/modeling_llama.py:73-135)
     so they are bit-identical to what the reference's forward multiplies by."""
-    hd = spec.head_dim
-    inv_freq = 1.0 / (spec.rope_theta ** (torch.arange(0, hd, 2, dtype=torch.int64).to(torch.float32) / hd))
+    inv_freq = rope_inv_freq(spec)
     freqs = torch.arange(max_pos, dtype=torch.float32)[:, None] * inv_freq[None, :]
     return freqs.cos().to(BF).to(device), freqs.sin().to(BF).to(device)
 
@@ -383,9 +435,7 @@ class ShardEngine:
             else:
                 ops.add_layernorm(h, L["ln1"], L["ln1b"], s.eps, out=x)
                 lin(x, L["wqkv"], bias=L["bqkv"], out=qkv)
-            if decode and _EXP_SKIP == "attn":
-                pass  # experiment knob (DLI_EXP_SKIP=attn): measure the step without attention
-            elif decode:
+            if decode:
                 # RoPE + KV append of the new token + split-KV attention in one kernel; the
                 # kernel indexes page-table rows by batch row, so it gets the slot's rows
                 ops.paged_attn_decode_fused(qkv, self.cos, self.sin, self.kv.k[li], self.kv.v[li], st["page_rows"],

@@ -190,8 +190,12 @@ class Worker:
         try:
             if model_name in self.batchers:
                 self.batchers.pop(model_name).stop()
-            for key in [k for k in self.loaded_models if k == model_name or k.startswith(f"{model_name}_")]:
-                eng = self.loaded_models.pop(key)  # Q7: per-shard engines too
+            # Q7: the lazily created per-shard engines too — keyed by the shard ids registered for THIS model, so
+            # another model whose name merely starts with "<model_name>_" stays loaded (the reference deletes the
+            # exact key only, worker/app.py:223-227)
+            keys = {model_name} | {f"{model_name}_{sid}" for sid in self.loaded_shards.get(model_name, {})}
+            for key in [k for k in self.loaded_models if k in keys]:
+                eng = self.loaded_models.pop(key)
                 if hasattr(eng, "unload"):
                     eng.unload()
             self.loaded_tokenizers.pop(model_name, None)

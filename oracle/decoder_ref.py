@@ -52,6 +52,7 @@ class ModelSpec:
     sliding_window: int = 0  # 0 = full attention
     max_pos: int = 8192
     tie_embeddings: bool = False
+    rope_scaling: Optional[dict] = None  # {"rope_type": "linear" | "llama3", "factor": ..., ...}
 
     @staticmethod
     def from_hf(cfg) -> "ModelSpec":
@@ -66,10 +67,13 @@ class ModelSpec:
             theta = rp.get("rope_theta", None) if isinstance(rp, dict) else None
             theta = theta or getattr(cfg, "rope_theta", 10000.0)
             win = getattr(cfg, "sliding_window", None) or 0
+            scaling = None
+            if isinstance(rp, dict) and rp.get("rope_type", "default") != "default":
+                scaling = {k: v for k, v in rp.items() if k != "rope_theta"}
             return ModelSpec("llama", cfg.num_hidden_layers, cfg.hidden_size, cfg.num_attention_heads,
                              cfg.num_key_value_heads, hd, cfg.intermediate_size, cfg.vocab_size, cfg.rms_norm_eps,
                              float(theta), int(win) if mt == "mistral" else 0, cfg.max_position_embeddings,
-                             bool(getattr(cfg, "tie_word_embeddings", False)))
+                             bool(getattr(cfg, "tie_word_embeddings", False)), scaling)
         raise ValueError(f"unsupported model_type {mt}")
 
 
@@ -101,6 +105,18 @@ def rope_cos_sin(spec: ModelSpec, positions: torch.Tensor, dtype) -> Tuple[torch
     Returns the half tables [T, hd/2] (HF concatenates the same half twice)."""
     hd = spec.head_dim
     inv_freq = 1.0 / (spec.rope_theta ** (torch.arange(0, hd, 2, dtype=torch.int64).to(torch.float32) / hd))
+    sc = spec.rope_scaling or {}
+    if sc.get("rope_type") == "linear":  # TF:modeling_rope_utils.py:133-184
+        inv_freq = inv_freq / sc["factor"]
+    elif sc.get("rope_type") == "llama3":  # TF:modeling_rope_utils.py:550-626
+        n0 = sc["original_max_position_embeddings"]
+        wl = 2 * math.pi / inv_freq
+        base = torch.where(wl > n0 / sc["low_freq_factor"], inv_freq / sc["factor"], inv_freq)
+        t = (n0 / wl - sc["low_freq_factor"]) / (sc["high_freq_factor"] - sc["low_freq_factor"])
+        mid = ~(wl < n0 / sc["high_freq_factor"]) * ~(wl > n0 / sc["low_freq_factor"])
+        inv_freq = torch.where(mid, (1 - t) * base / sc["factor"] + t * base, base)
+    elif sc:
+        raise ValueError(f"oracle: unsupported rope scaling {sc}")
     freqs = positions.to(torch.float32)[:, None] * inv_freq[None, :]
     return freqs.cos().to(dtype), freqs.sin().to(dtype)
 

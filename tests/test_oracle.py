@@ -99,3 +99,61 @@ def test_oracle_matches_transformers_live():
         g_ref = m.generate(ids, attention_mask=torch.ones_like(ids), max_length=24, do_sample=False, pad_token_id=0)
     torch.testing.assert_close(R.forward(ids, sd, spec), ref, rtol=0, atol=2e-4)
     assert torch.equal(R.greedy_generate(ids, sd, spec, 24, shards=R.shard_ranges(3, 3)), g_ref)
+
+
+# ------------------------------------------------------------------------------------- RoPE scaling
+_LLAMA31_ROPE = {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+                 "original_max_position_embeddings": 64, "rope_theta": 10000.0}
+
+
+def _scaled_cfg(transformers, rope):
+    return transformers.LlamaConfig(vocab_size=256, hidden_size=128, intermediate_size=256, num_hidden_layers=2,
+                                    num_attention_heads=2, num_key_value_heads=1, max_position_embeddings=512,
+                                    rms_norm_eps=1e-5, tie_word_embeddings=False, rope_parameters=dict(rope))
+
+
+@pytest.mark.parametrize("rope", [_LLAMA31_ROPE, {"rope_type": "linear", "factor": 4.0, "rope_theta": 10000.0}])
+def test_rope_scaling_matches_transformers(rope):
+    """`llama3` / `linear` rope scaling (SURVEY.md a9 "only if config says so"): the engine's host-side
+    inverse frequencies equal transformers' bit for bit, from the new-style config and from a
+    Llama-3.1-style config.json dict; the oracle's forward with the scaled table equals transformers'."""
+    transformers = pytest.importorskip("transformers")
+    from transformers.modeling_rope_utils import ROPE_INIT_FUNCTIONS
+
+    from dli_b200.engine import ModelSpec as ES, rope_inv_freq
+
+    cfg = _scaled_cfg(transformers, rope)
+    want, factor = ROPE_INIT_FUNCTIONS[rope["rope_type"]](cfg, "cpu")
+    assert factor == 1.0
+    assert torch.equal(rope_inv_freq(ES.from_hf_config(cfg)), want)
+    legacy = {"model_type": "llama", "hidden_size": 128, "num_attention_heads": 2, "num_key_value_heads": 1,
+              "num_hidden_layers": 2, "intermediate_size": 256, "vocab_size": 256, "rms_norm_eps": 1e-5,
+              "max_position_embeddings": 512, "rope_theta": 10000.0,
+              "rope_scaling": {k: v for k, v in rope.items() if k != "rope_theta"}}
+    assert torch.equal(rope_inv_freq(ES.from_hf_config(legacy)), want)
+
+    spec = R.ModelSpec.from_hf(cfg)
+    sd = R.seeded_state_dict(spec, seed=5, std=0.08, dtype=torch.float32)
+    m = transformers.AutoModelForCausalLM.from_config(cfg, dtype=torch.float32).eval()
+    m.load_state_dict(sd, strict=True)
+    ids = R.seeded_prompts(spec.vocab, 2, 150, seed=4)  # long enough that scaled and plain tables differ visibly
+    with torch.no_grad():
+        ref = m(ids).logits[:, -1]
+    torch.testing.assert_close(R.forward(ids, sd, spec), ref, rtol=0, atol=2e-4)
+    plain = R.ModelSpec(**{**spec.__dict__, "rope_scaling": None})
+    assert (R.forward(ids, sd, plain) - ref).abs().max() > 1e-2  # the scaling is not a no-op on this case
+
+
+def test_unknown_rope_scaling_is_refused():
+    """A checkpoint whose RoPE variant is not implemented must not load as plain RoPE (it would
+    generate wrong tokens silently)."""
+    from dli_b200.engine import ModelSpec as ES
+
+    base = {"model_type": "llama", "hidden_size": 128, "num_attention_heads": 2, "num_hidden_layers": 2,
+            "intermediate_size": 256, "vocab_size": 256}
+    for bad in ({"rope_type": "yarn", "factor": 4.0}, {"type": "dynamic", "factor": 2.0},
+                {"rope_type": "longrope", "short_factor": [1.0], "long_factor": [2.0]}):
+        with pytest.raises(ValueError, match="rope_type"):
+            ES.from_hf_config({**base, "rope_scaling": bad})
+    with pytest.raises(ValueError, match="llama3 needs"):
+        ES.from_hf_config({**base, "rope_scaling": {"rope_type": "llama3", "factor": 8.0}})

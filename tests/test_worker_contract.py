@@ -46,6 +46,28 @@ def test_error_paths_match_reference_byte_for_byte(tmp_path):
         assert _post(c, route, body) == (g["status"], g["response"]), (route, note)
 
 
+def test_unload_model_keeps_other_models_with_a_common_prefix():
+    """The reference deletes exactly loaded_models[model_name] (worker/app.py:223-227); the per-shard engines this
+    worker creates lazily are "<model>_<shard id>" entries and go too (Q7) — but "gpt2_medium" is not a shard of
+    "gpt2"."""
+    c, w = _client()
+
+    class Fake:
+        unloaded = False
+
+        def unload(self):
+            self.unloaded = True
+
+    full, shard, other = Fake(), Fake(), Fake()
+    w.loaded_models.update({"gpt2": full, "gpt2_1": shard, "gpt2_medium": other})
+    w.loaded_tokenizers.update({"gpt2": object(), "gpt2_medium": object()})
+    w.loaded_shards["gpt2"] = {1: {"path": "/x", "metadata": {}}}
+    assert _post(c, "/unload_model", {"model_name": "gpt2"})[0] == 200
+    assert full.unloaded and shard.unloaded and not other.unloaded
+    assert list(w.loaded_models) == ["gpt2_medium"] and list(w.loaded_tokenizers) == ["gpt2_medium"]
+    assert "gpt2" not in w.loaded_shards
+
+
 def test_shard_registration_health_and_unload_match_reference(tmp_path):
     c, w = _client()
     shard_dir = tmp_path / "tiny" / "shard_1"
