@@ -15,9 +15,15 @@ N > 1 : the same model split into N contiguous layer ranges (reference sharder
         per-GPU batch fixed, per-GPU weights shrink).
 
 value  : decode tokens/s with everything resident in HBM (CUDA-graph replay).
-e2e    : the same metric through the host-facing call: every step copies the
-         previous tokens host->device from pinned memory, runs the step, copies the
-         new tokens device->host and synchronises.
+e2e    : the same metric through the plugin call the reference's master makes
+         (reference worker/app.py:254-330 `run_inference`): POST /inference on the
+         drop-in Worker (werkzeug test client, no socket) with the 2k-token prompt as
+         host text -> tokenise -> host->device copy -> prefill -> K decode steps ->
+         device->host copy of the tokens -> decode to text -> JSON.  Decode rate =
+         K / (t[request with K+1 new tokens] - t[request with 1 new token]); the whole
+         request's seconds are reported beside it.
+extra.hf_gpu : transformers' own generate (bf16, sdpa) on the same GPU and shape — the only
+         existing GPU implementation of this path (what the reference runs with USE_GPU=1).
 """
 from __future__ import annotations
 
@@ -26,7 +32,6 @@ import json
 import os
 import statistics
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -47,77 +52,7 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
-class ClockSampler:
-    """Polls SM clock and throttle reasons through NVML while the timed region runs."""
-
-    def __init__(self, index=0, period_s=0.02):
-        self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._stop = threading.Event()
-        self._thr = None
-        self.period = period_s
-        try:
-            import pynvml
-
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
-        except Exception as e:  # noqa: BLE001
-            self.nv, self.err = None, str(e)
-
-    def _names(self, mask):
-        nv, out = self.nv, []
-        table = [("hw_slowdown", "nvmlClocksThrottleReasonHwSlowdown"),
-                 ("hw_thermal_slowdown", "nvmlClocksThrottleReasonHwThermalSlowdown"),
-                 ("sw_thermal_slowdown", "nvmlClocksThrottleReasonSwThermalSlowdown"),
-                 ("sw_power_cap", "nvmlClocksThrottleReasonSwPowerCap"),
-                 ("hw_power_brake", "nvmlClocksThrottleReasonHwPowerBrakeSlowdown")]
-        for name, attr in table:
-            bit = getattr(nv, attr, None)
-            if bit is not None and mask & bit:
-                out.append(name)
-        return out
-
-    def _run(self):
-        nv = self.nv
-        while not self._stop.is_set():
-            try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                fn = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
-                self.reasons.update(self._names(fn(self.h)))
-            except Exception:  # noqa: BLE001
-                pass
-            self._stop.wait(self.period)
-
-    def __enter__(self):
-        if self.nv:
-            self._thr = threading.Thread(target=self._run, daemon=True)
-            self._thr.start()
-        return self
-
-    def __exit__(self, *a):
-        self._stop.set()
-        if self._thr:
-            self._thr.join()
-
-    def summary(self):
-        if not self.nv:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": getattr(self, "err", "nvml unavailable")}
-        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons), "samples": len(self.samples)}
-
-
-def decode_step_bytes(spec, n_layers, has_head, B, S):
-    """Algorithmic HBM bytes of one decode stage pass."""
-    kv = spec.kv_bytes_per_token(n_layers)
-    return n_layers * spec.layer_weight_bytes() + (spec.head_weight_bytes() if has_head else 0) + B * S * kv + B * kv
-
-
-def prefill_flops(spec, B, T):
-    """Algorithmic FLOPs of a prefill: linear + causal attention + last-position head."""
-    p_layer = spec.layer_weight_bytes() // 2
-    return 2 * spec.n_layers * p_layer * B * T + 2 * spec.d_model * spec.vocab * B \
-        + 4 * B * (T * T // 2) * spec.n_heads * spec.head_dim * spec.n_layers
+from dli_b200.measure import ClockSampler, decode_step_bytes, prefill_flops  # noqa: E402
 
 
 def ev_time_ms(fn, stream=None):
@@ -165,22 +100,11 @@ def run_single(args, spec, peaks):
     step_bytes = decode_step_bytes(spec, spec.n_layers, True, B, S_mid)
     value = B * K / (ms / 1e3)
 
-    # ---- decode through the host-facing call -----------------------------------------------
-    t_in = torch.zeros(B, dtype=torch.int32).pin_memory()
-    t_out = torch.zeros(B, dtype=torch.int32).pin_memory()
-    t_in.copy_(eng._state(B)["tokens"].cpu())
-    for _ in range(3):
-        eng.decode_step_host(t_in, t_out)
-        t_in.copy_(t_out)
-
-    def host_loop():
-        for _ in range(K):
-            eng.decode_step_host(t_in, t_out)
-            t_in.copy_(t_out)
-
-    e2e_ms = ev_time_ms(host_loop)
-    e2e = {"value": B * K / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": 4 * B, "d2h_bytes_per_step": 4 * B,
-           "ms_per_step": e2e_ms / K}
+    # ---- decode through the plugin call (POST /inference on the drop-in worker) ---------------
+    if B == 1:
+        e2e = e2e_through_worker(eng, prompt[0], ctx, K)
+    else:  # the worker serves one prompt per request: larger batches go through the per-step host call
+        e2e = e2e_step_host(eng, B, K)
 
     # ---- dominant kernel: the gate/up weight-streaming projection ----------------------------
     roof = dominant_kernel_roofline(eng, spec, B, peaks)
@@ -196,17 +120,128 @@ def run_single(args, spec, peaks):
         "roofline_step": roof_step, "attn_splits": eng._state(B)["splits"],
         "weights_gb": eng.weight_bytes() / 1e9, "peaks": peaks["source"],
     }
+    extra["env"] = {k: v for k, v in os.environ.items() if k.startswith("DLI_")}  # knobs that change the measured path
     if args.batch == 1 and not args.no_extra:
         try:
             extra["decode_b32"] = batch_decode_extra(spec, 32, ctx, min(K, 32), peaks, args.page_size, eng)
         except Exception as e:  # noqa: BLE001
             extra["decode_b32"] = {"error": str(e)[:200]}
+    if not args.no_extra:
+        eng_w, eng_layers = eng.w, eng.layers
+        try:
+            eng.w, eng.layers = {}, []
+            eng.unload()  # frees KV and workspaces; the weights go with the references below
+            del eng_w, eng_layers
+            torch.cuda.empty_cache()
+            extra["hf_gpu"] = hf_gpu_comparator(spec, ctx)
+            extra["hf_gpu"]["ours_over_hf_decode"] = value / extra["hf_gpu"]["decode_tokens_per_s"]
+        except Exception as e:  # noqa: BLE001
+            extra["hf_gpu"] = {"error": str(e)[:300]}
     return {"value": value, "ms_per_step": ms_step, "e2e": e2e, "roofline": roof, "gpu_launches": launches,
             "clocks": clk.summary(), "extra": extra,
             "config": {"workload": f"{args.model} bf16 random-init, 1 GPU, batch {B} greedy decode at {ctx}-token context, "
                                    f"paged KV (page {args.page_size}); BASELINE.json configs[2]",
                        "batch": B, "ctx": ctx, "page_size": args.page_size, "parallelism": "1 stage",
                        "l2": f"inputs larger than L2: {step_bytes / 1e9:.2f} GB streamed per step vs 126 MB L2"}}
+
+
+def e2e_step_host(eng, B, K):
+    """Batch > 1: one decode step per call with HOST buffers (pinned tokens in, tokens out, sync per step)."""
+    t_in = torch.zeros(B, dtype=torch.int32).pin_memory()
+    t_out = torch.zeros(B, dtype=torch.int32).pin_memory()
+    t_in.copy_(eng._state(B)["tokens"].cpu())
+    for _ in range(3):
+        eng.decode_step_host(t_in, t_out)
+        t_in.copy_(t_out)
+
+    def host_loop():
+        for _ in range(K):
+            eng.decode_step_host(t_in, t_out)
+            t_in.copy_(t_out)
+
+    e2e_ms = ev_time_ms(host_loop)
+    return {"value": B * K / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": 4 * B, "d2h_bytes_per_step": 4 * B,
+            "ms_per_step": e2e_ms / K, "api": "ShardEngine.decode_step_host"}
+
+
+def e2e_through_worker(eng, prompt_row, ctx, K):
+    """The reference-facing plugin call: the drop-in Worker's POST /inference (worker.py, the route the
+    reference master posts to: master/dashboard/views.py:345-355, :412-421), greedy.  The engine already
+    holds the weights (the load routes are not part of the per-request path); everything a request does
+    — JSON, tokenising the prompt text, the host->device copy of the ids, prefill, K decode steps, the
+    device->host copy of the tokens, decoding to text — is inside the timed region."""
+    from werkzeug.test import Client
+
+    from dli_b200.worker import IdTokenizer, Worker
+
+    w = Worker(env={"MODEL_CACHE_DIR": "/nonexistent", "USE_GPU": "1", "DLI_MAX_SEQ_LEN": str(eng.max_seq_len)})
+    w.loaded_models["bench"] = eng
+    w.loaded_tokenizers["bench"] = IdTokenizer()
+    client = Client(w)
+    text = " ".join(str(int(t)) for t in prompt_row)
+
+    def request(n_new):
+        t0 = time.perf_counter()
+        r = client.post("/inference", json={"model_name": "bench", "prompt": text, "max_length": ctx + n_new,
+                                            "do_sample": False, "timeout": 600})
+        dt = time.perf_counter() - t0
+        body = r.get_json()
+        if r.status_code != 200 or body.get("status") != "success":
+            raise RuntimeError(f"/inference failed: {r.status_code} {body}")
+        n_out = len(body["result"].split())
+        if n_out != ctx + n_new:
+            raise RuntimeError(f"/inference returned {n_out} tokens, expected {ctx + n_new}")
+        return dt
+
+    request(1), request(K + 1)  # warm-up: graph capture for this state, allocator
+    t_first = min(request(1) for _ in range(3))
+    t_full = min(request(K + 1) for _ in range(2))
+    dec = max(t_full - t_first, 1e-9)
+    return {"value": K / dec, "unit": UNIT, "h2d_bytes_per_step": 4.0 * ctx / K, "d2h_bytes_per_step": 4.0 * (K + 1) / K,
+            "ms_per_step": dec / K * 1e3, "api": "Worker.inference (POST /inference, werkzeug test client)",
+            "request_s": t_full, "request_new_tokens": K + 1, "request_tokens_per_s": (K + 1) / t_full,
+            "prefill_request_s": t_first, "prompt_tokens": ctx,
+            "note": "value = K decode steps / (request with K+1 new tokens - request with 1 new token), both "
+                    "timed on the host clock around the HTTP handler; h2d = the int32 prompt ids amortised over K"}
+
+
+def hf_gpu_comparator(spec, ctx, n_new=32):
+    """transformers generate (bf16, sdpa, greedy) on this GPU at the same shape: the stock-PyTorch GPU
+    comparator BASELINE.md 5 names — what the reference's worker runs with USE_GPU=1
+    (reference worker/app.py:23-26,121-124,297-305) on a torch that supports the B200."""
+    import gc
+
+    import transformers
+
+    kw = dict(vocab_size=spec.vocab, hidden_size=spec.d_model, intermediate_size=spec.d_ff,
+              num_hidden_layers=spec.n_layers, num_attention_heads=spec.n_heads, num_key_value_heads=spec.n_kv_heads,
+              head_dim=spec.head_dim, max_position_embeddings=max(spec.max_pos, ctx + n_new + 8), rms_norm_eps=spec.eps,
+              tie_word_embeddings=spec.tie_embeddings, rope_parameters={"rope_type": "default", "rope_theta": spec.rope_theta})
+    cfg = (transformers.MistralConfig(sliding_window=spec.sliding_window, **kw) if spec.sliding_window
+           else transformers.LlamaConfig(**kw))
+    with torch.device("cuda"):
+        m = transformers.AutoModelForCausalLM.from_config(cfg, dtype=torch.bfloat16).eval()
+    ids = torch.randint(0, spec.vocab, (1, ctx), generator=torch.Generator().manual_seed(1)).cuda()
+    mask = torch.ones_like(ids)
+
+    def gen(n):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            m.generate(ids, attention_mask=mask, max_new_tokens=n, min_new_tokens=n, do_sample=False, pad_token_id=0)
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0
+
+    gen(2)
+    t1 = min(gen(1) for _ in range(2))
+    t2 = min(gen(1 + n_new) for _ in range(2))
+    out = {"decode_tokens_per_s": n_new / max(t2 - t1, 1e-9), "prefill_tokens_per_s": ctx / t1, "ms_per_step": (t2 - t1) / n_new * 1e3,
+           "impl": f"transformers {transformers.__version__} generate, bf16, attn_implementation={m.config._attn_implementation}, "
+                   f"torch {torch.__version__}", "sample": f"batch 1, {ctx}-token prompt, {n_new} decode steps"}
+    del m
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
 
 
 def dominant_kernel_roofline(eng, spec, B, peaks):
@@ -227,13 +262,18 @@ def dominant_kernel_roofline(eng, spec, B, peaks):
     ms = min(ev_time_ms(loop) for _ in range(3)) / len(ws)
     nbytes = 2 * spec.d_ff * spec.d_model * 2
     ach = nbytes / (ms / 1e3) / 1e9
-    traffic = None
+    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel from an `ncu --set full` capture
+    # (profiles/): a recorded measurement, not taken in this run — the capture's tree is named beside it
+    traffic, traffic_src = None, None
     tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("gate_up_projection_dram_bytes_per_launch")
+        rec = json.load(open(tp))
+        traffic = rec.get("gate_up_projection_dram_bytes_per_launch")
+        traffic_src = rec.get("source")
     return {"bound": "hbm", "kernel": "gemv_kernel<M,gated> (gate/up projection)" if B <= 4 else
             "gemm_tcgen05_kernel<swap,gated> (gate/up projection)", "achieved": ach, "peak": peaks["hbm_gbs"],
-            "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "traffic": traffic, "bytes_per_launch": nbytes,
+            "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,
+            "bytes_per_launch": nbytes,
             "us_per_launch": ms * 1e3, "peak_source": peaks["source"]}
 
 
@@ -241,7 +281,7 @@ def batch_decode_extra(spec, B, ctx, K, peaks, page_size, old_eng):
     """Extra (not the headline): batch-32 decode at the same context."""
     from dli_b200.engine import ShardEngine
 
-    max_len = ctx + K + 8
+    max_len = ctx + 3 * K + 16
     eng = ShardEngine(spec, max_batch=B, max_seq_len=max_len, page_size=page_size)
     eng.w, eng.layers = old_eng.w, old_eng.layers  # share the weights already in HBM
     g = torch.Generator().manual_seed(2)
@@ -250,9 +290,11 @@ def batch_decode_extra(spec, B, ctx, K, peaks, page_size, old_eng):
     pf_ms = ev_time_ms(lambda: eng.prefill(B, ctx, ids=ids))
     for _ in range(3):
         eng.decode_step(B)
-    ms = ev_time_ms(lambda: [eng.decode_step(B) for _ in range(K)]) / K
-    nbytes = decode_step_bytes(spec, spec.n_layers, True, B, ctx + 3 + K // 2)
-    out = {"tokens_per_s": B / (ms / 1e3), "ms_per_step": ms, "hbm_frac": nbytes / (ms / 1e3) / 1e9 / peaks["hbm_gbs"],
+    runs = [ev_time_ms(lambda: [eng.decode_step(B) for _ in range(K)]) / K for _ in range(3)]
+    ms = statistics.median(runs)
+    nbytes = decode_step_bytes(spec, spec.n_layers, True, B, ctx + 3 + 3 * K // 2)
+    out = {"tokens_per_s": B / (ms / 1e3), "ms_per_step": ms, "ms_per_step_runs": runs,
+           "hbm_frac": nbytes / (ms / 1e3) / 1e9 / peaks["hbm_gbs"],
            "bytes_per_step": nbytes, "prefill_tokens_per_s": B * ctx / (pf_ms / 1e3),
            "prefill_tensor_frac": prefill_flops(spec, B, ctx) / (pf_ms / 1e3) / 1e12 / peaks["bf16_tflops_sustained"]}
     eng.w, eng.layers = {}, []
@@ -276,10 +318,34 @@ def cpu_baseline(spec, args, new_tokens=4, prompt_len=16):
     _use_all_host_threads()
     t0 = time.time()
     r = P.time_cpu_decode(spec, prompt_len, new_tokens, greedy=True, warmup_tokens=0)
-    return {"value": r["decode_tok_s"], "unit": UNIT, "cores": r["threads"], "kind": "port",
-            "sample": r["sample"] + f" (transformers generate, the reference's worker/app.py path with USE_GPU=0); "
-                                    f"host cpu_count={os.cpu_count()}", "wall_s": time.time() - t0,
-            "prefill_tok_s": r["prefill_tok_s"]}
+    out = {"value": r["decode_tok_s"], "unit": UNIT, "cores": r["threads"], "kind": "port",
+           "sample": r["sample"] + f" (transformers generate, the reference's worker/app.py path with USE_GPU=0); "
+                                   f"host cpu_count={os.cpu_count()}", "wall_s": time.time() - t0,
+           "prefill_tok_s": r["prefill_tok_s"]}
+    try:
+        out["configs0"] = cpu_configs0()
+    except Exception as e:  # noqa: BLE001
+        out["configs0"] = {"error": str(e)[:200]}
+    return out
+
+
+def cpu_configs0():
+    """BASELINE.json configs[0]: GPT-2 small (124M) random-init, fp32 (the reference's default load dtype,
+    worker/app.py:121), USE_GPU=0, 32-token prompt -> 64 new tokens (max_length 96) through the port of the
+    reference's /inference body — greedy (the parity mode) and with the reference's own sampling call."""
+    from dli_b200.engine import NAMED_SPECS
+    from oracle import ref_worker_port as P
+
+    spec = NAMED_SPECS["gpt2"]
+    model = P.build_cpu_model(spec, dtype=torch.float32)
+    greedy = P.time_cpu_decode(spec, 32, 64, dtype=torch.float32, greedy=True, model=model, warmup_tokens=1)
+    sampled = P.time_cpu_decode(spec, 32, 64, dtype=torch.float32, greedy=False, model=model, warmup_tokens=0)
+    return {"workload": "GPT-2 small fp32 random-init, 1 worker, 1 shard, USE_GPU=0, 32-token prompt -> 64 tokens",
+            "cores": greedy["threads"], "kind": "port",
+            "greedy": {"request_s": greedy["t_total_s"], "tokens_per_s": 64 / greedy["t_total_s"],
+                       "decode_tokens_per_s": greedy["decode_tok_s"]},
+            "reference_sampling": {"request_s": sampled["t_total_s"], "tokens_per_s": 64 / sampled["t_total_s"],
+                                   "decode_tokens_per_s": sampled["decode_tok_s"]}}
 
 
 def run_reference(args, spec):
@@ -293,7 +359,7 @@ def run_reference(args, spec):
     prompt_len = 16
     g = torch.Generator().manual_seed(1)
     prompt = " ".join(str(int(i)) for i in torch.randint(0, spec.vocab, (prompt_len,), generator=g))
-    K, W = min(args.steps, 8), min(args.warmup, 1)
+    K, W = min(args.steps, 64), min(args.warmup, 2)  # bounded: ~0.12 s per token on the box's 16 cores
     if W:
         P.run_inference_port(model, tok, prompt, prompt_len + 1 + W, timeout=1e9, greedy=True)
     t0 = time.time()

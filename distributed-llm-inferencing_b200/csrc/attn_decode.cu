@@ -20,12 +20,13 @@
 //
 // Algorithmic bytes per launch: sum_b min(S_b, window) * KV * hd * 2 (K and V)
 // * 2 bytes; q/out/scratch are negligible.
+#include <stdlib.h>
+
 #include "mma_utils.cuh"
 
 namespace dli {
 
-constexpr int kAttnThreads = 128;
-constexpr int kAttnTile = 64;
+constexpr int kAttnThreads = 128;  // split-merge kernel; the decode kernel runs NW warps (template)
 
 // cp.async.bulk.prefetch.L2: one instruction moves a whole piece from HBM into L2.
 __device__ __forceinline__ void l2_prefetch_slice(const uint8_t* ptr, size_t bytes, size_t part, size_t nparts) {
@@ -40,16 +41,23 @@ __device__ __forceinline__ void l2_prefetch_slice(const uint8_t* ptr, size_t byt
   }
 }
 
-template <int HD, int NS>
+// NW warps per CTA, each owning 16 tokens of a (NW*16)-token KV tile; NS cp.async stages.
+template <int HD, int NS, int NW>
 struct DecodeSmem {
+  static constexpr int kThreads = NW * 32;
+  static constexpr int kTile = NW * 16;
   static constexpr int kRowBytes = HD * 2;
   static constexpr int kQBytes = 16 * kRowBytes;
-  static constexpr int kTileBytes = kAttnTile * kRowBytes;
+  static constexpr int kTileBytes = kTile * kRowBytes;
   static constexpr int kStageTotal = kQBytes + 2 * NS * kTileBytes;  // Q + NS stages x (K, V)
-  // NS == 4 (the few-CTA, batch-1 configuration) also holds this CTA's merged partial
+  // NS == 4, NW == 4 (the cluster-merge configuration) also holds this CTA's merged partial
   // (16 x HD fp32 + max/sum) where the other CTAs of its cluster can read it (DSMEM)
-  static constexpr int kClusterBytes = NS == 4 ? 16 * HD * 4 + 128 : 0;
-  static constexpr int kTotal = kStageTotal + kClusterBytes;
+  static constexpr int kClusterBytes = (NS == 4 && NW == 4) ? 16 * HD * 4 + 128 : 0;
+  // cross-warp merge area (re-uses the K/V staging memory): per warp 16 x HD partial O + 16 x (max, sum)
+  static constexpr int kRedBytes = NW * 16 * HD * 4 + NW * 16 * 2 * 4;
+  static constexpr int kTotal =
+      (kStageTotal > kQBytes + kRedBytes ? kStageTotal : kQBytes + kRedBytes) + kClusterBytes;
+  static constexpr int kClusterOff = kTotal - kClusterBytes;
 };
 
 // ---- thread-block cluster helpers (distributed shared memory) ------------------------------------
@@ -65,13 +73,18 @@ __device__ __forceinline__ float ld_dsmem_f32(uint32_t local_smem_addr, uint32_t
   return v;
 }
 
-// NS = cp.async stages.  NS = 3 (two CTAs per SM, two tiles each in flight) is the large-batch
-// configuration: 5.5-5.6 TB/s at 32-64 sequences x 2k tokens with ONE split, against 4.6-4.9 for
-// NS = 2 under programmatic dependent launch and 3.6 for NS = 4; NS = 4 puts a whole 256-token
-// split in flight at once, which is what a batch-1 step (latency-bound, one CTA per SM at most)
-// needs.
-template <int HD, int NS>
-__global__ void __launch_bounds__(kAttnThreads)
+// NS = cp.async stages, NW = warps.  Three configurations are used:
+//  * NW = 4, NS = 3 (two CTAs per SM, two 64-token tiles each in flight): the large-batch,
+//    bandwidth-bound case — 5.5-5.6 TB/s at 32-64 sequences x 2k tokens with ONE split.
+//  * NW = 16, NS = 1 / NW = 8, NS = 2 (one CTA per SM at most, a whole 256-token split in flight):
+//    the few-CTA case, i.e. a batch-1 step.  That case is not bandwidth- but ISSUE-bound: ncu on
+//    the former 4-warp form showed one warp per scheduler, stalled on fixed-latency dependencies
+//    between its ~3 000 instructions (address arithmetic of the cp.async staging, ldmatrix, MMA),
+//    14 k cycles per CTA for 117 KB of K/V.  Sixteen warps split the same tile four ways finer,
+//    so four warps per scheduler cover each other's latencies.
+//  * NW = 4, NS = 4: only for the thread-block-cluster merge (no scratch given).
+template <int HD, int NS, int NW>
+__global__ void __launch_bounds__(NW * 32)
 paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
                          const bf16* __restrict__ k_cache, const bf16* __restrict__ v_cache,
                          const int32_t* __restrict__ page_table, int max_pages,
@@ -81,9 +94,12 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
                          int fused, const bf16* __restrict__ cos_t, const bf16* __restrict__ sin_t,
                          bf16* k_cache_w, bf16* v_cache_w, int cluster_merge, const uint8_t* __restrict__ pf_ptr,
                          size_t pf_bytes) {
-  using L = DecodeSmem<HD, NS>;
+  using L = DecodeSmem<HD, NS, NW>;
   constexpr int RB = L::kRowBytes;
   constexpr int CH = HD / 8;  // 16-byte chunks per row
+  constexpr int kAttnThreads = L::kThreads;  // shadows the merge kernel's constant on purpose
+  constexpr int kAttnTile = L::kTile;
+  constexpr bool kStreamQ = NW > 8;  // 512 threads leave 128 registers: Q fragments are re-read per use
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t sQ = smem_u32(smem);
   const uint32_t sK = sQ + L::kQBytes;
@@ -143,7 +159,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
   float o[HD / 8][4];
 #pragma unroll
   for (int i = 0; i < HD / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
-  uint32_t qf[HD / 16][4];
+  uint32_t qf[kStreamQ ? 1 : HD / 16][4];
 
   // one commit group per stage (empty groups keep the count uniform)
 #pragma unroll
@@ -202,10 +218,12 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
         }
         __syncthreads();
       }
+      if (!kStreamQ) {
 #pragma unroll
-      for (int kk = 0; kk < HD / 16; ++kk) {
-        const int mi = lane >> 3;
-        ldmatrix_x4(qf[kk], sQ + swz<RB>((mi & 1) * 8 + (lane & 7), kk * 2 + (mi >> 1)));
+        for (int kk = 0; kk < HD / 16; ++kk) {
+          const int mi = lane >> 3;
+          ldmatrix_x4(qf[kStreamQ ? 0 : kk], sQ + swz<RB>((mi & 1) * 8 + (lane & 7), kk * 2 + (mi >> 1)));
+        }
       }
     }
 
@@ -218,8 +236,9 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
       uint32_t kf[4];
       const int mi = lane >> 3;
       ldmatrix_x4(kf, cK + swz<RB>(warp * 16 + (mi >> 1) * 8 + (lane & 7), kk * 2 + (mi & 1)));
-      mma_16816(s[0], qf[kk], kf[0], kf[1]);
-      mma_16816(s[1], qf[kk], kf[2], kf[3]);
+      if (kStreamQ) ldmatrix_x4(qf[0], sQ + swz<RB>((mi & 1) * 8 + (lane & 7), kk * 2 + (mi >> 1)));
+      mma_16816(s[0], qf[kStreamQ ? 0 : kk], kf[0], kf[1]);
+      mma_16816(s[1], qf[kStreamQ ? 0 : kk], kf[2], kf[3]);
     }
     // ---- mask + online softmax --------------------------------------------------------
     const int tok0 = tile * kAttnTile + warp * 16 + 2 * (lane & 3);
@@ -276,16 +295,16 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
     l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
   }
-  float* red_o = reinterpret_cast<float*>(smem + L::kQBytes);                        // [4][16][HD]
-  float* red_ml = reinterpret_cast<float*>(smem + L::kQBytes + NS * L::kTileBytes);  // [4][16][2]
+  float* red_o = reinterpret_cast<float*>(smem + L::kQBytes);  // [NW][16][HD]
+  float* red_ml = red_o + NW * 16 * HD;                        // [NW][16][2]
   {
     const int g = lane >> 2, t = lane & 3;
 #pragma unroll
-    for (int i = 0; i < HD / 8; ++i) {
+    for (int i = 0; i < HD / 8; ++i) {  // only the G query rows are ever read back
       float* p0 = red_o + ((size_t)(warp * 16 + g) * HD + i * 8 + 2 * t);
       float* p1 = red_o + ((size_t)(warp * 16 + g + 8) * HD + i * 8 + 2 * t);
-      p0[0] = o[i][0]; p0[1] = o[i][1];
-      p1[0] = o[i][2]; p1[1] = o[i][3];
+      if (g < G) { p0[0] = o[i][0]; p0[1] = o[i][1]; }
+      if (g + 8 < G) { p1[0] = o[i][2]; p1[1] = o[i][3]; }
     }
     if (t == 0) {
       red_ml[(warp * 16 + g) * 2 + 0] = m_run[0];
@@ -299,11 +318,11 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     const int row = idx / HD, col = idx - row * HD;
     float mmax = -INFINITY;
 #pragma unroll
-    for (int w = 0; w < 4; ++w) mmax = fmaxf(mmax, red_ml[(w * 16 + row) * 2]);
+    for (int w = 0; w < NW; ++w) mmax = fmaxf(mmax, red_ml[(w * 16 + row) * 2]);
     float acc = 0.f, lsum = 0.f;
     if (mmax != -INFINITY) {
 #pragma unroll
-      for (int w = 0; w < 4; ++w) {
+      for (int w = 0; w < NW; ++w) {
         const float f = exp2f((red_ml[(w * 16 + row) * 2] - mmax) * scale_log2);
         acc += f * red_o[(size_t)(w * 16 + row) * HD + col];
         lsum += f * red_ml[(w * 16 + row) * 2 + 1];
@@ -313,7 +332,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     if (num_splits == 1) {
       out[((size_t)b * H + h) * HD + col] = __float2bfloat16_rn(lsum > 0.f ? acc / lsum : 0.f);
     } else if (cluster_merge) {
-      float* cpo = reinterpret_cast<float*>(smem + L::kStageTotal);
+      float* cpo = reinterpret_cast<float*>(smem + L::kClusterOff);
       cpo[idx] = acc;
       if (col == 0) {
         cpo[16 * HD + row * 2 + 0] = mmax;
@@ -334,7 +353,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     // partial through distributed shared memory, in split order (deterministic) — no scratch
     // buffer in HBM, no second kernel.
     cluster_sync_all();
-    const uint32_t cpo_addr = smem_u32(smem + L::kStageTotal);
+    const uint32_t cpo_addr = smem_u32(smem + L::kClusterOff);
     const int total = G * HD;
     const int per = (total + num_splits - 1) / num_splits;
     const int lo = split * per, hi = min(lo + per, total);
@@ -412,15 +431,15 @@ attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restric
     *reinterpret_cast<uint32_t*>(o + i) = pack_bf16(acc[i] * inv, acc[i + 1] * inv);
 }
 
-template <int HD, int NS>
+template <int HD, int NS, int NW>
 static int launch_decode_ns(const void* q, int q_stride, const void* k_cache, const void* v_cache,
                             const int32_t* page_table, int max_pages, const int32_t* seq_lens, void* out,
                             void* scratch, int B, int H, int KV, int page_shift, int num_splits, float scale,
                             int window, cudaStream_t s, int fused, const void* cos_t, const void* sin_t,
                             const void* pf_a, size_t pf_a_bytes, const void* pf_b, size_t pf_b_bytes) {
-  using L = DecodeSmem<HD, NS>;
+  using L = DecodeSmem<HD, NS, NW>;
   static PerDeviceOnce once;
-  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(paged_attn_decode_kernel<HD, NS>,
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(paged_attn_decode_kernel<HD, NS, NW>,
                                                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                                     L::kTotal)));
   const float scale_log2 = scale * 1.4426950408889634f;
@@ -428,23 +447,25 @@ static int launch_decode_ns(const void* q, int q_stride, const void* k_cache, co
   float* part_ml = part_o ? part_o + (size_t)B * H * num_splits * HD : nullptr;
   const int sms = sm_count_cached();
   const int attn_ctas = num_splits * KV * B;
-  if (NS == 4 && num_splits > 1 && num_splits <= 8 && scratch == nullptr) {
-    // no scratch given: the splits of a (sequence, kv head) run as one thread-block cluster and
-    // merge through distributed shared memory inside the kernel
-    cudaError_t e = launch_kernel_cluster(
-        paged_attn_decode_kernel<HD, NS>, dim3(num_splits, KV, B), dim3(kAttnThreads), (size_t)L::kTotal, s,
-        (unsigned)num_splits, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table,
-        max_pages, seq_lens, (bf16*)out, (float*)nullptr, (float*)nullptr, H, KV, page_shift, num_splits, scale_log2,
-        window, fused, (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, 1,
-        (const uint8_t*)nullptr, (size_t)0);
-    if (e != cudaSuccess) return fail(DLI_ERR_CUDA, "paged_attn_decode_kernel (cluster): %s", cudaGetErrorString(e));
-    return DLI_OK;
+  if constexpr (NS == 4 && NW == 4) {
+    if (num_splits > 1 && num_splits <= 8 && scratch == nullptr) {
+      // no scratch given: the splits of a (sequence, kv head) run as one thread-block cluster and
+      // merge through distributed shared memory inside the kernel
+      cudaError_t e = launch_kernel_cluster(
+          paged_attn_decode_kernel<HD, NS, NW>, dim3(num_splits, KV, B), dim3(L::kThreads), (size_t)L::kTotal, s,
+          (unsigned)num_splits, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table,
+          max_pages, seq_lens, (bf16*)out, (float*)nullptr, (float*)nullptr, H, KV, page_shift, num_splits, scale_log2,
+          window, fused, (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, 1,
+          (const uint8_t*)nullptr, (size_t)0);
+      if (e != cudaSuccess) return fail(DLI_ERR_CUDA, "paged_attn_decode_kernel (cluster): %s", cudaGetErrorString(e));
+      return DLI_OK;
+    }
   }
   // prefetch CTAs only when the attention grid leaves SMs idle
   int extra = 0;
   if (pf_a && pf_a_bytes && attn_ctas < sms) extra = (sms - attn_ctas) / (KV * B);
   dim3 grid(num_splits + extra, KV, B);
-  DLI_LAUNCH("paged_attn_decode_kernel", paged_attn_decode_kernel<HD, NS>, grid, dim3(kAttnThreads),
+  DLI_LAUNCH("paged_attn_decode_kernel", paged_attn_decode_kernel<HD, NS, NW>, grid, dim3(L::kThreads),
              (size_t)L::kTotal, s, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, page_table,
              max_pages, seq_lens, (bf16*)out, part_o, part_ml, H, KV, page_shift, num_splits, scale_log2, window,
              fused, (const bf16*)cos_t, (const bf16*)sin_t, (bf16*)k_cache, (bf16*)v_cache, 0,
@@ -461,6 +482,13 @@ static int launch_decode_ns(const void* q, int q_stride, const void* k_cache, co
   return DLI_OK;
 }
 
+// DLI_ATTN_WIDE: warps per CTA of the few-CTA configuration (0 / 4 = the former 4-warp, 4-stage kernel;
+// 8; 16; default: chosen from the split length).  Measurement knob.
+static int attn_wide_env() {
+  static const int v = getenv("DLI_ATTN_WIDE") ? atoi(getenv("DLI_ATTN_WIDE")) : -1;
+  return v;
+}
+
 template <int HD>
 static int launch_decode(const void* q, int q_stride, const void* k_cache, const void* v_cache,
                          const int32_t* page_table, int max_pages, const int32_t* seq_lens,
@@ -468,14 +496,25 @@ static int launch_decode(const void* q, int q_stride, const void* k_cache, const
                          int num_splits, float scale, int window, cudaStream_t s, int fused = 0,
                          const void* cos_t = nullptr, const void* sin_t = nullptr, const void* pf_a = nullptr,
                          size_t pf_a_bytes = 0, const void* pf_b = nullptr, size_t pf_b_bytes = 0) {
-  // few CTAs (batch-1 style): one CTA per SM with a deep load pipeline; many CTAs: occupancy
-  if ((size_t)num_splits * KV * B <= (size_t)sm_count_cached())
-    return launch_decode_ns<HD, 4>(q, q_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B,
-                                   H, KV, page_shift, num_splits, scale, window, s, fused, cos_t, sin_t, pf_a,
-                                   pf_a_bytes, pf_b, pf_b_bytes);
-  return launch_decode_ns<HD, 3>(q, q_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B, H,
-                                 KV, page_shift, num_splits, scale, window, s, fused, cos_t, sin_t, pf_a, pf_a_bytes,
-                                 pf_b, pf_b_bytes);
+#define DLI_DECODE_ARGS                                                                                            \
+  q, q_stride, k_cache, v_cache, page_table, max_pages, seq_lens, out, scratch, B, H, KV, page_shift, num_splits, \
+      scale, window, s, fused, cos_t, sin_t, pf_a, pf_a_bytes, pf_b, pf_b_bytes
+  // many CTAs: occupancy (two 4-warp CTAs per SM, 3 stages)
+  if ((size_t)num_splits * KV * B > (size_t)sm_count_cached()) return launch_decode_ns<HD, 3, 4>(DLI_DECODE_ARGS);
+  // few CTAs (batch-1 style): at most one CTA per SM, the whole split in flight, many warps
+  const bool cluster = num_splits > 1 && num_splits <= 8 && scratch == nullptr;
+  int wide = attn_wide_env();
+  if (wide < 0) {
+    // longest split the page table allows, in tokens: one 256-token tile -> 16 warps on a single stage;
+    // longer splits loop over 128-token tiles with two stages
+    const long long max_tokens = ((long long)max_pages << page_shift);
+    const long long bound = window > 0 && window + 256 < max_tokens ? window + 256 : max_tokens;
+    wide = (bound + num_splits - 1) / num_splits <= 256 ? 16 : 8;
+  }
+  if (cluster || wide <= 4) return launch_decode_ns<HD, 4, 4>(DLI_DECODE_ARGS);
+  if (wide >= 16) return launch_decode_ns<HD, 1, 16>(DLI_DECODE_ARGS);
+  return launch_decode_ns<HD, 2, 8>(DLI_DECODE_ARGS);
+#undef DLI_DECODE_ARGS
 }
 
 }  // namespace dli

@@ -115,21 +115,49 @@ __global__ void decode_advance_kernel(const int32_t* __restrict__ tokens, int32_
   if (threadIdx.x == 0) *step = s + 1;
 }
 
-// Global argmax from per-slice candidates [n][B][2] = (best logit, token id bits): highest logit,
-// lowest token id on ties — the same winner a single argmax over the whole row picks.
-__global__ void argmax_merge_kernel(const float* __restrict__ cands, int n, int B, int32_t* __restrict__ out) {
+// Global argmax from candidates [n][B][2] = (best logit, index bits) — the per-slice candidates of a
+// vocabulary-parallel head, or the per-CTA candidates of the lm_head GEMV's fused epilogue: highest logit,
+// lowest index on ties — the same winner a single argmax over the whole row picks.  One warp per row;
+// lanes stride over the n candidates, then a shuffle tree.  Writes tokens[b] = idx_offset + index, or
+// (cand_out) the row's (logit, idx_offset + index) for a further merge across stages.
+__global__ void __launch_bounds__(256)
+argmax_merge_kernel(const float* __restrict__ cands, int n, int B, int idx_offset, int32_t* __restrict__ out,
+                    float* __restrict__ cand_out) {
   pdl_wait();
   pdl_trigger();
-  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+  const int lane = threadIdx.x & 31;
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += (gridDim.x * blockDim.x) >> 5) {
     float best = -INFINITY;
     int besti = 0x7fffffff;
-    for (int s = 0; s < n; ++s) {
+    for (int s = lane; s < n; s += 32) {
       const float v = cands[((size_t)s * B + b) * 2];
       const int i = reinterpret_cast<const int32_t*>(cands)[((size_t)s * B + b) * 2 + 1];
-      if (v > best || (v == best && i < besti)) { best = v; besti = i; }
+      if (i != 0x7fffffff && (besti == 0x7fffffff || v > best || (v == best && i < besti))) { best = v; besti = i; }
     }
-    out[b] = besti == 0x7fffffff ? 0 : besti;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+      if (oi != 0x7fffffff && (besti == 0x7fffffff || ov > best || (ov == best && oi < besti))) { best = ov; besti = oi; }
+    }
+    if (lane == 0) {
+      const int idx = (besti == 0x7fffffff ? 0 : besti) + idx_offset;
+      if (cand_out) {
+        cand_out[b * 2] = best;
+        reinterpret_cast<int32_t*>(cand_out)[b * 2 + 1] = idx;
+      } else {
+        out[b] = idx;
+      }
+    }
   }
+}
+
+int launch_argmax_merge(const float* cands, int n, int B, int idx_offset, int32_t* tokens, float* cand_out,
+                        cudaStream_t s) {
+  const int warps = 8;
+  DLI_LAUNCH("argmax_merge_kernel", argmax_merge_kernel, dim3((B + warps - 1) / warps), dim3(warps * 32), (size_t)0, s,
+             cands, n, B, idx_offset, tokens, cand_out);
+  return DLI_OK;
 }
 
 }  // namespace dli
@@ -151,9 +179,7 @@ int dli_argmax_merge(const float* cands, int n, int B, int32_t* out, dli_stream_
   using namespace dli;
   DLI_CHECK_ARG(cands && out && n > 0 && B >= 0, "dli_argmax_merge: bad arguments");
   if (B == 0) return DLI_OK;
-  DLI_LAUNCH("dli_argmax_merge", argmax_merge_kernel, dim3(1), dim3(256), (size_t)0, static_cast<cudaStream_t>(stream),
-             cands, n, B, out);
-  return DLI_OK;
+  return launch_argmax_merge(cands, n, B, 0, out, nullptr, static_cast<cudaStream_t>(stream));
 }
 
 int dli_decode_advance(const int32_t* tokens, int32_t* token_log, int32_t* positions, int32_t* seq_lens,

@@ -11,8 +11,11 @@
 // on kRows weight rows at a time; its 8 warps split K between them so that one
 // CTA iteration reads kRows contiguous 4 KB row segments (256 lanes x 16 B),
 // then partial sums are combined through shared memory (one warp per output).
-// Tasks (row groups) are dealt round-robin to a grid sized as a multiple of the
-// SM count, so every SM streams the same number of bytes.
+// The grid is a multiple of the SM count and every CTA owns a CONTIGUOUS, equally
+// sized share of the outputs (N/grid, +-1), walked in groups of <= kRows rows.  Dealing
+// whole 4-row tasks round-robin left a third of the CTAs with one task more than the
+// rest on the small matrices (o/down: 1024 tasks on 444 CTAs = 3 vs 2), and a CTA that
+// streams alone on its SM runs far below the SM's share of HBM bandwidth.
 //
 // Programmatic dependent launch: a CTA of the next kernel may move in while this
 // kernel drains; it waits (pdl_wait) before reading activations.  Prefetching the
@@ -38,8 +41,8 @@ __device__ __forceinline__ size_t gated_row(int n, int is_up) {
 template <int M, bool kGated, bool kNorm>
 __global__ void __launch_bounds__(kGemvThreads, M <= 2 ? 3 : 2)
 gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* __restrict__ bias,
-            const bf16* residual, bf16* y, int N, int K, int epilogue, int ntasks,
-            const bf16* __restrict__ ln_w, float eps, int pf_l2) {
+            const bf16* residual, bf16* y, int N, int K, int epilogue,
+            const bf16* __restrict__ ln_w, float eps, int pf_l2, float* __restrict__ cand) {
   // partial sums: [parity][value][thread]; value = row * M + m
   __shared__ float part[2][kGemvRows * M][kGemvThreads];
   __shared__ float red[kGemvWarps][M];
@@ -51,29 +54,41 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
   constexpr int kOutPerTask = kGated ? kGemvRows / 2 : kGemvRows;
   const uint4 zero = make_uint4(0, 0, 0, 0);
 
-  auto row_ptrs = [&](int task, const uint4* (&wrow)[kGemvRows]) {
-    const int n0 = task * kOutPerTask;
+  // This CTA's share of the N outputs: [n_lo, n_hi), in `ngroups` groups of <= kOutPerTask outputs
+  // whose sizes differ by at most one (10 outputs -> 4,3,3, not 4,4,2).
+  const int n_lo = (int)((long long)N * blockIdx.x / gridDim.x);
+  const int n_hi = (int)((long long)N * (blockIdx.x + 1) / gridDim.x);
+  const int ngroups = (n_hi - n_lo + kOutPerTask - 1) / kOutPerTask;
+
+  // rows of group [n0, n0 + cnt): row r is live when its output index r % kOutPerTask < cnt
+  auto row_ptrs = [&](int n0, int cnt, const uint4* (&wrow)[kGemvRows]) {
 #pragma unroll
     for (int r = 0; r < kGemvRows; ++r) {
       size_t row;
       if (kGated) {
-        const int n = min(n0 + (r % kOutPerTask), N - 1);
+        const int n = n0 + min(r % kOutPerTask, cnt - 1);
         row = gated_row(n, r / kOutPerTask);
       } else {
-        row = (size_t)min(n0 + r, N - 1);
+        row = (size_t)(n0 + min(r, cnt - 1));
       }
       wrow[r] = reinterpret_cast<const uint4*>(w + row * (size_t)K);
     }
   };
 
   const uint4* wrow[kGemvRows];
-  if (pf_l2 && (int)blockIdx.x < ntasks && tid < kGemvRows) {
+  if (pf_l2 && ngroups > 0 && tid < kGemvRows) {
     // Before waiting for the previous kernel: pull the head of this CTA's first weight rows into L2
     // with one bulk prefetch per row (no registers, shared memory or L1 footprint), so HBM keeps
     // streaming through the kernel boundary.  Worth ~1.5 us per layer on the 4-GEMV chain.
-    row_ptrs(blockIdx.x, wrow);
+    const int cnt0 = (n_hi - n_lo) / ngroups;
+    row_ptrs(n_lo, cnt0, wrow);
     const uint32_t bytes = (uint32_t)min((size_t)K * 2, (size_t)pf_l2) & ~15u;
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(wrow[tid]), "r"(bytes) : "memory");
+    const uint4* mine = wrow[0];
+#pragma unroll
+    for (int r = 1; r < kGemvRows; ++r)
+      if (tid == r) mine = wrow[r];  // (no dynamic indexing: keeps wrow in registers)
+    if (tid % kOutPerTask < cnt0)
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(mine), "r"(bytes) : "memory");
   }
   pdl_wait();
   pdl_trigger();  // the grid is resident at once (grid <= SMs x occupancy): successors may queue behind us
@@ -126,10 +141,21 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
     xv = xs;  // generic pointer into shared memory
   }
 
+  // fused greedy choice (lm_head): this CTA's best (bf16-rounded logit, output index) per x row,
+  // kept by lane 0 of the warp that finishes each output and merged through `red` at the end
+  float best_v[M];
+  int best_i[M];
+#pragma unroll
+  for (int m = 0; m < M; ++m) { best_v[m] = -INFINITY; best_i[m] = 0x7fffffff; }
+
   int parity = 0;
-  for (int task = blockIdx.x; task < ntasks; task += gridDim.x, parity ^= 1) {
-    const int n0 = task * kOutPerTask;
-    row_ptrs(task, wrow);
+  for (int g = 0; g < ngroups; ++g, parity ^= 1) {
+    const int n0 = n_lo + (int)((long long)(n_hi - n_lo) * g / ngroups);
+    const int cnt = n_lo + (int)((long long)(n_hi - n_lo) * (g + 1) / ngroups) - n0;
+    row_ptrs(n0, cnt, wrow);
+    bool live[kGemvRows];
+#pragma unroll
+    for (int r = 0; r < kGemvRows; ++r) live[r] = (r % kOutPerTask) < cnt;
     float acc[kGemvRows][M];
 #pragma unroll
     for (int r = 0; r < kGemvRows; ++r)
@@ -142,8 +168,8 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
       uint4 wv0[kGemvRows], wv1[kGemvRows];
 #pragma unroll
       for (int r = 0; r < kGemvRows; ++r) {
-        wv0[r] = p0 ? ld_stream_16B(wrow[r] + i0) : zero;
-        wv1[r] = p1 ? ld_stream_16B(wrow[r] + i1) : zero;
+        wv0[r] = (p0 && live[r]) ? ld_stream_16B(wrow[r] + i0) : zero;
+        wv1[r] = (p1 && live[r]) ? ld_stream_16B(wrow[r] + i1) : zero;
       }
       uint4 xa[M], xb[M];
 #pragma unroll
@@ -186,7 +212,7 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
       s = warp_sum(s);
       if (kGated) s2 = warp_sum(s2);
       const int n = n0 + c;
-      if (lane == 0 && n < N) {
+      if (lane == 0 && c < cnt) {
         float v;
         if (kGated) {
           const float g = round_bf16(s), u = round_bf16(s2);
@@ -197,21 +223,50 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
           if (epilogue & DLI_EPI_GELU_NEW) v = round_bf16(gelu_new_f(v));
           if (epilogue & DLI_EPI_RESIDUAL) v += __bfloat162float(residual[(size_t)m * N + n]);
         }
-        y[(size_t)m * N + n] = __float2bfloat16_rn(v);
+        const bf16 yb = __float2bfloat16_rn(v);
+        y[(size_t)m * N + n] = yb;
+        if (cand) {  // outputs of a warp arrive in increasing n: strict > keeps the lowest index on ties
+          const float yv = __bfloat162float(yb);
+#pragma unroll
+          for (int mm = 0; mm < M; ++mm)
+            if (mm == m && (yv > best_v[mm] || best_i[mm] == 0x7fffffff)) { best_v[mm] = yv; best_i[mm] = n; }
+        }
       }
     }
     // the other parity buffer is only rewritten after the next __syncthreads()
+  }
+  if (cand) {
+    // per-CTA candidate -> cand[(cta * M + m) * 2 + {0,1}] = (logit, index bits); a CTA with no
+    // outputs writes (-inf, INT_MAX).  dli_argmax_merge picks the global best, lowest index on ties.
+    __shared__ float cv[kGemvWarps][M];
+    __shared__ int ci[kGemvWarps][M];
+    if (lane == 0) {
+#pragma unroll
+      for (int m = 0; m < M; ++m) { cv[warp][m] = best_v[m]; ci[warp][m] = best_i[m]; }
+    }
+    __syncthreads();
+    if (tid < M) {
+      float bv = -INFINITY;
+      int bi = 0x7fffffff;
+      for (int ww = 0; ww < kGemvWarps; ++ww) {
+        const float v = cv[ww][tid];
+        const int i = ci[ww][tid];
+        if (i != 0x7fffffff && (bi == 0x7fffffff || v > bv || (v == bv && i < bi))) { bv = v; bi = i; }
+      }
+      cand[((size_t)blockIdx.x * M + tid) * 2 + 0] = bv;
+      cand[((size_t)blockIdx.x * M + tid) * 2 + 1] = __int_as_float(bi);
+    }
   }
 }
 
 template <int M, bool kGated, bool kNorm>
 static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf16* residual, bf16* y, int N, int K,
-                       int epilogue, const bf16* ln_w, float eps, cudaStream_t s) {
+                       int epilogue, const bf16* ln_w, float eps, cudaStream_t s, float* cand = nullptr,
+                       int* grid_out = nullptr) {
   constexpr int kOutPerTask = kGated ? kGemvRows / 2 : kGemvRows;
-  const int ntasks = (N + kOutPerTask - 1) / kOutPerTask;
+  const int ngroups_total = (N + kOutPerTask - 1) / kOutPerTask;
   const int sms = sm_count_cached();
   if (sms <= 0) return fail(DLI_ERR_CUDA, "gemv: no CUDA device");
-  // vectors per row prefetched across the kernel boundary: the whole row, or 512 (8 KB)
   const size_t dyn = kNorm ? (size_t)M * K * 2 : 0;
   // resident CTAs per SM for this instantiation on this device, redone when a call needs more shared memory
   static PerDeviceOnce once;
@@ -230,16 +285,20 @@ static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf1
     once.bytes[dev] = dyn;
   });
   const int occ = once.value[dev];
-  const int grid = ntasks < sms * occ ? ntasks : sms * occ;
+  // one resident wave; every CTA gets N/grid outputs (+-1)
+  const int grid = ngroups_total < sms * occ ? ngroups_total : sms * occ;
+  if (grid_out) *grid_out = grid;
+  // bytes per row prefetched into L2 across the kernel boundary (the whole row, or 8 KB)
   static const int pf_l2 = getenv("DLI_GEMV_PF_L2") ? atoi(getenv("DLI_GEMV_PF_L2")) : 8192;
   DLI_LAUNCH("gemv_kernel", gemv_kernel<M, kGated, kNorm>, dim3(grid), dim3(kGemvThreads), dyn, s, x, w, bias, residual,
-             y, N, K, epilogue, ntasks, ln_w, eps, pf_l2);
+             y, N, K, epilogue, ln_w, eps, pf_l2, cand);
   return DLI_OK;
 }
 
 template <bool kGated, bool kNorm>
 static int gemv_dispatch(const void* x, const void* w, const void* bias, const void* residual, void* y, int M, int N,
-                         int K, int epilogue, const void* ln_w, float eps, dli_stream_t stream) {
+                         int K, int epilogue, const void* ln_w, float eps, dli_stream_t stream,
+                         float* cand = nullptr, int* grid_out = nullptr) {
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // M > 4 is served in passes of <= 4 rows (weights re-streamed once per pass).
   for (int m0 = 0; m0 < M; m0 += 4) {
@@ -250,15 +309,19 @@ static int gemv_dispatch(const void* x, const void* w, const void* bias, const v
     const bf16 *wp = (const bf16*)w, *bp = (const bf16*)bias, *lp = (const bf16*)ln_w;
     int rc;
     switch (mm) {
-      case 1: rc = launch_gemv<1, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s); break;
-      case 2: rc = launch_gemv<2, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s); break;
-      case 3: rc = launch_gemv<3, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s); break;
-      default: rc = launch_gemv<4, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s); break;
+      case 1: rc = launch_gemv<1, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s, cand, grid_out); break;
+      case 2: rc = launch_gemv<2, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s, cand, grid_out); break;
+      case 3: rc = launch_gemv<3, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s, cand, grid_out); break;
+      default: rc = launch_gemv<4, kGated, kNorm>(xp, wp, bp, rp, yp, N, K, epilogue, lp, eps, s, cand, grid_out); break;
     }
     if (rc != DLI_OK) return rc;
   }
   return DLI_OK;
 }
+
+// elementwise.cu: one warp per row reduces [n][B] (logit, index) candidates
+int launch_argmax_merge(const float* cands, int n, int B, int idx_offset, int32_t* tokens, float* cand_out,
+                        cudaStream_t s);
 
 static int check_gemv(const char* name, const void* x, const void* w, const void* y, int M, int N, int K) {
   DLI_CHECK_ARG(x && w && y, "%s: null pointer", name);
@@ -314,6 +377,35 @@ int dli_rmsnorm_gemv_gated_silu_bf16(const void* h, const void* ln_w, float eps,
   DLI_CHECK_ARG(F % 128 == 0 && K <= 16384, "dli_rmsnorm_gemv_gated_silu_bf16: need F %% 128 == 0, K <= 16384");
   if (M == 0) return DLI_OK;
   return gemv_dispatch<true, true>(h, w_gu, nullptr, nullptr, y, M, F, K, 0, ln_w, eps, stream);
+}
+
+size_t dli_gemv_argmax_scratch_bytes(int M) {
+  const int sms = dli::sm_count_cached();
+  if (M <= 0 || M > 4 || sms <= 0) return 0;
+  return (size_t)sms * 8 /* resident CTAs per SM, upper bound */ * M * 2 * sizeof(float);
+}
+
+int dli_gemv_argmax_bf16(const void* h, const void* ln_w, float eps, const void* w, void* logits, int M, int N, int K,
+                         int idx_offset, int32_t* tokens, float* cand_out, void* scratch, size_t scratch_bytes,
+                         dli_stream_t stream) {
+  using namespace dli;
+  int rc = check_gemv("dli_gemv_argmax_bf16", h, w, logits, M, N, K);
+  if (rc != DLI_OK) return rc;
+  DLI_CHECK_ARG(M <= 4, "dli_gemv_argmax_bf16: at most 4 rows per call (got %d); larger batches use "
+                "dli_linear_bf16 + dli_argmax_bf16", M);
+  DLI_CHECK_ARG((tokens != nullptr) != (cand_out != nullptr),
+                "dli_gemv_argmax_bf16: give exactly one of tokens / cand_out");
+  DLI_CHECK_ARG(!ln_w || (aligned16(ln_w) && K <= 16384), "dli_gemv_argmax_bf16: ln_w must be 16-byte aligned, K <= 16384");
+  DLI_CHECK_ARG(idx_offset >= 0 && scratch && scratch_bytes >= dli_gemv_argmax_scratch_bytes(M) && aligned16(scratch),
+                "dli_gemv_argmax_bf16: scratch must hold dli_gemv_argmax_scratch_bytes(M) = %zu bytes (got %zu)",
+                dli_gemv_argmax_scratch_bytes(M), scratch_bytes);
+  if (M == 0) return DLI_OK;
+  int grid = 0;
+  float* cand = static_cast<float*>(scratch);
+  rc = ln_w ? gemv_dispatch<false, true>(h, w, nullptr, nullptr, logits, M, N, K, 0, ln_w, eps, stream, cand, &grid)
+            : gemv_dispatch<false, false>(h, w, nullptr, nullptr, logits, M, N, K, 0, nullptr, 0.f, stream, cand, &grid);
+  if (rc != DLI_OK) return rc;
+  return launch_argmax_merge(cand, grid, M, idx_offset, tokens, cand_out, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -312,12 +312,16 @@ class ShardEngine:
         self._finalize_layers()
 
     def load_random(self, seed: int = 0, std: float = 0.02) -> None:
-        """Random-init weights generated directly on the device (synthetic
-        benchmark weights of the named architecture; no checkpoints offline)."""
+        """Random-init weights generated directly on the device (synthetic benchmark weights of the named
+        architecture; no checkpoints offline).  Every tensor group has its own seed derived from (seed,
+        layer index) — not from the stage — so a stage of an N-way split holds exactly the weights the
+        full-range engine holds for the same layers (bench.py checks pipeline tokens against it)."""
         s, dev = self.spec, self.device
-        g = torch.Generator(device=dev).manual_seed(seed * 1000 + self.start)
 
-        def n(*shape, mean=0.0):
+        def gen(tag: int) -> torch.Generator:
+            return torch.Generator(device=dev).manual_seed(seed * 1_000_003 + tag)
+
+        def n(g, *shape, mean=0.0):
             out = torch.empty(*shape, dtype=BF, device=dev)
             # fill in slices to bound the fp32 temporary
             flat = out.view(-1)
@@ -331,19 +335,29 @@ class ShardEngine:
         self.layers = []
         if s.arch != "llama":
             raise NotImplementedError("load_random covers the llama family; use load_state_dict for gpt2")
+        EMBED, NORM, HEAD = 900_001, 900_002, 900_003  # tags beyond any layer index
         if self.is_first:
-            self.w["embed"] = n(s.vocab, d)
-        for _ in range(self.n_local):
+            self.w["embed"] = n(gen(EMBED), s.vocab, d)
+        for i in range(self.start, self.end + 1):
+            g = gen(i)
             self.layers.append({
-                "ln1": n(d, mean=1.0), "wqkv": n((s.n_heads + 2 * s.n_kv_heads) * hd, d), "wo": n(d, s.n_heads * hd),
-                "ln2": n(d, mean=1.0), "wgu": n(2 * ff, d), "wdown": n(d, ff),
+                "ln1": n(g, d, mean=1.0), "wqkv": n(g, (s.n_heads + 2 * s.n_kv_heads) * hd, d),
+                "wo": n(g, d, s.n_heads * hd), "ln2": n(g, d, mean=1.0), "wgu": n(g, 2 * ff, d), "wdown": n(g, d, ff),
             })
+
+        def head():
+            if s.tie_embeddings:
+                return self.w["embed"] if self.is_first else n(gen(EMBED), s.vocab, d)
+            return n(gen(HEAD), s.vocab, d)
+
         if self.head_shard is not None:
-            self.w["norm"] = n(d, mean=1.0)
-            self.w["head"] = n(self.v1 - self.v0, d)
+            self.w["norm"] = n(gen(NORM), d, mean=1.0)
+            full = head()  # the rows [v0, v1) of the SAME matrix the undivided head holds
+            self.w["head"] = full[self.v0:self.v1].clone()
+            del full
         elif self.is_last:
-            self.w["norm"] = n(d, mean=1.0)
-            self.w["head"] = self.w["embed"] if (s.tie_embeddings and self.is_first) else n(s.vocab, d)
+            self.w["norm"] = n(gen(NORM), d, mean=1.0)
+            self.w["head"] = head()
         self._finalize_layers()
 
     def _finalize_layers(self) -> None:
@@ -475,6 +489,13 @@ class ShardEngine:
         s = self.spec
         B = h_last.shape[0]
         xn = self._x[:B]
+        rows = st.get("row_sampling") if st is not None else None
+        if s.arch == "llama" and B <= _GEMV_MAX_ROWS and rows is None and self.sampling is None:
+            # greedy at <= 2 rows: the argmax rides in the lm_head GEMV's epilogue (per-CTA candidates + a
+            # one-warp merge), the [B, V] logits are written but never read back
+            ops.linear_argmax(h_last, self.w["head"], logits, self._head_scratch(B), tokens=tokens,
+                              ln_w=self.w["norm"], eps=s.eps)
+            return
         if s.arch == "llama" and B <= _GEMV_MAX_ROWS:
             ops.rmsnorm_linear(h_last, self.w["norm"], s.eps, self.w["head"], out=logits)
         else:
@@ -483,7 +504,6 @@ class ShardEngine:
             else:
                 ops.add_layernorm(h_last, self.w["norm"], self.w["normb"], s.eps, out=xn)
             ops.linear(xn, self.w["head"], out=logits)
-        rows = st.get("row_sampling") if st is not None else None
         if rows is not None:
             # rows of different requests (continuous batching): greedy token for every row, then the rows whose
             # request samples are overwritten by a draw keyed with the request's own seed and token position
@@ -493,6 +513,16 @@ class ShardEngine:
             ops.argmax(logits, out=tokens)
         else:
             ops.sample(logits, out=tokens, seed=st["seed"], step=st["step"], **self.sampling)
+
+    def _head_scratch(self, B: int) -> torch.Tensor:
+        """Per-CTA (logit, index) candidates of the fused lm_head argmax (shared by all slots: calls are
+        stream-ordered and every slot read is written by the same call)."""
+        if getattr(self, "_hs", None) is None or self._hs_rows < B:
+            self._hs = torch.empty(max(ops.gemv_argmax_scratch_bytes(B), 16) // 4, dtype=torch.float32,
+                                   device=self.device)
+            self._hs_rows = B
+            self._graphs.clear()
+        return self._hs
 
     # ------------------------------------------------------------------ prefill
     def _state(self, B: int, mb: int = 0) -> dict:
@@ -673,7 +703,9 @@ class ShardEngine:
         def body():
             s = self.spec
             if B <= _GEMV_MAX_ROWS and s.arch == "llama":
-                ops.rmsnorm_linear(st["hf"], self.w["norm"], s.eps, self.w["head"], out=st["logits"])
+                ops.linear_argmax(st["hf"], self.w["head"], st["logits"], self._head_scratch(B), cand=st["cand"],
+                                  ln_w=self.w["norm"], eps=s.eps, idx_offset=self.v0)
+                return
             else:
                 xn = self._x[:B]
                 if s.arch == "llama":
@@ -751,7 +783,8 @@ class ShardEngine:
             self._graphs.clear()
         st["seed"].fill_(int(seed))
         st["step"].fill_(-1)  # prefill draws with step -1, decode steps with 0, 1, ...
-        ids = input_ids.to(device=self.device, dtype=torch.int32, non_blocking=True).reshape(-1).contiguous()
+        # narrowed on the host first: the host->device copy is 4 bytes per prompt token
+        ids = input_ids.to(dtype=torch.int32).to(device=self.device, non_blocking=True).reshape(-1).contiguous()
         eager = return_logits or forced is not None
         if forced is not None:
             forced = forced.to(device=self.device, dtype=torch.int32)

@@ -388,3 +388,22 @@ def argmax_merge(cands, out):
     _lib.check("dli_argmax_merge", _lib.load().dli_argmax_merge(_p(cands), n, B, _p(out), _stream()))
     launch_count += 1
     return out
+
+
+def gemv_argmax_scratch_bytes(M) -> int:
+    return int(_lib.load().dli_gemv_argmax_scratch_bytes(M))
+
+
+def linear_argmax(h, w, logits, scratch, tokens=None, cand=None, ln_w=None, eps=0.0, idx_offset=0):
+    """lm_head for <= 4 rows with the greedy choice fused into the weight stream: logits = (rmsnorm(h) * ln_w
+    if ln_w is given else h) @ w.T, and tokens[m] = idx_offset + argmax (or `cand` [M, 2] float32 = (best logit,
+    idx_offset + index) for one vocabulary slice).  `scratch`: gemv_argmax_scratch_bytes(M) bytes."""
+    global launch_count
+    _req(h), _req(w), _req(logits), _req(ln_w), _req(tokens, torch.int32), _req(cand, torch.float32)
+    M, K = h.shape
+    N = w.shape[0]
+    _lib.check("dli_gemv_argmax_bf16", _lib.load().dli_gemv_argmax_bf16(
+        _p(h), _p(ln_w), float(eps), _p(w), _p(logits), M, N, K, int(idx_offset), _p(tokens), _p(cand), _p(scratch),
+        _bytes(scratch), _stream()))
+    launch_count += 2
+    return tokens if tokens is not None else cand

@@ -343,7 +343,7 @@ def run_pipeline_bench(args, spec, peaks):
     pf_ms = timed(prefill_all)
     runner.run("decode", W)  # warm-up rounds (captures the per-slot CUDA graphs)
     n0 = ops.launch_count
-    from bench import ClockSampler, decode_step_bytes
+    from .measure import ClockSampler, decode_step_bytes
 
     with ClockSampler(index=local) as clk:
         ms = timed(lambda: runner.run("decode", K))

@@ -310,6 +310,24 @@ int dli_argmax_candidate_bf16(const void* logits, int ld, int idx_offset, float*
                               int V, dli_stream_t stream);
 int dli_argmax_merge(const float* cands, int n, int B, int32_t* out, dli_stream_t stream);
 
+/* lm_head with the greedy choice fused into the weight stream (final norm + lm_head +
+ * argmax of TF:models/llama/modeling_llama.py:421,486-487 and TF:generation/utils.py:2762-2793
+ * with do_sample=False, as reached from worker/app.py:297-305) for M <= 4 rows:
+ *   logits[m, n] = bf16( sum_k xn[m,k] * w[n,k] ),  xn = rmsnorm(h) * ln_w (ln_w NULL: xn = h),
+ * exactly as dli_rmsnorm_gemv_bf16 / dli_gemv_bf16 write them, and while a CTA produces its
+ * share of the outputs it keeps the best (bf16 logit, n) it has seen; a second, one-warp-per-row
+ * kernel reduces the per-CTA candidates (highest logit, lowest n on ties = torch.argmax on the
+ * row).  The [M, N] logits are never read back.
+ *   tokens   != NULL: tokens[m] = idx_offset + argmax_n logits[m, n]
+ *   cand_out != NULL: cand_out[m] = (best logit, idx_offset + n as int32 bits) — one vocabulary
+ *                     slice of a pipeline's head, merged across stages by dli_argmax_merge
+ * (exactly one of the two).  scratch: dli_gemv_argmax_scratch_bytes(M) bytes of device memory
+ * for the per-CTA candidates; every slot read is written by the same call. */
+size_t dli_gemv_argmax_scratch_bytes(int M);
+int dli_gemv_argmax_bf16(const void* h, const void* ln_w, float eps, const void* w, void* logits,
+                         int M, int N, int K, int idx_offset, int32_t* tokens, float* cand_out,
+                         void* scratch, size_t scratch_bytes, dli_stream_t stream);
+
 /* The reference's default sampling epilogue (worker/app.py:297-305: do_sample=True,
  * top_k=50, top_p=0.95, temperature=0.8): TemperatureLogitsWarper -> TopKLogitsWarper
  * -> TopPLogitsWarper -> softmax -> multinomial (TF:generation/logits_process.py,

@@ -334,6 +334,67 @@ def test_gemv(cuda, M, N, K):
     _check_linear(ops.gemv(x, w, bias=bias, epilogue=ops.EPI_GELU_NEW), _lin_ref(x, w, bias, gelu=True), K)
 
 
+@pytest.mark.parametrize("N", [1, 2, 3, 5, 443, 444, 445, 1777, 4099])
+def test_gemv_every_output_written_once_for_ragged_row_counts(cuda, N):
+    """The GEMV gives every CTA a contiguous share of the outputs, walked in groups of <= 4 rows whose last
+    groups can be short: row counts around the grid size (444 CTAs on a B200) and not divisible by 4."""
+    from dli_b200 import ops
+
+    K = 512
+    gen = torch.Generator(device="cuda").manual_seed(N)
+    x = torch.randn(2, K, device=cuda, generator=gen).to(BF)
+    w = (torch.randn(N, K, device=cuda, generator=gen) * 0.05).to(BF)
+    y = torch.full((2, N + 8), 77.0, device=cuda, dtype=BF)  # guard columns behind the last row
+    ops.gemv(x, w, out=y.view(-1)[: 2 * N].view(2, N))
+    _check_linear(y.view(-1)[: 2 * N].view(2, N), _lin_ref(x, w), K)
+    assert bool((y.view(-1)[2 * N:] == 77.0).all())
+
+
+@pytest.mark.parametrize("M", [1, 2, 4])
+@pytest.mark.parametrize("N,K,norm", [(128256, 4096, True), (32000, 2048, True), (50257, 768, False), (17, 64, False),
+                                      (16032, 4096, True)])
+def test_lm_head_fused_argmax_equals_argmax_of_its_own_logits(cuda, M, N, K, norm):
+    """dli_gemv_argmax_bf16: logits bit-identical to the unfused GEMV, token == torch.argmax of those bf16
+    logits (lowest index on ties), candidate form == (max logit, offset + index)."""
+    from dli_b200 import ops
+
+    gen = torch.Generator(device="cuda").manual_seed(M + N)
+    h = torch.randn(M, K, device=cuda, generator=gen).to(BF)
+    w = (torch.randn(N, K, device=cuda, generator=gen) * 0.02).to(BF)
+    ln = (1.0 + 0.1 * torch.randn(K, device=cuda, generator=gen)).to(BF) if norm else None
+    ref_logits = ops.rmsnorm_linear(h, ln, 1e-5, w) if norm else ops.gemv(h, w)
+    logits = torch.empty(M, N, device=cuda, dtype=BF)
+    scratch = torch.empty(ops.gemv_argmax_scratch_bytes(M) // 4, device=cuda, dtype=torch.float32)
+    tokens = torch.full((M,), -1, device=cuda, dtype=torch.int32)
+    ops.linear_argmax(h, w, logits, scratch, tokens=tokens, ln_w=ln, eps=1e-5)
+    assert torch.equal(logits, ref_logits)
+    assert torch.equal(tokens.long(), torch.argmax(logits.float(), dim=-1))
+    cand = torch.zeros(M, 2, device=cuda, dtype=torch.float32)
+    ops.linear_argmax(h, w, logits, scratch, cand=cand, ln_w=ln, eps=1e-5, idx_offset=1000)
+    assert torch.equal(cand[:, 0], logits.float().max(dim=-1).values)
+    assert torch.equal(cand[:, 1].contiguous().view(torch.int32).long(), torch.argmax(logits.float(), dim=-1) + 1000)
+
+
+def test_lm_head_fused_argmax_ties_take_the_lowest_index(cuda):
+    """Identical weight rows give identical logits: the fused choice must be the first of them, wherever the
+    duplicates fall among the CTAs' shares."""
+    from dli_b200 import ops
+
+    K, N = 256, 5000
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    h = torch.randn(1, K, device=cuda, generator=gen).to(BF)
+    w = (torch.randn(N, K, device=cuda, generator=gen) * 0.02).to(BF)
+    best = (h.float() @ w.float().t()).argmax().item()
+    for dup in (0, 7, 2499, 2500, 4999):
+        w2 = w.clone()
+        w2[dup] = w[best]
+        logits = torch.empty(1, N, device=cuda, dtype=BF)
+        scratch = torch.empty(ops.gemv_argmax_scratch_bytes(1) // 4, device=cuda, dtype=torch.float32)
+        tokens = torch.zeros(1, device=cuda, dtype=torch.int32)
+        ops.linear_argmax(h, w2, logits, scratch, tokens=tokens)
+        assert tokens.item() == min(dup, best) == torch.argmax(logits.float(), dim=-1).item()
+
+
 def _gated_ref(x, wg, wu):
     g = (x.float() @ wg.float().t()).to(BF)
     u = (x.float() @ wu.float().t()).to(BF)
