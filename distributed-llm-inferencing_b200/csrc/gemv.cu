@@ -11,11 +11,10 @@
 // on kRows weight rows at a time; its 8 warps split K between them so that one
 // CTA iteration reads kRows contiguous 4 KB row segments (256 lanes x 16 B),
 // then partial sums are combined through shared memory (one warp per output).
-// The grid is a multiple of the SM count and every CTA owns a CONTIGUOUS, equally
-// sized share of the outputs (N/grid, +-1), walked in groups of <= kRows rows.  Dealing
-// whole 4-row tasks round-robin left a third of the CTAs with one task more than the
-// rest on the small matrices (o/down: 1024 tasks on 444 CTAs = 3 vs 2), and a CTA that
-// streams alone on its SM runs far below the SM's share of HBM bandwidth.
+// The grid is a multiple of the SM count; groups of kRows rows are dealt round-robin for
+// as many full waves as there are, and the rows of the ragged last wave are split evenly
+// over all CTAs (see `deal` in the kernel): a CTA left streaming alone on its SM runs far
+// below the SM's share of HBM bandwidth.
 //
 // Programmatic dependent launch: a CTA of the next kernel may move in while this
 // kernel drains; it waits (pdl_wait) before reading activations.  Prefetching the
@@ -42,7 +41,7 @@ template <int M, bool kGated, bool kNorm>
 __global__ void __launch_bounds__(kGemvThreads, M <= 2 ? 3 : 2)
 gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* __restrict__ bias,
             const bf16* residual, bf16* y, int N, int K, int epilogue,
-            const bf16* __restrict__ ln_w, float eps, int pf_l2, float* __restrict__ cand) {
+            const bf16* __restrict__ ln_w, float eps, int pf_l2, float* __restrict__ cand, int deal) {
   // partial sums: [parity][value][thread]; value = row * M + m
   __shared__ float part[2][kGemvRows * M][kGemvThreads];
   __shared__ float red[kGemvWarps][M];
@@ -54,11 +53,38 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
   constexpr int kOutPerTask = kGated ? kGemvRows / 2 : kGemvRows;
   const uint4 zero = make_uint4(0, 0, 0, 0);
 
-  // This CTA's share of the N outputs: [n_lo, n_hi), in `ngroups` groups of <= kOutPerTask outputs
-  // whose sizes differ by at most one (10 outputs -> 4,3,3, not 4,4,2).
-  const int n_lo = (int)((long long)N * blockIdx.x / gridDim.x);
-  const int n_hi = (int)((long long)N * (blockIdx.x + 1) / gridDim.x);
-  const int ngroups = (n_hi - n_lo + kOutPerTask - 1) / kOutPerTask;
+  // How the N outputs are dealt to the CTAs (`deal`):
+  //  0  whole groups of kOutPerTask outputs round-robin (group i -> CTA i % grid): at any moment the grid
+  //     streams one contiguous band of the matrix, but the last wave is ragged — on the small matrices a
+  //     third of the CTAs carry one group more than the rest (o/down: 1024 groups on 444 CTAs = 3 vs 2);
+  //  1  one contiguous, equally sized share per CTA (N/grid outputs, +-1), walked in groups of <= kOutPerTask
+  //     (measured: 444 far-apart streams cost the gate/up matrix 10 % of its bandwidth, 35.2 -> 39.0 us);
+  //  2  (default) the full waves round-robin as in 0, then the outputs of the ragged last wave split evenly
+  //     over ALL CTAs in groups of 1..kOutPerTask — the access pattern of 0 with the balance of 1.
+  const int full_waves = deal == 2 ? (N / kOutPerTask) / (int)gridDim.x : 0;  // waves of COMPLETE groups only
+  const int tail_begin = full_waves * (int)gridDim.x * kOutPerTask;           // first output of the tail
+  int n_lo = 0, n_hi = 0, ngroups;
+  if (deal == 0) {
+    const int groups_total = (N + kOutPerTask - 1) / kOutPerTask;
+    ngroups = (groups_total - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    if (ngroups < 0) ngroups = 0;
+  } else {
+    // this CTA's contiguous share [n_lo, n_hi) of the outputs from tail_begin on (deal 1: of all outputs)
+    n_lo = tail_begin + (int)((long long)(N - tail_begin) * blockIdx.x / gridDim.x);
+    n_hi = tail_begin + (int)((long long)(N - tail_begin) * (blockIdx.x + 1) / gridDim.x);
+    ngroups = full_waves + (n_hi - n_lo + kOutPerTask - 1) / kOutPerTask;
+  }
+  // group g of this CTA -> first output n0 and its number of outputs cnt (1..kOutPerTask)
+  auto group = [&](int g, int& n0, int& cnt) {
+    if (deal == 0 || g < full_waves) {
+      n0 = (g * (int)gridDim.x + (int)blockIdx.x) * kOutPerTask;
+      cnt = min(kOutPerTask, N - n0);
+    } else {
+      const int gs = ngroups - full_waves, gi = g - full_waves;  // sizes differ by at most one: 10 -> 4,3,3
+      n0 = n_lo + (int)((long long)(n_hi - n_lo) * gi / gs);
+      cnt = n_lo + (int)((long long)(n_hi - n_lo) * (gi + 1) / gs) - n0;
+    }
+  };
 
   // rows of group [n0, n0 + cnt): row r is live when its output index r % kOutPerTask < cnt
   auto row_ptrs = [&](int n0, int cnt, const uint4* (&wrow)[kGemvRows]) {
@@ -80,8 +106,9 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
     // Before waiting for the previous kernel: pull the head of this CTA's first weight rows into L2
     // with one bulk prefetch per row (no registers, shared memory or L1 footprint), so HBM keeps
     // streaming through the kernel boundary.  Worth ~1.5 us per layer on the 4-GEMV chain.
-    const int cnt0 = (n_hi - n_lo) / ngroups;
-    row_ptrs(n_lo, cnt0, wrow);
+    int n00, cnt0;
+    group(0, n00, cnt0);
+    row_ptrs(n00, cnt0, wrow);
     const uint32_t bytes = (uint32_t)min((size_t)K * 2, (size_t)pf_l2) & ~15u;
     const uint4* mine = wrow[0];
 #pragma unroll
@@ -150,8 +177,8 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
 
   int parity = 0;
   for (int g = 0; g < ngroups; ++g, parity ^= 1) {
-    const int n0 = n_lo + (int)((long long)(n_hi - n_lo) * g / ngroups);
-    const int cnt = n_lo + (int)((long long)(n_hi - n_lo) * (g + 1) / ngroups) - n0;
+    int n0, cnt;
+    group(g, n0, cnt);
     row_ptrs(n0, cnt, wrow);
     bool live[kGemvRows];
 #pragma unroll
@@ -290,8 +317,9 @@ static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf1
   if (grid_out) *grid_out = grid;
   // bytes per row prefetched into L2 across the kernel boundary (the whole row, or 8 KB)
   static const int pf_l2 = getenv("DLI_GEMV_PF_L2") ? atoi(getenv("DLI_GEMV_PF_L2")) : 8192;
+  static const int deal = getenv("DLI_GEMV_DEAL") ? atoi(getenv("DLI_GEMV_DEAL")) : 2;  // measurement knob, see kernel
   DLI_LAUNCH("gemv_kernel", gemv_kernel<M, kGated, kNorm>, dim3(grid), dim3(kGemvThreads), dyn, s, x, w, bias, residual,
-             y, N, K, epilogue, ln_w, eps, pf_l2, cand);
+             y, N, K, epilogue, ln_w, eps, pf_l2, cand, deal);
   return DLI_OK;
 }
 

@@ -13,19 +13,25 @@ three ways: this engine (bf16, CUDA-graph decode = the path bench.py times), tra
 reference would run on this GPU) and transformers fp32 ("truth").  Stated tolerance (the one tests/test_engine_gpu.py
 uses on the small models):
     max|ours - fp32| <= 2 x max|HF-bf16 - fp32| + 4e-3     (teacher-forced along HF-bf16's tokens, every step)
-    token == HF-fp32's token at every step whose fp32 top-1/top-2 margin exceeds twice that noise
-    free-running tokens == HF-bf16's up to the first step whose margin is below the noise
-Random-init weights give nearly flat logits, so "exact" can only be asked where the margin clears
-bf16 noise — transformers' own bf16 run disagrees with its fp32 run elsewhere.  The margins, noise and safe fraction
-are printed (-s) and asserted to be non-trivial.
+    token == HF-fp32's token at every step whose fp32 top-1/top-2 margin exceeds twice the bf16 error on the
+      leading candidates (margin-safe steps), and over all steps as often as HF-bf16's own token does (- 10 %)
+    free-running tokens == HF-bf16's up to the first step that is not margin-safe
+Random-init weights give nearly flat logits: at 32 layers and a 2k context the bf16 noise on a logit
+(~0.1, up to 0.5 somewhere in a 128k-entry row) is of the order of the median top-1/top-2 margin (~0.2), so
+transformers' own bf16 run picks fp32's token on only ~83 % of the steps (measured: 53 of 64, this engine 53 of 64)
+and "exact" can only be asked where the margin clears the noise.  Margins, noise and the counts are printed (-s),
+written to gpurun_out/full_depth_parity.jsonl and asserted to be non-trivial.
 """
 import gc
+import json
+import os
 
 import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
 BF = torch.bfloat16
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _hf_config(transformers, name):
@@ -116,32 +122,51 @@ def test_full_depth_model_matches_transformers_on_the_same_gpu(cuda, name, T, n_
     ours_free = eng.generate(ids, max_len)[0, T:]
     eng.unload()
 
-    hf_err = (hf_logits - truth).abs().amax(-1)          # transformers' own bf16 noise per step
+    # ---- noise and margins ------------------------------------------------------------------------------------------
+    hf_err = (hf_logits - truth).abs().amax(-1)          # transformers' own bf16 noise per step (max over the vocabulary)
     our_err = (ours_logits - truth).abs().amax(-1)
-    top2 = truth.topk(2, dim=-1).values
-    margin = top2[:, 0] - top2[:, 1]
-    noise = max(hf_err.max().item(), our_err.max().item())
-    safe = margin > 2.0 * noise
+    top = truth.topk(17, dim=-1)
+    margin = top.values[:, 0] - top.values[:, 1]
+    # A step is "margin-safe" when no bf16 implementation can pick another token than fp32 does: the error either
+    # implementation makes on the 16 best fp32 candidates is below half the top-1/top-2 margin, and nothing outside
+    # those 16 comes within reach (gap to the 17th > the two worst errors anywhere in the row).
+    idx = top.indices[:, :16]
+    local = torch.maximum((ours_logits.gather(1, idx) - top.values[:, :16]).abs().amax(-1),
+                          (hf_logits.gather(1, idx) - top.values[:, :16]).abs().amax(-1))
+    safe = (margin > 2.0 * local) & ((top.values[:, 0] - top.values[:, 16]) > 2.0 * torch.maximum(hf_err, our_err))
     scale = truth.abs().max().item()
-    rel = our_err.max().item() / scale
-    same_vs_truth = ours_logits.argmax(-1) == truth.argmax(-1)
-    agree_hf = (ours_tf[0, T:] == hf_tokens)
+    truth_tok = truth.argmax(-1)
+    ours_vs_truth = ours_logits.argmax(-1) == truth_tok
+    hf_vs_truth = hf_logits.argmax(-1) == truth_tok
+    agree_hf = ours_tf[0, T:] == hf_tokens
     first_unsafe = int((~safe).float().argmax().item()) if bool((~safe).any()) else n_new
-    print(f"\n[{name}] T={T} new={n_new}: max|ours-fp32|={our_err.max():.4f} max|HF-bf16-fp32|={hf_err.max():.4f} "
-          f"(logit scale {scale:.2f}, ours rel {rel:.4f}); fp32 margin min/median {margin.min():.4f}/"
-          f"{margin.median():.4f}; margin-safe steps {int(safe.sum())}/{n_new}; teacher-forced agreement with HF-bf16 "
-          f"{int(agree_hf.sum())}/{n_new}, with fp32 {int(same_vs_truth.sum())}/{n_new} (HF-bf16 vs fp32: "
-          f"{int((hf_logits.argmax(-1) == truth.argmax(-1)).sum())}/{n_new}); free-running identical to HF-bf16 for "
-          f"{int((ours_free == hf_tokens).long().cumprod(0).sum())} tokens, margin-safe prefix {first_unsafe}")
-    # logits: within twice transformers' own bf16 error against fp32 truth
-    assert our_err.max() <= 2.0 * hf_err.max() + 4e-3
-    # tokens: exact wherever the fp32 margin clears the bf16 noise of both implementations
-    assert bool(same_vs_truth[safe].all())
-    assert bool(agree_hf[safe].all())
-    # free-running (the graph path): identical to HF-bf16 over the margin-safe prefix
-    assert torch.equal(ours_free[:first_unsafe], hf_tokens[:first_unsafe])
-    # the graph path and the eager path of this engine agree step by step where they were fed the same history
     same_hist = int((ours_free == hf_tokens).long().cumprod(0).sum())
-    assert torch.equal(ours_free[: min(same_hist + 1, n_new)], ours_tf[0, T: T + min(same_hist + 1, n_new)])
-    # and the statement is not vacuous
-    assert int(safe.sum()) >= max(4, n_new // 8), "too few margin-safe steps to call this a parity check"
+    report = {"model": name, "prompt": T, "new": n_new, "logit_scale": scale, "max_err_ours_vs_fp32": our_err.max().item(),
+              "max_err_hf_bf16_vs_fp32": hf_err.max().item(), "median_err_ours": our_err.median().item(),
+              "median_err_hf_bf16": hf_err.median().item(), "fp32_margin_min": margin.min().item(),
+              "fp32_margin_median": margin.median().item(), "margin_safe_steps": int(safe.sum()),
+              "teacher_forced_equal_hf_bf16": int(agree_hf.sum()), "teacher_forced_equal_fp32": int(ours_vs_truth.sum()),
+              "hf_bf16_equal_fp32": int(hf_vs_truth.sum()), "free_running_equal_hf_bf16_prefix": same_hist,
+              "margin_safe_prefix": first_unsafe}
+    print("\n[full-depth parity] " + json.dumps(report))
+    try:  # kept with the run's other outputs when the box has the directory (gpurun merges it back)
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", "full_depth_parity.jsonl"), "a") as f:
+            f.write(json.dumps(report) + "\n")
+    except OSError:
+        pass
+    # logits: within twice transformers' own bf16 error against fp32 truth, worst step and typical step
+    assert our_err.max() <= 2.0 * hf_err.max() + 4e-3
+    assert our_err.median() <= 2.0 * hf_err.median() + 4e-3
+    # tokens: exact wherever the margin clears the noise ...
+    assert bool(ours_vs_truth[safe].all()) and bool(agree_hf[safe].all())
+    # ... and overall this engine picks fp32's token about as often as transformers' own bf16 run does (on
+    # random-init weights neither can be exact: the median margin is of the order of the bf16 noise)
+    assert int(ours_vs_truth.sum()) >= int(hf_vs_truth.sum()) - max(3, n_new // 10)
+    # free-running (the CUDA-graph path): identical to HF-bf16 over the margin-safe prefix
+    assert torch.equal(ours_free[:first_unsafe], hf_tokens[:first_unsafe])
+    # the graph path and the eager path of this engine agree step by step while they are fed the same history
+    k = min(same_hist + 1, n_new)
+    assert torch.equal(ours_free[:k], ours_tf[0, T: T + k])
+    # the statement must not be vacuous
+    assert int(safe.sum()) >= max(3, n_new // 10), "too few margin-safe steps to call this a parity check"
