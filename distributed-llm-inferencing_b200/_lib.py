@@ -62,6 +62,7 @@ SIGNATURES = {
     "dli_argmax_bf16": (_i, [_vp, _i, _vp, _i, _i, _vp]),
     "dli_argmax_candidate_bf16": (_i, [_vp, _i, _i, _vp, _i, _i, _vp]),
     "dli_argmax_merge": (_i, [_vp, _i, _i, _vp, _vp]),
+    "dli_argmax_merge_strided": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "dli_gemv_argmax_scratch_bytes": (_sz, [_i]),
     "dli_gemv_argmax_bf16": (_i, [_vp, _vp, _f, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "dli_sample_bf16": (_i, [_vp, _i, _vp, _i, _i, _f, _i, _f, _vp, _vp, _vp, _vp, _i, _vp]),

@@ -121,8 +121,8 @@ __global__ void decode_advance_kernel(const int32_t* __restrict__ tokens, int32_
 // lanes stride over the n candidates, then a shuffle tree.  Writes tokens[b] = idx_offset + index, or
 // (cand_out) the row's (logit, idx_offset + index) for a further merge across stages.
 __global__ void __launch_bounds__(256)
-argmax_merge_kernel(const float* __restrict__ cands, int n, int B, int idx_offset, int32_t* __restrict__ out,
-                    float* __restrict__ cand_out) {
+argmax_merge_kernel(const float* __restrict__ cands, int n, int B, int n_stride, int idx_offset,
+                    int32_t* __restrict__ out, float* __restrict__ cand_out) {
   pdl_wait();
   pdl_trigger();
   const int lane = threadIdx.x & 31;
@@ -130,8 +130,8 @@ argmax_merge_kernel(const float* __restrict__ cands, int n, int B, int idx_offse
     float best = -INFINITY;
     int besti = 0x7fffffff;
     for (int s = lane; s < n; s += 32) {
-      const float v = cands[((size_t)s * B + b) * 2];
-      const int i = reinterpret_cast<const int32_t*>(cands)[((size_t)s * B + b) * 2 + 1];
+      const float v = cands[(size_t)s * n_stride + b * 2];
+      const int i = reinterpret_cast<const int32_t*>(cands)[(size_t)s * n_stride + b * 2 + 1];
       if (i != 0x7fffffff && (besti == 0x7fffffff || v > best || (v == best && i < besti))) { best = v; besti = i; }
     }
 #pragma unroll
@@ -153,10 +153,10 @@ argmax_merge_kernel(const float* __restrict__ cands, int n, int B, int idx_offse
 }
 
 int launch_argmax_merge(const float* cands, int n, int B, int idx_offset, int32_t* tokens, float* cand_out,
-                        cudaStream_t s) {
+                        cudaStream_t s, int n_stride) {
   const int warps = 8;
   DLI_LAUNCH("argmax_merge_kernel", argmax_merge_kernel, dim3((B + warps - 1) / warps), dim3(warps * 32), (size_t)0, s,
-             cands, n, B, idx_offset, tokens, cand_out);
+             cands, n, B, n_stride > 0 ? n_stride : 2 * B, idx_offset, tokens, cand_out);
   return DLI_OK;
 }
 
@@ -179,7 +179,14 @@ int dli_argmax_merge(const float* cands, int n, int B, int32_t* out, dli_stream_
   using namespace dli;
   DLI_CHECK_ARG(cands && out && n > 0 && B >= 0, "dli_argmax_merge: bad arguments");
   if (B == 0) return DLI_OK;
-  return launch_argmax_merge(cands, n, B, 0, out, nullptr, static_cast<cudaStream_t>(stream));
+  return launch_argmax_merge(cands, n, B, 0, out, nullptr, static_cast<cudaStream_t>(stream), 0);
+}
+
+int dli_argmax_merge_strided(const float* cands, int n, int B, int n_stride, int32_t* out, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(cands && out && n > 0 && B >= 0 && n_stride >= 2 * B, "dli_argmax_merge_strided: bad arguments");
+  if (B == 0) return DLI_OK;
+  return launch_argmax_merge(cands, n, B, 0, out, nullptr, static_cast<cudaStream_t>(stream), n_stride);
 }
 
 int dli_decode_advance(const int32_t* tokens, int32_t* token_log, int32_t* positions, int32_t* seq_lens,

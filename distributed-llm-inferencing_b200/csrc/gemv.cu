@@ -11,10 +11,9 @@
 // on kRows weight rows at a time; its 8 warps split K between them so that one
 // CTA iteration reads kRows contiguous 4 KB row segments (256 lanes x 16 B),
 // then partial sums are combined through shared memory (one warp per output).
-// The grid is a multiple of the SM count; groups of kRows rows are dealt round-robin for
-// as many full waves as there are, and the rows of the ragged last wave are split evenly
-// over all CTAs (see `deal` in the kernel): a CTA left streaming alone on its SM runs far
-// below the SM's share of HBM bandwidth.
+// Groups of kRows rows are dealt round-robin to a grid sized as a multiple of the SM count,
+// so at any moment the grid streams one contiguous band of the matrix (two balanced
+// dealings were measured and lost, see `deal` in the kernel).
 //
 // Programmatic dependent launch: a CTA of the next kernel may move in while this
 // kernel drains; it waits (pdl_wait) before reading activations.  Prefetching the
@@ -54,13 +53,16 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
   const uint4 zero = make_uint4(0, 0, 0, 0);
 
   // How the N outputs are dealt to the CTAs (`deal`):
-  //  0  whole groups of kOutPerTask outputs round-robin (group i -> CTA i % grid): at any moment the grid
+  //  0  (default) whole groups of kOutPerTask outputs round-robin (group i -> CTA i % grid): at any moment the grid
   //     streams one contiguous band of the matrix, but the last wave is ragged — on the small matrices a
   //     third of the CTAs carry one group more than the rest (o/down: 1024 groups on 444 CTAs = 3 vs 2);
   //  1  one contiguous, equally sized share per CTA (N/grid outputs, +-1), walked in groups of <= kOutPerTask
   //     (measured: 444 far-apart streams cost the gate/up matrix 10 % of its bandwidth, 35.2 -> 39.0 us);
-  //  2  (default) the full waves round-robin as in 0, then the outputs of the ragged last wave split evenly
-  //     over ALL CTAs in groups of 1..kOutPerTask — the access pattern of 0 with the balance of 1.
+  //  2  the full waves round-robin as in 0, then the outputs of the ragged last wave split evenly over ALL
+  //     CTAs in groups of 1..kOutPerTask — the access pattern of 0 with the balance of 1.
+  // Measured on the Llama-3-8B batch-1 step (B200, profiles/r2_notes.md): 0 -> 2.985 ms, 2 -> 3.062 ms,
+  // 1 -> 3.171 ms.  The ragged wave costs less than short groups do (fewer loads in flight per thread), so
+  // 0 stays the default; 1 and 2 remain selectable (DLI_GEMV_DEAL) to reproduce the comparison.
   const int full_waves = deal == 2 ? (N / kOutPerTask) / (int)gridDim.x : 0;  // waves of COMPLETE groups only
   const int tail_begin = full_waves * (int)gridDim.x * kOutPerTask;           // first output of the tail
   int n_lo = 0, n_hi = 0, ngroups;
@@ -317,7 +319,7 @@ static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf1
   if (grid_out) *grid_out = grid;
   // bytes per row prefetched into L2 across the kernel boundary (the whole row, or 8 KB)
   static const int pf_l2 = getenv("DLI_GEMV_PF_L2") ? atoi(getenv("DLI_GEMV_PF_L2")) : 8192;
-  static const int deal = getenv("DLI_GEMV_DEAL") ? atoi(getenv("DLI_GEMV_DEAL")) : 2;  // measurement knob, see kernel
+  static const int deal = getenv("DLI_GEMV_DEAL") ? atoi(getenv("DLI_GEMV_DEAL")) : 0;  // measurement knob, see kernel
   DLI_LAUNCH("gemv_kernel", gemv_kernel<M, kGated, kNorm>, dim3(grid), dim3(kGemvThreads), dyn, s, x, w, bias, residual,
              y, N, K, epilogue, ln_w, eps, pf_l2, cand, deal);
   return DLI_OK;
@@ -349,7 +351,7 @@ static int gemv_dispatch(const void* x, const void* w, const void* bias, const v
 
 // elementwise.cu: one warp per row reduces [n][B] (logit, index) candidates
 int launch_argmax_merge(const float* cands, int n, int B, int idx_offset, int32_t* tokens, float* cand_out,
-                        cudaStream_t s);
+                        cudaStream_t s, int n_stride = 0);
 
 static int check_gemv(const char* name, const void* x, const void* w, const void* y, int M, int N, int K) {
   DLI_CHECK_ARG(x && w && y, "%s: null pointer", name);

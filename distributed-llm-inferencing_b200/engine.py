@@ -418,9 +418,14 @@ class ShardEngine:
         return max(1, min((tiles + 3) // 4, want, 64))
 
     # ------------------------------------------------------------------ one layer range
-    def _layers_forward(self, h, rows, positions, seq_ids, seq_lens, prefill_shape, st):
-        """h: [rows, d] residual stream (updated in place).  prefill_shape=(B,T) or None for decode."""
+    def _layers_forward(self, h, rows, positions, seq_ids, seq_lens, prefill_shape, st, h_in=None, h_out=None):
+        """h: [rows, d] residual stream (updated in place).  prefill_shape=(B,T) or None for decode.
+        h_in: where the stage's INPUT lives when that is not h (read only: the first norm and the first
+        residual add read it, e.g. a neighbour's hidden state inside a pipeline mailbox); h_out: where the
+        LAST projection writes the stage's output when that is not h."""
         s = self.spec
+        res = h if h_in is None else h_in  # residual source until the first projection has written h
+        last_li = len(self.layers) - 1
         x, qkv, attn, act = self._x[:rows], self._qkv[:rows], self._attn[:rows], self._act[:rows]
         H, KV, hd = s.n_heads, s.n_kv_heads, s.head_dim
         decode = prefill_shape is None
@@ -441,13 +446,14 @@ class ShardEngine:
             return ops.linear_gated_silu(x_, w_, out=out)
 
         for li, L in enumerate(self.layers):
+            dst = h_out if (li == last_li and h_out is not None) else h
             if fuse_norm:
-                ops.rmsnorm_linear(h, L["ln1"], s.eps, L["wqkv"], out=qkv)
+                ops.rmsnorm_linear(res, L["ln1"], s.eps, L["wqkv"], out=qkv)
             elif s.arch == "llama":
-                ops.add_rmsnorm(h, L["ln1"], s.eps, out=x)
+                ops.add_rmsnorm(res, L["ln1"], s.eps, out=x)
                 lin(x, L["wqkv"], out=qkv)
             else:
-                ops.add_layernorm(h, L["ln1"], L["ln1b"], s.eps, out=x)
+                ops.add_layernorm(res, L["ln1"], L["ln1b"], s.eps, out=x)
                 lin(x, L["wqkv"], bias=L["bqkv"], out=qkv)
             if decode:
                 # RoPE + KV append of the new token + split-KV attention in one kernel; the
@@ -469,19 +475,21 @@ class ShardEngine:
                     ops.attn_prefill(qkv, attn, prefill_shape[0], prefill_shape[1], H, KV, hd, self.scale,
                                      window=s.sliding_window)
             if s.arch == "llama":
-                lin(attn, L["wo"], residual=h, out=h)
+                lin(attn, L["wo"], residual=res, out=h)
+                res = h
                 if fuse_norm:
                     ops.rmsnorm_linear_gated_silu(h, L["ln2"], s.eps, L["wgu"], out=act)
                 else:
                     ops.add_rmsnorm(h, L["ln2"], s.eps, out=x)
                     gated(x, L["wgu"], act)
-                lin(act, L["wdown"], residual=h, out=h)
+                lin(act, L["wdown"], residual=h, out=dst)
             else:
-                lin(attn, L["wo"], bias=L["bo"], residual=h, out=h)
+                lin(attn, L["wo"], bias=L["bo"], residual=res, out=h)
+                res = h
                 ops.add_layernorm(h, L["ln2"], L["ln2b"], s.eps, out=x)
                 lin(x, L["wfc"], bias=L["bfc"], out=act, epilogue=ops.EPI_GELU_NEW)
-                lin(act, L["wdown"], bias=L["bdown"], residual=h, out=h)
-        return h
+                lin(act, L["wdown"], bias=L["bdown"], residual=h, out=dst)
+        return h if h_out is None else h_out
 
     def _head(self, h_last, logits, tokens, st=None):
         """final norm + lm_head + token choice on [B, d]: greedy argmax, or (self.sampling)
@@ -741,6 +749,144 @@ class ShardEngine:
         st = self._dec[(B, mb)]
         ops.argmax_merge(st["cands"], st["tokens"])
         return st["tokens"]
+
+    # ------------------------------------------------------------------ pipeline mailboxes
+    # Decode hand-off between pipeline stages without per-pair sends (pipeline.MailboxRunner): every tick each
+    # stage contributes ONE fixed-size "mail" — [hidden tile b x d bf16 | head candidate b x (logit, id) | token
+    # ids b x int32] — and one all-gather per tick delivers all N mails to everybody.  Tick t writes mail_out[t % P]
+    # and the exchange fills mail_in[t % P][src]; the kernels of a slot read and write those buffers in place
+    # (their addresses are fixed per slot, so they are baked into the slot's CUDA graphs): no copies either side.
+    def attach_mailbox(self, b: int, n_slots: int, period: int, hop: int, rank: int, world: int) -> None:
+        """b sequences per slot, n_slots slots in flight, `period` ticks per round of a slot, `hop` ticks between
+        a stage and the next.  The head lives on the last stage (has_head) or is split over the stages (head_shard)."""
+        d = self.spec.d_model
+        off_c = b * d * 2
+        off_t = off_c + b * 8
+        nbytes = (off_t + b * 4 + 255) // 256 * 256
+        dev = self.device
+        out = torch.zeros(period, nbytes, dtype=torch.uint8, device=dev)
+        inn = torch.zeros(period, world, nbytes, dtype=torch.uint8, device=dev)
+        m = {"b": b, "M": n_slots, "P": period, "H": hop, "rank": rank, "N": world, "bytes": nbytes, "out": out, "in": inn,
+             "vp": self.head_shard is not None}
+        m["out_h"] = [out[p, :off_c].view(BF).view(b, d) for p in range(period)]
+        m["out_cand"] = [out[p, off_c:off_t].view(torch.float32).view(b, 2) for p in range(period)]
+        m["out_tok"] = [out[p, off_t:off_t + b * 4].view(torch.int32) for p in range(period)]
+        m["in_h"] = [[inn[p, r, :off_c].view(BF).view(b, d) for r in range(world)] for p in range(period)]
+        m["in_tok"] = [inn[p, world - 1, off_t:off_t + b * 4].view(torch.int32) for p in range(period)]
+        m["in_cands_ptr"] = [inn[p].data_ptr() + off_c for p in range(period)]  # set r starts r * nbytes later
+        self._mail = m
+        self._graphs = {k: v for k, v in self._graphs.items() if not (isinstance(k[-1], str) and k[-1].startswith("mail"))}
+
+    def _graphed(self, key, body, restore=()):
+        """Run `body` as a CUDA graph captured on first use (after one eager warm-up run whose effect on the
+        tensors in `restore` is undone, so the captured state is the state before the call)."""
+        if not self.use_cuda_graph:
+            body()
+            return
+        if key not in self._graphs:
+            saved = [t.clone() for t in restore]
+            side = torch.cuda.Stream(device=self.device)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                body()  # warm-up outside capture (function attributes, occupancy caches, lazy allocations)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            for t, v in zip(restore, saved):
+                t.copy_(v)
+            g = torch.cuda.CUDAGraph()
+            n0 = ops.launch_count
+            # thread_local: other threads (NCCL's watchdog polling its events) must not invalidate the capture
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                body()
+            launches = ops.launch_count - n0
+            for t, v in zip(restore, saved):
+                t.copy_(v)
+            torch.cuda.synchronize()
+            self._graphs[key] = (g, launches)
+        g, launches = self._graphs[key]
+        g.replay()
+        ops.launch_count += launches
+
+    def mail_phase(self, sigma: int, slot: int) -> int:
+        """Tick phase (t mod P) at which the piece with stage offset `sigma` (a stage index; N for the head slices,
+        N+1 / N for stage 0 taking the token in) works on `slot`."""
+        m = self._mail
+        return (slot + m["H"] * sigma) % m["P"]
+
+    def mail_compute(self, mb: int) -> None:
+        """This stage's decode step of slot mb: input from the mailbox the previous stage's mail arrived in (stage 0:
+        the slot's token), output into this tick's outgoing mail (last stage with the whole head: the chosen tokens)."""
+        m = self._mail
+        B, H, P = m["b"], m["H"], m["P"]
+        ph = self.mail_phase(m["rank"], mb)
+        rd = (ph - H) % P
+        st = self._dec[(B, mb)]
+        self._workspace(B)
+
+        def body():
+            h = st["h"]
+            if self.is_first:
+                if self.spec.arch == "gpt2":
+                    ops.embedding(st["tokens"], self.w["embed"], out=h, positions=st["positions"], pos_table=self.w["wpe"])
+                else:
+                    ops.embedding(st["tokens"], self.w["embed"], out=h)
+                h_in = None
+            else:
+                h_in = m["in_h"][rd][m["rank"] - 1]
+            h_out = None if self.has_head else m["out_h"][ph]
+            self._layers_forward(h, B, st["positions"], st["seq_ids"], st["seq_lens"], None, st, h_in=h_in, h_out=h_out)
+            tokens = st["tokens"]
+            if self.has_head:
+                tokens = m["out_tok"][ph]
+                self._head(h, st["logits"], tokens, st)
+            log = st["token_log"] if (self.has_head or (m["vp"] and self.is_first)) else None
+            ops.decode_advance(tokens, log, st["positions"], st["seq_lens"], st["step"])
+
+        self._graphed((B, mb, "mail_compute"), body, restore=[st[k] for k in ("positions", "seq_lens", "step")])
+
+    def mail_head(self, mb: int) -> None:
+        """Vocabulary-parallel head: final norm + this stage's rows of the head on slot mb's final hidden state (as it
+        arrived from the last stage), the slice's best (logit, token id) into this tick's outgoing mail."""
+        m = self._mail
+        B, H, P, N = m["b"], m["H"], m["P"], m["N"]
+        ph = self.mail_phase(N, mb)
+        hf = m["in_h"][(ph - H) % P][N - 1]
+        st = self._dec[(B, mb)]
+        cand = m["out_cand"][ph]
+        self._workspace(B)
+
+        def body():
+            s = self.spec
+            if B <= _GEMV_MAX_ROWS and s.arch == "llama":
+                ops.linear_argmax(hf, self.w["head"], st["logits"], self._head_scratch(B), cand=cand,
+                                  ln_w=self.w["norm"], eps=s.eps, idx_offset=self.v0)
+                return
+            xn = self._x[:B]
+            if s.arch == "llama":
+                ops.add_rmsnorm(hf, self.w["norm"], s.eps, out=xn)
+            else:
+                ops.add_layernorm(hf, self.w["norm"], self.w["normb"], s.eps, out=xn)
+            ops.linear(xn, self.w["head"], out=st["logits"])
+            ops.argmax_candidate(st["logits"], self.v0, cand)
+
+        self._graphed((B, mb, "mail_head"), body)
+
+    def mail_ingest(self, mb: int) -> None:
+        """Stage 0: slot mb's next input token from the mail that just arrived — the global argmax over the stages'
+        candidates (vocabulary-parallel head; lowest id wins ties) or the last stage's chosen token."""
+        m = self._mail
+        B, H, P, N = m["b"], m["H"], m["P"], m["N"]
+        ph = self.mail_phase(N + 1 if m["vp"] else N, mb)
+        rd = (ph - H) % P
+        st = self._dec[(B, mb)]
+
+        def body():
+            if m["vp"]:
+                ops.argmax_merge_strided(m["in_cands_ptr"][rd], N, B, m["bytes"] // 4, st["tokens"])
+            else:
+                st["tokens"].copy_(m["in_tok"][rd])  # 4*b bytes, device to device
+
+        self._graphed((B, mb, "mail_ingest"), body, restore=[st["tokens"]])
 
     def decode_step_host(self, tokens_in: torch.Tensor, tokens_out: torch.Tensor) -> torch.Tensor:
         """One decode step with HOST buffers, the per-token call a streaming client

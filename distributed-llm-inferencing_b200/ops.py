@@ -390,6 +390,16 @@ def argmax_merge(cands, out):
     return out
 
 
+def argmax_merge_strided(cands_ptr: int, n: int, B: int, n_stride: int, out):
+    """argmax_merge over n candidate sets [B, 2] float32 that start n_stride floats apart (raw device pointer:
+    the sets sit inside the pipeline's mailboxes)."""
+    global launch_count
+    _req(out, torch.int32)
+    _lib.check("dli_argmax_merge_strided", _lib.load().dli_argmax_merge_strided(cands_ptr, n, B, n_stride, _p(out), _stream()))
+    launch_count += 1
+    return out
+
+
 def gemv_argmax_scratch_bytes(M) -> int:
     return int(_lib.load().dli_gemv_argmax_scratch_bytes(M))
 

@@ -204,6 +204,194 @@ class VocabParallelRunner:
                     req.wait()
 
 
+# ------------------------------------------------------------------------------ mailbox pipeline (decode)
+class DistExchange:
+    """The per-tick exchange over torch.distributed: ONE all-gather of every stage's outgoing mail
+    (NCCL over NVLink on the B200 box, gloo in the CPU tests).  With a `comm_stream` the collective is issued on
+    that stream behind an event of the compute stream, so it runs while the compute stream goes on with the next
+    tick; wait() makes the current stream wait for it."""
+
+    def __init__(self, group=None, comm_stream=None):
+        self.group, self.comm = group, comm_stream
+
+    def issue(self, mail_out: torch.Tensor, mail_in: torch.Tensor, phase=None):
+        if self.comm is None:
+            return dist.all_gather_into_tensor(mail_in.view(-1), mail_out, group=self.group, async_op=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(ev)
+            return dist.all_gather_into_tensor(mail_in.view(-1), mail_out, group=self.group, async_op=True)
+
+    def wait(self, work) -> None:
+        work.wait()
+
+
+class LocalExchange:
+    """The same exchange between N stages living in ONE process (tests: N layer ranges on one GPU, driven tick by
+    tick in rank order): issue() copies the mail straight into every stage's incoming mailbox."""
+
+    def __init__(self):
+        self.stages = []  # filled by the caller: stage objects in rank order
+
+    def bind(self, rank: int):
+        ex = self
+
+        class _Port:
+            def issue(self, mail_out, mail_in, phase=None):
+                for st in ex.stages:
+                    st.mail_in(phase)[rank].copy_(mail_out)
+                return None
+
+            def wait(self, work):
+                pass
+
+        return _Port()
+
+
+class MailboxRunner:
+    """Decode pipeline over per-tick mailboxes.
+
+    Stage s works on slot u mod P at tick t = u + H*s (H = `hop` ticks between neighbouring stages); the head
+    slices of a vocabulary-parallel head (vp) run at stage offset N and stage 0 takes the slot's next token in at
+    offset N+1 (vp) or N (whole head on the last stage), so a slot's round lasts P = max(M, H*(N+1)) or
+    max(M, H*N) ticks.  Every tick ends with one exchange (all-gather of the stages' mails, see
+    ShardEngine.attach_mailbox); tick t reads what the exchange of tick t-H delivered.  H = 1 is the serialised
+    schedule (the next tick waits for the exchange it has just issued); H = 2 leaves a whole tick for the exchange,
+    which then runs on its own stream UNDER the next tick's kernels — the hand-off disappears from the critical
+    path at the price of twice the slots in flight.
+
+    `stage` needs: is_first; mail_out(phase), mail_in(phase) -> tensors; compute(slot); head(slot); ingest(slot).
+    Slots become active with open()/run() and stay so until close_slot()/the run's last round: the serving loop
+    (pipeline_worker.py) lets requests join and leave between ticks, the benchmark times whole periods of a full
+    pipeline."""
+
+    def __init__(self, stage, rank: int, world: int, n_micro: int, hop: int = 2, vp: bool = True, exchange=None):
+        self.stage, self.rank, self.N, self.M, self.H, self.vp = stage, rank, world, n_micro, hop, vp
+        self.sig_head = world
+        self.sig_in = world + 1 if vp else world
+        self.P = max(n_micro, hop * self.sig_in)
+        self.ex = exchange if exchange is not None else DistExchange()
+        self.t = 0
+        self.pending = {}
+        # slot j is active for stage-0 ticks u = j (mod P) with begin[j] <= u < end[j]
+        self.begin = [None] * n_micro
+        self.end = [None] * n_micro
+
+    # -- slot windows -------------------------------------------------------------------------------------------
+    def next_u(self, slot: int, not_before: int = None) -> int:
+        """First stage-0 tick >= not_before (default: now) that belongs to `slot`."""
+        t0 = self.t if not_before is None else not_before
+        return t0 + (slot - t0) % self.P
+
+    def open_slot(self, slot: int, rounds: int = None) -> int:
+        """Slot's first round starts at its next stage-0 tick; `rounds` None = until close_slot().  Every rank
+        must make the same calls at the same tick.  Returns the tick of the slot's first stage-0 step."""
+        u0 = self.next_u(slot)
+        self.begin[slot] = u0
+        self.end[slot] = None if rounds is None else u0 + rounds * self.P
+        return u0
+
+    def close_slot(self, slot: int) -> int:
+        """No round of `slot` starts at or after now; rounds already under way finish.  Returns the tick by which
+        the slot's last token has been taken in by stage 0."""
+        if self.begin[slot] is None:
+            return self.t
+        self.end[slot] = max(self.begin[slot], self.next_u(slot))
+        return self.end[slot] - self.P + self.H * self.sig_in + 1
+
+    def _active(self, sigma: int, t: int):
+        u = t - self.H * sigma
+        if u < 0:
+            return None
+        j = u % self.P
+        if j >= self.M or self.begin[j] is None or u < self.begin[j] or (self.end[j] is not None and u >= self.end[j]):
+            return None
+        return j
+
+    def busy(self) -> bool:
+        """Is any piece of any open round still to run at or after the current tick?"""
+        for j in range(self.M):
+            if self.begin[j] is None:
+                continue
+            if self.end[j] is None:
+                return True
+            last_u = self.end[j] - self.P  # stage-0 tick of the slot's last round (< begin: no round at all)
+            if last_u >= self.begin[j] and last_u + self.H * self.sig_in >= self.t:
+                return True
+        return False
+
+    # -- one tick ------------------------------------------------------------------------------------------------
+    def tick(self) -> None:
+        t, st = self.t, self.stage
+        w = self.pending.pop(t - self.H, None)
+        if w is not None:
+            self.ex.wait(w)  # the exchange issued H ticks ago carries this tick's inputs
+        if st.is_first:
+            j = self._active(self.sig_in, t)
+            if j is not None:
+                st.ingest(j)
+        j = self._active(self.rank, t)
+        if j is not None:
+            st.compute(j)
+        if self.vp:
+            j = self._active(self.sig_head, t)
+            if j is not None:
+                st.head(j)
+        ph = t % self.P
+        self.pending[t] = self.ex.issue(st.mail_out(ph), st.mail_in(ph), phase=ph)
+        self.t += 1
+
+    def ticks(self, n: int) -> None:
+        for _ in range(n):
+            self.tick()
+
+    def flush(self) -> None:
+        """Wait for every exchange still in flight (before the host reads results, or before a barrier)."""
+        for t in sorted(self.pending):
+            w = self.pending.pop(t)
+            if w is not None:
+                self.ex.wait(w)
+
+    def run(self, n_rounds: int) -> None:
+        """n_rounds tokens for every slot, from a drained pipeline to a drained pipeline (fill and drain included)."""
+        for j in range(self.M):
+            self.open_slot(j, n_rounds)
+        while self.busy():
+            self.tick()
+        self.flush()
+
+
+class MailStage:
+    """A ShardEngine in mailbox mode as the runner's stage."""
+
+    def __init__(self, engine, b: int, n_micro: int, runner_period: int, hop: int, rank: int, world: int):
+        self.eng, self.b = engine, b
+        self.is_first = engine.is_first
+        engine.attach_mailbox(b, n_micro, runner_period, hop, rank, world)
+        for mb in range(n_micro):
+            engine._make_state(b, mb)
+
+    def mail_out(self, phase):
+        return self.eng._mail["out"][phase]
+
+    def mail_in(self, phase):
+        return self.eng._mail["in"][phase]
+
+    def compute(self, slot):
+        self.eng.mail_compute(slot)
+
+    def head(self, slot):
+        self.eng.mail_head(slot)
+
+    def ingest(self, slot):
+        self.eng.mail_ingest(slot)
+
+
+def mailbox_period(n_micro: int, world: int, hop: int, vp: bool) -> int:
+    return max(n_micro, hop * (world + 1 if vp else world))
+
+
 def chunk_plan(prompt_len: int, want_chunks: int):
     """(chunks, tokens per chunk, tokens in the last chunk) for a prompt fed in about `want_chunks` chunks:
     equal chunks of ceil(T / want) tokens, the last one takes the rest (never empty)."""

@@ -309,6 +309,11 @@ int dli_argmax_bf16(const void* logits, int ld, int32_t* out, int B, int V,
 int dli_argmax_candidate_bf16(const void* logits, int ld, int idx_offset, float* cand, int B,
                               int V, dli_stream_t stream);
 int dli_argmax_merge(const float* cands, int n, int B, int32_t* out, dli_stream_t stream);
+/* Same, for candidate sets that do not lie back to back: set s starts n_stride floats after set s-1
+ * (n_stride >= 2*B) — the per-stage candidates inside the pipeline's all-gathered mailboxes
+ * (pipeline.py), read where the exchange put them. */
+int dli_argmax_merge_strided(const float* cands, int n, int B, int n_stride, int32_t* out,
+                             dli_stream_t stream);
 
 /* lm_head with the greedy choice fused into the weight stream (final norm + lm_head +
  * argmax of TF:models/llama/modeling_llama.py:421,486-487 and TF:generation/utils.py:2762-2793

@@ -13,8 +13,9 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 from golden_util import load_case, spec_kwargs  # noqa: E402
 
 from dli_b200.engine import ModelSpec, ShardEngine  # noqa: E402
-from dli_b200.pipeline import (EngineStage, PipelineRunner, VocabParallelRunner, build_stage_engine,  # noqa: E402
-                               init_distributed, run_chunked_prefill)
+from dli_b200.pipeline import (DistExchange, EngineStage, MailboxRunner, MailStage, PipelineRunner,  # noqa: E402
+                               VocabParallelRunner, build_stage_engine, init_distributed, mailbox_period,
+                               run_chunked_prefill)
 from oracle import decoder_ref as R  # noqa: E402
 
 
@@ -39,7 +40,14 @@ def main():
     first = None
     if stage.is_last and not vp:
         first = torch.stack([eng._state(b, mb)["tokens"].clone() for mb in range(M)])  # [M, b]
-    runner.run("decode", rounds)
+    hop = int(os.environ.get("DLI_CHECK_MAIL", "0"))  # > 0: decode over per-tick mailboxes with this hop
+    if hop:
+        P = mailbox_period(M, world, hop, vp)
+        ms = MailStage(eng, b, M, P, hop, rank, world)
+        comm = torch.cuda.Stream() if hop > 1 else None  # hop 2: the all-gather runs under the next tick
+        MailboxRunner(ms, rank, world, M, hop=hop, vp=vp, exchange=DistExchange(comm_stream=comm)).run(rounds)
+    else:
+        runner.run("decode", rounds)
     torch.cuda.synchronize()
     ok = True
     holder = stage.is_first if vp else stage.is_last  # who ends up with the tokens

@@ -658,7 +658,7 @@ def test_batched_decode_uses_splitk_and_matches_small_batch(cuda):
                           (1, 32, 4, 64, 32, [300], 3, 0), (1, 64, 8, 128, 16, [1500], 8, 512)])
 def test_cluster_dsmem_merge_matches_scratch_merge(cuda, B, H, KV, hd, page, lens, splits, window):
     """scratch == NULL: the splits run as one thread-block cluster and merge through distributed
-    shared memory; same result as partials-in-HBM + merge kernel up to the order of one fp32 sum."""
+    shared memory; same result as partials-in-HBM + merge kernel within the attention tolerance."""
     from dli_b200 import ops
 
     gen = torch.Generator(device="cuda").manual_seed(31 + H)
@@ -674,7 +674,10 @@ def test_cluster_dsmem_merge_matches_scratch_merge(cuda, B, H, KV, hd, page, len
         ops.paged_attn_decode_fused(qkv.clone(), cos, sin, kc2, vc2, page_table, seq_lens, out, H, KV, hd, hd ** -0.5,
                                     num_splits=splits, scratch=sc, window=window)
         outs.append(out)
-    _ulp_close(outs[1], outs[0], max_ulp=1, min_exact=0.99)
+    # The scratch path now runs the many-warp kernel (16 tokens per warp instead of 64 per tile), so the two paths
+    # round their bf16 probabilities against different running maxima: equal within the attention tolerance (2e-2 on
+    # O(1) values, what test_paged_attn_decode allows against fp32), not to the ulp.
+    torch.testing.assert_close(outs[1].float(), outs[0].float(), rtol=2e-2, atol=2e-2)
     # too many splits for a cluster and no scratch: refused with a clear message
     from dli_b200 import _lib
     with pytest.raises(_lib.DliError, match="cluster merge"):

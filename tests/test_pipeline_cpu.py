@@ -403,3 +403,153 @@ def test_chunk_plan_covers_the_prompt_exactly():
     assert chunk_plan(8192, 8) == (8, 1024, 1024)
     assert chunk_plan(10, 3) == (3, 4, 2)
     assert chunk_plan(5, 1) == (1, 5, 5)
+
+
+# ------------------------------------------------------------------------------ mailbox pipeline (one all-gather per tick)
+class ToyMailStage:
+    """The toy model of ToyStage / ToyVPStage in mailbox form: mail = [hidden b*d | candidate b*2 | token b] floats."""
+
+    def __init__(self, rank, world, n_micro, b, d, P, H, vp):
+        self.rank, self.N, self.b, self.d, self.P, self.H, self.vp = rank, world, b, d, P, H, vp
+        self.is_first, self.is_last = rank == 0, rank == world - 1
+        L = b * d + 3 * b
+        self.out = torch.zeros(P, L)
+        self.inn = torch.zeros(P, world, L)
+        self.tokens = [torch.arange(b, dtype=torch.float32) + 10 * mb for mb in range(n_micro)]  # first inputs
+        self.steps = [0] * n_micro
+        self.final = [[] for _ in range(n_micro)]   # stage 0: tokens taken in
+        self.made = [[] for _ in range(n_micro)]    # last stage without vp: tokens produced
+
+    def mail_out(self, ph):
+        return self.out[ph]
+
+    def mail_in(self, ph):
+        return self.inn[ph]
+
+    def _h(self, mail):
+        return mail[: self.b * self.d].view(self.b, self.d)
+
+    def compute(self, mb):
+        ph = (mb + self.H * self.rank) % self.P
+        rd = (ph - self.H) % self.P
+        h = (self.tokens[mb][:, None].expand(self.b, self.d) if self.is_first else self._h(self.inn[rd][self.rank - 1])).clone()
+        h = h * 3 + (self.rank + 1) + self.steps[mb]
+        self.steps[mb] += 1
+        if self.is_last and not self.vp:
+            tok = (h.sum(dim=1).long() % 1000).float()
+            self.out[ph][self.b * self.d + 2 * self.b:] = tok
+            self.made[mb].append(tok.int().clone())
+        else:
+            self._h(self.out[ph]).copy_(h)
+
+    def head(self, mb):
+        ph = (mb + self.H * self.N) % self.P
+        hf = self._h(self.inn[(ph - self.H) % self.P][self.N - 1])
+        val, idx = ToyVPStage.propose(hf, self.rank)
+        c = self.out[ph][self.b * self.d: self.b * self.d + 2 * self.b].view(self.b, 2)
+        c[:, 0], c[:, 1] = val, idx
+
+    def ingest(self, mb):
+        sig = self.N + 1 if self.vp else self.N
+        rd = ((mb + self.H * sig) % self.P - self.H) % self.P
+        if self.vp:
+            c = self.inn[rd][:, self.b * self.d: self.b * self.d + 2 * self.b].reshape(self.N, self.b, 2)
+            key = c[:, :, 0] * 10000 - c[:, :, 1]
+            tok = c[key.argmax(dim=0), torch.arange(self.b), 1].clone()
+        else:
+            tok = self.inn[rd][self.N - 1][self.b * self.d + 2 * self.b:].clone()
+        self.tokens[mb] = tok
+        self.final[mb].append(tok.int().clone())
+
+
+def sequential_mail(world, mb, b, d, rounds, vp):
+    log, src = [], torch.arange(b, dtype=torch.float32) + 10 * mb
+    for step in range(rounds):
+        h = src[:, None].expand(b, d).clone()
+        for s in range(world):
+            h = h * 3 + (s + 1) + step
+        if vp:
+            vals, ids = zip(*(ToyVPStage.propose(h, s) for s in range(world)))
+            key = torch.stack(vals) * 10000 - torch.stack(ids)
+            tok = torch.stack(ids)[key.argmax(dim=0), torch.arange(b)]
+        else:
+            tok = (h.sum(dim=1).long() % 1000).float()
+        log.append(tok.int().tolist())
+        src = tok.float()
+    return log
+
+
+def _mail_worker(rank, world, port, n_micro, rounds, hop, vp, dynamic, q):
+    from dli_b200.pipeline import DistExchange, MailboxRunner, mailbox_period
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    P = mailbox_period(n_micro, world, hop, vp)
+    stage = ToyMailStage(rank, world, n_micro, 2, 4, P, hop, vp)
+    runner = MailboxRunner(stage, rank, world, n_micro, hop=hop, vp=vp, exchange=DistExchange())
+    assert runner.P == P
+    if not dynamic:
+        runner.run(rounds)
+        runner.run(1)  # a second run continues every slot's generation from the drained pipeline
+        want_rounds = [rounds + 1] * n_micro
+    else:
+        # slots join at different ticks and one leaves early, as requests do in the serving loop
+        runner.open_slot(0)
+        runner.ticks(3)
+        for j in range(1, n_micro):
+            runner.open_slot(j)
+        runner.ticks(2 * P + 1)
+        runner.close_slot(0)
+        runner.ticks(2 * P)
+        for j in range(1, n_micro):
+            runner.close_slot(j)
+        while runner.busy():
+            runner.tick()
+        runner.flush()
+        # rounds every slot was open for: its stage-0 ticks inside [begin, end)
+        want_rounds = [(runner.end[j] - runner.begin[j] + P - 1) // P for j in range(n_micro)]
+    if rank == 0:
+        q.put(([torch.stack(l).tolist() if l else [] for l in stage.final], want_rounds))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_micro,rounds,hop,vp,dynamic", [
+    (2, 3, 3, 1, True, False), (2, 6, 3, 2, True, False), (3, 2, 2, 2, True, False), (3, 8, 2, 2, True, False),
+    (2, 2, 3, 1, False, False), (3, 6, 2, 2, False, False), (2, 1, 4, 2, False, False),
+    (2, 6, 0, 2, True, True), (3, 4, 0, 2, False, True), (2, 3, 0, 1, True, True),
+])
+def test_mailbox_pipeline_matches_sequential_over_gloo(world, n_micro, rounds, hop, vp, dynamic):
+    """One all-gather of fixed-size mails per tick replaces every pairwise send: tokens equal the sequential toy model
+    for hop 1 (serialised) and hop 2 (exchange under the next tick), with the head split over the stages (vp) or on the
+    last stage, for fixed runs and for slots that join and leave between ticks."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_mail_worker, args=(r, world, port, n_micro, rounds, hop, vp, dynamic, q))
+             for r in range(world)]
+    [p.start() for p in procs]
+    got, want_rounds = q.get(timeout=120)
+    [p.join(timeout=60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    for mb in range(n_micro):
+        n = want_rounds[mb] if want_rounds else len(got[mb])
+        assert n > 0 and len(got[mb]) == n
+        assert got[mb] == sequential_mail(world, mb, 2, 4, n, vp), (mb, got[mb])
+    if dynamic:
+        assert len(set(want_rounds)) > 1 or n_micro <= 3  # the scenario really has slots of different lifetimes
+
+
+def test_mailbox_schedule_every_piece_reads_what_was_delivered():
+    """Pure schedule check: with P = max(M, H*(N+1)) the mail a piece reads at tick t (phase (t-H) mod P) is never
+    overwritten between its delivery and its use, for every stage offset."""
+    from dli_b200.pipeline import mailbox_period
+
+    for N in (1, 2, 4, 8):
+        for H in (1, 2):
+            for vp in (True, False):
+                for M in (1, N, 2 * N + 2, 20):
+                    P = mailbox_period(M, N, H, vp)
+                    assert P >= M and P >= H * (N + 1 if vp else N) and P > H or N == 1
+                    # tick t writes phase t % P; the next write of that phase is tick t + P > t + H (its reader)
+                    assert P > H or (N == 1 and not vp and M == 1)

@@ -24,6 +24,19 @@ def test_nccl_pipeline_equals_single_engine(cuda, world, vp):
     assert p.returncode == 0 and "PIPELINE_OK" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
 
 
+@pytest.mark.parametrize("world,vp,hop", [(2, 1, 2), (2, 1, 1), (2, 0, 2), (4, 1, 2), (4, 0, 1)])
+def test_nccl_mailbox_pipeline_equals_single_engine(cuda, world, vp, hop):
+    """Decode over per-tick mailboxes (one NCCL all-gather per tick; hop 2 = on its own stream under the next tick's
+    kernels): tokens equal the single engine's."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs, have {torch.cuda.device_count()}")
+    env = dict(os.environ, DLI_PIPE_VP=str(vp), DLI_CHECK_MAIL=str(hop))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29620 + world + 10 * vp + hop), os.path.join(ROOT, "tests", "pipeline_check.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert p.returncode == 0 and "PIPELINE_OK" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
+
+
 @pytest.mark.parametrize("world,vp,chunks", [(2, 0, 3), (2, 1, 4), (4, 1, 3)])
 def test_nccl_pipeline_with_chunked_prefill(cuda, world, vp, chunks):
     """Prompts fed in chunks, the stages working on different chunks at once: tokens equal the
