@@ -10,9 +10,14 @@ N = 1 : config[2] of BASELINE.json — Llama-3-8B shape, bf16, random-init weigh
         batch 1, 2k-token context, paged KV (the north-star target).  Also reports
         the 2k-token prefill and (extra) batch-32 decode.
 N > 1 : the same model split into N contiguous layer ranges (reference sharder
-        formula), one stage per GPU, hidden states handed over with NCCL
-        send/recv, N micro-batches of `batch` sequences in flight (weak scaling:
-        per-GPU batch fixed, per-GPU weights shrink).
+        formula), one stage per GPU; decode hands hidden states, head candidates and
+        tokens over in per-tick mailboxes (one NCCL all-gather per tick, issued on its
+        own stream under the next tick's kernels), 2(N+1) micro-batch slots of `batch`
+        sequences in flight so that every stage works every tick (weak scaling: per-GPU
+        batch fixed, per-GPU weights shrink).  Before timing, rank 0 checks the
+        pipeline's first tokens against the single-GPU engine on the same weights and
+        the run aborts on a mismatch (extra.parity_check); extra.named_config runs the
+        BASELINE.json configuration that is stated for exactly N GPUs.
 
 value  : decode tokens/s with everything resident in HBM (CUDA-graph replay).
 e2e    : the same metric through the plugin call the reference's master makes
@@ -410,7 +415,13 @@ def main():
     if world > 1 or args.gpus > 1:
         from dli_b200.pipeline import run_pipeline_bench
 
-        res = run_pipeline_bench(args, spec, peaks)
+        import torch.distributed as dist
+
+        try:
+            res = run_pipeline_bench(args, spec, peaks)
+        finally:
+            if dist.is_initialized():
+                dist.destroy_process_group()
         if rank != 0:
             return
     else:

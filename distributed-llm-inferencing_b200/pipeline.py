@@ -485,109 +485,246 @@ def build_stage_engine(spec, rank: int, world: int, local: int, max_batch: int, 
                        page_size=page_size, head_shard=(rank, world) if vocab_parallel else None)
 
 
-def run_pipeline_bench(args, spec, peaks):
-    """bench.py's N > 1 arm (launched by torchrun, one rank per GPU)."""
+def _timed(fn):
+    """Device time of fn() in ms, max over ranks, bracketed by barriers and synchronisation on both sides."""
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.barrier()
+    return t.item()
+
+
+def measure_pipeline(spec, model_name, rank, world, local, b, n_slots, ctx, K, W, page_size, peaks, vp=True, hop=2,
+                     prompt_seed=1, parity_tokens=0, timed_prefill=True):
+    """One pipeline configuration: `world` stages (reference sharder ranges), n_slots micro-batch slots of b
+    sequences, every sequence with `ctx` tokens of context in the middle of the timed region.  Prefill over
+    send/recv (chunked for long prompts on many stages), decode over per-tick mailboxes (MailboxRunner, `hop`).
+    K whole periods of the FULL pipeline are timed (no fill or drain inside the timed region).
+    parity_tokens > 0: rank 0 also runs the single full-range engine on every slot's prompt, teacher-forced along
+    the pipeline's first tokens, and raises unless the pipeline picked the single engine's token at every step
+    (or one whose logit ties with it to the last bf16 bit)."""
     from . import ops
+    from .measure import ClockSampler, decode_step_bytes
 
-    rank, world, local = init_distributed()
-    b, ctx, K, W = args.batch, args.ctx, args.steps, max(args.warmup, 3)
-    vp = os.environ.get("DLI_PIPE_VP", "1") == "1"  # lm_head split by vocabulary rows over the stages
-    M = world + 1 if vp else world  # slots in flight: every stage busy every tick
-    max_len = ctx + 2 * (K + W) + 16
-    eng = build_stage_engine(spec, rank, world, local, M * b, max_len, args.page_size, vocab_parallel=vp)
+    M, N = n_slots, world
+    P = mailbox_period(M, N, hop, vp)
+    warm_rounds = max(W, 3, parity_tokens)
+    prompt_len = max(8, ctx - warm_rounds - K // 2)  # so that the context is `ctx` in the middle of the timed region
+    max_len = prompt_len + warm_rounds + 2 * K + 16  # warm-up, the timed rounds, the host-streamed rounds, drain
+    eng = build_stage_engine(spec, rank, world, local, M * b, max_len, page_size, vocab_parallel=vp)
     eng.load_random(seed=0)
-    # chunked prefill (DLI_PREFILL_CHUNKS=C): stages work on different chunks of a prompt at once.  It is for
-    # long prompts on many stages (70B, 8 stages, 8k tokens, 8 chunks: 8.8 -> 7.0 s for 36 prompts); at 2k-token
-    # prompts the smaller GEMMs and the mma.sync paged attention cost more than the pipelining returns
-    # (8B, 2 stages: 50 -> 74 ms), so the default only turns it on for >= 4 stages and >= 4k tokens.
-    chunks = int(os.environ.get("DLI_PREFILL_CHUNKS", "8" if (world >= 4 and ctx >= 4096) else "1"))
-    stage = EngineStage(eng, b, ctx, max_len, M, prefill_chunks=chunks)
+    # chunked prefill: stages work on different chunks of a prompt at once.  It pays for long prompts on many stages
+    # (70B, 8 stages, 8k tokens, 8 chunks: 8.8 -> 5.5 s for 36 prompts), not at 2k tokens on 2 stages.
+    chunks = int(os.environ.get("DLI_PREFILL_CHUNKS", "8" if (world >= 4 and prompt_len >= 4000) else "1"))
+    stage = EngineStage(eng, b, prompt_len, max_len, M, prefill_chunks=chunks)
+    g = torch.Generator().manual_seed(prompt_seed)
+    prompts = [torch.randint(0, spec.vocab, (b * prompt_len,), generator=g, dtype=torch.int32) for _ in range(M)]
     if stage.is_first:
-        g = torch.Generator().manual_seed(1)
         for mb in range(M):
-            stage.prompt_ids[mb] = torch.randint(0, spec.vocab, (b * ctx,), generator=g, dtype=torch.int32).cuda()
-    runner = (VocabParallelRunner if vp else PipelineRunner)(stage, rank, world, M)
-
-    def timed(fn):
-        torch.cuda.synchronize()
-        dist.barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        fn()
-        e1.record()
-        torch.cuda.synchronize()
-        t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.barrier()
-        return t.item()
+            stage.prompt_ids[mb] = prompts[mb].cuda()
+    pf_runner = (VocabParallelRunner if vp else PipelineRunner)(stage, rank, world, M)
 
     def prefill_all():
         run_chunked_prefill(stage, rank, world, M, stage.chunks)  # chunks 0..C-2 of every slot (nothing if C == 1)
-        runner.run("prefill")  # last chunk + head + first token
+        pf_runner.run("prefill")  # last chunk + head + first token (lands in stage 0's per-slot token buffer)
 
-    prefill_all()  # warm-up: lazy module loads, function attributes, NCCL connections
-    for mb in range(M):
-        eng.start_batch(b, ctx, max_len, mb=mb)
-    pf_ms = timed(prefill_all)
-    runner.run("decode", W)  # warm-up rounds (captures the per-slot CUDA graphs)
+    if timed_prefill:
+        prefill_all()  # warm-up: lazy module loads, function attributes, NCCL connections
+        for mb in range(M):
+            eng.start_batch(b, prompt_len, max_len, mb=mb)
+        pf_ms = _timed(prefill_all)
+    else:
+        pf_ms = _timed(prefill_all)  # a single pass (first-call costs included); used for the large named shapes
+    firsts = None
+    if not vp and eng.is_last:
+        firsts = torch.stack([eng._state(b, mb)["tokens"].clone() for mb in range(M)])  # [M, b]
+
+    ms_stage = MailStage(eng, b, M, P, hop, rank, world)
+    comm = torch.cuda.Stream() if hop > 1 else None
+    runner = MailboxRunner(ms_stage, rank, world, M, hop=hop, vp=vp, exchange=DistExchange(comm_stream=comm))
+    for j in range(M):
+        runner.open_slot(j)
+    fill = hop * (N + 1 if vp else N)
+    runner.ticks(warm_rounds * P + fill)  # fills the pipeline, captures every slot's graphs, warm-up rounds
+    runner.flush()
+
+    parity = None
+    if parity_tokens:
+        parity = _parity_against_single_engine(spec, eng, rank, world, local, b, M, prompt_len, prompts, firsts, vp,
+                                               parity_tokens, page_size)
     n0 = ops.launch_count
-    from .measure import ClockSampler, decode_step_bytes
-
     with ClockSampler(index=local) as clk:
-        ms = timed(lambda: runner.run("decode", K))
+        ms = _timed(lambda: (runner.ticks(K * P), runner.flush()))
     launches = torch.tensor([ops.launch_count - n0], device="cuda")
     dist.all_reduce(launches)
 
-    # e2e: one round at a time; the pipeline head (rank 0, the stage the master addresses)
-    # copies each round's tokens to pinned host memory and synchronises, as a streaming
-    # client needs.  Inputs of a round are the previous round's tokens, which arrive over
-    # NVLink from the last stage, so there is no host->device copy in steady state.
+    # host-facing rounds: rank 0 (the stage the master addresses) copies every round's tokens of every slot to pinned
+    # host memory and synchronises once per round, as a client streaming the tokens needs
     host_tok = torch.zeros(M, b, dtype=torch.int32).pin_memory()
 
-    def stream_to_host(r, mb, toks):
-        # what a streaming client needs: the slot's new tokens in pinned host memory; rank 0 blocks
-        # once per round until the round's copies have landed
-        host_tok[mb].copy_(toks, non_blocking=True)
-        if mb == M - 1:
-            torch.cuda.current_stream().synchronize()
-
     def host_rounds():
-        if vp:
-            runner.run("decode", K, on_tokens=stream_to_host)
-            return
         for _ in range(K):
-            runner.run("decode", 2)  # 2 rounds: the first round's tokens return to stage 0
-            if rank == 0:
+            runner.ticks(P)
+            if rank == 0 and vp:
                 for mb in range(M):
                     host_tok[mb].copy_(eng._state(b, mb)["tokens"], non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+                torch.cuda.current_stream().synchronize()
+        runner.flush()
 
-    e2e_ms = timed(host_rounds) / (1 if vp else 2)  # per round
-    n_local = eng.n_local
-    S_mid = ctx + W + K // 2
-    stage_bytes = decode_step_bytes(spec, n_local, eng.is_last and not vp, b, S_mid)
+    stream_ms = _timed(host_rounds)
+    for j in range(M):
+        runner.close_slot(j)
+    while runner.busy():
+        runner.tick()
+    runner.flush()
+    torch.cuda.synchronize()
+
+    S_mid = prompt_len + warm_rounds + K // 2
+    stage_bytes = decode_step_bytes(spec, eng.n_local, eng.is_last and not vp, b, S_mid)
     if vp:
         stage_bytes += (eng.v1 - eng.v0) * spec.d_model * 2  # this stage's rows of the head
-    # a stage pass (one tick) is the roofline unit: bytes of one pass / tick time
-    P = max(M, world + 1) if vp else max(M, world)
-    tick_ms = ms / ((K - 1) * P + M + world + (1 if vp else -1))
+    tick_ms = ms / (K * P)
+    busy = min(M, P) / P  # share of ticks in which a stage has a slot to work on
     ach = torch.tensor([stage_bytes / (tick_ms / 1e3) / 1e9], device="cuda")
     dist.all_reduce(ach, op=dist.ReduceOp.MIN)
-    value = M * b * K / (ms / 1e3)
+    # what a pure layer pipeline can reach at this batch: every stage re-reads its weights once per slot (SURVEY 8d)
+    ceiling = M * b / (P * (stage_bytes / (peaks["hbm_gbs"] * 1e9)))
+    res = {"value": M * b * K / (ms / 1e3), "ms_per_step": ms / K, "gpu_launches": int(launches.item()),
+           "clocks": clk.summary(), "tick_ms": tick_ms, "prefill_ms": pf_ms,
+           "prefill_tokens_per_s": M * b * prompt_len / (pf_ms / 1e3), "prefill_chunks": stage.chunks,
+           "stream_tokens_per_s": M * b * K / (stream_ms / 1e3), "stage_bytes": stage_bytes,
+           "stage_pass_gbs": ach.item(), "stage_pass_frac": ach.item() / peaks["hbm_gbs"], "busy_ticks": busy,
+           "pp_ceiling_tokens_per_s": ceiling, "slots": M, "b": b, "period": P, "hop": hop, "vp": vp,
+           "prompt_len": prompt_len, "ctx_mid": S_mid, "parity_check": parity,
+           "workload": f"{model_name} bf16 random-init, {world} pipeline stages (contiguous layer ranges, reference "
+                       f"sharder formula) on {world} GPUs, {M} micro-batch slots x {b} sequences greedy decode at "
+                       f"{S_mid}-token context, mailbox hand-off (one NCCL all-gather per tick, hop {hop})"}
+    eng.unload()
+    del eng, stage, ms_stage, runner
+    torch.cuda.empty_cache()
+    return res
+
+
+def _parity_against_single_engine(spec, eng, rank, world, local, b, M, prompt_len, prompts, firsts, vp, n_tok, page_size):
+    """Gather the pipeline's first n_tok tokens of every slot on rank 0 and check them against the single
+    full-range engine holding the same (per-layer seeded) weights.  Returns "ok" / "ok (k ties)" / a skip reason;
+    raises RuntimeError on a real mismatch (every rank raises, so torchrun exits non-zero)."""
+    from .engine import ShardEngine
+
+    dev = torch.device(f"cuda:{local}")
+    holder = 0 if vp else world - 1
+    toks = torch.zeros(M, n_tok, b, dtype=torch.int32, device=dev)
+    if rank == holder:
+        for mb in range(M):
+            st = eng._state(b, mb)
+            if vp:   # stage 0 logs the token it consumes at each step: log[0] is the prefill's token
+                toks[mb] = st["token_log"][:n_tok]
+            else:    # the last stage logs what it produces: the prefill's token, then log[0..]
+                toks[mb, 0] = firsts[mb]
+                toks[mb, 1:] = st["token_log"][:n_tok - 1]
+    dist.broadcast(toks, src=holder)
+    verdict = torch.zeros(2, dtype=torch.int32, device=dev)  # (status: 0 ok, 1 mismatch, 2 skipped; ties)
+    total_w = spec.n_layers * spec.layer_weight_bytes() + 2 * spec.head_weight_bytes()
+    if rank == 0:
+        free = torch.cuda.mem_get_info()[0]
+        if free < total_w + (12 << 30):
+            verdict[0] = 2
+        else:
+            full = ShardEngine(spec, device=str(dev), max_batch=b, max_seq_len=prompt_len + n_tok + 8, page_size=page_size)
+            full.load_random(seed=0)
+            ties = 0
+            for mb in range(M):
+                pipe = toks[mb].t().contiguous()  # [b, n_tok]
+                ids = prompts[mb].view(b, prompt_len).long()
+                out, logits = full.generate(ids, prompt_len + n_tok, return_logits=True, forced=pipe[:, :-1])
+                own = out[:, prompt_len:]
+                for i in range(n_tok):
+                    for r in range(b):
+                        if int(own[r, i]) == int(pipe[r, i]):
+                            continue
+                        row = logits[i][r]
+                        if float(row[int(pipe[r, i])]) >= float(row.max()) - 2.0 ** -7 * max(1.0, abs(float(row.max()))):
+                            ties += 1  # the two tokens' logits tie to the last bf16 bit: either is a greedy choice
+                        else:
+                            verdict[0] = 1
+            verdict[1] = ties
+            full.unload()
+            del full
+            torch.cuda.empty_cache()
+    dist.broadcast(verdict, src=0)
+    status, ties = int(verdict[0]), int(verdict[1])
+    if status == 1:
+        raise RuntimeError("pipeline tokens differ from the single-GPU engine's on the same weights and prompts")
+    if status == 2:
+        return "skipped: the full model does not fit beside this stage on one GPU"
+    return "ok" if ties == 0 else f"ok ({ties} bf16-level ties)"
+
+
+# BASELINE.json configs run on exactly N GPUs: (model, total batch, context, note)
+NAMED_CONFIGS = {
+    2: ("tinyllama-1.1b", 1, 1024, "configs[1]: TinyLlama-1.1B, 2 layer-range shards, batch 1 greedy decode"),
+    4: ("mistral-7b", 64, 4096, "configs[3]: Mistral-7B, 4 shards, micro-batched decode, batch 64, 4k context"),
+    8: ("llama-3-70b", 32, 8192, "configs[4]: Llama-3-70B, 8 shards, batch 32 decode at 8k context"),
+}
+
+
+def run_pipeline_bench(args, spec, peaks):
+    """bench.py's N > 1 arm (launched by torchrun, one rank per GPU)."""
+    rank, world, local = init_distributed()
+    b, ctx, K, W = args.batch, args.ctx, args.steps, max(args.warmup, 3)
+    vp = os.environ.get("DLI_PIPE_VP", "1") == "1"  # lm_head split by vocabulary rows over the stages
+    hop = int(os.environ.get("DLI_PIPE_HOP", "2"))  # 2: the exchange runs under the next tick's kernels
+    M = mailbox_period(1, world, hop, vp)           # slots in flight: every stage busy every tick
+    main = measure_pipeline(spec, args.model, rank, world, local, b, M, ctx, K, W, args.page_size, peaks, vp=vp,
+                            hop=hop, parity_tokens=8)
+    named = None
+    if world in NAMED_CONFIGS and not args.no_extra:
+        from .engine import NAMED_SPECS
+
+        name, B, nctx, note = NAMED_CONFIGS[world]
+        try:
+            # the stated batch split into one slot per stage (slots of B/N sequences; a single slot at batch 1);
+            # hop 1: with no more slots than stages there is nothing to overlap the exchange with
+            slots = min(world, B)
+            r = measure_pipeline(NAMED_SPECS[name], name, rank, world, local, B // slots, slots, nctx, min(K, 16), 3,
+                                 args.page_size, peaks, vp=(B > 1), hop=1, prompt_seed=3,
+                                 parity_tokens=4 if name != "llama-3-70b" else 0, timed_prefill=False)
+            named = {"config": note, "decode_tokens_per_s": r["value"], "batch": B, "ctx": r["ctx_mid"],
+                     "micro_batches": r["slots"], "sequences_per_micro_batch": r["b"], "tick_ms": r["tick_ms"],
+                     "stage_pass_frac": r["stage_pass_frac"], "busy_ticks": r["busy_ticks"],
+                     "pp_only_ceiling_tokens_per_s": r["pp_ceiling_tokens_per_s"],
+                     "prefill_tokens_per_s": r["prefill_tokens_per_s"], "prefill_chunks": r["prefill_chunks"],
+                     "parity_check": r["parity_check"], "clocks": r["clocks"], "workload": r["workload"],
+                     "note": "a pure layer pipeline re-reads every stage's weights once per micro-batch, so its ceiling is "
+                             "batch / (period x stage-pass time at the HBM peak), not the once-per-step figure of BASELINE.md 4"}
+        except RuntimeError as e:
+            if "pipeline tokens differ" in str(e):
+                raise
+            named = {"config": note, "error": str(e)[:300]}
     roof = {"bound": "hbm", "kernel": "stage pass (all kernels of one micro-batch on one stage)",
-            "achieved": ach.item(), "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach.item() / peaks["hbm_gbs"],
-            "traffic": None, "bytes_per_launch": stage_bytes, "micro_batches": M,
+            "achieved": main["stage_pass_gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": main["stage_pass_frac"],
+            "traffic": None, "bytes_per_launch": main["stage_bytes"], "micro_batches": main["slots"],
             "note": "min over stages; every stage re-reads its weights once per micro-batch (SURVEY 8d)"}
-    return {"value": value, "ms_per_step": ms / K, "gpu_launches": int(launches.item()), "clocks": clk.summary(),
-            "e2e": {"value": M * b * K / (e2e_ms / 1e3), "unit": "tokens/s", "h2d_bytes_per_step": 0,
-                    "d2h_bytes_per_step": 4 * M * b, "ms_per_step": e2e_ms / K},
+    Mb = main["slots"] * main["b"]
+    return {"value": main["value"], "ms_per_step": main["ms_per_step"], "gpu_launches": main["gpu_launches"],
+            "clocks": main["clocks"],
+            "e2e": {"value": main["stream_tokens_per_s"], "unit": "tokens/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 4 * Mb, "ms_per_step": Mb * 1e3 / main["stream_tokens_per_s"],
+                    "api": "MailboxRunner.ticks + per-round copy of the new tokens to pinned host memory on rank 0"},
             "roofline": roof,
-            "extra": {"prefill_tokens_per_s": M * b * ctx / (pf_ms / 1e3), "prefill_ms": pf_ms,
-                      "prefill_chunks": stage.chunks, "tick_ms": tick_ms,
-                      "peaks": peaks["source"]},
-            "config": {"workload": f"{args.model} bf16 random-init, {world} pipeline stages (contiguous layer ranges, "
-                                   f"reference sharder formula) on {world} GPUs, {M} micro-batches x batch {b} greedy "
-                                   f"decode at {ctx}-token context, NCCL send/recv hand-off",
-                       "batch": M * b, "micro_batches": M, "ctx": ctx, "page_size": args.page_size,
-                       "parallelism": f"pp{world}" + ("+vocab-parallel head" if vp else ""), "l2": "inputs larger than L2: each stage pass streams its weight "
-                                                          f"slice ({stage_bytes / 1e9:.2f} GB) from HBM"}}
+            "extra": {"prefill_tokens_per_s": main["prefill_tokens_per_s"], "prefill_ms": main["prefill_ms"],
+                      "prefill_chunks": main["prefill_chunks"], "tick_ms": main["tick_ms"], "period_ticks": main["period"],
+                      "hop": hop, "parity_check": main["parity_check"], "peaks": peaks["source"],
+                      "pp_only_ceiling_tokens_per_s": main["pp_ceiling_tokens_per_s"], "named_config": named,
+                      "env": {k: v for k, v in os.environ.items() if k.startswith("DLI_")}},
+            "config": {"workload": main["workload"], "batch": Mb, "micro_batches": main["slots"], "ctx": main["ctx_mid"],
+                       "page_size": args.page_size,
+                       "parallelism": f"pp{world}" + ("+vocab-parallel head" if vp else ""),
+                       "l2": "inputs larger than L2: each stage pass streams its weight slice "
+                             f"({main['stage_bytes'] / 1e9:.2f} GB) from HBM"}}
