@@ -581,8 +581,10 @@ class ShardEngine:
                 "h": torch.empty(B, self.spec.d_model, dtype=BF, device=dev),
                 "logits": torch.empty(B, self.spec.vocab, dtype=BF, device=dev) if self.has_head else None,
                 # persistent: its address is baked into the captured decode graph
+                # the stage that chooses the tokens logs them; stage 0 logs the tokens it consumes (a pipeline head
+                # answers the requests, and with a vocabulary-parallel head only it ever sees the final choice)
                 "token_log": torch.zeros(self.max_seq_len, B, dtype=torch.int32, device=dev)
-                if (self.has_head or (self.head_shard is not None and self.is_first)) else None,
+                if (self.has_head or self.is_first) else None,
             }
             if self.head_shard is not None:
                 st, w = self._dec[(B, mb)], self.head_shard[1]
@@ -839,7 +841,7 @@ class ShardEngine:
             if self.has_head:
                 tokens = m["out_tok"][ph]
                 self._head(h, st["logits"], tokens, st)
-            log = st["token_log"] if (self.has_head or (m["vp"] and self.is_first)) else None
+            log = st["token_log"] if (self.has_head or self.is_first) else None
             ops.decode_advance(tokens, log, st["positions"], st["seq_lens"], st["step"])
 
         self._graphed((B, mb, "mail_compute"), body, restore=[st[k] for k in ("positions", "seq_lens", "step")])

@@ -1,199 +1,369 @@
-"""N reference-style workers on the N GPUs of one box, their shards joined by an NCCL pipeline.
+"""N reference-style workers on the N GPUs of one box, their shards joined by an NCCL pipeline that serves
+CONCURRENT requests.
 
-The reference deploys one worker per node, registers shard i on node i (`/load_shard`,
-worker/app.py:139-206; one node per (model, shard): master/dashboard/models.py:27-28) and sends
-`/inference` with the shard list to the first node (master/dashboard/views.py:318-355) — whose
-worker then runs only its own shard (worker/app.py:336).  Here
+The reference deploys one worker per node, registers shard i on node i (`/load_shard`, worker/app.py:139-206; one
+node per (model, shard): master/dashboard/models.py:27-28) and sends `/inference` with the shards of the first node
+that has any (master/dashboard/views.py:318-355) — whose worker then runs only its own shard (worker/app.py:336,
+SURVEY.md A.3 Q2), one request at a time (one sync gunicorn worker, worker/Dockerfile:45).  Here
 
     python -m torch.distributed.run --nproc-per-node N -m dli_b200.pipeline_worker --port 5000
 
-starts N workers in one process group: rank r is "node r" (HTTP on port+r, GPU r) with the same
-routes as a single worker.  `/load_shard` registers shard r on rank r exactly as before.  When rank
-0 receives an `/inference` whose `shard_ids` name shards that live on the other ranks, it tells
-them over a control group (gloo) and all ranks run the layer-range pipeline of pipeline.py: hidden
-states travel GPU to GPU by NCCL send/recv, the last stage chooses the tokens (greedy or the
-reference's sampling call) and they come back to rank 0, which answers the request.  Shard i must
-be registered on rank i (shard i <-> GPU i).
+starts N workers in one process group: rank r is "node r" (HTTP on port+r, GPU r) with the same routes as a single
+worker.  `/load_shard` registers shard r on rank r exactly as before.  An `/inference` that names shards of a model
+split over the group (`metadata.json: num_shards == N`; the listed ids may be only the receiving node's, which is
+what the reference master sends) is served by ALL ranks: a request arriving on another rank is handed to rank 0.
 
-The generation runs in blocks of a few decode rounds; between blocks the LAST stage (it sees the
-tokens) decides whether every sequence has hit an EOS id or the deadline has passed and broadcasts
-that one flag, so all ranks leave the loop together.
+Serving loop (PipelineServer, one thread per rank, in lockstep):
+  * the decode pipeline of pipeline.MailboxRunner runs continuously with P = hop * N slots of one sequence each, the
+    whole head on the last stage (greedy or the reference's sampling call, per request, seeded);
+  * every `block` rounds rank 0 reads the new tokens, completes the requests that reached `max_length`, an EOS id or
+    their deadline, and broadcasts ONE plan over the control group (gloo): slots to close, slots to free, requests
+    to admit.  Every rank applies the plan: a joining request is prefilled through the stages (hidden states by
+    NCCL send/recv) into a free slot while the decode pipeline pauses between two ticks, then joins the ticks.
+So a token of ONE request still costs a trip through the N stages, but up to hop * N requests share those trips —
+what the reference's serialisation and the round-1 group (one request, one slot) could not do.
 """
 from __future__ import annotations
 
+import queue
 import sys
+import threading
 import time
-from typing import Callable, Dict, List, Optional
+from concurrent.futures import Future
+from typing import Dict, List, Optional
 
 import torch
 import torch.distributed as dist
 
-BLOCK = 8  # decode rounds between two stop checks
+BLOCK = 4        # decode rounds between two plans
+IDLE_BEAT = 20.0  # seconds between heartbeats of an idle group (keeps the control collective from timing out)
 
 
-class PipelineGroup:
-    """Control plane of the worker group.  `stage_factory(cmd)` returns the object that runs this
-    rank's part of a request (see CudaStageRun below; the CPU tests plug in a toy)."""
+# ------------------------------------------------------------------------------ what a rank's GPU side must offer
+class StageBackend:
+    """The data plane of one rank as the serving loop sees it (CUDA: CudaBackend; the CPU tests plug in a toy)."""
 
-    def __init__(self, rank: int, world: int, ctrl_group, stage_factory: Callable[[dict], "StageRun"]):
-        self.rank, self.world, self.ctrl, self.factory = rank, world, ctrl_group, stage_factory
+    n_slots: int
 
-    # ------------------------------------------------------------------ rank 0: called by the HTTP handler
-    def generate(self, cmd: dict) -> List[int]:
-        """Broadcast the request and take part in it; returns the new tokens (rank 0 only)."""
+    def prepare(self, model: str) -> None: ...              # make `model`'s stage resident (raise ValueError if it cannot be)
+    def check_request(self, req: dict) -> None: ...          # raise ValueError if this rank cannot serve the request
+    def join(self, slot: int, req: dict) -> None: ...        # prefill the request into `slot` (all ranks, collectively)
+    def runner(self): ...                                    # the MailboxRunner of the resident model
+    def read_tokens(self, slot: int, n: int) -> List[int]: ...  # rank 0: the first n tokens the slot has produced
+    def release(self, slot: int) -> None: ...                # the slot's KV pages
+    def reset(self) -> None: ...                             # forget the resident model (all ranks together)
+
+
+class _Req:
+    def __init__(self, cmd: dict):
+        self.cmd = cmd
+        self.future: Future = Future()
+        self.slot: Optional[int] = None
+        self.start_round = 0
+
+
+class PipelineServer:
+    """Control plane.  Rank 0: submit() from any thread; every rank: serve_forever() in one thread."""
+
+    def __init__(self, rank: int, world: int, ctrl_group, backend: StageBackend, block: int = BLOCK):
+        self.rank, self.world, self.ctrl, self.be, self.block = rank, world, ctrl_group, backend, block
+        self.queue: "queue.Queue[_Req]" = queue.Queue()
+        self.model: Optional[str] = None
+        self.active: Dict[int, _Req] = {}    # slot -> request (rank 0)
+        self.closing: List[int] = []         # slots closed by the last plan: freed by the next one
+        self.draining: List[int] = []
+        self.rounds_done: Dict[int, int] = {}
+        self._stop = threading.Event()
+        self.stats = {"blocks": 0, "joined": 0, "max_active": 0}
+
+    # ------------------------------------------------------------------ rank 0, any thread
+    def submit(self, cmd: dict) -> Future:
+        """cmd: {model, ids, max_length, deadline, gen}.  The future yields the list of NEW token ids."""
         assert self.rank == 0
-        dist.broadcast_object_list([dict(cmd, op="generate")], src=0, group=self.ctrl)
-        return self._run(cmd)
+        r = _Req(cmd)
+        self.queue.put(r)
+        return r.future
 
     def shutdown(self) -> None:
-        assert self.rank == 0
-        dist.broadcast_object_list([{"op": "stop"}], src=0, group=self.ctrl)
+        self._stop.set()
+        self.queue.put(None)
 
-    # ------------------------------------------------------------------ ranks > 0: main loop
-    def serve_forever(self) -> None:
+    # ------------------------------------------------------------------ rank 0, loop thread: the next plan
+    def _plan(self) -> dict:
+        """Blocks while there is nothing to do (heartbeats keep the other ranks' collective alive)."""
+        last_beat = time.time()
         while True:
-            box = [None]
-            dist.broadcast_object_list(box, src=0, group=self.ctrl)
-            cmd = box[0]
-            if cmd.get("op") == "stop":
-                return
+            if self._stop.is_set():
+                return {"op": "stop"}
+            joins, pend = [], []
+            free = [s for s in range(self.be.n_slots) if s not in self.active and s not in self.closing
+                    and s not in self.draining]
+            while True:
+                try:
+                    r = self.queue.get_nowait()
+                except queue.Empty:
+                    break
+                if r is None:
+                    continue
+                pend.append(r)
+            keep = []
+            for r in pend:
+                model = r.cmd["model"]
+                if self.model is not None and model != self.model and (self.active or joins):
+                    keep.append(r)  # another model is being served: wait until its requests have left
+                elif not free:
+                    keep.append(r)
+                else:
+                    if self.model is None or not (self.active or joins):
+                        self.model = model
+                    r.slot = free.pop(0)
+                    joins.append(r)
+            for r in keep:
+                self.queue.put(r)
+            if joins or self.active or self.closing or self.draining:
+                self._joining = joins
+                return {"op": "run", "model": self.model, "close": list(self.closing), "free": list(self.draining),
+                        "active": len(self.active),
+                        "join": [(r.slot, {k: v for k, v in r.cmd.items() if k != "deadline"}) for r in joins],
+                        "rounds": self.block}
+            if time.time() - last_beat > IDLE_BEAT:
+                return {"op": "idle"}
             try:
-                self._run(cmd)
-            except Exception as e:  # noqa: BLE001 — rank 0 raises the same error to the client (see _run)
-                print(f"[dli pipeline worker {self.rank}] request failed: {type(e).__name__}: {e}", file=sys.stderr,
-                      flush=True)
+                r = self.queue.get(timeout=0.5)
+                if r is not None:
+                    self.queue.put(r)
+            except queue.Empty:
+                pass
 
     # ------------------------------------------------------------------ every rank
-    def _run(self, cmd: dict) -> Optional[List[int]]:
-        # 1. every rank builds (or finds) its stage; any failure is agreed on before the pipeline starts
-        run, err = None, None
+    def serve_forever(self) -> None:
+        while True:
+            box = [self._plan() if self.rank == 0 else None]
+            dist.broadcast_object_list(box, src=0, group=self.ctrl)
+            plan = box[0]
+            if plan["op"] == "stop":
+                return
+            if plan["op"] == "idle":
+                continue
+            try:
+                self._apply(plan)
+            except Exception as e:  # noqa: BLE001 — a data-plane failure: fail what is in flight, keep serving
+                print(f"[dli pipeline worker {self.rank}] block failed: {type(e).__name__}: {e}", file=sys.stderr, flush=True)
+                if self.rank == 0:
+                    for r in list(self.active.values()) + list(getattr(self, "_joining", [])):
+                        if not r.future.done():
+                            r.future.set_exception(e)
+                    self.active.clear()
+
+    def _agree(self, errs: dict) -> dict:
+        """Union of every rank's {key: message} (first rank wins per key), identical on all ranks."""
+        box: List[Optional[dict]] = [None] * self.world
+        dist.all_gather_object(box, errs, group=self.ctrl)
+        out: dict = {}
+        for d in box:
+            for k, v in (d or {}).items():
+                out.setdefault(k, v)
+        return out
+
+    def _apply(self, plan: dict) -> None:
+        be = self.be
+        # 1. the model's stage on every rank ("*": a rank that cannot serve the model fails every joining request),
+        #    then every joining request on its own (a request one rank must refuse fails alone, for everybody)
+        errs: dict = {}
+
+        def msg(e):
+            return str(e) if isinstance(e, ValueError) else f"{type(e).__name__}: {e}"
+
         try:
-            run = self.factory(cmd)
+            be.prepare(plan["model"])
         except Exception as e:  # noqa: BLE001
-            err = f"{type(e).__name__}: {e}" if not isinstance(e, ValueError) else str(e)
-        errs: List[Optional[str]] = [None] * self.world
-        dist.all_gather_object(errs, err, group=self.ctrl)
-        bad = [e for e in errs if e]
-        if bad:
-            raise ValueError(bad[0])
-        # 2. prefill, then decode in blocks; the last stage decides when to stop
-        n_new = cmd["max_length"] - len(cmd["ids"])
-        run.prefill()
-        done = 1  # tokens produced so far
-        reason = 0
-        while done < n_new:
-            k = min(BLOCK, n_new - done)
-            run.decode(k)
-            done += k
-            reason = run.agree_stop(cmd.get("deadline"))
-            if reason:
-                break
-        # 3. the last stage owns the token log; rank 0 answers the request
-        box = [run.tokens(done) if self.rank == self.world - 1 else None]
-        dist.broadcast_object_list(box, src=self.world - 1, group=self.ctrl)
-        run.close()
-        if reason == 2:
-            raise TimeoutError("Inference generation timed out")
-        return box[0] if self.rank == 0 else None
+            errs["*"] = msg(e)
+        if not errs:
+            for slot, req in plan["join"]:
+                try:
+                    be.check_request(req)
+                except Exception as e:  # noqa: BLE001
+                    errs[slot] = msg(e)
+        errs = self._agree(errs)
+        joins = [(slot, req) for slot, req in plan["join"] if "*" not in errs and slot not in errs]
+        if self.rank == 0:
+            for r in self._joining:
+                if "*" in errs or r.slot in errs:
+                    r.future.set_exception(ValueError(errs.get("*", errs.get(r.slot))))
+            self._joining = [r for r in self._joining if "*" not in errs and r.slot not in errs]
+        if "*" in errs:
+            # A model change that one rank could not follow (models only change while no request is active).  Ranks
+            # that did switch and ranks that did not must not tick together — their runners' tick counters, which
+            # address the mailboxes, would differ — so EVERY rank forgets its resident model; the next plan rebuilds
+            # it everywhere at once.
+            be.reset()
+            self.model, self.closing, self.draining = None, [], []
+            return
+        runner = be.runner()
+        # 2. slots whose last rounds have drained: their KV pages go back; slots to close: no further round starts
+        for s in plan["free"]:
+            be.release(s)
+        for s in plan["close"]:
+            runner.close_slot(s)
+        # 3. admit: prompt pass through the stages, then the slot joins the ticks
+        for slot, req in joins:
+            be.join(slot, req)
+            runner.open_slot(slot)
+        # 4. the block
+        runner.ticks(plan["rounds"] * runner.P)
+        runner.flush()
+        # 5. rank 0: bookkeeping for the next plan
+        if self.rank == 0:
+            self._after_block(plan, joins)
+
+    def _after_block(self, plan: dict, joins) -> None:
+        self.draining = list(plan["close"])  # closed in this block: their in-flight rounds are through by the next
+        self.closing = []
+        for r in getattr(self, "_joining", []):
+            if r.slot is not None and any(s == r.slot for s, _ in joins):
+                self.active[r.slot] = r
+                self.rounds_done[r.slot] = 0
+                self.stats["joined"] += 1
+        self._joining = []
+        self.stats["blocks"] += 1
+        self.stats["max_active"] = max(self.stats["max_active"], len(self.active))
+        now = time.time()
+        for slot, r in list(self.active.items()):
+            self.rounds_done[slot] += plan["rounds"]
+            n_target = r.cmd["max_length"] - len(r.cmd["ids"])
+            have = min(self.rounds_done[slot], n_target)  # tokens the slot has CONSUMED = produced and fed back
+            toks = self.be.read_tokens(slot, have)
+            eos = tuple(r.cmd.get("eos") or ())
+            hit = next((i for i, t in enumerate(toks) if t in eos), None)
+            if hit is not None:
+                r.future.set_result(toks[: hit + 1])
+            elif have >= n_target:
+                r.future.set_result(toks[:n_target])
+            elif r.cmd.get("deadline") is not None and now > r.cmd["deadline"]:
+                r.future.set_exception(TimeoutError("Inference generation timed out"))
+            else:
+                continue
+            del self.active[slot]
+            self.closing.append(slot)
 
 
-class StageRun:
-    """What PipelineGroup needs from a rank's part of one request."""
+# ------------------------------------------------------------------------------ CUDA data plane of one rank
+class CudaBackend(StageBackend):
+    """This rank's ShardEngine of the resident model, in mailbox mode with one sequence per slot."""
 
-    def prefill(self) -> None: ...
-    def decode(self, rounds: int) -> None: ...
-    def agree_stop(self, deadline: Optional[float]) -> int: ...  # 0 = go on, 1 = every sequence finished, 2 = deadline
-    def tokens(self, n: int) -> List[int]: ...  # last stage: the n new tokens
-    def close(self) -> None: ...
+    def __init__(self, worker, rank: int, world: int, hop: int = 2):
+        from .pipeline import mailbox_period
 
+        self.worker, self.rank, self.world, self.hop = worker, rank, world, hop
+        self.n_slots = mailbox_period(1, world, hop, False)  # P = hop * N: every stage busy when all slots are taken
+        self.model = None
+        self.eng = None
+        self._runner = None
+        self._rows = {}
 
-# ------------------------------------------------------------------------------ CUDA stage of one request
-class CudaStageRun(StageRun):
-    """This rank's ShardEngine driven by pipeline.PipelineRunner for one request (one slot, batch 1)."""
+    def prepare(self, model: str) -> None:
+        if model == self.model and self.eng is not None:
+            return
+        from .pipeline import DistExchange, MailboxRunner, MailStage
 
-    def __init__(self, worker, rank: int, world: int, cmd: dict):
-        from .engine import all_finished  # noqa: F401  (used in agree_stop)
-        from .pipeline import EngineStage, PipelineRunner
-
-        model, shard_ids = cmd["model"], list(cmd["shard_ids"])
-        if len(shard_ids) != world:
-            raise ValueError(f"{len(shard_ids)} shards requested but the worker group has {world} GPUs "
-                             "(one shard per GPU)")
-        sid = sorted(shard_ids)[rank]  # shard i <-> GPU i
-        with worker._lock:
-            if sid not in worker.loaded_shards.get(model, {}):
-                raise ValueError(f"Shard {sid} of model {model} is not loaded")
-            info = worker.loaded_shards[model][sid]
+        w = self.worker
+        with w._lock:
+            shards = w.loaded_shards.get(model, {})
+            mine = [sid for sid, info in shards.items()
+                    if info["metadata"].get("num_shards") == self.world and info["metadata"].get("shard_id", sid) == self.rank]
+            if not mine:
+                # the ids are the sharder's 0..N-1; a worker registered under another id is matched by layer range
+                mine = [sid for sid, info in shards.items() if info["metadata"].get("num_shards") == self.world]
+            if not mine:
+                raise ValueError(f"Shard {self.rank} of model {model} is not loaded")
+            sid = mine[0]
+            info = shards[sid]
             md = info["metadata"]
             key = f"{model}_{sid}"
-            if key not in worker.loaded_models:  # lazy weight load on first use, like worker/app.py:345-349
-                worker.loaded_models[key] = worker._engine(info["path"], md["start_layer"], md["end_layer"])
-            eng = worker.loaded_models[key]
-        if eng.is_first != (rank == 0) or eng.is_last != (rank == world - 1):
-            raise ValueError(f"shard {sid} (layers {md['start_layer']}-{md['end_layer']}) is registered on GPU {rank}: "
+            if key not in w.loaded_models:  # lazy weight load on first use, like worker/app.py:345-349
+                w.loaded_models[key] = w._engine(info["path"], md["start_layer"], md["end_layer"], max_batch=self.n_slots)
+            eng = w.loaded_models[key]
+        if eng.is_first != (self.rank == 0) or eng.is_last != (self.rank == self.world - 1):
+            raise ValueError(f"shard {sid} (layers {md['start_layer']}-{md['end_layer']}) is registered on GPU {self.rank}: "
                              "shard i of N must live on GPU i")
-        self.eng, self.rank, self.world = eng, rank, world
-        ids = torch.tensor(cmd["ids"], dtype=torch.int32, device=eng.device)
-        T = len(cmd["ids"])
-        self.stage = EngineStage(eng, 1, T, cmd["max_length"], 1)
-        if eng.is_first:
-            self.stage.prompt_ids[0] = ids
-        gen = cmd.get("gen") or {}
-        mode = (dict(temperature=float(gen.get("temperature", 0.8)), top_k=int(gen.get("top_k", 50)),
-                     top_p=float(gen.get("top_p", 0.95))) if gen.get("do_sample") else None)
-        if mode != eng.sampling:  # the token choice lives on the last stage; harmless elsewhere
-            eng.sampling = mode
-            eng._graphs.clear()
-        st = eng._state(1, 0)
-        st.pop("row_sampling", None)
-        st["seed"].fill_(int(gen.get("seed", 0)))
-        st["step"].fill_(-1)
-        self.runner = PipelineRunner(self.stage, rank, world, 1, return_last=True)
-        self.flag = torch.zeros(1, dtype=torch.int32, device=eng.device)
-        self.first = None
-        self.done = 0
+        if eng.max_batch < self.n_slots:
+            raise ValueError(f"engine of shard {sid} was created for {eng.max_batch} sequences, the group needs {self.n_slots}")
+        self.eng, self.model = eng, model
+        stage = MailStage(eng, 1, self.n_slots, self.n_slots, self.hop, self.rank, self.world)
+        comm = torch.cuda.Stream(device=eng.device) if self.hop > 1 else None
+        self._runner = MailboxRunner(stage, self.rank, self.world, self.n_slots, hop=self.hop, vp=False,
+                                     exchange=DistExchange(comm_stream=comm))
+        self._rows = {}
+        self._pf_in = None
 
-    def prefill(self) -> None:
-        self.runner.run("prefill")
-        st = self.eng._state(1, 0)
-        if self.eng.is_last:
-            self.first = st["tokens"].clone()
+    def runner(self):
+        return self._runner
+
+    def reset(self) -> None:
+        self.model, self.eng, self._runner, self._rows = None, None, None, {}
+
+    def check_request(self, req: dict) -> None:
+        from .engine import check_max_length
+
+        T = len(req["ids"])
+        check_max_length(T, req["max_length"])
+        if req["max_length"] + BLOCK + 2 > self.eng.max_seq_len:
+            raise ValueError(f"max_length {req['max_length']} exceeds what this worker group holds per sequence "
+                             f"({self.eng.max_seq_len - BLOCK - 2}; DLI_MAX_SEQ_LEN)")
+
+    def _slot_rows(self, slot: int) -> dict:
+        """Persistent per-slot token-choice state of the last stage (its addresses are baked into the slot's graph):
+        greedy, or the reference's sampling call keyed by (the request's seed, the token's position)."""
+        if slot not in self._rows:
+            st, dev = self.eng._state(1, slot), self.eng.device
+            self._rows[slot] = {"seeds": torch.zeros(1, dtype=torch.int64, device=dev), "steps": st["positions"],
+                                "mask": torch.zeros(1, dtype=torch.int32, device=dev),
+                                "params": dict(temperature=0.8, top_k=50, top_p=0.95)}
+        return self._rows[slot]
+
+    def join(self, slot: int, req: dict) -> None:
+        eng, rank, world = self.eng, self.rank, self.world
+        T = len(req["ids"])
+        eng.start_batch(1, T, req["max_length"] + BLOCK + 2, mb=slot)
+        st = eng._state(1, slot)
+        gen = req.get("gen") or {}
+        if eng.has_head:
+            rows = self._slot_rows(slot)
+            rows["seeds"].fill_(int(gen.get("seed", 0)))
+            rows["mask"].fill_(1 if gen.get("do_sample") else 0)
+            # the prompt's last position keys the first new token; decode steps then key by the slot's position
+            st["row_sampling"] = dict(rows, steps=torch.tensor([T - 1], dtype=torch.int32, device=eng.device))
+        d = eng.spec.d_model
+        if rank == 0:
+            ids = torch.tensor(req["ids"], dtype=torch.int32, device=eng.device)
+            x = eng.prefill(1, T, ids=ids, mb=slot)
+        else:
+            buf = torch.empty(T, d, dtype=torch.bfloat16, device=eng.device)
+            dist.recv(buf, src=rank - 1)
+            x = eng.prefill(1, T, hidden=buf, mb=slot)
+        if rank < world - 1:
+            dist.send(x.contiguous(), dst=rank + 1)
+        if eng.has_head:
+            st["row_sampling"] = self._slot_rows(slot)
+            dist.send(st["tokens"], dst=0)  # the first token goes to the pipeline head
+        if rank == 0:
+            dist.recv(st["tokens"], src=world - 1)
         st["step"].zero_()
-        self.done = 1
 
-    def decode(self, rounds: int) -> None:
-        self.runner.run("decode", rounds)
-        self.done += rounds
+    def read_tokens(self, slot: int, n: int) -> List[int]:
+        torch.cuda.current_stream().synchronize()
+        return self.eng._state(1, slot)["token_log"][:n, 0].tolist()
 
-    def _seen(self) -> torch.Tensor:  # last stage: [done, 1] tokens so far
-        log = self.eng._state(1, 0)["token_log"]
-        return torch.cat((self.first[None], log[: self.done - 1]), dim=0)
-
-    def agree_stop(self, deadline: Optional[float]) -> int:
-        from .engine import all_finished
-
-        if self.rank == self.world - 1:
-            torch.cuda.current_stream().synchronize()
-            reason = 0
-            if all_finished(self._seen(), self.eng.eos_token_ids):
-                reason = 1
-            elif deadline is not None and time.time() > deadline:
-                reason = 2
-            self.flag.fill_(reason)
-        dist.broadcast(self.flag, src=self.world - 1)
-        return int(self.flag.item())
-
-    def tokens(self, n: int) -> List[int]:
-        return self._seen()[:n, 0].tolist()
-
-    def close(self) -> None:
-        pass
+    def release(self, slot: int) -> None:
+        self.eng.kv.release(slot)
+        self.eng._state(1, slot)["seq_lens"].zero_()  # an idle row: its decode steps touch nothing
 
 
 # ------------------------------------------------------------------------------ the worker of one rank
-def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None):
-    """A Worker (same routes as worker.py) bound to GPU `local`, whose sharded /inference runs the
-    NCCL pipeline when the requested shards are not all resident on this rank."""
+def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None, base_port: int = 5000,
+                      host: str = "127.0.0.1", hop: int = 2):
+    """A Worker (same routes as worker.py) bound to GPU `local`, whose sharded /inference goes to the group's
+    serving loop when the model is split over the group."""
     from .engine import apply_eos, check_max_length
     from .worker import Worker
 
@@ -201,37 +371,88 @@ def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None):
         def __init__(self):
             super().__init__(env)
             self.cuda_device = f"cuda:{local}"
-            self.group = PipelineGroup(rank, world, ctrl_group, lambda cmd: CudaStageRun(self, rank, world, cmd))
+            self.backend = CudaBackend(self, rank, world, hop=hop)
+            self.server = PipelineServer(rank, world, ctrl_group, self.backend)
 
         def dispatch(self, method, path, data, headers):
             if torch.cuda.is_available():
                 torch.cuda.set_device(local)  # HTTP handler threads start on device 0; this worker owns GPU `local`
+            if method == "POST" and path == "/inference" and rank != 0 and self._is_group_request(data or {}):
+                return self._forward_to_head(data, headers)
             return super().dispatch(method, path, data, headers)
+
+        def _is_group_request(self, data) -> bool:
+            """Does the request name shards of a model that is split over the whole group (num_shards == N)?"""
+            shards = self.loaded_shards.get(data.get("model_name"), {})
+            ids = data.get("shard_ids") or []
+            return world > 1 and bool(ids) and any(
+                sid in shards and shards[sid]["metadata"].get("num_shards") == world for sid in ids)
+
+        def _forward_to_head(self, data, headers):
+            """The reference master posts to whichever node it finds first (views.py:337-340): hand the request to
+            rank 0, the pipeline head, and relay its answer."""
+            import requests
+
+            hdr = {"Authorization": headers["Authorization"]} if headers.get("Authorization") else {}
+            r = requests.post(f"http://{host}:{base_port}/inference", json=data, headers=hdr,
+                              timeout=float(data.get("timeout", 60)) + 60)
+            return r.json(), r.status_code
 
         def run_shard_inference(self, model_name, prompt, shard_ids, max_length, deadline=None, gen=None):
             local_shards = self.loaded_shards.get(model_name, {})
-            if world == 1 or all(s in local_shards for s in shard_ids):
+            group_model = world > 1 and any(
+                s in local_shards and local_shards[s]["metadata"].get("num_shards") == world for s in shard_ids)
+            if not group_model:
+                if world > 1 and not all(s in local_shards for s in shard_ids):
+                    raise ValueError(f"Shard {[s for s in shard_ids if s not in local_shards][0]} of model {model_name} is not loaded")
                 return super().run_shard_inference(model_name, prompt, shard_ids, max_length, deadline, gen)
-            if rank != 0:
-                raise ValueError("send /inference for a model sharded over the GPUs to the first worker (rank 0)")
-            if model_name not in self.loaded_tokenizers:
-                raise ValueError(f"Shard {sorted(shard_ids)[0]} of model {model_name} is not loaded")
             tokenizer = self.loaded_tokenizers[model_name]
             ids = tokenizer(prompt, return_tensors="pt")["input_ids"][0]
             check_max_length(len(ids), max_length)
-            new = self.group.generate({"model": model_name, "shard_ids": list(shard_ids), "ids": ids.tolist(),
-                                       "max_length": int(max_length), "deadline": deadline, "gen": gen or {}})
-            eng = self.loaded_models.get(f"{model_name}_{sorted(shard_ids)[0]}")
-            new = apply_eos(torch.tensor([new], dtype=torch.int64), tuple(getattr(eng, "eos_token_ids", ())),
-                            getattr(eng, "pad_token_id", None))
+            eos, pad = self._stop_ids(model_name)
+            fut = self.server.submit({"model": model_name, "ids": ids.tolist(), "max_length": int(max_length),
+                                      "deadline": deadline, "gen": gen or {}, "eos": list(eos)})
+            wait = None if deadline is None else max(1.0, deadline - time.time() + 30)
+            new = fut.result(timeout=wait)
+            new = apply_eos(torch.tensor([new], dtype=torch.int64), eos, pad)
             return tokenizer.decode(torch.cat((ids.long(), new[0])), skip_special_tokens=True)
+
+        def _stop_ids(self, model_name):
+            import json
+            import os
+
+            from .worker import _stop_tokens
+
+            for info in self.loaded_shards.get(model_name, {}).values():
+                p = info["path"]
+                if os.path.exists(os.path.join(p, "config.json")):
+                    return _stop_tokens(p, json.load(open(os.path.join(p, "config.json"))))
+            return (), None
+
+        def inference(self, data):
+            # the group's requests wait on their future OUTSIDE the worker lock, so that they overlap
+            data = data or {}
+            if (rank == 0 and data.get("shard_ids") and data.get("model_name") and data.get("prompt")
+                    and self._is_group_request(data)):
+                start = time.time()
+                try:
+                    result = self.run_shard_inference(data["model_name"], data["prompt"], data["shard_ids"],
+                                                      data.get("max_length", 100), start + data.get("timeout", 60),
+                                                      self._gen_kwargs(data))
+                    return {"status": "success", "result": result, "execution_time": time.time() - start}, 200
+                except TimeoutError as e:
+                    return {"status": "error", "message": str(e) or "Inference generation timed out"}, 408
+                except Exception as e:  # noqa: BLE001
+                    return {"status": "error", "message": f"Inference failed: {str(e)}"}, 500
+            return super().inference(data)
 
     return GroupWorker()
 
 
 def main(argv=None):
     import argparse
-    import threading
+    import datetime
+    import os
 
     from werkzeug.serving import make_server
 
@@ -243,18 +464,18 @@ def main(argv=None):
     ap.add_argument("--port", type=int, default=5000)
     a = ap.parse_args(argv)
     rank, world, local = init_distributed()
-    ctrl = dist.new_group(backend="gloo")
-    w = make_group_worker(rank, world, local, ctrl)
+    ctrl = dist.new_group(backend="gloo", timeout=datetime.timedelta(hours=12))
+    head_host = "127.0.0.1" if a.host in ("0.0.0.0", "") else a.host
+    w = make_group_worker(rank, world, local, ctrl, base_port=a.port, host=head_host,
+                          hop=int(os.environ.get("DLI_PIPE_HOP", "2")))
     srv = make_server(a.host, a.port + rank, w, threaded=True)
-    if rank == 0:
-        try:
-            srv.serve_forever()
-        finally:
-            w.group.shutdown()
-    else:
-        threading.Thread(target=srv.serve_forever, daemon=True).start()
-        torch.cuda.set_device(local)
-        w.group.serve_forever()
+    http = threading.Thread(target=srv.serve_forever, daemon=True)
+    http.start()
+    torch.cuda.set_device(local)
+    try:
+        w.server.serve_forever()  # every rank: the serving loop (rank 0 plans, the others follow)
+    finally:
+        srv.shutdown()
     dist.destroy_process_group()
 
 

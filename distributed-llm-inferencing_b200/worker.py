@@ -118,14 +118,16 @@ class Worker:
         raise FileNotFoundError(f"{model_name} is not a local model directory and the Hugging Face hub is not "
                                 f"reachable (looked in {self.model_cache_dir})")
 
-    def _engine(self, path: str, start=0, end=None):
+    def _engine(self, path: str, start=0, end=None, max_batch=None):
         from .engine import ModelSpec, ShardEngine
 
         if self.device != "cuda":
             raise RuntimeError("this worker has no CPU path: it needs a CUDA device and USE_GPU=1")
         cfg = json.load(open(os.path.join(path, "config.json")))
         spec = ModelSpec.from_hf_config(cfg)
-        eng = ShardEngine(spec, start, end, device=self.cuda_device, max_batch=self.max_batch if end is None else 1,
+        if max_batch is None:
+            max_batch = self.max_batch if end is None else 1
+        eng = ShardEngine(spec, start, end, device=self.cuda_device, max_batch=max_batch,
                           max_seq_len=min(self.max_seq_len, spec.max_pos))
         eng.load_state_dict(load_hf_state_dict(path, eng.start, eng.end, spec.n_layers))
         eng.eos_token_ids, eng.pad_token_id = _stop_tokens(path, cfg)

@@ -282,82 +282,141 @@ def test_chunked_prefill_schedule_over_gloo(world, n_micro, n_chunks):
                 assert h == [float(want)] * 3
 
 
-# ------------------------------------------------------------------------------ worker-group control plane
-def _group_worker(rank, world, port, q):
-    """PipelineGroup over gloo with a toy StageRun: token i of a request is base + i; the stop decision is
-    taken by the last rank and reaches everybody; a rank that cannot serve a request fails it for all."""
+# ------------------------------------------------------------------------------ worker-group serving loop
+def toy_generate(world, first, n):
+    """Tokens a ToyMailStage pipeline (b = 1, head on the last stage) consumes, starting from `first`."""
+    out, src = [], float(first)
+    for step in range(n):
+        out.append(int(src))
+        h = torch.full((1, 4), src)
+        for s in range(world):
+            h = h * 3 + (s + 1) + step
+        src = float(h.sum(dim=1).long() % 1000)
+    return out
+
+
+def _server_worker(rank, world, port, q):
+    """PipelineServer over gloo with a toy data plane: concurrent requests share the pipeline's slots, leave at
+    max_length / EOS / deadline, a request no rank can serve fails alone, and the group keeps serving."""
+    import threading
     import time
 
-    from dli_b200.pipeline_worker import PipelineGroup, StageRun
+    from dli_b200.pipeline import DistExchange, MailboxRunner, mailbox_period
+    from dli_b200.pipeline_worker import PipelineServer, StageBackend
 
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     ctrl = dist.new_group(backend="gloo")
+    hop = 2
+    P = mailbox_period(1, world, hop, False)
 
-    class Toy(StageRun):
-        def __init__(self, cmd):
-            if cmd.get("missing_on") == rank:
-                raise ValueError(f"Shard {rank} of model toy is not loaded")
-            self.cmd, self.done, self.flag = cmd, 0, torch.zeros(1, dtype=torch.int32)
+    class Toy(StageBackend):
+        n_slots = P
 
-        def prefill(self):
-            self.done = 1
+        def __init__(self):
+            self.stage = ToyMailStage(rank, world, P, 1, 4, P, hop, False)
+            self.stage.consumed = [[] for _ in range(P)]
+            orig = self.stage.compute
 
-        def decode(self, rounds):
-            self.done += rounds
+            def compute(mb):
+                if rank == 0:
+                    self.stage.consumed[mb].append(int(self.stage.tokens[mb][0]))
+                orig(mb)
 
-        def agree_stop(self, deadline):
-            if rank == world - 1:
-                toks = [self.cmd["base"] + i for i in range(self.done)]
-                r = 1 if self.cmd.get("eos") in toks else (2 if deadline is not None and time.time() > deadline else 0)
-                self.flag.fill_(r)
-            dist.broadcast(self.flag, src=world - 1)
-            return int(self.flag.item())
+            self.stage.compute = compute
+            self._runner = MailboxRunner(self.stage, rank, world, P, hop=hop, vp=False, exchange=DistExchange())
 
-        def tokens(self, n):
-            return [self.cmd["base"] + i for i in range(n)]
+        def prepare(self, model):
+            if model == "missing" and rank == world - 1:
+                raise ValueError(f"Shard {rank} of model missing is not loaded")
 
-        def close(self):
+        def check_request(self, req):
+            if len(req["ids"]) >= req["max_length"]:
+                raise ValueError("Input length of input_ids is too long")
+
+        def join(self, slot, req):
+            self.stage.steps[slot] = 0
+            self.stage.tokens[slot] = torch.tensor([float(sum(req["ids"]) % 1000)])
+            self.stage.consumed[slot] = []
+
+        def runner(self):
+            return self._runner
+
+        def read_tokens(self, slot, n):
+            return self.stage.consumed[slot][:n]
+
+        def release(self, slot):
             pass
 
-    g = PipelineGroup(rank, world, ctrl, Toy)
+        def reset(self):  # all ranks together: a fresh runner, tick counter back to zero everywhere
+            self._runner = MailboxRunner(self.stage, rank, world, P, hop=hop, vp=False, exchange=DistExchange())
+
+    srv = PipelineServer(rank, world, ctrl, Toy(), block=2)
     if rank == 0:
         out = {}
-        out["full"] = g.generate({"ids": [1, 2, 3], "max_length": 3 + 21, "base": 100})
-        out["eos"] = g.generate({"ids": [1, 2, 3], "max_length": 3 + 40, "base": 100, "eos": 111})
-        try:
-            g.generate({"ids": [1], "max_length": 9, "base": 0, "missing_on": world - 1})
-        except ValueError as e:
-            out["missing"] = str(e)
-        try:
-            g.generate({"ids": [1], "max_length": 40, "base": 0, "deadline": time.time() - 1})
-        except TimeoutError as e:
-            out["timeout"] = str(e)
-        out["after"] = g.generate({"ids": [7], "max_length": 4, "base": 5})  # the group still serves
-        g.shutdown()
+
+        def client():
+            try:
+                reqs = {f"r{i}": {"model": "toy", "ids": [i + 1, 7], "max_length": 2 + n, "deadline": None, "gen": {}}
+                        for i, n in enumerate([5, 9, 3, 12, 6, 4])}  # six requests on four slots
+                eos_tok = toy_generate(world, 101, 20)[6]
+                reqs["eos"] = {"model": "toy", "ids": [94, 7], "max_length": 2 + 20, "deadline": None, "gen": {}, "eos": [eos_tok]}
+                futs = {k: srv.submit(v) for k, v in reqs.items()}
+                late = srv.submit({"model": "toy", "ids": [1, 1], "max_length": 300, "deadline": time.time() - 1, "gen": {}})
+                bad = srv.submit({"model": "toy", "ids": [1, 2, 3], "max_length": 3, "deadline": None, "gen": {}})
+                for k, f in futs.items():
+                    out[k] = (reqs[k], f.result(timeout=100))
+                for name, f in (("late", late), ("bad", bad)):
+                    try:
+                        f.result(timeout=100)
+                        out[name] = "no error"
+                    except Exception as e:  # noqa: BLE001
+                        out[name] = f"{type(e).__name__}: {e}"
+                try:
+                    srv.submit({"model": "missing", "ids": [5], "max_length": 9, "deadline": None, "gen": {}}).result(timeout=100)
+                except Exception as e:  # noqa: BLE001
+                    out["missing"] = str(e)
+                r = {"model": "toy", "ids": [40, 2], "max_length": 6, "deadline": None, "gen": {}}
+                out["after"] = (r, srv.submit(r).result(timeout=100))  # the group still serves
+                out["stats"] = dict(srv.stats)
+            finally:
+                srv.shutdown()
+
+        th = threading.Thread(target=client)
+        th.start()
+        srv.serve_forever()
+        th.join()
         q.put(out)
     else:
-        g.serve_forever()
+        srv.serve_forever()
     dist.barrier()
     dist.destroy_process_group()
 
 
 @pytest.mark.parametrize("world", [2, 3])
-def test_worker_group_control_plane_over_gloo(world):
+def test_worker_group_serves_concurrent_requests_over_gloo(world):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_group_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_server_worker, args=(r, world, port, q)) for r in range(world)]
     [p.start() for p in procs]
-    out = q.get(timeout=120)
+    out = q.get(timeout=180)
     [p.join(timeout=60) for p in procs]
     assert all(p.exitcode == 0 for p in procs)
-    assert out["full"] == [100 + i for i in range(21)]
-    # EOS (token 111 = the 12th) is noticed at the next block boundary: 1 + 8 + 8 = 17 tokens were produced
-    assert out["eos"] == [100 + i for i in range(17)]
-    assert out["missing"] == f"Shard {world - 1} of model toy is not loaded"
-    assert out["timeout"] == "Inference generation timed out"
-    assert out["after"] == [5, 6, 7]
+    for k, v in out.items():
+        if k in ("late", "bad", "missing", "stats"):
+            continue
+        req, toks = v
+        n = req["max_length"] - len(req["ids"])
+        want = toy_generate(world, sum(req["ids"]) % 1000, n)
+        if req.get("eos"):
+            want = want[: want.index(req["eos"][0]) + 1]
+            assert len(want) == 7
+        assert toks == want, (k, toks, want)
+    assert out["late"] == "TimeoutError: Inference generation timed out"
+    assert out["bad"].startswith("ValueError: Input length of input_ids")
+    assert out["missing"] == f"Shard {world - 1} of model missing is not loaded"
+    assert out["stats"]["max_active"] >= 3  # requests really shared the pipeline
 
 
 # ------------------------------------------------------------------------------ block-wise decode (return_last)

@@ -113,6 +113,23 @@ def test_worker_group_serves_a_sharded_model_over_http(cuda, tmp_path):
         too_short = requests.post(f"http://127.0.0.1:{port}/inference", json=dict(req, max_length=T), timeout=60)
         assert too_short.status_code == 500 and "Input length of input_ids" in too_short.json()["message"]
         assert requests.post(f"http://127.0.0.1:{port}/inference", json=req, timeout=300).json()["result"] == got
+        # what the unchanged reference master sends: only the FIRST node's shard ids (views.py:337-340) — the group
+        # still runs the whole pipeline; and a request that lands on the other node is handed to the pipeline head
+        only_first = requests.post(f"http://127.0.0.1:{port}/inference", json=dict(req, shard_ids=[0]), timeout=300)
+        assert only_first.status_code == 200 and only_first.json()["result"] == got, only_first.text
+        on_other = requests.post(f"http://127.0.0.1:{port + 1}/inference", json=dict(req, shard_ids=[1]), timeout=300)
+        assert on_other.status_code == 200 and on_other.json()["result"] == got, on_other.text
+        # concurrent requests share the pipeline's slots (the reference serialises them, worker/Dockerfile:45):
+        # every one gets exactly the text it gets alone
+        from concurrent.futures import ThreadPoolExecutor
+
+        others = [dict(req, prompt=" ".join(str(int(i)) for i in c["prompts"][k % c["prompts"].shape[0]].roll(k)),
+                       max_length=T + 12 + 3 * k, do_sample=bool(k % 2), seed=k) for k in range(5)]
+        alone = [requests.post(f"http://127.0.0.1:{port}/inference", json=o, timeout=300).json()["result"] for o in others]
+        with ThreadPoolExecutor(max_workers=5) as ex:
+            together = list(ex.map(lambda o: requests.post(f"http://127.0.0.1:{port}/inference", json=o, timeout=300).json(), others))
+        assert [t.get("result") for t in together] == alone, together
+        assert len(alone[0].split()) == T + 12 and len(alone[4].split()) == T + 24
         # worker 1 is a complete worker too: an unsharded model on ITS GPU gives the same text
         solo = requests.post(f"http://127.0.0.1:{port + 1}/inference",
                              json={"model_name": full, "prompt": prompt, "max_length": T + 20, "do_sample": False},
