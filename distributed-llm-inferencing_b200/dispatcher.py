@@ -5,8 +5,9 @@ default).  SURVEY.md §8f rank 2.  Kept semantics: shards known -> /inference wi
 (max_length 100, timeout 60, HTTP timeout 120, views.py:345-355); no shards -> /load_model
 (HTTP timeout 300) then /inference on the first active node (views.py:391-421); a non-200
 answer or `status != success` is a failure with the worker's message.
-Fixed relative to the reference: shard ids are ordered and sent to the node that holds them
-all (the reference takes "the first node that has shards", views.py:337-340); shards that
+Fixed relative to the reference: ALL shard ids of the model are sent, ordered, to the pipeline
+head — the node holding the first shard — whether the shards sit on one node or one per node (the
+reference takes "the first node that has shards" and sends only its ids, views.py:337-340); shards that
 are registered with the master but not yet on the worker are (re)announced with /load_shard
 first (no reference view ever calls it); the Authorization header is sent when a key is
 configured (the reference master never sends it, so AUTH_ENABLED=1 breaks it).
@@ -53,14 +54,25 @@ def dispatch_inference(nodes: List[Node], model_name: str, prompt: str, max_leng
     holders = [n for n in active if n.shards.get(model_name)]
     body = {"model_name": model_name, "prompt": prompt, "max_length": max_length, "timeout": timeout, **(extra or {})}
     if holders:
-        # the node that holds the most shards of the model runs the (in-process) layer-range chain
-        node = max(holders, key=lambda n: len(n.shards[model_name]))
-        ids = sorted(node.shards[model_name], key=lambda i: (str(type(i)), i))
+        order = lambda i: (str(type(i)), i)  # noqa: E731 — ids of one model are all ints or all strings
+        # every shard is announced to the node that holds it (one node per (model, shard):
+        # master/dashboard/models.py:27-28), lowest id first
+        owner = {}
+        for n in holders:
+            for sid in n.shards[model_name]:
+                owner.setdefault(sid, n)
+        ids = sorted(owner, key=order)
         for sid in ids:
-            _check(post(f"{node.url}/load_shard", json={"model_name": model_name, "shard_id": sid,
-                                                        "shard_path": node.shards[model_name][sid]},
+            n = owner[sid]
+            _check(post(f"{n.url}/load_shard", json={"model_name": model_name, "shard_id": sid,
+                                                     "shard_path": n.shards[model_name][sid]},
                         headers=headers, timeout=300), f"load_shard {sid}")
-        return _check(post(f"{node.url}/inference", json={**body, "shard_ids": ids}, headers=headers, timeout=120),
+        # ONE /inference with ALL shard ids, in order, to the pipeline head: the node holding the first shard.  With
+        # every shard on one node that node chains them in-process; with one shard per node (the reference's
+        # deployment, served here by pipeline_worker.py) the head drives the group.  The reference instead takes
+        # "the first node that has shards" and sends only that node's ids (views.py:337-340).
+        head = owner[ids[0]]
+        return _check(post(f"{head.url}/inference", json={**body, "shard_ids": ids}, headers=headers, timeout=120),
                       "inference")["result"]
     if not active:
         raise DispatchError("No active worker nodes available")

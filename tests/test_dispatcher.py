@@ -53,3 +53,23 @@ def test_dispatch_without_shards_loads_model_on_first_active_node():
     assert [p for _, p, _, _, _ in log] == ["/load_model"] and log[0][4] == 300
     with pytest.raises(DispatchError, match="No active worker nodes available"):
         dispatch_inference([Node("http://b:5000", is_active=False)], "org/none", "hi", post=post)
+
+
+def test_dispatch_with_one_shard_per_node_addresses_the_pipeline_head(tmp_path):
+    """The reference's deployment: shard i on node i (models.py:27-28).  Every node gets its own /load_shard, and the
+    node of the FIRST shard gets one /inference naming all shards in order (pipeline_worker.py serves it)."""
+    ws = {f"http://n{i}:5000": Worker(env={"MODEL_CACHE_DIR": "/nonexistent", "USE_GPU": "0"}) for i in range(3)}
+    log = []
+    post = _transport(ws, log)
+    nodes = []
+    for i in (2, 0, 1):  # registered in no particular order
+        p = tmp_path / f"shard_{i}"
+        p.mkdir()
+        nodes.append(Node(f"http://n{i}:5000", shards={"m": {i: str(p)}}))
+    with pytest.raises(DispatchError, match="Inference failed"):  # no CUDA here: the worker's own message
+        dispatch_inference(nodes, "m", "1 2 3", post=post)
+    assert [(b, p, j.get("shard_id")) for b, p, j, _, _ in log[:3]] == [
+        ("http://n0:5000", "/load_shard", 0), ("http://n1:5000", "/load_shard", 1), ("http://n2:5000", "/load_shard", 2)]
+    assert log[3][0] == "http://n0:5000" and log[3][1] == "/inference" and log[3][2]["shard_ids"] == [0, 1, 2]
+    assert len(log) == 4
+    assert all(list(ws[f"http://n{i}:5000"].loaded_shards["m"]) == [i] for i in range(3))

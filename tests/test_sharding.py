@@ -84,3 +84,59 @@ def test_gpt2_tied_head_reads_embedding_on_last_stage():
     assert not sharding.tensor_in_range("model.embed_tokens.weight", 2, 3, False, True, tied=False)
     with pytest.raises(FileNotFoundError):
         sharding._tensor_files("/nonexistent-dir")
+
+
+@pytest.mark.parametrize("case_name,n_shards", [("llama_tiny", 3), ("gpt2_tiny", 2)])
+def test_sharder_command_streams_a_model_directory(tmp_path, case_name, n_shards):
+    """`python -m dli_b200.sharding --model_name --num_shards --output_dir` (the reference command's arguments,
+    shard_model.py:11-14) on a multi-file source directory: same layout and metadata as the reference's sharder, the
+    same tensors as write_shards(), written a few tensors at a time (tiny --max_file_gb forces multi-file shards)."""
+    import subprocess
+    import sys
+
+    from safetensors.torch import save_file
+
+    from dli_b200.engine import ModelSpec
+
+    c = load_case(case_name)
+    cfg = spec_kwargs(c["config"])
+    spec = ModelSpec.from_hf_config(cfg)
+    sd = R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"])
+    src = tmp_path / "cache" / "org_tiny"
+    src.mkdir(parents=True)
+    names = sorted(sd)
+    half = len(names) // 2
+    files = {"model-00001-of-00002.safetensors": names[:half], "model-00002-of-00002.safetensors": names[half:]}
+    for fn, ks in files.items():
+        save_file({k: sd[k].contiguous() for k in ks}, str(src / fn))
+    json.dump({"metadata": {}, "weight_map": {k: fn for fn, ks in files.items() for k in ks}},
+              open(src / "model.safetensors.index.json", "w"))
+    json.dump(cfg, open(src / "config.json", "w"))
+    json.dump({"eos_token_id": 2}, open(src / "generation_config.json", "w"))
+    (src / "tokenizer.json").write_text("{}")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = tmp_path / "model_shards"
+    p = subprocess.run([sys.executable, "-m", "dli_b200.sharding", "--model_name", "org/tiny", "--num_shards", str(n_shards),
+                        "--output_dir", str(out), "--cache_dir", str(tmp_path / "cache"), "--max_file_gb", "0.00002"],
+                       cwd=root, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert f"Successfully sharded model org/tiny into {n_shards} shards" in p.stdout
+    base = out / "org_tiny"
+    assert (base / "tokenizer" / "tokenizer.json").exists()
+    want_paths = sharding.write_shards(sd, cfg, "org/tiny", n_shards, str(tmp_path / "ref"))
+    seen = set()
+    for i in range(n_shards):
+        d = base / f"shard_{i}"
+        md = json.load(open(d / "metadata.json"))
+        assert md == sharding.shard_metadata("org/tiny", i, n_shards, spec.n_layers)
+        assert json.load(open(d / "config.json")) == cfg and (d / "generation_config.json").exists()
+        assert (d / "model.safetensors.index.json").exists()  # several small files + an index
+        got = sharding.load_hf_state_dict(str(d), md["start_layer"], md["end_layer"])
+        want = sharding.load_hf_state_dict(want_paths[i], md["start_layer"], md["end_layer"])
+        assert set(got) == set(want) and all(torch.equal(got[k], want[k]) for k in want)
+        seen |= set(got)
+    assert seen == set(sd)
+    # a name that is nowhere local is an error, not a download
+    p = subprocess.run([sys.executable, "-m", "dli_b200.sharding", "--model_name", "org/absent", "--cache_dir", str(tmp_path)],
+                       cwd=root, capture_output=True, text=True, timeout=120)
+    assert p.returncode == 1 and "not a local model directory" in p.stdout
