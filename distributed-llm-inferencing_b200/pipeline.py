@@ -666,6 +666,86 @@ def _parity_against_single_engine(spec, eng, rank, world, local, b, M, prompt_le
     return "ok" if ties == 0 else f"ok ({ties} bf16-level ties)"
 
 
+_CTRL = {}
+
+
+def serve_e2e(spec, model_name, rank, world, local, ctx, n_short, n_long, hop, page_size=16):
+    """End to end through the plugin call at N GPUs: the worker group of pipeline_worker.py with this rank's stage
+    injected (random-init weights, nothing read from disk), and hop*N CONCURRENT `POST /inference` requests on the
+    head worker (werkzeug test client, no socket), each a `ctx`-token prompt given as text, greedy.  Every request's
+    prompt ids travel host -> device, its tokens device -> host, inside the timed region.  Decode rate = the extra
+    tokens of the long batch over the short one / the extra wall time; the whole batch's seconds are reported too."""
+    import threading
+    import time
+    from concurrent.futures import ThreadPoolExecutor
+
+    from .pipeline_worker import BLOCK, make_group_worker
+    from .sharding import shard_metadata
+    from .worker import IdTokenizer
+
+    if "g" not in _CTRL:
+        import datetime
+
+        _CTRL["g"] = dist.new_group(backend="gloo", timeout=datetime.timedelta(hours=2))
+    w = make_group_worker(rank, world, local, _CTRL["g"], env={"MODEL_CACHE_DIR": "/nonexistent", "USE_GPU": "1"}, hop=hop)
+    P = w.backend.n_slots
+    eng = build_stage_engine(spec, rank, world, local, P, ctx + n_long + BLOCK + 8, page_size, vocab_parallel=False)
+    eng.load_random(seed=0)
+    name = "bench/" + model_name
+    w.loaded_shards[name] = {rank: {"path": "(in memory)", "metadata": shard_metadata(name, rank, world, spec.n_layers)}}
+    w.loaded_tokenizers[name] = IdTokenizer()
+    w.loaded_models[f"{name}_{rank}"] = eng
+    out = None
+    if rank != 0:
+        w.server.serve_forever()
+    else:
+        from werkzeug.test import Client
+
+        loop = threading.Thread(target=lambda: (torch.cuda.set_device(local), w.server.serve_forever()))
+        loop.start()
+        try:
+            g = torch.Generator().manual_seed(11)
+            texts = [" ".join(str(int(t)) for t in torch.randint(0, spec.vocab, (ctx,), generator=g)) for _ in range(P)]
+
+            def one(args):
+                text, n_new = args
+                r = Client(w).post("/inference", json={"model_name": name, "prompt": text, "shard_ids": list(range(world)),
+                                                    "max_length": ctx + n_new, "do_sample": False, "timeout": 600})
+                body = r.get_json()
+                if r.status_code != 200 or len(body["result"].split()) != ctx + n_new:
+                    raise RuntimeError(f"/inference on the worker group failed: {r.status_code} {str(body)[:200]}")
+
+            def batch(n_new):
+                t0 = time.perf_counter()
+                with ThreadPoolExecutor(max_workers=P) as ex:
+                    list(ex.map(one, [(t, n_new) for t in texts]))
+                return time.perf_counter() - t0
+
+            batch(n_short)  # warm-up: weights resident, graphs of every slot captured, P2P connections up
+            t_short = batch(n_short)
+            t_long = batch(n_long)
+            extra = P * (n_long - n_short)
+            steps = n_long - n_short
+            out = {"value": extra / max(t_long - t_short, 1e-9), "unit": "tokens/s",
+                   "h2d_bytes_per_step": 4.0 * ctx * P / steps, "d2h_bytes_per_step": 4.0 * P * n_long / steps,
+                   "ms_per_step": (t_long - t_short) / steps * 1e3,
+                   "api": f"{P} concurrent POST /inference on the worker group's head (werkzeug test client) -> "
+                          "pipeline_worker.PipelineServer -> MailboxRunner",
+                   "concurrent_requests": P, "request_batch_s": t_long, "new_tokens_per_request": n_long,
+                   "request_tokens_per_s": P * n_long / t_long, "short_batch_s": t_short, "prompt_tokens": ctx,
+                   "server_stats": dict(w.server.stats),
+                   "note": "value = extra tokens of the long batch over the short one / extra wall time; head on the "
+                           "last stage (serves greedy and sampled requests alike), so its tick is longer than the "
+                           "vocabulary-parallel bench's"}
+        finally:
+            w.server.shutdown()
+            loop.join()
+    eng.unload()
+    torch.cuda.empty_cache()
+    dist.barrier()
+    return out
+
+
 # BASELINE.json configs run on exactly N GPUs: (model, total batch, context, note)
 NAMED_CONFIGS = {
     2: ("tinyllama-1.1b", 1, 1024, "configs[1]: TinyLlama-1.1B, 2 layer-range shards, batch 1 greedy decode"),
@@ -707,6 +787,11 @@ def run_pipeline_bench(args, spec, peaks):
             if "pipeline tokens differ" in str(e):
                 raise
             named = {"config": note, "error": str(e)[:300]}
+    e2e = None
+    try:
+        e2e = serve_e2e(spec, args.model, rank, world, local, ctx, 8, 8 + max(16, min(K, 64)) // 4 * 4, hop, args.page_size)
+    except Exception as e:  # noqa: BLE001 — the line still carries the device-timed numbers
+        e2e_err = f"{type(e).__name__}: {str(e)[:200]}"
     roof = {"bound": "hbm", "kernel": "stage pass (all kernels of one micro-batch on one stage)",
             "achieved": main["stage_pass_gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": main["stage_pass_frac"],
             "traffic": None, "bytes_per_launch": main["stage_bytes"], "micro_batches": main["slots"],
@@ -714,13 +799,16 @@ def run_pipeline_bench(args, spec, peaks):
     Mb = main["slots"] * main["b"]
     return {"value": main["value"], "ms_per_step": main["ms_per_step"], "gpu_launches": main["gpu_launches"],
             "clocks": main["clocks"],
-            "e2e": {"value": main["stream_tokens_per_s"], "unit": "tokens/s", "h2d_bytes_per_step": 0,
-                    "d2h_bytes_per_step": 4 * Mb, "ms_per_step": Mb * 1e3 / main["stream_tokens_per_s"],
-                    "api": "MailboxRunner.ticks + per-round copy of the new tokens to pinned host memory on rank 0"},
+            "e2e": e2e if e2e is not None else {
+                "value": main["stream_tokens_per_s"], "unit": "tokens/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 4 * Mb, "ms_per_step": Mb * 1e3 / main["stream_tokens_per_s"],
+                "api": "MailboxRunner.ticks + per-round copy of the new tokens to pinned host memory on rank 0"
+                       + ("" if rank != 0 else f" (the worker-group request path failed: {e2e_err})")},
             "roofline": roof,
             "extra": {"prefill_tokens_per_s": main["prefill_tokens_per_s"], "prefill_ms": main["prefill_ms"],
                       "prefill_chunks": main["prefill_chunks"], "tick_ms": main["tick_ms"], "period_ticks": main["period"],
                       "hop": hop, "parity_check": main["parity_check"], "peaks": peaks["source"],
+                      "stream_tokens_per_s": main["stream_tokens_per_s"],
                       "pp_only_ceiling_tokens_per_s": main["pp_ceiling_tokens_per_s"], "named_config": named,
                       "env": {k: v for k, v in os.environ.items() if k.startswith("DLI_")}},
             "config": {"workload": main["workload"], "batch": Mb, "micro_batches": main["slots"], "ctx": main["ctx_mid"],
