@@ -383,10 +383,10 @@ def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None, b
 
         def _is_group_request(self, data) -> bool:
             """Does the request name shards of a model that is split over the whole group (num_shards == N)?"""
+            # whichever ids the request lists (the reference master lists only the ids of the node it picked)
             shards = self.loaded_shards.get(data.get("model_name"), {})
-            ids = data.get("shard_ids") or []
-            return world > 1 and bool(ids) and any(
-                sid in shards and shards[sid]["metadata"].get("num_shards") == world for sid in ids)
+            return world > 1 and bool(data.get("shard_ids")) and any(
+                info["metadata"].get("num_shards") == world for info in shards.values())
 
         def _forward_to_head(self, data, headers):
             """The reference master posts to whichever node it finds first (views.py:337-340): hand the request to
@@ -400,8 +400,7 @@ def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None, b
 
         def run_shard_inference(self, model_name, prompt, shard_ids, max_length, deadline=None, gen=None):
             local_shards = self.loaded_shards.get(model_name, {})
-            group_model = world > 1 and any(
-                s in local_shards and local_shards[s]["metadata"].get("num_shards") == world for s in shard_ids)
+            group_model = world > 1 and any(i["metadata"].get("num_shards") == world for i in local_shards.values())
             if not group_model:
                 if world > 1 and not all(s in local_shards for s in shard_ids):
                     raise ValueError(f"Shard {[s for s in shard_ids if s not in local_shards][0]} of model {model_name} is not loaded")
