@@ -13,7 +13,8 @@
 // then partial sums are combined through shared memory (one warp per output).
 // Groups of kRows rows are dealt round-robin to a grid sized as a multiple of the SM count,
 // so at any moment the grid streams one contiguous band of the matrix (two balanced
-// dealings were measured and lost, see `deal` in the kernel).
+// dealings were measured and lost, see `deal` in the kernel; so did a software-pipelined
+// 2-row variant for the small matrices, profiles/r2_notes.md).
 //
 // Programmatic dependent launch: a CTA of the next kernel may move in while this
 // kernel drains; it waits (pdl_wait) before reading activations.  Prefetching the
@@ -288,196 +289,6 @@ gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* 
   }
 }
 
-// ---- the same GEMV for matrices of FEW tasks per CTA (o, qkv and down projections of a batch-1 step) -------------
-// With 4-row tasks those matrices give a CTA two or three tasks, so the last wave is ragged (1024 tasks on 444 CTAs:
-// a third of the CTAs run 3 tasks, the rest 2) and the SMs that finish early idle while HBM drains at a fraction of
-// its rate.  Here a task is 2 rows (twice as many, half as long: 5 vs 4.6 instead of 3 vs 2.3) and the loads are
-// software-pipelined: the weights of step s+1 — the next K chunk of the task, or the first chunk of the CTA's NEXT
-// task — are requested before step s is multiplied and before a finished task's partial sums go through shared
-// memory, so a thread keeps two steps (8 x 16 B) in flight as the 4-row kernel does with one, across task ends.
-// Per output the multiply-adds and the 256-partial sum run in the same order as in gemv_kernel: bit-identical.
-constexpr int kPipeRows = 2;
-
-template <int M, bool kNorm>
-__global__ void __launch_bounds__(kGemvThreads, 3)
-gemv_pipe_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, const bf16* __restrict__ bias,
-                 const bf16* residual, bf16* y, int N, int K, int epilogue, const bf16* __restrict__ ln_w, float eps,
-                 int pf_l2) {
-  constexpr int R = kPipeRows;
-  __shared__ float part[2][R * M][kGemvThreads];
-  __shared__ float red[kGemvWarps][M];
-  extern __shared__ __align__(16) uint8_t xnorm_raw[];  // kNorm: normalised x, [M][K] bf16
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int kvec = K >> 3;
-  const int spt = (kvec + 2 * kGemvThreads - 1) / (2 * kGemvThreads);  // steps per task (2 vectors per thread each)
-  const int ntasks = (N + R - 1) / R;
-  const int my_tasks = (int)blockIdx.x < ntasks ? (ntasks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-  const int total = my_tasks * spt;
-  const uint4 zero = make_uint4(0, 0, 0, 0);
-
-  if (pf_l2 && my_tasks > 0 && tid < R) {  // head of the first task's rows into L2 before the dependency wait
-    const size_t row = (size_t)min((int)blockIdx.x * R + tid, N - 1);
-    const uint32_t bytes = (uint32_t)min((size_t)K * 2, (size_t)pf_l2) & ~15u;
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(w + row * (size_t)K), "r"(bytes) : "memory");
-  }
-  pdl_wait();
-  pdl_trigger();
-
-  const uint4* xv = reinterpret_cast<const uint4*>(x);
-  if (kNorm) {  // RMSNorm prologue, exactly as in gemv_kernel
-    float ss[M];
-#pragma unroll
-    for (int m = 0; m < M; ++m) ss[m] = 0.f;
-    for (int i = tid; i < kvec; i += kGemvThreads) {
-#pragma unroll
-      for (int m = 0; m < M; ++m) {
-        float f[8];
-        unpack8(ld_16B(xv + (size_t)m * kvec + i), f);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) ss[m] += f[e] * f[e];
-      }
-    }
-#pragma unroll
-    for (int m = 0; m < M; ++m) {
-      ss[m] = warp_sum(ss[m]);
-      if (lane == 0) red[warp][m] = ss[m];
-    }
-    __syncthreads();
-    float rstd[M];
-#pragma unroll
-    for (int m = 0; m < M; ++m) {
-      float t = 0.f;
-#pragma unroll
-      for (int ww = 0; ww < kGemvWarps; ++ww) t += red[ww][m];
-      rstd[m] = rsqrtf(t / (float)K + eps);
-    }
-    uint4* xs = reinterpret_cast<uint4*>(xnorm_raw);
-    const uint4* lw = reinterpret_cast<const uint4*>(ln_w);
-    for (int i = tid; i < kvec; i += kGemvThreads) {
-      float g[8];
-      unpack8(ld_16B(lw + i), g);
-#pragma unroll
-      for (int m = 0; m < M; ++m) {
-        float f[8];
-        unpack8(ld_16B(xv + (size_t)m * kvec + i), f);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = g[e] * round_bf16(f[e] * rstd[m]);
-        xs[(size_t)m * kvec + i] = pack8(f);
-      }
-    }
-    __syncthreads();
-    xv = xs;
-  }
-
-  struct Buf {
-    uint4 a[R], b[R];
-  };
-  float acc[R][M];
-#pragma unroll
-  for (int r = 0; r < R; ++r)
-#pragma unroll
-    for (int m = 0; m < M; ++m) acc[r][m] = 0.f;
-  int parity = 0;
-
-  auto issue = [&](int s, Buf& bf) {
-    const int t = s / spt, j = s - t * spt;
-    const int n0 = ((int)blockIdx.x + t * (int)gridDim.x) * R;
-    const int i0 = tid + 2 * j * kGemvThreads, i1 = i0 + kGemvThreads;
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const uint4* row = reinterpret_cast<const uint4*>(w + (size_t)min(n0 + r, N - 1) * (size_t)K);
-      bf.a[r] = i0 < kvec ? ld_stream_16B(row + i0) : zero;
-      bf.b[r] = i1 < kvec ? ld_stream_16B(row + i1) : zero;
-    }
-  };
-  auto consume = [&](int s, const Buf& bf) {
-    const int t = s / spt, j = s - t * spt;
-    const int i0 = tid + 2 * j * kGemvThreads, i1 = i0 + kGemvThreads;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int i = h ? i1 : i0;
-      float xf[M][8];
-#pragma unroll
-      for (int m = 0; m < M; ++m) unpack8(i < kvec ? ld_16B(xv + (size_t)m * kvec + i) : zero, xf[m]);
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        float wf[8];
-        unpack8(h ? bf.b[r] : bf.a[r], wf);
-#pragma unroll
-        for (int m = 0; m < M; ++m)
-#pragma unroll
-          for (int e = 0; e < 8; ++e) acc[r][m] = fmaf(wf[e], xf[m][e], acc[r][m]);
-      }
-    }
-    if (j != spt - 1) return;
-    // the task is complete: 256 partials per output through shared memory, one warp per output, fixed order
-    const int n0 = ((int)blockIdx.x + t * (int)gridDim.x) * R;
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-#pragma unroll
-      for (int m = 0; m < M; ++m) {
-        part[parity][r * M + m][tid] = acc[r][m];
-        acc[r][m] = 0.f;
-      }
-    __syncthreads();
-    for (int o = warp; o < R * M; o += kGemvWarps) {
-      const int c = o / M, m = o - c * M;
-      float sum = 0.f;
-#pragma unroll
-      for (int ww = 0; ww < kGemvWarps; ++ww) sum += part[parity][c * M + m][ww * 32 + lane];
-      sum = warp_sum(sum);
-      const int n = n0 + c;
-      if (lane == 0 && n < N) {
-        if (epilogue & DLI_EPI_BIAS) sum += __bfloat162float(bias[n]);
-        float v = round_bf16(sum);
-        if (epilogue & DLI_EPI_GELU_NEW) v = round_bf16(gelu_new_f(v));
-        if (epilogue & DLI_EPI_RESIDUAL) v += __bfloat162float(residual[(size_t)m * N + n]);
-        y[(size_t)m * N + n] = __float2bfloat16_rn(v);
-      }
-    }
-    parity ^= 1;  // the other buffer is only rewritten after the next task's __syncthreads()
-  };
-
-  Buf A, B;
-  if (total > 0) issue(0, A);
-  for (int s = 0; s < total; s += 2) {
-    if (s + 1 < total) issue(s + 1, B);
-    consume(s, A);
-    if (s + 1 < total) {
-      if (s + 2 < total) issue(s + 2, A);
-      consume(s + 1, B);
-    }
-  }
-}
-
-template <int M, bool kNorm>
-static int launch_gemv_pipe(const bf16* x, const bf16* w, const bf16* bias, const bf16* residual, bf16* y, int N, int K,
-                            int epilogue, const bf16* ln_w, float eps, cudaStream_t s, int pf_l2) {
-  const int sms = sm_count_cached();
-  if (sms <= 0) return fail(DLI_ERR_CUDA, "gemv: no CUDA device");
-  const size_t dyn = kNorm ? (size_t)M * K * 2 : 0;
-  static PerDeviceOnce once;
-  {
-    const int d = current_device_slot();
-    if (d < 0) return DLI_ERR_CUDA;
-    std::lock_guard<std::mutex> lock(once.mu);
-    if (dyn > once.bytes[d]) once.done[d] = false;
-  }
-  DLI_ONCE_PER_DEVICE(once, dev, {
-    DLI_CUDA_CALL(cudaFuncSetAttribute(gemv_pipe_kernel<M, kNorm>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)(dyn > 131072 ? dyn : 131072)));
-    int o = 0;
-    DLI_CUDA_CALL(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, gemv_pipe_kernel<M, kNorm>, kGemvThreads, dyn));
-    once.value[dev] = o > 0 ? o : 1;
-    once.bytes[dev] = dyn;
-  });
-  const int ntasks = (N + kPipeRows - 1) / kPipeRows;
-  const int grid = ntasks < sms * once.value[dev] ? ntasks : sms * once.value[dev];
-  DLI_LAUNCH("gemv_pipe_kernel", gemv_pipe_kernel<M, kNorm>, dim3(grid), dim3(kGemvThreads), dyn, s, x, w, bias, residual, y,
-             N, K, epilogue, ln_w, eps, pf_l2);
-  return DLI_OK;
-}
-
 template <int M, bool kGated, bool kNorm>
 static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf16* residual, bf16* y, int N, int K,
                        int epilogue, const bf16* ln_w, float eps, cudaStream_t s, float* cand = nullptr,
@@ -508,12 +319,6 @@ static int launch_gemv(const bf16* x, const bf16* w, const bf16* bias, const bf1
   if (grid_out) *grid_out = grid;
   // bytes per row prefetched into L2 across the kernel boundary (the whole row, or 8 KB)
   static const int pf_l2 = getenv("DLI_GEMV_PF_L2") ? atoi(getenv("DLI_GEMV_PF_L2")) : 8192;
-  // Few 4-row tasks per CTA (fewer than DLI_GEMV_PIPE, default 8; 0 = never): the pipelined 2-row kernel
-  static const int pipe_below = getenv("DLI_GEMV_PIPE") ? atoi(getenv("DLI_GEMV_PIPE")) : 8;
-  if constexpr (!kGated && M <= 2) {
-    if (cand == nullptr && ngroups_total < pipe_below * grid)
-      return launch_gemv_pipe<M, kNorm>(x, w, bias, residual, y, N, K, epilogue, ln_w, eps, s, pf_l2);
-  }
   static const int deal = getenv("DLI_GEMV_DEAL") ? atoi(getenv("DLI_GEMV_DEAL")) : 0;  // measurement knob, see kernel
   DLI_LAUNCH("gemv_kernel", gemv_kernel<M, kGated, kNorm>, dim3(grid), dim3(kGemvThreads), dyn, s, x, w, bias, residual,
              y, N, K, epilogue, ln_w, eps, pf_l2, cand, deal);

@@ -395,30 +395,6 @@ def test_lm_head_fused_argmax_ties_take_the_lowest_index(cuda):
         assert tokens.item() == min(dup, best) == torch.argmax(logits.float(), dim=-1).item()
 
 
-@pytest.mark.parametrize("M", [1, 2])
-@pytest.mark.parametrize("N,K", [(4096, 4096), (4096, 14336), (6144, 4096), (1000, 264), (5, 512), (2047, 2048)])
-def test_pipelined_gemv_is_bit_identical_to_the_four_row_kernel(cuda, M, N, K):
-    """Matrices of few tasks per CTA go to the software-pipelined 2-row kernel (gemv_pipe_kernel) at <= 2 rows of x;
-    4 rows of x always take the 4-row kernel.  Both sum every output in the same order, so a row of x gives the same
-    bits either way — with bias, GELU and residual epilogues and with the fused RMSNorm prologue."""
-    from dli_b200 import ops
-
-    gen = torch.Generator(device="cuda").manual_seed(N + K + M)
-    x = torch.randn(M, K, device=cuda, generator=gen).to(BF)
-    x4 = x[:1].repeat(4, 1).contiguous() if M == 1 else torch.cat((x, x)).contiguous()
-    w = (torch.randn(N, K, device=cuda, generator=gen) * 0.02).to(BF)
-    bias = torch.randn(N, device=cuda, generator=gen).to(BF)
-    res = torch.randn(M, N, device=cuda, generator=gen).to(BF)
-    res4 = res[:1].repeat(4, 1).contiguous() if M == 1 else torch.cat((res, res)).contiguous()
-    assert torch.equal(ops.gemv(x, w), ops.gemv(x4, w)[:M])
-    assert torch.equal(ops.gemv(x, w, bias=bias, residual=res), ops.gemv(x4, w, bias=bias, residual=res4)[:M])
-    assert torch.equal(ops.gemv(x, w, bias=bias, epilogue=ops.EPI_GELU_NEW), ops.gemv(x4, w, bias=bias, epilogue=ops.EPI_GELU_NEW)[:M])
-    _check_linear(ops.gemv(x, w), _lin_ref(x, w), K)
-    if K % 8 == 0 and K <= 16384:
-        ln = (1.0 + 0.1 * torch.randn(K, device=cuda, generator=gen)).to(BF)
-        assert torch.equal(ops.rmsnorm_linear(x, ln, 1e-5, w, residual=res), ops.rmsnorm_linear(x4, ln, 1e-5, w, residual=res4)[:M])
-
-
 def _gated_ref(x, wg, wu):
     g = (x.float() @ wg.float().t()).to(BF)
     u = (x.float() @ wu.float().t()).to(BF)
