@@ -777,7 +777,8 @@ class ShardEngine:
         m["in_tok"] = [inn[p, world - 1, off_t:off_t + b * 4].view(torch.int32) for p in range(period)]
         m["in_cands_ptr"] = [inn[p].data_ptr() + off_c for p in range(period)]  # set r starts r * nbytes later
         self._mail = m
-        self._graphs = {k: v for k, v in self._graphs.items() if not (isinstance(k[-1], str) and k[-1].startswith("mail"))}
+        self._graphs = {k: v for k, v in self._graphs.items()
+                        if not any(isinstance(e, str) and e.startswith("mail") for e in k)}
 
     def _graphed(self, key, body, restore=()):
         """Run `body` as a CUDA graph captured on first use (after one eager warm-up run whose effect on the
@@ -815,7 +816,7 @@ class ShardEngine:
         m = self._mail
         return (slot + m["H"] * sigma) % m["P"]
 
-    def mail_compute(self, mb: int) -> None:
+    def mail_compute(self, mb: int, dry: bool = False):
         """This stage's decode step of slot mb: input from the mailbox the previous stage's mail arrived in (stage 0:
         the slot's token), output into this tick's outgoing mail (last stage with the whole head: the chosen tokens)."""
         m = self._mail
@@ -844,9 +845,11 @@ class ShardEngine:
             log = st["token_log"] if (self.has_head or self.is_first) else None
             ops.decode_advance(tokens, log, st["positions"], st["seq_lens"], st["step"])
 
+        if dry:
+            return body, [st[k] for k in ("positions", "seq_lens", "step")]
         self._graphed((B, mb, "mail_compute"), body, restore=[st[k] for k in ("positions", "seq_lens", "step")])
 
-    def mail_head(self, mb: int) -> None:
+    def mail_head(self, mb: int, dry: bool = False):
         """Vocabulary-parallel head: final norm + this stage's rows of the head on slot mb's final hidden state (as it
         arrived from the last stage), the slice's best (logit, token id) into this tick's outgoing mail."""
         m = self._mail
@@ -871,6 +874,8 @@ class ShardEngine:
             ops.linear(xn, self.w["head"], out=st["logits"])
             ops.argmax_candidate(st["logits"], self.v0, cand)
 
+        if dry:
+            return body, []
         self._graphed((B, mb, "mail_head"), body)
 
     def mail_ingest(self, mb: int) -> None:
@@ -888,7 +893,28 @@ class ShardEngine:
             else:
                 st["tokens"].copy_(m["in_tok"][rd])  # 4*b bytes, device to device
 
+        if dry:
+            return body, [st["tokens"]]
         self._graphed((B, mb, "mail_ingest"), body, restore=[st["tokens"]])
+
+    def mail_tick(self, ingest: Optional[int], compute: Optional[int], head: Optional[int]) -> None:
+        """Everything this stage does in one tick — token in (stage 0), the stage's decode step, the head slice —
+        as ONE CUDA graph per combination of slots (in a full pipeline the combination is a function of the tick's
+        phase, so there are P graphs): one submission per tick instead of three, no idle gaps between them."""
+        bodies, restore = [], []
+        for fn, slot in ((self.mail_ingest, ingest), (self.mail_compute, compute), (self.mail_head, head)):
+            if slot is not None:
+                b, r = fn(slot, dry=True)
+                bodies.append(b)
+                restore += r
+        if not bodies:
+            return
+
+        def body():
+            for b in bodies:
+                b()
+
+        self._graphed((self._mail["b"], "mail_tick", ingest, compute, head), body, restore=restore)
 
     def decode_step_host(self, tokens_in: torch.Tensor, tokens_out: torch.Tensor) -> torch.Tensor:
         """One decode step with HOST buffers, the per-token call a streaming client

@@ -327,17 +327,18 @@ class MailboxRunner:
         w = self.pending.pop(t - self.H, None)
         if w is not None:
             self.ex.wait(w)  # the exchange issued H ticks ago carries this tick's inputs
-        if st.is_first:
-            j = self._active(self.sig_in, t)
-            if j is not None:
-                st.ingest(j)
-        j = self._active(self.rank, t)
-        if j is not None:
-            st.compute(j)
-        if self.vp:
-            j = self._active(self.sig_head, t)
-            if j is not None:
-                st.head(j)
+        ji = self._active(self.sig_in, t) if st.is_first else None
+        jc = self._active(self.rank, t)
+        jh = self._active(self.sig_head, t) if self.vp else None
+        if hasattr(st, "tick_all"):
+            st.tick_all(ji, jc, jh)  # one submission for the whole tick
+        else:
+            if ji is not None:
+                st.ingest(ji)
+            if jc is not None:
+                st.compute(jc)
+            if jh is not None:
+                st.head(jh)
         ph = t % self.P
         self.pending[t] = self.ex.issue(st.mail_out(ph), st.mail_in(ph), phase=ph)
         self.t += 1
@@ -386,6 +387,9 @@ class MailStage:
 
     def ingest(self, slot):
         self.eng.mail_ingest(slot)
+
+    def tick_all(self, ingest, compute, head):
+        self.eng.mail_tick(ingest, compute, head)
 
 
 def mailbox_period(n_micro: int, world: int, hop: int, vp: bool) -> int:
