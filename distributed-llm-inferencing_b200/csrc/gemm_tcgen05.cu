@@ -686,7 +686,17 @@ int dli_gemm_bf16(const void* x, const void* w, const void* bias, const void* re
   if (M <= 32) return launch_gemm<32, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   if (M <= 64) return launch_gemm<64, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   if (M <= 128) return launch_gemm<128, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
-  if (N % 256 == 0 || N >= 2048) return launch_gemm<256, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  if (N % 256 == 0 || N >= 2048) {
+    // Wave quantisation: the persistent kernel walks m_tiles x n_tiles tiles on one CTA per SM, and a 2k-token
+    // prefill has few of them (o / down: 16 x 16 = 256 tiles = 1.73 waves of 148, qkv 2.59).  240-column tiles
+    // (UMMA N = 240) give 288 and 416 tiles = 1.95 and 2.81 waves: the same number of rounds of shorter tiles.
+    // Cost model: rounds x tile width; 256 wins whenever M is large (tens of thousands of rows).
+    const int sms = sm_count_cached() > 0 ? sm_count_cached() : 148;
+    const long long m_tiles = (M + 127) / 128;
+    auto cost = [&](int bn) { return ((m_tiles * ((N + bn - 1) / bn) + sms - 1) / sms) * bn; };
+    if (cost(240) < cost(256)) return launch_gemm<240, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+    return launch_gemm<256, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+  }
   if (N % 128 == 0 || N > 128) return launch_gemm<128, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   if (N > 32) return launch_gemm<64, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   return launch_gemm<32, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);

@@ -878,7 +878,7 @@ class ShardEngine:
             return body, []
         self._graphed((B, mb, "mail_head"), body)
 
-    def mail_ingest(self, mb: int) -> None:
+    def mail_ingest(self, mb: int, dry: bool = False):
         """Stage 0: slot mb's next input token from the mail that just arrived — the global argmax over the stages'
         candidates (vocabulary-parallel head; lowest id wins ties) or the last stage's chosen token."""
         m = self._mail
