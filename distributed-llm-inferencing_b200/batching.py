@@ -50,6 +50,7 @@ class ContinuousBatcher:
         self._stop = threading.Event()
         self._thread: Optional[threading.Thread] = None
         self.steps = 0
+        self.grow = 64  # tokens of KV pages a sequence reserves ahead (the pool is shared on demand)
         st = engine._make_state(self.B, 0)  # the joint decode state: row i <-> sequence i
         st["seq_lens"].zero_()               # all rows idle
         st["positions"].zero_()
@@ -95,7 +96,15 @@ class ContinuousBatcher:
             except queue.Empty:
                 return
             T = len(req.ids)
-            eng.start_batch(1, T, req.max_length, mb=i)  # sequence id i: reserves its KV pages
+            try:
+                # sequence id i: pages for the prompt and the next GROW tokens; step() reserves more as it grows
+                eng.start_batch(1, T, req.max_length, mb=i, reserve_len=T + self.grow)
+            except RuntimeError as e:  # the shared page pool is empty right now
+                if any(s is not None for s in self.slots):
+                    self.pending.put(req)  # wait for a running request to leave
+                else:
+                    req.future.set_exception(e)  # nothing will ever free enough pages
+                return
             ids = req.ids.to(device=eng.device, dtype=torch.int32)
             dev = eng.device
             self._rows["seeds"][i:i + 1].fill_(req.seed)
@@ -144,6 +153,24 @@ class ContinuousBatcher:
         if not any(s is not None for s in self.slots):
             return 0
         eng = self.eng
+        # paged KV on demand: a sequence about to outgrow its pages takes GROW tokens' worth more from the shared pool
+        grew = False
+        for i, req in enumerate(self.slots):
+            if req is None:
+                continue
+            cur = len(req.ids) + len(req.out)  # tokens in the cache after this step
+            if cur > eng.kv.capacity(i):
+                try:
+                    grew |= eng.kv.reserve(i, min(req.max_length, cur + self.grow))
+                except RuntimeError as e:
+                    req.future.set_exception(e)
+                    self.slots[i] = None
+                    eng._state(self.B, 0)["seq_lens"][i:i + 1].zero_()
+                    eng.kv.release(i)
+        if grew:
+            eng.kv.commit()
+        if not any(s is not None for s in self.slots):
+            return 0
         toks = eng.decode_step(self.B)  # replayed CUDA graph over all rows (idle rows are no-ops for the caches)
         self._tok_host.copy_(toks, non_blocking=True)
         torch.cuda.current_stream().synchronize()

@@ -157,10 +157,14 @@ class PagedKVCache:
     layers.  Replaces the grow-by-torch.cat cache of TF:cache_utils.py:102-121
     (an O(S) copy per layer per token) with in-place page writes."""
 
-    def __init__(self, n_layers, n_kv, hd, page_size, max_seqs, max_seq_len, device):
+    def __init__(self, n_layers, n_kv, hd, page_size, max_seqs, max_seq_len, device, pool_tokens=None):
+        """pool_tokens: size of the page pool in tokens; default max_seqs * max_seq_len (every sequence can reach the
+        maximum at once).  A smaller pool is shared on demand: sequences reserve pages as they grow (the continuous
+        batcher does) and a reservation that finds the pool empty raises."""
         self.page_size = page_size
         self.max_pages = (max_seq_len + page_size - 1) // page_size
-        self.num_pages = max_seqs * self.max_pages
+        self.num_pages = max_seqs * self.max_pages if not pool_tokens else \
+            max(self.max_pages, (int(pool_tokens) + page_size - 1) // page_size)
         self.k = [torch.zeros(self.num_pages, n_kv, page_size, hd, dtype=BF, device=device) for _ in range(n_layers)]
         self.v = [torch.zeros(self.num_pages, n_kv, page_size, hd, dtype=BF, device=device) for _ in range(n_layers)]
         self.free: List[int] = list(range(self.num_pages - 1, -1, -1))
@@ -168,18 +172,28 @@ class PagedKVCache:
         self._host_table = torch.zeros(max_seqs, self.max_pages, dtype=torch.int32)
         self.page_table = self._host_table.to(device)
 
-    def reserve(self, seq: int, n_tokens: int) -> None:
-        """Make sure sequence `seq` owns pages for `n_tokens` tokens."""
+    def capacity(self, seq: int) -> int:
+        """Tokens sequence `seq` has pages for."""
+        return len(self.owned.get(seq, ())) * self.page_size
+
+    def reserve(self, seq: int, n_tokens: int) -> bool:
+        """Make sure sequence `seq` owns pages for `n_tokens` tokens.  Returns True if pages were added (the caller
+        then commit()s the page table before the next kernel reads it)."""
         need = (n_tokens + self.page_size - 1) // self.page_size
         if need > self.max_pages:
             raise ValueError(f"sequence of {n_tokens} tokens exceeds max_seq_len of the cache")
         have = self.owned.setdefault(seq, [])
+        if len(have) >= need:
+            return False
+        if need - len(have) > len(self.free):
+            raise RuntimeError("KV cache out of pages")
         while len(have) < need:
             if not self.free:
                 raise RuntimeError("KV cache out of pages")
             p = self.free.pop()
             self._host_table[seq, len(have)] = p
             have.append(p)
+        return True
 
     def commit(self) -> None:
         self.page_table.copy_(self._host_table, non_blocking=True)
@@ -199,7 +213,7 @@ class PagedKVCache:
 class ShardEngine:
     def __init__(self, spec: ModelSpec, start_layer: int = 0, end_layer: Optional[int] = None,
                  device: str = "cuda:0", max_batch: int = 1, max_seq_len: int = 2048, page_size: int = 16,
-                 use_cuda_graph: bool = True, head_shard: Optional[tuple] = None):
+                 use_cuda_graph: bool = True, head_shard: Optional[tuple] = None, kv_pool_tokens: Optional[int] = None):
         """head_shard=(rank, world): vocabulary-parallel lm_head for a pipeline — every stage holds
         rows [rank*ceil(V/world), ...) of the head (the reference's sharder copies the head into
         every shard anyway, shard_model.py:76-78), so the last stage does not carry the whole
@@ -231,7 +245,7 @@ class ShardEngine:
         self.w: Dict[str, torch.Tensor] = {}
         self.layers: List[Dict[str, torch.Tensor]] = []
         self.kv = PagedKVCache(self.n_local, spec.n_kv_heads, spec.head_dim, page_size, max_batch, max_seq_len,
-                               self.device)
+                               self.device, pool_tokens=kv_pool_tokens)
         if spec.arch == "llama":
             self.cos, self.sin = rope_tables(spec, max_seq_len, self.device)
         else:
@@ -536,7 +550,7 @@ class ShardEngine:
     def _state(self, B: int, mb: int = 0) -> dict:
         return self._dec[(B, mb)]
 
-    def start_batch(self, B: int, prompt_len: int, max_total_len: int, mb: int = 0) -> None:
+    def start_batch(self, B: int, prompt_len: int, max_total_len: int, mb: int = 0, reserve_len: Optional[int] = None) -> None:
         """Reserve KV pages for the B sequences of micro-batch slot `mb` (sequence ids
         mb*B .. mb*B+B-1) and reset the slot's decode state.  Slot 0 with the full
         batch is the single-GPU case; a pipeline stage keeps one slot per micro-batch
@@ -547,7 +561,8 @@ class ShardEngine:
             raise ValueError(f"total length {max_total_len} > max_seq_len {self.max_seq_len}")
         for b in range(mb * B, (mb + 1) * B):
             self.kv.release(b)
-            self.kv.reserve(b, max_total_len)
+        for b in range(mb * B, (mb + 1) * B):  # reserve_len < max_total_len: the caller grows the sequence on demand
+            self.kv.reserve(b, max_total_len if reserve_len is None else min(max_total_len, reserve_len))
         self.kv.commit()
         self._make_state(B, mb)
         st = self._dec[(B, mb)]

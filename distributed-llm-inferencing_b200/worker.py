@@ -101,6 +101,9 @@ class Worker:
         # (continuous batching; greedy or the reference's sampling call per request); the reference serialises requests (worker/Dockerfile:45)
         self.batching = env.get("DLI_BATCHING", "0") == "1"
         self.max_batch = int(env.get("DLI_MAX_BATCH", "8")) if self.batching else 1
+        # DLI_KV_POOL_TOKENS: size of the paged KV pool in tokens (default: max batch x max sequence length, i.e. every
+        # sequence can reach the maximum at once); with batching, sequences take pages from it as they grow
+        self.kv_pool_tokens = int(env.get("DLI_KV_POOL_TOKENS", "0")) or None
         self.batchers: Dict[str, object] = {}
         # With batching the WSGI server is threaded: everything that touches the dicts above or runs an
         # engine directly holds this lock; only the wait on a batcher's future happens outside it.
@@ -128,7 +131,7 @@ class Worker:
         if max_batch is None:
             max_batch = self.max_batch if end is None else 1
         eng = ShardEngine(spec, start, end, device=self.cuda_device, max_batch=max_batch,
-                          max_seq_len=min(self.max_seq_len, spec.max_pos))
+                          max_seq_len=min(self.max_seq_len, spec.max_pos), kv_pool_tokens=self.kv_pool_tokens)
         eng.load_state_dict(load_hf_state_dict(path, eng.start, eng.end, spec.n_layers))
         eng.eos_token_ids, eng.pad_token_id = _stop_tokens(path, cfg)
         eng.prefill_chunk = self.prefill_chunk

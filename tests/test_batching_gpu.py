@@ -134,3 +134,49 @@ def test_sampled_requests_are_reproducible_and_independent_of_the_batch(cuda):
     assert torch.equal(together[1], alone_g)  # greedy row untouched by the sampling kernel
     assert not torch.equal(run([(prompts[0], True, 124)])[0], alone_s)
     assert not torch.equal(run([(prompts[0], False, 0)])[0], alone_s)  # and it is not just the argmax
+
+
+def test_kv_pages_are_taken_on_demand_from_a_shared_pool(cuda):
+    """A page pool smaller than max_batch x max_seq_len: sequences reserve pages as they grow, a request that finds
+    the pool empty waits for a running one to leave, and every request still gets the tokens it gets alone."""
+    from dli_b200.batching import ContinuousBatcher
+    from dli_b200.engine import ModelSpec, ShardEngine
+    from oracle import decoder_ref as R
+
+    c = load_case("llama_tiny")
+    spec = ModelSpec.from_hf_config(spec_kwargs(c["config"]))
+    sd = R.seeded_state_dict(R.ModelSpec(**spec.__dict__), c["seed"], c["std"])
+    g = torch.Generator().manual_seed(9)
+    reqs = [(torch.randint(0, spec.vocab, (T,), generator=g), T + n) for T, n in [(20, 30), (18, 40), (25, 22), (9, 50), (30, 31)]]
+    full = ShardEngine(spec, max_batch=4, max_seq_len=128)
+    full.load_state_dict(sd)
+    b = ContinuousBatcher(full, max_batch=4)
+    alone = []
+    for ids, ml in reqs:
+        f = b.submit(ids, ml)
+        while not f.done():
+            b.step()
+        alone.append(f.result())
+    small = ShardEngine(spec, max_batch=4, max_seq_len=128, kv_pool_tokens=160)  # 10 pages of 16 for up to 4 x 8
+    small.load_state_dict(sd)
+    assert small.kv.num_pages == 10
+    b2 = ContinuousBatcher(small, max_batch=4)
+    b2.grow = 16
+    futs = [b2.submit(ids, ml) for ids, ml in reqs]
+    low = small.kv.num_pages
+    for _ in range(2000):
+        if all(f.done() for f in futs):
+            break
+        b2.step()
+        low = min(low, len(small.kv.free))
+    assert all(f.done() for f in futs)
+    for f, want in zip(futs, alone):
+        assert torch.equal(f.result(), want)
+    assert low <= 2 and len(small.kv.free) == 10  # the pool really ran (nearly) dry, and everything came back
+    # a long request takes most of the pool once it has drained
+    big = b2.submit(torch.randint(0, spec.vocab, (100,), generator=g), 127)
+    for _ in range(400):
+        if big.done():
+            break
+        b2.step()
+    assert big.done() and big.exception() is None  # 127 tokens = 8 pages <= 10: fits once the pool is empty again
