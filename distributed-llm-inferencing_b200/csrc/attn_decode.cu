@@ -168,6 +168,31 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     cp_async_commit();
   }
 
+  // Fused form: cos/sin of the new position, and on the CTA that owns the last tile the new token's k, v and cache
+  // page, are needed only once the first K/V tile has landed.  Requested here, their round trips hide under that
+  // wait instead of following it (the kernel is bound by its chain of dependent loads, not by bandwidth).
+  // Every thread rotates elements i = tid % (HD/2) only (the block size is a multiple of HD/2), so one pair does.
+  float pre_c = 1.f, pre_s = 0.f, pre_k1 = 0.f, pre_k2 = 0.f;
+  uint4 pre_v = make_uint4(0u, 0u, 0u, 0u);
+  int pre_page = 0;
+  if (fused && t_begin < t_end) {
+    const int pos = seq_len - 1, half = HD / 2;
+    if (cos_t) {
+      pre_c = __bfloat162float(cos_t[(size_t)pos * half + (tid % half)]);
+      pre_s = __bfloat162float(sin_t[(size_t)pos * half + (tid % half)]);
+    }
+    if (t_end == tile_hi && tid < half + CH) {
+      pre_page = pt[pos >> page_shift];
+      if (tid < half) {
+        const bf16* knew = q + (size_t)b * q_stride + (size_t)(H + kvh) * HD;
+        pre_k1 = __bfloat162float(knew[tid]);
+        pre_k2 = __bfloat162float(knew[tid + half]);
+      } else {
+        pre_v = ld_16B(q + (size_t)b * q_stride + (size_t)(H + KV + kvh) * HD + (tid - half) * 8);
+      }
+    }
+  }
+
   for (int tile = t_begin; tile < t_end; ++tile) {
     const int stage = (tile - t_begin) % NS;
     cp_async_wait<NS - 1>();  // all but the newest NS-1 groups have landed: this tile is in
@@ -177,15 +202,12 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
       // this CTA owns the tile of the new token (position seq_len-1): rotate its k, store
       // k and v to the cache page and patch them into the staged tile
       const int pos = seq_len - 1, row = pos - tile * kAttnTile, half = HD / 2;
-      const int page = pt[pos >> page_shift];
-      const size_t coff = ((((size_t)page * KV + kvh) << page_shift) + (pos & page_mask)) * HD;
-      const bf16* knew = q + (size_t)b * q_stride + (size_t)(H + kvh) * HD;
-      const bf16* vnew = q + (size_t)b * q_stride + (size_t)(H + KV + kvh) * HD;
+      const size_t coff = ((((size_t)pre_page * KV + kvh) << page_shift) + (pos & page_mask)) * HD;
       if (tid < half) {
         const int i = tid;
-        float x1 = __bfloat162float(knew[i]), x2 = __bfloat162float(knew[i + half]);
+        float x1 = pre_k1, x2 = pre_k2;
         if (cos_t) {
-          const float c = __bfloat162float(cos_t[(size_t)pos * half + i]), sn = __bfloat162float(sin_t[(size_t)pos * half + i]);
+          const float c = pre_c, sn = pre_s;
           const float o1 = round_bf16(x1 * c) + round_bf16(-x2 * sn);
           const float o2 = round_bf16(x2 * c) + round_bf16(x1 * sn);
           x1 = o1; x2 = o2;
@@ -197,7 +219,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
         *reinterpret_cast<bf16*>(smem + (cK - sQ) + swz<RB>(row, (i + half) >> 3) + (i & 7) * 2) = b2;
       } else if (tid < half + CH) {
         const int c = tid - half;
-        const uint4 u = ld_16B(vnew + c * 8);
+        const uint4 u = pre_v;
         st_16B(v_cache_w + coff + c * 8, u);
         *reinterpret_cast<uint4*>(smem + (cV - sQ) + swz<RB>(row, c)) = u;
       }
@@ -206,13 +228,13 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     if (tile == t_begin) {
       if (fused && cos_t) {
         // rotate the G query rows in shared memory (rotate-half, bf16 op by op)
-        const int pos = seq_len - 1, half = HD / 2;
+        const int half = HD / 2;
         for (int idx = tid; idx < G * half; idx += kAttnThreads) {
           const int g = idx / half, i = idx - g * half;
           bf16* p1 = reinterpret_cast<bf16*>(smem + swz<RB>(g, i >> 3) + (i & 7) * 2);
           bf16* p2 = reinterpret_cast<bf16*>(smem + swz<RB>(g, (i + half) >> 3) + (i & 7) * 2);
           const float x1 = __bfloat162float(*p1), x2 = __bfloat162float(*p2);
-          const float c = __bfloat162float(cos_t[(size_t)pos * half + i]), sn = __bfloat162float(sin_t[(size_t)pos * half + i]);
+          const float c = pre_c, sn = pre_s;  // i == tid % half on every iteration
           *p1 = __float2bfloat16_rn(round_bf16(x1 * c) + round_bf16(-x2 * sn));
           *p2 = __float2bfloat16_rn(round_bf16(x2 * c) + round_bf16(x1 * sn));
         }
@@ -395,6 +417,26 @@ attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restric
   pdl_trigger();
   if (bh >= n_bh) return;
   const float* ml = part_ml + (size_t)bh * num_splits * 2;
+  const float* po = part_o + (size_t)bh * num_splits * HD + lane * VEC;
+  // the first 8 splits' partial outputs are requested together with the (max, sum) pairs: one L2 round trip for
+  // a 2k-context merge (9 splits) instead of two dependent ones
+  constexpr int kPre = 8;
+  float pv[kPre][VEC];
+#pragma unroll
+  for (int s = 0; s < kPre; ++s) {
+    if (s < num_splits) {
+      if (VEC == 4) {
+        const float4 t = *reinterpret_cast<const float4*>(po + (size_t)s * HD);
+        pv[s][0] = t.x; pv[s][1] = t.y; pv[s][2] = t.z; pv[s][VEC - 1] = t.w;
+      } else {
+        const float2 t = *reinterpret_cast<const float2*>(po + (size_t)s * HD);
+        pv[s][0] = t.x; pv[s][VEC - 1] = t.y;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) pv[s][i] = 0.f;
+    }
+  }
   // up to 64 splits: lane owns splits lane and lane + 32
   float m0 = -INFINITY, l0 = 0.f, m1 = -INFINITY, l1 = 0.f;
   if (lane < num_splits) { m0 = ml[lane * 2]; l0 = ml[lane * 2 + 1]; }
@@ -409,9 +451,14 @@ attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restric
   float acc[VEC];
 #pragma unroll
   for (int i = 0; i < VEC; ++i) acc[i] = 0.f;
-  const float* po = part_o + (size_t)bh * num_splits * HD + lane * VEC;
+#pragma unroll
+  for (int s = 0; s < kPre; ++s) {  // (splits beyond num_splits hold zeros and a zero weight)
+    const float f = __shfl_sync(0xffffffffu, f0, s);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) acc[i] += (s < num_splits ? f : 0.f) * pv[s][i];
+  }
 #pragma unroll 8
-  for (int s = 0; s < num_splits; ++s) {
+  for (int s = kPre; s < num_splits; ++s) {
     const float f = __shfl_sync(0xffffffffu, s < 32 ? f0 : f1, s & 31);
     float v[VEC];
     if (VEC == 4) {
