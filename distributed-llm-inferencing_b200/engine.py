@@ -773,13 +773,21 @@ class ShardEngine:
     # ids b x int32] — and one all-gather per tick delivers all N mails to everybody.  Tick t writes mail_out[t % P]
     # and the exchange fills mail_in[t % P][src]; the kernels of a slot read and write those buffers in place
     # (their addresses are fixed per slot, so they are baked into the slot's CUDA graphs): no copies either side.
-    def attach_mailbox(self, b: int, n_slots: int, period: int, hop: int, rank: int, world: int) -> None:
+    def attach_mailbox(self, b: int, n_slots: int, period: int, hop: int, rank: int, world: int,
+                       with_logits: bool = False) -> None:
         """b sequences per slot, n_slots slots in flight, `period` ticks per round of a slot, `hop` ticks between
-        a stage and the next.  The head lives on the last stage (has_head) or is split over the stages (head_shard)."""
+        a stage and the next.  The head lives on the last stage (has_head) or is split over the stages (head_shard).
+        with_logits (vocabulary-parallel head, one sequence per slot): the mail also carries this stage's slice of
+        the logits row, so that stage 0 can SAMPLE from the whole row (the reference's default call) and not only
+        take the argmax."""
         d = self.spec.d_model
         off_c = b * d * 2
         off_t = off_c + b * 8
-        nbytes = (off_t + b * 4 + 255) // 256 * 256
+        off_l = (off_t + b * 4 + 15) // 16 * 16
+        per = (self.spec.vocab + world - 1) // world  # vocabulary rows per stage (the last one may hold fewer)
+        if with_logits and (b != 1 or self.head_shard is None):
+            raise ValueError("logits travel in the mail only with a vocabulary-parallel head and one sequence per slot")
+        nbytes = ((off_l + per * 2 if with_logits else off_t + b * 4) + 255) // 256 * 256
         dev = self.device
         out = torch.zeros(period, nbytes, dtype=torch.uint8, device=dev)
         inn = torch.zeros(period, world, nbytes, dtype=torch.uint8, device=dev)
@@ -791,6 +799,14 @@ class ShardEngine:
         m["in_h"] = [[inn[p, r, :off_c].view(BF).view(b, d) for r in range(world)] for p in range(period)]
         m["in_tok"] = [inn[p, world - 1, off_t:off_t + b * 4].view(torch.int32) for p in range(period)]
         m["in_cands_ptr"] = [inn[p].data_ptr() + off_c for p in range(period)]  # set r starts r * nbytes later
+        m["with_logits"] = with_logits
+        if with_logits:
+            m["per"] = per
+            m["out_logits"] = [out[p, off_l:off_l + (self.v1 - self.v0) * 2].view(BF).view(1, self.v1 - self.v0)
+                               for p in range(period)]
+            m["in_logits"] = [inn[p, :, off_l:off_l + per * 2].view(BF) for p in range(period)]  # [N, per], strided
+            if self.is_first:
+                m["logits_row"] = torch.zeros(1, world * per, dtype=BF, device=dev)  # the slices side by side
         self._mail = m
         self._graphs = {k: v for k, v in self._graphs.items()
                         if not any(isinstance(e, str) and e.startswith("mail") for e in k)}
@@ -873,12 +889,13 @@ class ShardEngine:
         hf = m["in_h"][(ph - H) % P][N - 1]
         st = self._dec[(B, mb)]
         cand = m["out_cand"][ph]
+        logits = m["out_logits"][ph] if m["with_logits"] else st["logits"]
         self._workspace(B)
 
         def body():
             s = self.spec
             if B <= _GEMV_MAX_ROWS and s.arch == "llama":
-                ops.linear_argmax(hf, self.w["head"], st["logits"], self._head_scratch(B), cand=cand,
+                ops.linear_argmax(hf, self.w["head"], logits, self._head_scratch(B), cand=cand,
                                   ln_w=self.w["norm"], eps=s.eps, idx_offset=self.v0)
                 return
             xn = self._x[:B]
@@ -886,16 +903,19 @@ class ShardEngine:
                 ops.add_rmsnorm(hf, self.w["norm"], s.eps, out=xn)
             else:
                 ops.add_layernorm(hf, self.w["norm"], self.w["normb"], s.eps, out=xn)
-            ops.linear(xn, self.w["head"], out=st["logits"])
-            ops.argmax_candidate(st["logits"], self.v0, cand)
+            ops.linear(xn, self.w["head"], out=logits)
+            ops.argmax_candidate(logits, self.v0, cand)
 
         if dry:
             return body, []
         self._graphed((B, mb, "mail_head"), body)
 
-    def mail_ingest(self, mb: int, dry: bool = False):
+    def mail_ingest(self, mb: int, dry: bool = False, sample: bool = False):
         """Stage 0: slot mb's next input token from the mail that just arrived — the global argmax over the stages'
-        candidates (vocabulary-parallel head; lowest id wins ties) or the last stage's chosen token."""
+        candidates (vocabulary-parallel head; lowest id wins ties) or the last stage's chosen token.  sample (mail
+        with logits): the stages' logits slices are put side by side and the slot's token is drawn from the whole row
+        with the slot's st["row_sampling"] (seed, mask, the reference's temperature / top-k / top-p), keyed by the
+        position of the token that produced the logits — the draw the whole head on one stage makes."""
         m = self._mail
         B, H, P, N = m["b"], m["H"], m["P"], m["N"]
         ph = self.mail_phase(N + 1 if m["vp"] else N, mb)
@@ -905,21 +925,27 @@ class ShardEngine:
         def body():
             if m["vp"]:
                 ops.argmax_merge_strided(m["in_cands_ptr"][rd], N, B, m["bytes"] // 4, st["tokens"])
+                if sample:
+                    rows, per = st["row_sampling"], m["per"]
+                    m["logits_row"].view(N, per).copy_(m["in_logits"][rd])  # one strided copy: slice r -> columns r*per..
+                    torch.sub(st["positions"], 1, out=rows["steps"])     # stage 0 has already advanced past that token
+                    ops.sample_rows(m["logits_row"][:, :self.spec.vocab], st["tokens"], rows["seeds"], rows["steps"],
+                                    rows["mask"], **rows["params"])
             else:
                 st["tokens"].copy_(m["in_tok"][rd])  # 4*b bytes, device to device
 
         if dry:
             return body, [st["tokens"]]
-        self._graphed((B, mb, "mail_ingest"), body, restore=[st["tokens"]])
+        self._graphed((B, mb, "mail_ingest", sample), body, restore=[st["tokens"]])
 
-    def mail_tick(self, ingest: Optional[int], compute: Optional[int], head: Optional[int]) -> None:
+    def mail_tick(self, ingest: Optional[int], compute: Optional[int], head: Optional[int], sample: bool = False) -> None:
         """Everything this stage does in one tick — token in (stage 0), the stage's decode step, the head slice —
         as ONE CUDA graph per combination of slots (in a full pipeline the combination is a function of the tick's
         phase, so there are P graphs): one submission per tick instead of three, no idle gaps between them."""
         bodies, restore = [], []
         for fn, slot in ((self.mail_ingest, ingest), (self.mail_compute, compute), (self.mail_head, head)):
             if slot is not None:
-                b, r = fn(slot, dry=True)
+                b, r = fn(slot, dry=True, sample=sample) if fn == self.mail_ingest else fn(slot, dry=True)
                 bodies.append(b)
                 restore += r
         if not bodies:
@@ -929,7 +955,8 @@ class ShardEngine:
             for b in bodies:
                 b()
 
-        self._graphed((self._mail["b"], "mail_tick", ingest, compute, head), body, restore=restore)
+        self._graphed((self._mail["b"], "mail_tick", ingest, compute, head, sample and ingest is not None), body,
+                      restore=restore)
 
     def decode_step_host(self, tokens_in: torch.Tensor, tokens_out: torch.Tensor) -> torch.Tensor:
         """One decode step with HOST buffers, the per-token call a streaming client

@@ -366,10 +366,12 @@ class MailboxRunner:
 class MailStage:
     """A ShardEngine in mailbox mode as the runner's stage."""
 
-    def __init__(self, engine, b: int, n_micro: int, runner_period: int, hop: int, rank: int, world: int):
+    def __init__(self, engine, b: int, n_micro: int, runner_period: int, hop: int, rank: int, world: int,
+                 with_logits: bool = False):
         self.eng, self.b = engine, b
         self.is_first = engine.is_first
-        engine.attach_mailbox(b, n_micro, runner_period, hop, rank, world)
+        self.sampling = set()  # slots whose request samples (stage 0 then draws from the whole logits row)
+        engine.attach_mailbox(b, n_micro, runner_period, hop, rank, world, with_logits=with_logits)
         for mb in range(n_micro):
             engine._make_state(b, mb)
 
@@ -389,7 +391,7 @@ class MailStage:
         self.eng.mail_ingest(slot)
 
     def tick_all(self, ingest, compute, head):
-        self.eng.mail_tick(ingest, compute, head)
+        self.eng.mail_tick(ingest, compute, head, sample=ingest is not None and ingest in self.sampling)
 
 
 def mailbox_period(n_micro: int, world: int, hop: int, vp: bool) -> int:
@@ -692,8 +694,8 @@ def serve_e2e(spec, model_name, rank, world, local, ctx, n_short, n_long, hop, p
 
         _CTRL["g"] = dist.new_group(backend="gloo", timeout=datetime.timedelta(hours=2))
     w = make_group_worker(rank, world, local, _CTRL["g"], env={"MODEL_CACHE_DIR": "/nonexistent", "USE_GPU": "1"}, hop=hop)
-    P = w.backend.n_slots
-    eng = build_stage_engine(spec, rank, world, local, P, ctx + n_long + BLOCK + 8, page_size, vocab_parallel=False)
+    P = w.backend.max_slots  # hop * (N + 1): the head is split over the stages
+    eng = build_stage_engine(spec, rank, world, local, P, ctx + n_long + BLOCK + 8, page_size, vocab_parallel=True)
     eng.load_random(seed=0)
     name = "bench/" + model_name
     w.loaded_shards[name] = {rank: {"path": "(in memory)", "metadata": shard_metadata(name, rank, world, spec.n_layers)}}
@@ -738,9 +740,7 @@ def serve_e2e(spec, model_name, rank, world, local, ctx, n_short, n_long, hop, p
                    "concurrent_requests": P, "request_batch_s": t_long, "new_tokens_per_request": n_long,
                    "request_tokens_per_s": P * n_long / t_long, "short_batch_s": t_short, "prompt_tokens": ctx,
                    "server_stats": dict(w.server.stats),
-                   "note": "value = extra tokens of the long batch over the short one / extra wall time; head on the "
-                           "last stage (serves greedy and sampled requests alike), so its tick is longer than the "
-                           "vocabulary-parallel bench's"}
+                   "note": "value = extra tokens of the long batch over the short one / extra wall time"}
         finally:
             w.server.shutdown()
             loop.join()

@@ -45,7 +45,8 @@ class StageBackend:
 
     n_slots: int
 
-    def prepare(self, model: str) -> None: ...              # make `model`'s stage resident (raise ValueError if it cannot be)
+    def probe(self, model: str) -> dict: return {}          # cheap facts about `model` here; every rank sees all of them
+    def prepare(self, model: str, probes=None) -> None: ...  # make `model`'s stage resident (raise ValueError if it cannot be)
     def check_request(self, req: dict) -> None: ...          # raise ValueError if this rank cannot serve the request
     def join(self, slot: int, req: dict) -> None: ...        # prefill the request into `slot` (all ranks, collectively)
     def runner(self): ...                                    # the MailboxRunner of the resident model
@@ -167,30 +168,49 @@ class PipelineServer:
 
     def _apply(self, plan: dict) -> None:
         be = self.be
-        # 1. the model's stage on every rank ("*": a rank that cannot serve the model fails every joining request),
-        #    then every joining request on its own (a request one rank must refuse fails alone, for everybody)
-        errs: dict = {}
 
         def msg(e):
             return str(e) if isinstance(e, ValueError) else f"{type(e).__name__}: {e}"
 
+        # 1a. what every rank knows about the model (is its shard registered, can the head be split): all ranks see
+        #     all answers, so they take the same decisions ("*": a failure that concerns every joining request)
+        errs, probe = {}, None
         try:
-            be.prepare(plan["model"])
+            probe = be.probe(plan["model"])
         except Exception as e:  # noqa: BLE001
             errs["*"] = msg(e)
+        box: List[Optional[dict]] = [None] * self.world
+        dist.all_gather_object(box, {"errs": errs, "probe": probe}, group=self.ctrl)
+        errs = {}
+        for d in box:
+            for k, v in d["errs"].items():
+                errs.setdefault(k, v)
+        # 1b. the model's stage on every rank (may load weights), then every joining request on its own (a request
+        #     one rank must refuse fails alone, for everybody)
+        errs2: dict = {}
         if not errs:
-            for slot, req in plan["join"]:
-                try:
-                    be.check_request(req)
-                except Exception as e:  # noqa: BLE001
-                    errs[slot] = msg(e)
-        errs = self._agree(errs)
+            try:
+                be.prepare(plan["model"], [d["probe"] for d in box])
+            except Exception as e:  # noqa: BLE001
+                errs2["*"] = msg(e)
+            if not errs2:
+                for slot, req in plan["join"]:
+                    try:
+                        if slot >= be.n_slots:
+                            raise ValueError("no free slot")  # planned for a model with more slots: rank 0 re-queues it
+                        be.check_request(req)
+                    except Exception as e:  # noqa: BLE001
+                        errs2[slot] = msg(e)
+            errs = self._agree(errs2)
         joins = [(slot, req) for slot, req in plan["join"] if "*" not in errs and slot not in errs]
         if self.rank == 0:
             for r in self._joining:
-                if "*" in errs or r.slot in errs:
+                if "*" not in errs and errs.get(r.slot) == "no free slot":
+                    r.slot = None
+                    self.queue.put(r)
+                elif "*" in errs or r.slot in errs:
                     r.future.set_exception(ValueError(errs.get("*", errs.get(r.slot))))
-            self._joining = [r for r in self._joining if "*" not in errs and r.slot not in errs]
+            self._joining = [r for r in self._joining if "*" not in errs and r.slot is not None and r.slot not in errs]
         if "*" in errs:
             # A model change that one rank could not follow (models only change while no request is active).  Ranks
             # that did switch and ranks that did not must not tick together — their runners' tick counters, which
@@ -249,58 +269,101 @@ class PipelineServer:
 
 # ------------------------------------------------------------------------------ CUDA data plane of one rank
 class CudaBackend(StageBackend):
-    """This rank's ShardEngine of the resident model, in mailbox mode with one sequence per slot."""
+    """This rank's ShardEngine of the resident model, in mailbox mode with one sequence per slot.
+
+    Two head layouts, agreed by all ranks per model (probe -> prepare):
+      * vocabulary-parallel (Llama-family shards in the sharder's directory layout): every stage holds V/N rows of the
+        lm_head, read from the LAST shard's directory, so no stage carries the whole [V, d] matrix on top of its layers;
+        stage 0 takes the argmax over the stages' candidates, or — for a request that samples — draws from the whole
+        logits row, whose slices travel in the mails; hop*(N+1) slots;
+      * the whole head on the last stage (GPT-2, or head files not found): hop*N slots."""
 
     def __init__(self, worker, rank: int, world: int, hop: int = 2):
+        import os
+
         from .pipeline import mailbox_period
 
         self.worker, self.rank, self.world, self.hop = worker, rank, world, hop
-        self.n_slots = mailbox_period(1, world, hop, False)  # P = hop * N: every stage busy when all slots are taken
+        self.allow_vp = os.environ.get("DLI_GROUP_VP", "1") == "1"
+        self.max_slots = mailbox_period(1, world, hop, True)
+        self.n_slots = mailbox_period(1, world, hop, False)
         self.model = None
         self.eng = None
+        self.vp = False
         self._runner = None
+        self._stage = None
         self._rows = {}
 
-    def prepare(self, model: str) -> None:
+    # -- which shard is mine, and can its head be split? ---------------------------------------------------------
+    def _my_shard(self, model: str):
+        shards = self.worker.loaded_shards.get(model, {})
+        mine = [sid for sid, info in shards.items()
+                if info["metadata"].get("num_shards") == self.world and info["metadata"].get("shard_id", sid) == self.rank]
+        if not mine:  # registered under another id: matched by the group size alone
+            mine = [sid for sid, info in shards.items() if info["metadata"].get("num_shards") == self.world]
+        if not mine:
+            raise ValueError(f"Shard {self.rank} of model {model} is not loaded")
+        return mine[0], shards[mine[0]]
+
+    def _head_dir(self, info):
+        """Directory that stores the final norm and lm_head: the last shard's (this one's on the last rank; else its
+        sibling `shard_<N-1>` in the sharder's layout, shard_model.py:94)."""
+        import os
+
+        if self.rank == self.world - 1:
+            return info["path"]
+        cand = os.path.join(os.path.dirname(os.path.normpath(info["path"])), f"shard_{self.world - 1}")
+        return cand if os.path.exists(os.path.join(cand, "config.json")) else None
+
+    def probe(self, model: str) -> dict:
+        import json
+        import os
+
+        with self.worker._lock:
+            sid, info = self._my_shard(model)
+            eng = self.worker.loaded_models.get(f"{model}_{sid}")
+        if eng is not None:  # already resident (or put there by a host that built it itself): its layout decides
+            return {"vp": eng.head_shard is not None}
+        cfg_path = os.path.join(info["path"], "config.json")
+        arch = json.load(open(cfg_path)).get("model_type") if os.path.exists(cfg_path) else None
+        return {"vp": bool(self.allow_vp and arch in ("llama", "mistral") and self._head_dir(info))}
+
+    def prepare(self, model: str, probes=None) -> None:
         if model == self.model and self.eng is not None:
             return
         from .pipeline import DistExchange, MailboxRunner, MailStage
 
+        vp = bool(probes) and all(p and p.get("vp") for p in probes)
         w = self.worker
         with w._lock:
-            shards = w.loaded_shards.get(model, {})
-            mine = [sid for sid, info in shards.items()
-                    if info["metadata"].get("num_shards") == self.world and info["metadata"].get("shard_id", sid) == self.rank]
-            if not mine:
-                # the ids are the sharder's 0..N-1; a worker registered under another id is matched by layer range
-                mine = [sid for sid, info in shards.items() if info["metadata"].get("num_shards") == self.world]
-            if not mine:
-                raise ValueError(f"Shard {self.rank} of model {model} is not loaded")
-            sid = mine[0]
-            info = shards[sid]
+            sid, info = self._my_shard(model)
             md = info["metadata"]
             key = f"{model}_{sid}"
             if key not in w.loaded_models:  # lazy weight load on first use, like worker/app.py:345-349
-                w.loaded_models[key] = w._engine(info["path"], md["start_layer"], md["end_layer"], max_batch=self.n_slots)
+                w.loaded_models[key] = w._engine(info["path"], md["start_layer"], md["end_layer"], max_batch=self.max_slots,
+                                                 head_shard=(self.rank, self.world) if vp else None,
+                                                 head_path=self._head_dir(info) if vp else None)
             eng = w.loaded_models[key]
+        if (eng.head_shard is not None) != vp:
+            raise ValueError(f"shard {sid} of model {model} is resident with another head layout than the group agreed on")
         if eng.is_first != (self.rank == 0) or eng.is_last != (self.rank == self.world - 1):
             raise ValueError(f"shard {sid} (layers {md['start_layer']}-{md['end_layer']}) is registered on GPU {self.rank}: "
                              "shard i of N must live on GPU i")
-        if eng.max_batch < self.n_slots:
-            raise ValueError(f"engine of shard {sid} was created for {eng.max_batch} sequences, the group needs {self.n_slots}")
-        self.eng, self.model = eng, model
-        stage = MailStage(eng, 1, self.n_slots, self.n_slots, self.hop, self.rank, self.world)
+        n_slots = self.hop * (self.world + 1 if vp else self.world)
+        if eng.max_batch < n_slots:
+            raise ValueError(f"engine of shard {sid} was created for {eng.max_batch} sequences, the group needs {n_slots}")
+        self.eng, self.model, self.vp, self.n_slots = eng, model, vp, n_slots
+        self._stage = MailStage(eng, 1, n_slots, n_slots, self.hop, self.rank, self.world, with_logits=vp)
         comm = torch.cuda.Stream(device=eng.device) if self.hop > 1 else None
-        self._runner = MailboxRunner(stage, self.rank, self.world, self.n_slots, hop=self.hop, vp=False,
+        self._runner = MailboxRunner(self._stage, self.rank, self.world, n_slots, hop=self.hop, vp=vp,
                                      exchange=DistExchange(comm_stream=comm))
         self._rows = {}
-        self._pf_in = None
 
     def runner(self):
         return self._runner
 
     def reset(self) -> None:
-        self.model, self.eng, self._runner, self._rows = None, None, None, {}
+        self.model, self.eng, self._runner, self._stage, self._rows = None, None, None, None, {}
 
     def check_request(self, req: dict) -> None:
         from .engine import check_max_length
@@ -312,27 +375,34 @@ class CudaBackend(StageBackend):
                              f"({self.eng.max_seq_len - BLOCK - 2}; DLI_MAX_SEQ_LEN)")
 
     def _slot_rows(self, slot: int) -> dict:
-        """Persistent per-slot token-choice state of the last stage (its addresses are baked into the slot's graph):
-        greedy, or the reference's sampling call keyed by (the request's seed, the token's position)."""
+        """Persistent per-slot token-choice state on the stage that chooses (the last stage; stage 0 with the head split):
+        its addresses are baked into the slot's graphs.  Greedy, or the reference's sampling call keyed by (the request's
+        seed, the token's position)."""
         if slot not in self._rows:
             st, dev = self.eng._state(1, slot), self.eng.device
-            self._rows[slot] = {"seeds": torch.zeros(1, dtype=torch.int64, device=dev), "steps": st["positions"],
+            steps = torch.zeros(1, dtype=torch.int32, device=dev) if self.vp else st["positions"]
+            self._rows[slot] = {"seeds": torch.zeros(1, dtype=torch.int64, device=dev), "steps": steps,
                                 "mask": torch.zeros(1, dtype=torch.int32, device=dev),
                                 "params": dict(temperature=0.8, top_k=50, top_p=0.95)}
         return self._rows[slot]
 
     def join(self, slot: int, req: dict) -> None:
+        from . import ops
+
         eng, rank, world = self.eng, self.rank, self.world
         T = len(req["ids"])
         eng.start_batch(1, T, req["max_length"] + BLOCK + 2, mb=slot)
         st = eng._state(1, slot)
         gen = req.get("gen") or {}
-        if eng.has_head:
+        sample = bool(gen.get("do_sample"))
+        chooser = eng.is_first if self.vp else eng.has_head
+        if chooser:
             rows = self._slot_rows(slot)
             rows["seeds"].fill_(int(gen.get("seed", 0)))
-            rows["mask"].fill_(1 if gen.get("do_sample") else 0)
+            rows["mask"].fill_(1 if sample else 0)
             # the prompt's last position keys the first new token; decode steps then key by the slot's position
             st["row_sampling"] = dict(rows, steps=torch.tensor([T - 1], dtype=torch.int32, device=eng.device))
+        (self._stage.sampling.add if sample else self._stage.sampling.discard)(slot)
         d = eng.spec.d_model
         if rank == 0:
             ids = torch.tensor(req["ids"], dtype=torch.int32, device=eng.device)
@@ -343,11 +413,31 @@ class CudaBackend(StageBackend):
             x = eng.prefill(1, T, hidden=buf, mb=slot)
         if rank < world - 1:
             dist.send(x.contiguous(), dst=rank + 1)
-        if eng.has_head:
+        if not self.vp:
+            if eng.has_head:
+                dist.send(st["tokens"], dst=0)  # the first token goes to the pipeline head
+            if rank == 0:
+                dist.recv(st["tokens"], src=world - 1)
+        else:
+            # the last stage's final hidden state to every stage; each computes its head slice; stage 0 chooses
+            dist.broadcast(st["hf"], src=world - 1)
+            eng.head_slice_step(1, slot)
+            cands = torch.empty(world, 1, 2, dtype=torch.float32, device=eng.device)
+            dist.all_gather_into_tensor(cands.view(-1), st["cand"].reshape(-1).clone())
+            if rank == 0:
+                ops.argmax_merge(cands, st["tokens"])
+            if sample:
+                per = (eng.spec.vocab + world - 1) // world
+                mine = torch.zeros(per, dtype=torch.bfloat16, device=eng.device)
+                mine[: eng.v1 - eng.v0].copy_(st["logits"][0])
+                row = torch.empty(world * per, dtype=torch.bfloat16, device=eng.device)
+                dist.all_gather_into_tensor(row, mine)
+                if rank == 0:
+                    r = st["row_sampling"]
+                    ops.sample_rows(row.view(1, -1)[:, : eng.spec.vocab], st["tokens"], r["seeds"], r["steps"], r["mask"],
+                                    **r["params"])
+        if chooser:
             st["row_sampling"] = self._slot_rows(slot)
-            dist.send(st["tokens"], dst=0)  # the first token goes to the pipeline head
-        if rank == 0:
-            dist.recv(st["tokens"], src=world - 1)
         st["step"].zero_()
 
     def read_tokens(self, slot: int, n: int) -> List[int]:
@@ -357,6 +447,8 @@ class CudaBackend(StageBackend):
     def release(self, slot: int) -> None:
         self.eng.kv.release(slot)
         self.eng._state(1, slot)["seq_lens"].zero_()  # an idle row: its decode steps touch nothing
+        if self._stage is not None:
+            self._stage.sampling.discard(slot)
 
 
 # ------------------------------------------------------------------------------ the worker of one rank

@@ -110,6 +110,23 @@ def load_hf_state_dict(path: str, start_layer: int = 0, end_layer: Optional[int]
     return out
 
 
+def load_named_tensors(path: str, names) -> Dict[str, torch.Tensor]:
+    """Only the tensors called `names` from a Hugging Face directory (those that exist there)."""
+    want, out = set(names), {}
+    for f in _tensor_files(path):
+        if f.endswith(".safetensors"):
+            from safetensors import safe_open
+
+            with safe_open(f, framework="pt", device="cpu") as sf:
+                for name in sf.keys():
+                    if name in want:
+                        out[name] = sf.get_tensor(name)
+        else:
+            sd = torch.load(f, map_location="cpu", weights_only=True)
+            out.update({k: v for k, v in sd.items() if k in want})
+    return out
+
+
 def write_shards(state_dict: Dict[str, torch.Tensor], config: Dict[str, object], model_name: str, n_shards: int,
                  output_dir: str = "model_shards") -> List[str]:
     """Real shard materialiser: the same CLI contract as

@@ -121,8 +121,12 @@ class Worker:
         raise FileNotFoundError(f"{model_name} is not a local model directory and the Hugging Face hub is not "
                                 f"reachable (looked in {self.model_cache_dir})")
 
-    def _engine(self, path: str, start=0, end=None, max_batch=None):
+    def _engine(self, path: str, start=0, end=None, max_batch=None, head_shard=None, head_path=None):
+        """head_shard=(rank, world) + head_path: a stage of a worker group with the lm_head split by vocabulary rows
+        over the stages; the final norm and this stage's rows of the head are read from `head_path`, the directory of
+        the LAST shard (the only one that stores them)."""
         from .engine import ModelSpec, ShardEngine
+        from .sharding import load_named_tensors
 
         if self.device != "cuda":
             raise RuntimeError("this worker has no CPU path: it needs a CUDA device and USE_GPU=1")
@@ -131,8 +135,13 @@ class Worker:
         if max_batch is None:
             max_batch = self.max_batch if end is None else 1
         eng = ShardEngine(spec, start, end, device=self.cuda_device, max_batch=max_batch,
-                          max_seq_len=min(self.max_seq_len, spec.max_pos), kv_pool_tokens=self.kv_pool_tokens)
-        eng.load_state_dict(load_hf_state_dict(path, eng.start, eng.end, spec.n_layers))
+                          max_seq_len=min(self.max_seq_len, spec.max_pos), kv_pool_tokens=self.kv_pool_tokens,
+                          head_shard=head_shard)
+        sd = load_hf_state_dict(path, eng.start, eng.end, spec.n_layers)
+        if head_shard is not None:
+            sd.update(load_named_tensors(head_path, ("model.norm.weight", "lm_head.weight") + (
+                ("model.embed_tokens.weight",) if spec.tie_embeddings else ())))
+        eng.load_state_dict(sd)
         eng.eos_token_ids, eng.pad_token_id = _stop_tokens(path, cfg)
         eng.prefill_chunk = self.prefill_chunk
         return eng

@@ -326,7 +326,8 @@ def _server_worker(rank, world, port, q):
             self.stage.compute = compute
             self._runner = MailboxRunner(self.stage, rank, world, P, hop=hop, vp=False, exchange=DistExchange())
 
-        def prepare(self, model):
+        def prepare(self, model, probes=None):
+            assert probes is not None and len(probes) == world
             if model == "missing" and rank == world - 1:
                 raise ValueError(f"Shard {rank} of model missing is not loaded")
 
