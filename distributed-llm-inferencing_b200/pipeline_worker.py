@@ -14,8 +14,12 @@ split over the group (`metadata.json: num_shards == N`; the listed ids may be on
 what the reference master sends) is served by ALL ranks: a request arriving on another rank is handed to rank 0.
 
 Serving loop (PipelineServer, one thread per rank, in lockstep):
-  * the decode pipeline of pipeline.MailboxRunner runs continuously with P = hop * N slots of one sequence each, the
-    whole head on the last stage (greedy or the reference's sampling call, per request, seeded);
+  * the decode pipeline of pipeline.MailboxRunner runs continuously with one sequence per slot.  Llama-family shards
+    in the sharder's directory layout get a vocabulary-parallel head (every stage reads its V/N rows of lm_head from
+    the last shard's directory; hop * (N+1) slots): stage 0 takes the argmax over the stages' candidates, or — for a
+    request that samples like the reference — draws from the whole logits row, whose slices travel in the mails,
+    keyed by (the request's seed, the token's position).  Otherwise (GPT-2, head files elsewhere) the whole head
+    stays on the last stage (hop * N slots).  All ranks agree on the layout per model;
   * every `block` rounds rank 0 reads the new tokens, completes the requests that reached `max_length`, an EOS id or
     their deadline, and broadcasts ONE plan over the control group (gloo): slots to close, slots to free, requests
     to admit.  Every rank applies the plan: a joining request is prefilled through the stages (hidden states by

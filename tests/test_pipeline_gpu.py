@@ -150,8 +150,15 @@ def test_worker_group_serves_a_sharded_model_over_http(cuda, tmp_path):
     want = json.loads(cl.post("/inference", json=req).get_data(as_text=True))["result"]
     assert got == want and again == got, (got, want, out[-2000:])
     assert sampled[0] == sampled[1] and len(sampled[0].split()) == T + 20
-    # the group splits the head over the stages and draws on stage 0 from the gathered logits row: same draw, same
-    # text as the worker that holds the whole head (keyed by seed and position)
-    want_sampled = json.loads(cl.post("/inference", json=dict(req, do_sample=True, seed=4)).get_data(as_text=True))["result"]
-    assert sampled[0] == want_sampled, (sampled[0], want_sampled)
+    # The group splits the head over the stages and draws on stage 0 from the logits row gathered in the mails, keyed
+    # by (seed, token position) like the continuous batcher: same draw, same text as a batching worker that holds the
+    # whole model and the whole head.
+    wb = Worker({"MODEL_CACHE_DIR": str(tmp_path), "DLI_BATCHING": "1", "DLI_MAX_BATCH": "2"})
+    cb = Client(wb)
+    try:
+        want_sampled = json.loads(cb.post("/inference", json={"model_name": full, "prompt": prompt, "max_length": T + 20,
+                                                              "do_sample": True, "seed": 4}).get_data(as_text=True))
+        assert want_sampled.get("result") == sampled[0], (sampled[0], want_sampled)
+    finally:
+        cb.post("/unload_model", json={"model_name": full})
 
