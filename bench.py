@@ -355,18 +355,23 @@ def cpu_configs0():
 
 def run_reference(args, spec):
     """--impl reference: the reference's CPU path (port, see oracle/ref_worker_port.py),
-    all host threads, each step = one decoded token at a short context (bounded sample)."""
+    all host threads, each step = one decoded token at the product arm's context (batch 1, `--ctx` tokens), decode
+    rate = K tokens / (t[K+1 new tokens] - t[1 new token])."""
     from oracle import ref_worker_port as P
 
     _use_all_host_threads()
     model = P.build_cpu_model(spec)
     tok = P.IdTokenizer()
-    prompt_len = 16
-    g = torch.Generator().manual_seed(1)
-    prompt = " ".join(str(int(i)) for i in torch.randint(0, spec.vocab, (prompt_len,), generator=g))
     K, W = min(args.steps, 64), min(args.warmup, 2)  # bounded: ~0.12 s per token on the box's 16 cores
-    if W:
-        P.run_inference_port(model, tok, prompt, prompt_len + 1 + W, timeout=1e9, greedy=True)
+    # the product arm's context (DLI_REF_CTX bounds it: the prompt pass of an 8B model costs the host cores ~10-20 s
+    # per call and the arm makes two of them)
+    prompt_len = max(1, min(int(os.environ.get("DLI_REF_CTX", args.ctx)), spec.max_pos - K - 2))
+    g = torch.Generator().manual_seed(1)
+    ids = torch.randint(0, spec.vocab, (prompt_len,), generator=g)
+    prompt = " ".join(str(int(i)) for i in ids)
+    if W:  # warm-up on a short prompt: thread pool, allocator, first-call costs
+        short = " ".join(str(int(i)) for i in ids[:16])
+        P.run_inference_port(model, tok, short, min(16, prompt_len) + 1 + W, timeout=1e9, greedy=True)
     t0 = time.time()
     P.run_inference_port(model, tok, prompt, prompt_len + 1, timeout=1e9, greedy=True)
     t_pf = time.time() - t0
@@ -380,7 +385,8 @@ def run_reference(args, spec):
     return {"metric": METRIC, "value": v, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": K,
             "warmup": W, "ms_per_step": dt / K * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"{args.model} bf16 random-init, batch 1 greedy decode (CPU bounded sample)"},
+            "config": {"workload": f"{args.model} bf16 random-init, batch 1 greedy decode at {prompt_len}-token context "
+                                   f"(CPU, {K} steps)", "batch": 1, "ctx": prompt_len},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
