@@ -776,11 +776,24 @@ def run_pipeline_bench(args, spec, peaks):
             # the stated batch split into one slot per stage (slots of B/N sequences; a single slot at batch 1);
             # hop 1: with no more slots than stages there is nothing to overlap the exchange with
             slots = min(world, B)
-            r = measure_pipeline(NAMED_SPECS[name], name, rank, world, local, B // slots, slots, nctx, min(K, 16), 3,
-                                 args.page_size, peaks, vp=(B > 1), hop=1, prompt_seed=3,
+            nspec, nb = NAMED_SPECS[name], B // slots
+            # Head layout by bytes per round of the slots: split over the stages, every stage streams its layers plus
+            # V/N rows of the head on N+1 ticks (one tick of the period is idle with N slots); whole on the last
+            # stage, that stage streams layers + the whole head on N ticks.  Mistral's 32k-row head is cheaper kept
+            # whole (4 x 3.75 GB against 5 x 3.56 GB), the 128k-row heads are cheaper split.
+            from .measure import decode_step_bytes
+            from .sharding import shard_ranges as _ranges
+
+            n_last = _ranges(nspec.n_layers, world)[-1]
+            stage = decode_step_bytes(nspec, n_last[1] - n_last[0] + 1, False, nb, nctx)
+            head = nspec.head_weight_bytes()
+            named_vp = B > 1 and (world + 1) * (stage + head / world) < world * (stage + head)
+            r = measure_pipeline(nspec, name, rank, world, local, nb, slots, nctx, min(K, 16), 3,
+                                 args.page_size, peaks, vp=named_vp, hop=1, prompt_seed=3,
                                  parity_tokens=4 if name != "llama-3-70b" else 0, timed_prefill=False)
             named = {"config": note, "decode_tokens_per_s": r["value"], "batch": B, "ctx": r["ctx_mid"],
                      "micro_batches": r["slots"], "sequences_per_micro_batch": r["b"], "tick_ms": r["tick_ms"],
+                     "head": "split by vocabulary rows over the stages" if named_vp else "whole, on the last stage",
                      "stage_pass_frac": r["stage_pass_frac"], "busy_ticks": r["busy_ticks"],
                      "pp_only_ceiling_tokens_per_s": r["pp_ceiling_tokens_per_s"],
                      "prefill_tokens_per_s": r["prefill_tokens_per_s"], "prefill_chunks": r["prefill_chunks"],
