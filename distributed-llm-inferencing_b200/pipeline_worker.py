@@ -189,6 +189,17 @@ class PipelineServer:
         for d in box:
             for k, v in d["errs"].items():
                 errs.setdefault(k, v)
+        if not errs and any((d["probe"] or {}).get("stale") for d in box):
+            # some rank's resident engine was unloaded behind the pipeline's back: every rank rebuilds its stage now
+            # (together: the runners' tick counters must agree); what was in flight on the old engines is lost
+            be.reset()
+            if self.rank == 0:
+                for r in self.active.values():
+                    if not r.future.done():
+                        r.future.set_exception(RuntimeError("the model was unloaded while the request was running"))
+                self.active.clear()
+            self.closing, self.draining = [], []
+            plan = dict(plan, close=[], free=[], active=0)
         # 1b. the model's stage on every rank (may load weights), then every joining request on its own (a request
         #     one rank must refuse fails alone, for everybody)
         errs2: dict = {}
@@ -326,11 +337,13 @@ class CudaBackend(StageBackend):
         with self.worker._lock:
             sid, info = self._my_shard(model)
             eng = self.worker.loaded_models.get(f"{model}_{sid}")
+        # stale: /unload_model (or a re-registration) took this rank's resident engine away since the last plan
+        stale = self.model == model and self.eng is not None and eng is not self.eng
         if eng is not None:  # already resident (or put there by a host that built it itself): its layout decides
-            return {"vp": eng.head_shard is not None}
+            return {"vp": eng.head_shard is not None, "stale": stale}
         cfg_path = os.path.join(info["path"], "config.json")
         arch = json.load(open(cfg_path)).get("model_type") if os.path.exists(cfg_path) else None
-        return {"vp": bool(self.allow_vp and arch in ("llama", "mistral") and self._head_dir(info))}
+        return {"vp": bool(self.allow_vp and arch in ("llama", "mistral") and self._head_dir(info)), "stale": stale}
 
     def prepare(self, model: str, probes=None) -> None:
         if model == self.model and self.eng is not None:
@@ -469,6 +482,14 @@ def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None, b
             self.cuda_device = f"cuda:{local}"
             self.backend = CudaBackend(self, rank, world, hop=hop)
             self.server = PipelineServer(rank, world, ctrl_group, self.backend)
+
+        def _release_engine(self, key, eng) -> None:
+            # The stage that is resident in the serving pipeline may be in the middle of a block of ticks on another
+            # thread: only drop the references here.  The pipeline notices at its next plan (probe: "stale"), all
+            # ranks rebuild together, and the memory goes when the old runner and its graphs are released.
+            if eng is self.backend.eng:
+                return
+            super()._release_engine(key, eng)
 
         def dispatch(self, method, path, data, headers):
             if torch.cuda.is_available():

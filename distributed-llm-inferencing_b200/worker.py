@@ -209,9 +209,7 @@ class Worker:
             # exact key only, worker/app.py:223-227)
             keys = {model_name} | {f"{model_name}_{sid}" for sid in self.loaded_shards.get(model_name, {})}
             for key in [k for k in self.loaded_models if k in keys]:
-                eng = self.loaded_models.pop(key)
-                if hasattr(eng, "unload"):
-                    eng.unload()
+                self._release_engine(key, self.loaded_models.pop(key))
             self.loaded_tokenizers.pop(model_name, None)
             self.loaded_shards.pop(model_name, None)
             if self.device == "cuda":
@@ -219,6 +217,11 @@ class Worker:
             return {"status": "success", "message": f"Model {model_name} unloaded successfully"}, 200
         except Exception as e:  # noqa: BLE001
             return {"status": "error", "message": f"Failed to unload model: {str(e)}"}, 500
+
+    def _release_engine(self, key, eng) -> None:
+        """Free an engine that /unload_model has just removed (weights, KV pages, captured graphs)."""
+        if hasattr(eng, "unload"):
+            eng.unload()
 
     def inference(self, data):
         data = data or {}

@@ -135,6 +135,15 @@ def test_worker_group_serves_a_sharded_model_over_http(cuda, tmp_path):
                              json={"model_name": full, "prompt": prompt, "max_length": T + 20, "do_sample": False},
                              timeout=300)
         assert solo.status_code == 200 and solo.json()["result"] == got, solo.text
+        # /unload_model on ONE node while the group has the model resident: the next request fails with the reference's
+        # message for everybody, nothing crashes, and after the shard is registered again the group rebuilds and serves
+        assert requests.post(f"http://127.0.0.1:{port + 1}/unload_model", json={"model_name": "org/tiny"}, timeout=60).status_code == 200
+        gone = requests.post(f"http://127.0.0.1:{port}/inference", json=req, timeout=120)
+        assert gone.status_code == 500 and "Shard 1 of model org/tiny is not loaded" in gone.json()["message"], gone.text
+        assert requests.post(f"http://127.0.0.1:{port + 1}/load_shard",
+                             json={"model_name": "org/tiny", "shard_id": 1, "shard_path": paths[1]}, timeout=60).status_code == 200
+        back = requests.post(f"http://127.0.0.1:{port}/inference", json=req, timeout=300)
+        assert back.status_code == 200 and back.json()["result"] == got, back.text
     finally:
         os.killpg(p.pid, signal.SIGTERM)
         try:
