@@ -70,6 +70,7 @@ class ContinuousBatcher:
         ids = torch.as_tensor(input_ids, dtype=torch.int64).reshape(-1).cpu()
         req = _Request(ids, int(max_length), None if timeout is None else time.time() + timeout,
                        do_sample=bool(do_sample), seed=int(seed))
+        req.future.request = req  # a streaming caller reads req.out (the tokens so far) while it waits
         if len(ids) == 0:
             req.future.set_exception(ValueError("empty prompt"))
         elif req.max_length > self.eng.max_seq_len:

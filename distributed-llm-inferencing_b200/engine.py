@@ -975,8 +975,10 @@ class ShardEngine:
     def generate(self, input_ids: torch.Tensor, max_length: int, return_logits: bool = False,
                  forced: Optional[torch.Tensor] = None, deadline: Optional[float] = None,
                  do_sample: bool = False, temperature: float = 0.8, top_k: int = 50, top_p: float = 0.95,
-                 seed: int = 0):
-        """Greedy generate (the parity mode of worker/app.py:297-305: the reference
+                 seed: int = 0, on_tokens=None):
+        """on_tokens(ids [B, T + k] int64 on the host): called every 8 decode steps with everything generated so far
+        (a streaming client's progress; the steps stay on the CUDA-graph path).
+        Greedy generate (the parity mode of worker/app.py:297-305: the reference
         samples, see SURVEY.md §0 F3).  input_ids: int [B, T] on any device;
         `max_length` is the TOTAL length like the reference's.  Returns int64
         [B, max_length] on the host, plus the per-step last-position logits
@@ -1018,12 +1020,15 @@ class ShardEngine:
         eos = tuple(self.eos_token_ids) if forced is None else ()
         try:
             for i in range(n_new - 1):
-                if (deadline is not None or eos) and (i & 7) == 0:
+                if (deadline is not None or eos or on_tokens is not None) and (i & 7) == 0:
                     # the reference can only check its timeout around generate() (worker/app.py:293,:311);
                     # here it is checked between decode steps, together with the EOS rule
                     torch.cuda.current_stream().synchronize()
                     if deadline is not None and time.time() > deadline:
                         raise TimeoutError("Inference generation timed out")
+                    if on_tokens is not None:
+                        sofar = torch.stack(toks) if eager else torch.cat((toks[0][None], st["token_log"][:i]), dim=0)
+                        on_tokens(torch.cat((input_ids.cpu().long(), sofar.t().cpu().long()), dim=1))
                     if eos:
                         seen = torch.stack(toks) if eager else torch.cat((toks[0][None], st["token_log"][:i]), dim=0)
                         if all_finished(seen, eos):
@@ -1108,10 +1113,11 @@ class LocalChain:
     @torch.no_grad()
     def generate(self, input_ids: torch.Tensor, max_length: int, deadline: Optional[float] = None,
                  do_sample: bool = False, temperature: float = 0.8, top_k: int = 50, top_p: float = 0.95,
-                 seed: int = 0) -> torch.Tensor:
+                 seed: int = 0, on_tokens=None) -> torch.Tensor:
         if len(self.engines) == 1:
             return self.engines[0].generate(input_ids, max_length, deadline=deadline, do_sample=do_sample,
-                                            temperature=temperature, top_k=top_k, top_p=top_p, seed=seed)
+                                            temperature=temperature, top_k=top_k, top_p=top_p, seed=seed,
+                                            on_tokens=on_tokens)
         B, T = input_ids.shape
         check_max_length(T, max_length)
         n_new = max_length - T
@@ -1133,10 +1139,12 @@ class LocalChain:
         toks = [x.clone()]
         eos = tuple(last.eos_token_ids)
         for i in range(n_new - 1):
-            if (deadline is not None or eos) and (i & 7) == 0:
+            if (deadline is not None or eos or on_tokens is not None) and (i & 7) == 0:
                 torch.cuda.current_stream().synchronize()
                 if deadline is not None and time.time() > deadline:
                     raise TimeoutError("Inference generation timed out")
+                if on_tokens is not None:
+                    on_tokens(torch.cat((input_ids.cpu().long(), torch.stack(toks, dim=1).cpu().long()), dim=1))
                 if eos and all_finished(torch.stack(toks), eos):
                     break
             first._state(B)["tokens"].copy_(toks[-1])

@@ -64,7 +64,8 @@ class _Req:
         self.cmd = cmd
         self.future: Future = Future()
         self.slot: Optional[int] = None
-        self.start_round = 0
+        self.partial: List[int] = []  # the new tokens known so far (updated after every block)
+        self.future.request = self
 
 
 class PipelineServer:
@@ -268,6 +269,7 @@ class PipelineServer:
             n_target = r.cmd["max_length"] - len(r.cmd["ids"])
             have = min(self.rounds_done[slot], n_target)  # tokens the slot has CONSUMED = produced and fed back
             toks = self.be.read_tokens(slot, have)
+            r.partial = toks
             eos = tuple(r.cmd.get("eos") or ())
             hit = next((i for i, t in enumerate(toks) if t in eos), None)
             if hit is not None:
@@ -529,6 +531,7 @@ def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None, b
             fut = self.server.submit({"model": model_name, "ids": ids.tolist(), "max_length": int(max_length),
                                       "deadline": deadline, "gen": gen or {}, "eos": list(eos)})
             wait = None if deadline is None else max(1.0, deadline - time.time() + 30)
+            self._wait_streaming(fut, tokenizer, ids, lambda: fut.request.partial)
             new = fut.result(timeout=wait)
             new = apply_eos(torch.tensor([new], dtype=torch.int64), eos, pad)
             return tokenizer.decode(torch.cat((ids.long(), new[0])), skip_special_tokens=True)

@@ -108,6 +108,7 @@ class Worker:
         # With batching the WSGI server is threaded: everything that touches the dicts above or runs an
         # engine directly holds this lock; only the wait on a batcher's future happens outside it.
         self._lock = threading.RLock()
+        self._progress = threading.local()  # .cb(text) while the calling thread serves a streaming /inference
         self.routes = {("GET", "/health"): self.health, ("POST", "/load_model"): self.load_model,
                        ("POST", "/load_shard"): self.load_shard, ("POST", "/unload_model"): self.unload_model,
                        ("POST", "/inference"): self.inference}
@@ -218,6 +219,25 @@ class Worker:
         except Exception as e:  # noqa: BLE001
             return {"status": "error", "message": f"Failed to unload model: {str(e)}"}, 500
 
+    def _on_tokens(self, tokenizer):
+        """Progress callback for the generate paths of the calling thread, or None when nobody is streaming."""
+        cb = getattr(self._progress, "cb", None)
+        if cb is None:
+            return None
+        return lambda ids: cb(tokenizer.decode(ids[0], skip_special_tokens=True))
+
+    def _wait_streaming(self, fut, tokenizer, prompt_ids, new_tokens):
+        """Wait for a batcher / worker-group future; while streaming, report the tokens it has so far."""
+        from concurrent.futures import wait
+
+        on = self._on_tokens(tokenizer)
+        while on is not None and not fut.done():
+            wait([fut], timeout=0.05)
+            toks = list(new_tokens())
+            if toks:
+                on(torch.cat((prompt_ids.long(), torch.tensor(toks, dtype=torch.int64)))[None])
+        return fut
+
     def _release_engine(self, key, eng) -> None:
         """Free an engine that /unload_model has just removed (weights, KV pages, captured graphs)."""
         if hasattr(eng, "unload"):
@@ -251,11 +271,12 @@ class Worker:
                         raise TimeoutError("Inference preparation timed out")
                     if batcher is None:
                         outputs = model.generate(ids, max_length=max_length, deadline=deadline,
-                                                 **self._gen_kwargs(data))
+                                                 on_tokens=self._on_tokens(tokenizer), **self._gen_kwargs(data))
                 if batcher is not None:  # joins the running batch; the wait is outside the lock
                     gen = self._gen_kwargs(data)
-                    outputs = batcher.submit(ids[0], max_length, timeout, do_sample=gen["do_sample"],
-                                             seed=gen["seed"]).result()[None]
+                    fut = batcher.submit(ids[0], max_length, timeout, do_sample=gen["do_sample"], seed=gen["seed"])
+                    self._wait_streaming(fut, tokenizer, ids[0], lambda: getattr(fut, "request").out)
+                    outputs = fut.result()[None]
                 result = tokenizer.decode(outputs[0], skip_special_tokens=True)
                 if (time.time() - start_time) > timeout:
                     raise TimeoutError("Inference generation timed out")
@@ -288,7 +309,8 @@ class Worker:
             engines.append(self.loaded_models[key])
         tokenizer = self.loaded_tokenizers[model_name]
         ids = tokenizer(prompt, return_tensors="pt")["input_ids"]
-        outputs = LocalChain(engines).generate(ids, max_length=max_length, deadline=deadline, **(gen or {}))
+        outputs = LocalChain(engines).generate(ids, max_length=max_length, deadline=deadline,
+                                               on_tokens=self._on_tokens(tokenizer), **(gen or {}))
         return tokenizer.decode(outputs[0], skip_special_tokens=True)
 
     # ------------------------------------------------------------------ WSGI
@@ -306,9 +328,55 @@ class Worker:
         with self._lock:
             return fn(data)
 
+    def stream_inference(self, data, headers):
+        """`"stream": true` on /inference (an extension; the reference answers with one JSON body, worker/app.py:314-318):
+        newline-delimited JSON — {"status": "partial", "result": <text so far>} as tokens arrive (every 8 decode steps
+        on one GPU, every block of rounds in a worker group), then the reference's own final object (or error object)
+        with its HTTP status under "http_status"."""
+        import queue
+
+        q: "queue.Queue" = queue.Queue()
+        plain = {k: v for k, v in data.items() if k != "stream"}
+        hdrs = dict(headers)
+
+        def work():
+            self._progress.cb = lambda text: q.put(("partial", text))
+            try:
+                out = self.dispatch("POST", "/inference", plain, hdrs)
+            except Exception as e:  # noqa: BLE001
+                out = ({"status": "error", "message": f"Inference failed: {e}"}, 500)
+            finally:
+                self._progress.cb = None
+            q.put(("final", out))
+
+        threading.Thread(target=work, daemon=True).start()
+
+        def lines():
+            last = None
+            while True:
+                kind, v = q.get()
+                if kind == "partial":
+                    if v != last:
+                        last = v
+                        yield json.dumps({"status": "partial", "result": v}) + "\n"
+                else:
+                    body, code = v
+                    yield json.dumps(dict(body, http_status=code)) + "\n"
+                    return
+
+        return Response(lines(), status=200, mimetype="application/x-ndjson")
+
     def __call__(self, environ, start_response):
         req = Request(environ)
         data = req.get_json(silent=True) if req.method == "POST" else None
+        if req.method == "POST" and req.path == "/inference" and isinstance(data, dict) and data.get("stream"):
+            if self.auth_enabled and req.headers.get("Authorization") != f"Bearer {self.auth_key}":
+                body, code = {"status": "error", "message": "Unauthorized access"}, 401
+            elif not data.get("model_name") or not data.get("prompt"):
+                body, code = {"status": "error", "message": "Model name and prompt are required"}, 400
+            else:
+                return self.stream_inference(data, req.headers)(environ, start_response)
+            return Response(json.dumps(body), status=code, mimetype="application/json")(environ, start_response)
         body, code = self.dispatch(req.method, req.path, data, req.headers)
         return Response(json.dumps(body), status=code, mimetype="application/json")(environ, start_response)
 

@@ -135,6 +135,14 @@ def test_worker_group_serves_a_sharded_model_over_http(cuda, tmp_path):
                              json={"model_name": full, "prompt": prompt, "max_length": T + 20, "do_sample": False},
                              timeout=300)
         assert solo.status_code == 200 and solo.json()["result"] == got, solo.text
+        # "stream": true — text so far after every block of rounds, then the plain answer
+        with requests.post(f"http://127.0.0.1:{port}/inference", json=dict(req, max_length=T + 40, stream=True),
+                           timeout=300, stream=True) as sr:
+            lines = [json.loads(ln) for ln in sr.iter_lines() if ln]
+        long_plain = requests.post(f"http://127.0.0.1:{port}/inference", json=dict(req, max_length=T + 40), timeout=300).json()
+        assert lines[-1]["http_status"] == 200 and lines[-1]["result"] == long_plain["result"], lines[-1]
+        parts = [ln["result"] for ln in lines[:-1]]
+        assert len(parts) >= 2 and all(b.startswith(a) for a, b in zip(parts, parts[1:] + [lines[-1]["result"]]))
         # /unload_model on ONE node while the group has the model resident: the next request fails with the reference's
         # message for everybody, nothing crashes, and after the shard is registered again the group rebuilds and serves
         assert requests.post(f"http://127.0.0.1:{port + 1}/unload_model", json={"model_name": "org/tiny"}, timeout=60).status_code == 200

@@ -211,3 +211,57 @@ def test_stop_tokens_come_from_generation_config_first(tmp_path):
     assert _stop_tokens(str(tmp_path), {}) == ((), None)
     (tmp_path / "generation_config.json").write_text(json.dumps({"eos_token_id": [128001, 128009], "pad_token_id": 0}))
     assert _stop_tokens(str(tmp_path), cfg) == ((128001, 128009), 0)
+
+
+# ------------------------------------------------------------------ streaming (an extension: "stream": true)
+def _lines(resp):
+    return [json.loads(ln) for ln in resp.get_data(as_text=True).splitlines() if ln.strip()]
+
+
+def test_streaming_request_errors_keep_the_reference_shapes():
+    """Without "stream" nothing changes; with it, malformed / unauthorised requests still get the reference's plain JSON
+    and status, and a failure inside the request arrives as the last line with its status under "http_status"."""
+    c, _ = _client({"USE_GPU": "0"})
+    r = c.post("/inference", json={"model_name": "m", "stream": True})
+    assert r.status_code == 400 and r.get_json() == {"status": "error", "message": "Model name and prompt are required"}
+    ca, _ = _client({"AUTH_ENABLED": "1", "AUTH_KEY": "k"})
+    r = ca.post("/inference", json={"model_name": "m", "prompt": "1 2", "stream": True})
+    assert r.status_code == 401 and r.get_json()["message"] == "Unauthorized access"
+    r = c.post("/inference", json={"model_name": "org/none", "prompt": "1 2", "stream": True})
+    assert r.status_code == 200 and r.mimetype == "application/x-ndjson"
+    out = _lines(r)
+    assert len(out) == 1 and out[0]["status"] == "error" and out[0]["http_status"] == 500
+    assert out[0]["message"].startswith("Failed to load model: ")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batching", [False, True])
+def test_streamed_inference_ends_with_the_plain_answer(cuda, shard_dirs, batching):
+    """Partial lines carry the text so far (each a prefix of the next), the last line is the reference's own response
+    object and equals what the same request returns without "stream" — one GPU, with and without continuous batching,
+    unsharded and as an in-process chain of two shards."""
+    case, spec, sd, paths, full = shard_dirs
+    env = {"MODEL_CACHE_DIR": os.path.dirname(full)}
+    if batching:
+        env.update(DLI_BATCHING="1", DLI_MAX_BATCH="2")
+    c, w = _client(env)
+    prompt = " ".join(str(int(i)) for i in case["prompts"][0])
+    T = len(case["prompts"][0])
+    reqs = [{"model_name": full, "prompt": prompt, "max_length": T + 40, "do_sample": False}]
+    if not batching:
+        for i, p in enumerate(paths):
+            assert _post(c, "/load_shard", {"model_name": "org/tiny", "shard_id": i, "shard_path": p})[0] == 200
+        reqs.append({"model_name": "org/tiny", "prompt": prompt, "shard_ids": [0, 1], "max_length": T + 40, "do_sample": False})
+    try:
+        for req in reqs:
+            code, plain = _post(c, "/inference", req)
+            assert code == 200
+            out = _lines(c.post("/inference", json=dict(req, stream=True)))
+            final = out[-1]
+            assert final["http_status"] == 200 and final["status"] == "success" and final["result"] == plain["result"]
+            parts = [o["result"] for o in out[:-1]]
+            assert parts and all(o["status"] == "partial" for o in out[:-1])
+            assert all(b.startswith(a) for a, b in zip(parts, parts[1:] + [final["result"]]))
+            assert len(parts[0].split()) > T  # progress, not just the prompt
+    finally:
+        c.post("/unload_model", json={"model_name": full})
