@@ -83,10 +83,12 @@ class PipelineServer:
         self.stats = {"blocks": 0, "joined": 0, "max_active": 0}
 
     # ------------------------------------------------------------------ rank 0, any thread
-    def submit(self, cmd: dict) -> Future:
-        """cmd: {model, ids, max_length, deadline, gen}.  The future yields the list of NEW token ids."""
+    def submit(self, cmd: dict, on_partial=None) -> Future:
+        """cmd: {model, ids, max_length, deadline, gen}.  The future yields the list of NEW token ids.
+        on_partial(new_tokens_so_far) is called from the serving thread after every block (streaming)."""
         assert self.rank == 0
         r = _Req(cmd)
+        r.on_partial = on_partial
         self.queue.put(r)
         return r.future
 
@@ -270,6 +272,11 @@ class PipelineServer:
             have = min(self.rounds_done[slot], n_target)  # tokens the slot has CONSUMED = produced and fed back
             toks = self.be.read_tokens(slot, have)
             r.partial = toks
+            if getattr(r, "on_partial", None) is not None and toks:
+                try:
+                    r.on_partial(toks)
+                except Exception:  # noqa: BLE001 — a client's progress sink must not stop the pipeline
+                    pass
             eos = tuple(r.cmd.get("eos") or ())
             hit = next((i for i, t in enumerate(toks) if t in eos), None)
             if hit is not None:
@@ -528,10 +535,14 @@ def make_group_worker(rank: int, world: int, local: int, ctrl_group, env=None, b
             ids = tokenizer(prompt, return_tensors="pt")["input_ids"][0]
             check_max_length(len(ids), max_length)
             eos, pad = self._stop_ids(model_name)
-            fut = self.server.submit({"model": model_name, "ids": ids.tolist(), "max_length": int(max_length),
-                                      "deadline": deadline, "gen": gen or {}, "eos": list(eos)})
+            on = self._on_tokens(tokenizer)  # streaming: the text so far after every block of rounds
+            n_new = int(max_length) - len(ids)
+            fut = self.server.submit(
+                {"model": model_name, "ids": ids.tolist(), "max_length": int(max_length), "deadline": deadline,
+                 "gen": gen or {}, "eos": list(eos)},
+                on_partial=None if on is None else (
+                    lambda toks: on(torch.cat((ids.long(), torch.tensor(toks[:n_new], dtype=torch.int64)))[None])))
             wait = None if deadline is None else max(1.0, deadline - time.time() + 30)
-            self._wait_streaming(fut, tokenizer, ids, lambda: fut.request.partial)
             new = fut.result(timeout=wait)
             new = apply_eos(torch.tensor([new], dtype=torch.int64), eos, pad)
             return tokenizer.decode(torch.cat((ids.long(), new[0])), skip_special_tokens=True)
