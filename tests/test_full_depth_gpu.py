@@ -8,6 +8,7 @@ token IDs must match exactly, logits within a stated bf16 tolerance").  The othe
   * Llama-3-8B   (32 layers), 2 048-token prompt -> 64 greedy tokens  (configs[2], the headline)
   * TinyLlama-1.1B (22 layers), 512-token prompt -> 64 tokens         (configs[1])
   * Mistral-7B   (32 layers), 4 200-token prompt -> 24 tokens, so the 4 096-token window bites (configs[3])
+  * GPT-2 small  (12 layers), 32-token prompt -> 64 tokens: configs[0]'s model and shape on the CUDA path
 
 three ways: this engine (bf16, CUDA-graph decode = the path bench.py times), transformers bf16 sdpa (what the
 reference would run on this GPU) and transformers fp32 ("truth").  Stated tolerance (the one tests/test_engine_gpu.py
@@ -38,6 +39,9 @@ def _hf_config(transformers, name):
     from dli_b200.engine import NAMED_SPECS
 
     s = NAMED_SPECS[name]
+    if s.arch == "gpt2":
+        return s, transformers.GPT2Config(vocab_size=s.vocab, n_embd=s.d_model, n_layer=s.n_layers, n_head=s.n_heads,
+                                          n_positions=s.max_pos, n_inner=s.d_ff, layer_norm_epsilon=s.eps)
     kw = dict(vocab_size=s.vocab, hidden_size=s.d_model, intermediate_size=s.d_ff, num_hidden_layers=s.n_layers,
               num_attention_heads=s.n_heads, num_key_value_heads=s.n_kv_heads, head_dim=s.head_dim,
               max_position_embeddings=s.max_pos, rms_norm_eps=s.eps, tie_word_embeddings=False,
@@ -71,6 +75,15 @@ def _seeded_state_dict(spec, device, seed):
     return sd
 
 
+def _gpt2_state_dict(transformers, cfg, device, seed):
+    """GPT-2 keeps transformers' own (seeded) initialisation — Conv1D layout, learned positions, tied head — rounded
+    to bf16 so that all three runs hold the same weights."""
+    torch.manual_seed(seed)
+    with torch.device(device):
+        m = transformers.AutoModelForCausalLM.from_config(cfg, dtype=torch.float32)
+    return {k: v.detach().to(BF) for k, v in m.state_dict().items()}
+
+
 def _hf_model(transformers, cfg, sd, dtype, device):
     with torch.device(device):  # parameters and the rotary buffers are created on the GPU
         m = transformers.AutoModelForCausalLM.from_config(cfg, dtype=dtype)
@@ -79,7 +92,7 @@ def _hf_model(transformers, cfg, sd, dtype, device):
 
 
 @pytest.mark.parametrize("name,T,n_new", [("llama-3-8b", 2048, 64), ("tinyllama-1.1b", 512, 64),
-                                          ("mistral-7b", 4200, 24)])
+                                          ("mistral-7b", 4200, 24), ("gpt2", 32, 64)])  # gpt2: configs[0]'s shape
 def test_full_depth_model_matches_transformers_on_the_same_gpu(cuda, name, T, n_new):
     transformers = pytest.importorskip("transformers")
     from dli_b200.engine import ShardEngine
@@ -90,7 +103,7 @@ def test_full_depth_model_matches_transformers_on_the_same_gpu(cuda, name, T, n_
     need = int(3.3 * w_bf16) + (8 << 30)  # peak: the bf16 state dict + the fp32 transformers model
     if free < need:
         pytest.skip(f"needs ~{need >> 30} GiB of free HBM, {free >> 30} GiB available")
-    sd = _seeded_state_dict(spec, cuda, seed=2024)
+    sd = _gpt2_state_dict(transformers, cfg, cuda, 2024) if spec.arch == "gpt2" else _seeded_state_dict(spec, cuda, seed=2024)
     ids = torch.randint(0, spec.vocab, (1, T), generator=torch.Generator().manual_seed(1))
     max_len = T + n_new
 
