@@ -157,7 +157,27 @@ inline EncodeTiledFn get_encode_fn() {
 }
 
 // 2-D bf16 row-major [rows, K] tensor, box = [box_rows, 64 elements], 128-byte swizzle.
+// A tensor map is a pure function of (address, shape, box): the last few are kept per thread, so the weight matrices
+// a prefill walks layer after layer are encoded once instead of once per launch.
+struct TmapKey {
+  const void* base;
+  int rows, K, box_rows;
+  size_t stride;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && rows == o.rows && K == o.K && box_rows == o.box_rows && stride == o.stride;
+  }
+};
 inline int make_tmap(CUtensorMap* tm, const void* base, int rows, int K, int box_rows, size_t row_stride_elems = 0) {
+  constexpr int kSlots = 256;
+  struct Slot { TmapKey key; CUtensorMap map; bool used; };
+  static thread_local Slot cache[kSlots] = {};
+  const TmapKey key{base, rows, K, box_rows, row_stride_elems};
+  const size_t h = (reinterpret_cast<uintptr_t>(base) >> 8) * 1000003u + (size_t)rows * 31 + (size_t)box_rows * 7 + (size_t)K;
+  Slot& slot = cache[h % kSlots];
+  if (slot.used && slot.key == key) {
+    *tm = slot.map;
+    return DLI_OK;
+  }
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return fail(DLI_ERR_CUDA, "gemm: cuTensorMapEncodeTiled is not available from the driver");
   cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
@@ -168,6 +188,9 @@ inline int make_tmap(CUtensorMap* tm, const void* base, int rows, int K, int box
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(DLI_ERR_CUDA, "gemm: cuTensorMapEncodeTiled failed (CUresult %d)", (int)r);
+  slot.key = key;
+  slot.map = *tm;
+  slot.used = true;
   return DLI_OK;
 }
 
