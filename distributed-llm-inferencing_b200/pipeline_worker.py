@@ -80,6 +80,8 @@ class PipelineServer:
         self.draining: List[int] = []
         self.rounds_done: Dict[int, int] = {}
         self._stop = threading.Event()
+        self._failed = False                 # this rank's last block raised: told to the group with the next plan
+        self._joining: List[_Req] = []
         self.stats = {"blocks": 0, "joined": 0, "max_active": 0}
 
     # ------------------------------------------------------------------ rank 0, any thread
@@ -117,13 +119,13 @@ class PipelineServer:
             keep = []
             for r in pend:
                 model = r.cmd["model"]
-                if self.model is not None and model != self.model and (self.active or joins):
-                    keep.append(r)  # another model is being served: wait until its requests have left
+                if self.model is not None and model != self.model and (self.active or joins or self.closing or self.draining):
+                    keep.append(r)  # another model is being served: wait until its requests have left and their slots are freed
                 elif not free:
                     keep.append(r)
                 else:
                     if self.model is None or not (self.active or joins):
-                        self.model = model
+                        self.model = model  # (closing and draining are empty here: see the first branch)
                     r.slot = free.pop(0)
                     joins.append(r)
             for r in keep:
@@ -157,11 +159,18 @@ class PipelineServer:
                 self._apply(plan)
             except Exception as e:  # noqa: BLE001 — a data-plane failure: fail what is in flight, keep serving
                 print(f"[dli pipeline worker {self.rank}] block failed: {type(e).__name__}: {e}", file=sys.stderr, flush=True)
+                # The slots' state (open rounds, KV pages) is unknown now.  Ranks must rebuild their stages TOGETHER (the
+                # runners' tick counters address the mailboxes), so the failure is only noted here; the next plan's
+                # first exchange tells every rank, and all of them start again from an empty pipeline.  (A failure every
+                # rank meets at the same point — the KV pool running out in a join — or one on rank 0's bookkeeping is
+                # repaired this way; a rank failing alone inside an NCCL call cannot be repaired from here.)
+                self._failed = True
                 if self.rank == 0:
                     for r in list(self.active.values()) + list(getattr(self, "_joining", [])):
                         if not r.future.done():
                             r.future.set_exception(e)
                     self.active.clear()
+                    self._joining = []
 
     def _agree(self, errs: dict) -> dict:
         """Union of every rank's {key: message} (first rank wins per key), identical on all ranks."""
@@ -187,19 +196,22 @@ class PipelineServer:
         except Exception as e:  # noqa: BLE001
             errs["*"] = msg(e)
         box: List[Optional[dict]] = [None] * self.world
-        dist.all_gather_object(box, {"errs": errs, "probe": probe}, group=self.ctrl)
+        dist.all_gather_object(box, {"errs": errs, "probe": probe, "failed": self._failed}, group=self.ctrl)
+        self._failed = False
         errs = {}
         for d in box:
             for k, v in d["errs"].items():
                 errs.setdefault(k, v)
-        if not errs and any((d["probe"] or {}).get("stale") for d in box):
-            # some rank's resident engine was unloaded behind the pipeline's back: every rank rebuilds its stage now
-            # (together: the runners' tick counters must agree); what was in flight on the old engines is lost
+        failed = any(d["failed"] for d in box)
+        if failed or (not errs and any((d["probe"] or {}).get("stale") for d in box)):
+            # some rank's last block failed, or its resident engine was unloaded behind the pipeline's back: every rank
+            # rebuilds its stage now (together: the runners' tick counters must agree); what was in flight is lost
             be.reset()
             if self.rank == 0:
+                why = "a block of the pipeline failed" if failed else "the model was unloaded while the request was running"
                 for r in self.active.values():
                     if not r.future.done():
-                        r.future.set_exception(RuntimeError("the model was unloaded while the request was running"))
+                        r.future.set_exception(RuntimeError(why))
                 self.active.clear()
             self.closing, self.draining = [], []
             plan = dict(plan, close=[], free=[], active=0)
@@ -389,6 +401,8 @@ class CudaBackend(StageBackend):
         return self._runner
 
     def reset(self) -> None:
+        if self.eng is not None:
+            self.eng.kv.release_all()  # the slots' pages: the engine may stay resident in the worker's registry
         self.model, self.eng, self._runner, self._stage, self._rows = None, None, None, None, {}
 
     def check_request(self, req: dict) -> None:

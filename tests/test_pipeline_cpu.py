@@ -336,6 +336,8 @@ def _server_worker(rank, world, port, q):
                 raise ValueError("Input length of input_ids is too long")
 
         def join(self, slot, req):
+            if req["ids"][0] == 666:  # every rank fails at the same point, before any exchange
+                raise RuntimeError("KV cache out of pages")
             self.stage.steps[slot] = 0
             self.stage.tokens[slot] = torch.tensor([float(sum(req["ids"]) % 1000)])
             self.stage.consumed[slot] = []
@@ -344,6 +346,9 @@ def _server_worker(rank, world, port, q):
             return self._runner
 
         def read_tokens(self, slot, n):
+            if self.stage.consumed[slot][:1] == [777] and not getattr(self, "glitched", False):
+                self.glitched = True  # rank 0's bookkeeping fails once, after a block every other rank finished
+                raise RuntimeError("bookkeeping")
             return self.stage.consumed[slot][:n]
 
         def release(self, slot):
@@ -379,6 +384,22 @@ def _server_worker(rank, world, port, q):
                     out["missing"] = str(e)
                 r = {"model": "toy", "ids": [40, 2], "max_length": 6, "deadline": None, "gen": {}}
                 out["after"] = (r, srv.submit(r).result(timeout=100))  # the group still serves
+                # a block that fails (on every rank in a join; on rank 0 alone after the ticks): what was in flight fails,
+                # every rank rebuilds its stage with the next plan, and later requests get the right tokens again
+                for name, ids in (("boom", [666, 0]), ("glitch", [777, 0])):
+                    side = srv.submit({"model": "toy", "ids": [3, 3], "max_length": 40, "deadline": None, "gen": {}})
+                    try:
+                        srv.submit({"model": "toy", "ids": ids, "max_length": 12, "deadline": None, "gen": {}}).result(timeout=100)
+                        out[name] = "no error"
+                    except Exception as e:  # noqa: BLE001
+                        out[name] = f"{type(e).__name__}: {e}"
+                    try:
+                        side.result(timeout=100)
+                        out[name + "_side"] = "no error"
+                    except Exception as e:  # noqa: BLE001
+                        out[name + "_side"] = f"{type(e).__name__}: {e}"
+                    r = {"model": "toy", "ids": [41 + len(name), 2], "max_length": 11, "deadline": None, "gen": {}}
+                    out["after_" + name] = (r, srv.submit(r).result(timeout=100))
                 out["stats"] = dict(srv.stats)
             finally:
                 srv.shutdown()
@@ -405,7 +426,7 @@ def test_worker_group_serves_concurrent_requests_over_gloo(world):
     [p.join(timeout=60) for p in procs]
     assert all(p.exitcode == 0 for p in procs)
     for k, v in out.items():
-        if k in ("late", "bad", "missing", "stats"):
+        if k in ("late", "bad", "missing", "stats", "boom", "glitch", "boom_side", "glitch_side"):
             continue
         req, toks = v
         n = req["max_length"] - len(req["ids"])
@@ -417,6 +438,9 @@ def test_worker_group_serves_concurrent_requests_over_gloo(world):
     assert out["late"] == "TimeoutError: Inference generation timed out"
     assert out["bad"].startswith("ValueError: Input length of input_ids")
     assert out["missing"] == f"Shard {world - 1} of model missing is not loaded"
+    assert out["boom"] == "RuntimeError: KV cache out of pages" and out["glitch"] == "RuntimeError: bookkeeping"
+    # the request that shared the failed block fails with it (its slot's state is gone), never with wrong tokens
+    assert out["boom_side"].startswith("RuntimeError") and out["glitch_side"].startswith("RuntimeError")
     assert out["stats"]["max_active"] >= 3  # requests really shared the pipeline
 
 
