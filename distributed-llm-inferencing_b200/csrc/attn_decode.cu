@@ -279,13 +279,13 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
       const float m_new = fmaxf(m_run[r], mx);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float corr = exp2f((m_run[r] - m_use) * scale_log2);
+      const float corr = ex2_ftz((m_run[r] - m_use) * scale_log2);
       m_run[r] = m_new;
       float p[4];
-      p[0] = exp2f((s[0][2 * r] - m_use) * scale_log2);
-      p[1] = exp2f((s[0][2 * r + 1] - m_use) * scale_log2);
-      p[2] = exp2f((s[1][2 * r] - m_use) * scale_log2);
-      p[3] = exp2f((s[1][2 * r + 1] - m_use) * scale_log2);
+      p[0] = ex2_ftz((s[0][2 * r] - m_use) * scale_log2);
+      p[1] = ex2_ftz((s[0][2 * r + 1] - m_use) * scale_log2);
+      p[2] = ex2_ftz((s[1][2 * r] - m_use) * scale_log2);
+      p[3] = ex2_ftz((s[1][2 * r + 1] - m_use) * scale_log2);
       l_run[r] = l_run[r] * corr + (p[0] + p[1] + p[2] + p[3]);
       pa[r] = pack_bf16(p[0], p[1]);      // a0 (row g) / a1 (row g+8): tokens 2t,2t+1
       pa[2 + r] = pack_bf16(p[2], p[3]);  // a2 / a3: tokens 8+2t, 8+2t+1
@@ -345,7 +345,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     if (mmax != -INFINITY) {
 #pragma unroll
       for (int w = 0; w < NW; ++w) {
-        const float f = exp2f((red_ml[(w * 16 + row) * 2] - mmax) * scale_log2);
+        const float f = ex2_ftz((red_ml[(w * 16 + row) * 2] - mmax) * scale_log2);
         acc += f * red_o[(size_t)(w * 16 + row) * HD + col];
         lsum += f * red_ml[(w * 16 + row) * 2 + 1];
       }
@@ -387,7 +387,7 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
       float acc = 0.f, lsum = 0.f;
       if (mmax != -INFINITY) {
         for (int sp = 0; sp < num_splits; ++sp) {
-          const float f = exp2f((ld_dsmem_f32(cpo_addr + (16 * HD + row * 2) * 4, sp) - mmax) * scale_log2);
+          const float f = ex2_ftz((ld_dsmem_f32(cpo_addr + (16 * HD + row * 2) * 4, sp) - mmax) * scale_log2);
           acc += f * ld_dsmem_f32(cpo_addr + idx * 4, sp);
           lsum += f * ld_dsmem_f32(cpo_addr + (16 * HD + row * 2 + 1) * 4, sp);
         }
@@ -444,8 +444,8 @@ attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restric
   const float mmax = warp_max(fmaxf(m0, m1));
   float f0 = 0.f, f1 = 0.f;
   if (mmax != -INFINITY) {
-    f0 = exp2f((m0 - mmax) * scale_log2);
-    f1 = exp2f((m1 - mmax) * scale_log2);
+    f0 = ex2_ftz((m0 - mmax) * scale_log2);
+    f1 = ex2_ftz((m1 - mmax) * scale_log2);
   }
   const float lsum = warp_sum(f0 * l0 + f1 * l1);
   float acc[VEC];

@@ -151,13 +151,13 @@ attn_prefill_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int T,
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
       const float m_new = fmaxf(m_run[r], mx);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float corr = exp2f((m_run[r] - m_use) * scale_log2);
+      const float corr = ex2_ftz((m_run[r] - m_use) * scale_log2);
       m_run[r] = m_new;
       float rs = 0.f;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float p0 = exp2f((s[j][2 * r] - m_use) * scale_log2);
-        const float p1 = exp2f((s[j][2 * r + 1] - m_use) * scale_log2);
+        const float p0 = ex2_ftz((s[j][2 * r] - m_use) * scale_log2);
+        const float p1 = ex2_ftz((s[j][2 * r + 1] - m_use) * scale_log2);
         rs += p0 + p1;
         // n-tile j = tokens 8j..8j+7 -> k-step j/2, low (a0/a1) or high (a2/a3) half
         pa[j >> 1][(j & 1) * 2 + r] = pack_bf16(p0, p1);

@@ -228,13 +228,16 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
       mbar_wait(s_full + 8 * st, (it >> 1) & 1);
       tcgen05_fence_after();
       float s[64];
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tS + st * 128 + lane_off + col0 + c * 32, r);
+      {
+        uint32_t r0[32], r1[32];  // both halves requested before the one wait: one TMEM round trip per tile
+        tmem_ld_32x32(tS + st * 128 + lane_off + col0, r0);
+        tmem_ld_32x32(tS + st * 128 + lane_off + col0 + 32, r1);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(r[i]);
+        for (int i = 0; i < 32; ++i) {
+          s[i] = __uint_as_float(r0[i]);
+          s[32 + i] = __uint_as_float(r1[i]);
+        }
       }
       tcgen05_fence_before();
       __syncwarp();
@@ -258,11 +261,19 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
       }
       float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       xch[(it & 1) * 256 + half * 128 + row] = mx;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      // only the two warps that share a TMEM lane quadrant meet (named barrier 1 + quad, 64 threads): the four
+      // quadrants do not wait for each other
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
       mx = fmaxf(mx, xch[(it & 1) * 256 + (half ^ 1) * 128 + row]);
-      const float m_new = fmaxf(m_run, mx);
+      // Lazy reference maximum: the exponentials only need a COMMON reference per row, not the true running
+      // maximum, so m_run moves only when the tile's maximum exceeds it by more than 2^kLazyLog2 (p stays
+      // <= 256, exact in bf16's range; sums are fp32).  Then corr == 1 on almost every tile and the
+      // TMEM round trip that rescales O below is skipped.  (-inf - -inf = NaN compares false: a fully
+      // masked tile leaves m_run alone.)
+      constexpr float kLazyLog2 = 8.f;
+      const float m_new = ((mx - m_run) * scale_log2 > kLazyLog2) ? mx : m_run;
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float corr = exp2f((m_run - m_use) * scale_log2);
+      const float corr = ex2_ftz((m_run - m_use) * scale_log2);
       m_run = m_new;
       // p = 2^(s*scale - m*scale): one FFMA feeds each exp2; four partial sums
       const float ms = m_use * scale_log2;
@@ -271,7 +282,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
       for (int i = 0; i < 64; i += 4) {
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          s[i + u] = exp2f(fmaf(s[i + u], scale_log2, -ms));
+          s[i + u] = ex2_ftz(fmaf(s[i + u], scale_log2, -ms));
           rs4[u] += s[i + u];
         }
       }
@@ -314,7 +325,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
     }
     // ---- epilogue: O / l -> bf16 (the two halves of a row add their partial sums) ----
     xch[(it & 1) * 256 + half * 128 + row] = l_run;
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
     l_run += xch[(it & 1) * 256 + (half ^ 1) * 128 + row];
     mbar_wait(pv_done, (it - 1) & 1);
     tcgen05_fence_after();

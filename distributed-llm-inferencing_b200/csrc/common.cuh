@@ -126,6 +126,15 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 // ... and allow the next kernel of the stream to start launching.
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// 2^x as ONE MUFU.EX2: exp2f() without -ftz wraps the instruction in a range test and two predicated multiplies
+// so that results below 2^-126 come out as denormals (4 issue slots per call); softmax weights that small
+// contribute nothing, so the flash-attention loops flush them to zero instead.
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
