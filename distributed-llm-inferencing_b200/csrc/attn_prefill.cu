@@ -36,8 +36,10 @@ attn_prefill_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int T,
   const uint32_t sV = sK + 2 * kTileBytes;
 
   pdl_wait();
-  const int qtile = gridDim.x - 1 - blockIdx.x;
-  const int h = blockIdx.y, b = blockIdx.z;
+  // z (dispatched slowest) walks the query tiles from the longest to the shortest, x and y the heads and sequences:
+  // the longest CTAs of all heads start first (see attn_prefill_tc.cu)
+  const int qtile = gridDim.z - 1 - blockIdx.z;
+  const int h = blockIdx.x, b = blockIdx.y;
   const int kvh = h / (H / KV);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const size_t ld = (size_t)(H + 2 * KV) * HD;
@@ -206,7 +208,7 @@ static int launch_prefill(const void* qkv, void* out, int B, int T, int H, int K
   static PerDeviceOnce once;
   DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(
                                      attn_prefill_kernel<HD, kPaged>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem)));
-  dim3 grid((T + kPfTile - 1) / kPfTile, H, B);
+  dim3 grid(H, B, (T + kPfTile - 1) / kPfTile);
   DLI_LAUNCH("attn_prefill_kernel", (attn_prefill_kernel<HD, kPaged>), grid, dim3(kPfThreads), (size_t)kSmem, s,
              (const bf16*)qkv, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window, (const bf16*)k_cache,
              (const bf16*)v_cache, page_table, max_pages, page_shift, prefix);
@@ -222,7 +224,7 @@ extern "C" int dli_attn_prefill_bf16(const void* qkv, void* out, int B, int T, i
   DLI_CHECK_ARG(hd == 64 || hd == 128, "dli_attn_prefill_bf16: hd must be 64 or 128 (got %d)", hd);
   DLI_CHECK_ARG(B >= 0 && T >= 0 && H > 0 && KV > 0 && H % KV == 0 && window >= 0,
                 "dli_attn_prefill_bf16: bad sizes B=%d T=%d H=%d KV=%d", B, T, H, KV);
-  DLI_CHECK_ARG(H <= 65535 && B <= 65535, "dli_attn_prefill_bf16: H/B out of grid range");
+  DLI_CHECK_ARG(B <= 65535 && T <= 65535 * 64, "dli_attn_prefill_bf16: B/T out of grid range");
   DLI_CHECK_ARG(aligned16(qkv) && aligned16(out), "dli_attn_prefill_bf16: pointers must be 16-byte aligned");
   if (B == 0 || T == 0) return DLI_OK;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -250,7 +252,7 @@ extern "C" int dli_attn_prefill_paged_bf16(const void* qkv, void* out, const voi
   DLI_CHECK_ARG((long long)prefix + T <= (long long)max_pages * page_size,
                 "dli_attn_prefill_paged_bf16: prefix + T = %d exceeds the page table (%d pages of %d)", prefix + T,
                 max_pages, page_size);
-  DLI_CHECK_ARG(H <= 65535 && B <= 65535, "dli_attn_prefill_paged_bf16: H/B out of grid range");
+  DLI_CHECK_ARG(B <= 65535 && T <= 65535 * 64, "dli_attn_prefill_paged_bf16: B/T out of grid range");
   DLI_CHECK_ARG(aligned16(qkv) && aligned16(out) && aligned16(k_cache) && aligned16(v_cache),
                 "dli_attn_prefill_paged_bf16: pointers must be 16-byte aligned");
   if (B == 0 || T == 0) return DLI_OK;

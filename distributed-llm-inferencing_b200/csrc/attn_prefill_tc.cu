@@ -80,8 +80,13 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_mem + 128);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qtile = gridDim.x - 1 - blockIdx.x;  // heavier (later) query tiles first
-  const int h = blockIdx.y, b = blockIdx.z;
+  // CTAs are dispatched x fastest, z slowest: z walks the query tiles from the last (most key tiles) to the first,
+  // x and y the heads and sequences of one query tile.  So the longest CTAs of ALL heads start first and the
+  // shortest fill the tail (with the tile index fastest, the last head's 16-tile CTA started when 31/32 of the
+  // work was dispatched and the other SMs waited for it), and the CTAs running at any time read the same
+  // few key/value tiles from L2.
+  const int qtile = gridDim.z - 1 - blockIdx.z;
+  const int h = blockIdx.x, b = blockIdx.y;
   const int kvh = h / (H / KV);
   const int q0 = qtile * kTcTile;
   const int qpos0 = (kPaged ? prefix : 0) + q0;  // absolute position of the tile's first query row
@@ -364,7 +369,7 @@ extern "C" int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T
   DLI_CHECK_ARG(hd == 128, "dli_attn_prefill_tc_bf16: head_dim must be 128 (got %d); use dli_attn_prefill_bf16", hd);
   DLI_CHECK_ARG(B >= 0 && T >= 0 && H > 0 && KV > 0 && H % KV == 0 && window >= 0,
                 "dli_attn_prefill_tc_bf16: bad sizes B=%d T=%d H=%d KV=%d", B, T, H, KV);
-  DLI_CHECK_ARG(H <= 65535 && B <= 65535, "dli_attn_prefill_tc_bf16: H/B out of grid range");
+  DLI_CHECK_ARG(B <= 65535 && T <= 65535 * 64, "dli_attn_prefill_tc_bf16: B/T out of grid range");
   DLI_CHECK_ARG(aligned16(qkv) && aligned16(out), "dli_attn_prefill_tc_bf16: pointers must be 16-byte aligned");
   if (B == 0 || T == 0) return DLI_OK;
   static PerDeviceOnce once;
@@ -375,7 +380,7 @@ extern "C" int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T
   // the packed qkv matrix [B*T, cols]; box = 128 rows x 64 columns (one swizzle span)
   int rc = make_tmap(&tm, qkv, B * T, cols, 128);
   if (rc != DLI_OK) return rc;
-  dim3 grid((T + kTcTile - 1) / kTcTile, H, B);
+  dim3 grid(H, B, (T + kTcTile - 1) / kTcTile);
   DLI_LAUNCH("attn_prefill_tc_kernel", attn_prefill_tc_kernel<false>, grid, dim3(kTcThreads), (size_t)kTcSmem,
              static_cast<cudaStream_t>(stream), tm, tm, tm, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window,
              (const int32_t*)nullptr, 0, 0, 0, 0);
@@ -404,7 +409,7 @@ int launch_attn_prefill_tc_paged(const void* qkv, void* out, const void* k_cache
   if (rc != DLI_OK) return rc;
   int shift = 0;
   while ((1 << shift) < page_size) ++shift;
-  dim3 grid((T + kTcTile - 1) / kTcTile, H, B);
+  dim3 grid(H, B, (T + kTcTile - 1) / kTcTile);
   DLI_LAUNCH("attn_prefill_tc_kernel", attn_prefill_tc_kernel<true>, grid, dim3(kTcThreads), (size_t)kTcSmem, s, tm,
              tmK, tmV, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window, page_table, max_pages, shift, prefix,
              (int)rows);
