@@ -1,7 +1,8 @@
 // Causal prefill attention on the 5th-generation tensor cores (head_dim 128).
 //
-// One CTA = 128 query rows of one head; KV tiles of 128 tokens.  Both GEMMs of
-// flash attention are tcgen05.mma with fp32 accumulators in TMEM:
+// Work item = 128 query rows of one head; KV tiles of 128 tokens; one persistent CTA per SM walks a
+// length-sorted list of items (see TcItem below).  Both GEMMs of flash attention are tcgen05.mma
+// with fp32 accumulators in TMEM:
 //   S = Q K^T   : A = Q tile, B = K tile, both K-major (hd contiguous), SWIZZLE_128B, via TMA
 //   O += P V    : A = P (bf16, written to shared memory by the softmax warps in the same
 //                 K-major swizzled layout), B = V tile as an MN-major operand (hd contiguous,
@@ -24,7 +25,7 @@ constexpr int kSpanBytes = 128 * 64 * 2;  // one [128 rows x 64 elements] swizzl
 constexpr int kTileBytes2 = 2 * kSpanBytes;  // a [128 x 128] bf16 operand tile: 32 KB
 
 // smem: Q | K0 K1 | V0 V1 | P | barriers
-constexpr int kTcSmem = 6 * kTileBytes2 + 1024 + 256 + 2048;  // + row max / sum exchange
+constexpr int kTcSmem = 6 * kTileBytes2 + 1024 + 256 + 2048 + 1024;  // + barriers, row max exchange, row sum exchange
 
 __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32]) {
   asm volatile(
@@ -56,6 +57,17 @@ __host__ __device__ constexpr uint32_t make_idesc_attn(bool b_mn_major) {
          ((uint32_t)(128 >> 4) << 24);
 }
 
+// One work item = one 128-row query tile of one head of one sequence.  The kernel is PERSISTENT: a CTA per SM walks a
+// static list of items, so the TMEM allocation, the barrier set-up and the launch of a CTA are paid once per SM and
+// the output pass of an item (O from TMEM, normalise, store) runs while the producer loads the next item's Q, K, V and
+// the MMA warp computes its first two score tiles.  The list is sorted by length (the last query tile of every head
+// first: it has the most key tiles) and dealt to the CTAs in serpentine order — round r gives CTA c item
+// r*G + c, the next round item r*G + (G-1-c) — which evens out the sum of lengths per CTA without any counter in
+// global memory.  Measured on B200, T = 2048 / 4096, 32 heads: 65.0 / 190.1 us with one CTA per item.
+struct TcItem {
+  int h, b, kvh, q0, qpos0, t_begin, t_end, row_base;
+};
+
 // kPaged (chunked prefill): the T query rows are a chunk at positions prefix .. prefix+T-1; K and V tiles come
 // from the paged cache through two more tensor maps (the cache seen as [pages*KV*page_size, hd] rows, box = one
 // page x 64 columns): the 32 lanes of the producer warp each issue one page-sized box of a 128-token tile.
@@ -65,7 +77,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, bf16* __restrict__ out, int T, int H, int KV,
                        float scale_log2, int window, const int32_t* __restrict__ page_table, int max_pages,
-                       int page_shift, int prefix, int cache_rows) {
+                       int page_shift, int prefix, int cache_rows, int B, int n_qtiles) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const uint32_t sQ = smem_addr(smem);
@@ -76,29 +88,38 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
   const uint32_t bars = smem_addr(bar_mem);
   // barrier slots (8 B each)
   const uint32_t q_full = bars, k_full = bars + 8, k_empty = bars + 24, v_full = bars + 40, v_empty = bars + 56,
-                 s_full = bars + 72, s_empty = bars + 88, p_full = bars + 104, pv_done = bars + 112;
+                 s_full = bars + 72, s_empty = bars + 88, p_full = bars + 104, pv_done = bars + 112,
+                 q_empty = bars + 120;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_mem + 128);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // CTAs are dispatched x fastest, z slowest: z walks the query tiles from the last (most key tiles) to the first,
-  // x and y the heads and sequences of one query tile.  So the longest CTAs of ALL heads start first and the
-  // shortest fill the tail (with the tile index fastest, the last head's 16-tile CTA started when 31/32 of the
-  // work was dispatched and the other SMs waited for it), and the CTAs running at any time read the same
-  // few key/value tiles from L2.
-  const int qtile = gridDim.z - 1 - blockIdx.z;
-  const int h = blockIdx.x, b = blockIdx.y;
-  const int kvh = h / (H / KV);
-  const int q0 = qtile * kTcTile;
-  const int qpos0 = (kPaged ? prefix : 0) + q0;  // absolute position of the tile's first query row
-  int t_begin = 0;
-  if (window > 0 && qpos0 - window + 1 > 0) t_begin = (qpos0 - window + 1) / kTcTile;
-  // last key tile: the one holding the last query row's own position (the diagonal tile when prefix == 0)
-  const int t_end = kPaged ? min((prefix + T + kTcTile - 1) / kTcTile, (qpos0 + kTcTile - 1) / kTcTile + 1) : qtile + 1;
-  const int row_base = b * T;   // row of token 0 of this sequence in the packed qkv matrix
+  const int n_hb = H * B;
+  const int n_items = n_hb * n_qtiles;
+  const int G = gridDim.x, cta = blockIdx.x;
+
+  // item r of this CTA (serpentine deal of the length-sorted list); false when the list is exhausted
+  auto get_item = [&](int r, TcItem& it) -> bool {
+    const int idx = r * G + ((r & 1) ? G - 1 - cta : cta);
+    if (idx >= n_items) return false;
+    const int level = idx / n_hb, hb = idx - level * n_hb;
+    const int qtile = n_qtiles - 1 - level;  // longest first
+    it.b = hb / H;
+    it.h = hb - it.b * H;
+    it.kvh = it.h / (H / KV);
+    it.q0 = qtile * kTcTile;
+    it.qpos0 = (kPaged ? prefix : 0) + it.q0;  // absolute position of the tile's first query row
+    it.t_begin = 0;
+    if (window > 0 && it.qpos0 - window + 1 > 0) it.t_begin = (it.qpos0 - window + 1) / kTcTile;
+    // last key tile: the one holding the last query row's own position (the diagonal tile when prefix == 0)
+    it.t_end = kPaged ? min((prefix + T + kTcTile - 1) / kTcTile, (it.qpos0 + kTcTile - 1) / kTcTile + 1) : qtile + 1;
+    it.row_base = it.b * T;  // row of token 0 of this sequence in the packed qkv matrix
+    return true;
+  };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm);
     mbar_init(q_full, 1);
+    mbar_init(q_empty, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(k_full + 8 * i, 1);
       mbar_init(k_empty + 8 * i, 1);
@@ -117,73 +138,86 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  const uint32_t tS = tmem_base, tO = tmem_base + 256;
+  const uint32_t tS = tmem_base, tO = tmem_base + 256;  // S0 | S1 | O, 128 columns each
 
+  // Running counters, the same in every role by construction: n = items this CTA has started, g = key tiles it has
+  // started over all items.  The K/V/S buffers alternate with g and the barrier parities follow g (Q: n).
+  // O needs no second buffer: the first P.V of an item waits for P, which the softmax warps write only after they
+  // have read the previous item's O in its output pass.
   if (warp == 0 && kPaged) {
     // ---------------- TMA producer, paged K/V: one page-sized box per lane ----------------
     if (lane == 0) {
       tma_prefetch_desc(&tmK);
       tma_prefetch_desc(&tmV);
-      mbar_expect_tx(q_full, kTileBytes2);
-      tma_load_2d(sQ, &tm, q_full, h * kTcHd, row_base + q0);
-      tma_load_2d(sQ + kSpanBytes, &tm, q_full, h * kTcHd + 64, row_base + q0);
     }
     const int page_size = 1 << page_shift;
     const int nb = kTcTile >> page_shift;  // boxes per 64-column half of a tile (<= 16)
     const int half = lane / nb, bi = lane - half * nb;
     const int total = prefix + T;
-    int it = 0;
-    for (int j = t_begin; j < t_end; ++j, ++it) {
-      const int st = it & 1;
-      const uint32_t ph = (it >> 1) & 1;
-      const int tok0 = j * kTcTile + bi * page_size;
-      int row = cache_rows;  // out of bounds: the box is zero-filled
-      if (lane < 2 * nb && tok0 < total)
-        row = (page_table[(size_t)b * max_pages + (tok0 >> page_shift)] * KV + kvh) << page_shift;
-      const uint32_t dst = (uint32_t)(st * kTileBytes2 + half * kSpanBytes + bi * page_size * 128);
+    int g = 0;
+    TcItem w;
+    for (int n = 0; get_item(n, w); ++n) {
       if (lane == 0) {
-        mbar_wait(k_empty + 8 * st, ph ^ 1);
-        mbar_expect_tx(k_full + 8 * st, kTileBytes2);
+        mbar_wait(q_empty, (n & 1) ^ 1);  // the last S = Q K^T of the previous item has read Q
+        mbar_expect_tx(q_full, kTileBytes2);
+        tma_load_2d(sQ, &tm, q_full, w.h * kTcHd, w.row_base + w.q0);
+        tma_load_2d(sQ + kSpanBytes, &tm, q_full, w.h * kTcHd + 64, w.row_base + w.q0);
       }
-      __syncwarp();
-      if (lane < 2 * nb) tma_load_2d(sK + dst, &tmK, k_full + 8 * st, half * 64, row);
-      if (lane == 0) {
-        mbar_wait(v_empty + 8 * st, ph ^ 1);
-        mbar_expect_tx(v_full + 8 * st, kTileBytes2);
+      for (int j = w.t_begin; j < w.t_end; ++j, ++g) {
+        const int st = g & 1;
+        const uint32_t ph = (g >> 1) & 1;
+        const int tok0 = j * kTcTile + bi * page_size;
+        int row = cache_rows;  // out of bounds: the box is zero-filled
+        if (lane < 2 * nb && tok0 < total)
+          row = (page_table[(size_t)w.b * max_pages + (tok0 >> page_shift)] * KV + w.kvh) << page_shift;
+        const uint32_t dst = (uint32_t)(st * kTileBytes2 + half * kSpanBytes + bi * page_size * 128);
+        if (lane == 0) {
+          mbar_wait(k_empty + 8 * st, ph ^ 1);
+          mbar_expect_tx(k_full + 8 * st, kTileBytes2);
+        }
+        __syncwarp();
+        if (lane < 2 * nb) tma_load_2d(sK + dst, &tmK, k_full + 8 * st, half * 64, row);
+        if (lane == 0) {
+          mbar_wait(v_empty + 8 * st, ph ^ 1);
+          mbar_expect_tx(v_full + 8 * st, kTileBytes2);
+        }
+        __syncwarp();
+        if (lane < 2 * nb) tma_load_2d(sV + dst, &tmV, v_full + 8 * st, half * 64, row);
       }
-      __syncwarp();
-      if (lane < 2 * nb) tma_load_2d(sV + dst, &tmV, v_full + 8 * st, half * 64, row);
     }
   } else if (warp == 0) {
     if (lane == 0) {
       // ---------------- TMA producer ----------------
-      mbar_expect_tx(q_full, kTileBytes2);
-      tma_load_2d(sQ, &tm, q_full, h * kTcHd, row_base + q0);
-      tma_load_2d(sQ + kSpanBytes, &tm, q_full, h * kTcHd + 64, row_base + q0);
-      int it = 0;
-      for (int j = t_begin; j < t_end; ++j, ++it) {
-        const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
-        const int krow = row_base + j * kTcTile;
-        mbar_wait(k_empty + 8 * st, ph ^ 1);
-        mbar_expect_tx(k_full + 8 * st, kTileBytes2);
-        tma_load_2d(sK + st * kTileBytes2, &tm, k_full + 8 * st, (H + kvh) * kTcHd, krow);
-        tma_load_2d(sK + st * kTileBytes2 + kSpanBytes, &tm, k_full + 8 * st, (H + kvh) * kTcHd + 64, krow);
-        mbar_wait(v_empty + 8 * st, ph ^ 1);
-        mbar_expect_tx(v_full + 8 * st, kTileBytes2);
-        tma_load_2d(sV + st * kTileBytes2, &tm, v_full + 8 * st, (H + KV + kvh) * kTcHd, krow);
-        tma_load_2d(sV + st * kTileBytes2 + kSpanBytes, &tm, v_full + 8 * st, (H + KV + kvh) * kTcHd + 64, krow);
+      int g = 0;
+      TcItem w;
+      for (int n = 0; get_item(n, w); ++n) {
+        mbar_wait(q_empty, (n & 1) ^ 1);
+        mbar_expect_tx(q_full, kTileBytes2);
+        tma_load_2d(sQ, &tm, q_full, w.h * kTcHd, w.row_base + w.q0);
+        tma_load_2d(sQ + kSpanBytes, &tm, q_full, w.h * kTcHd + 64, w.row_base + w.q0);
+        for (int j = w.t_begin; j < w.t_end; ++j, ++g) {
+          const int st = g & 1;
+          const uint32_t ph = (g >> 1) & 1;
+          const int krow = w.row_base + j * kTcTile;
+          mbar_wait(k_empty + 8 * st, ph ^ 1);
+          mbar_expect_tx(k_full + 8 * st, kTileBytes2);
+          tma_load_2d(sK + st * kTileBytes2, &tm, k_full + 8 * st, (H + w.kvh) * kTcHd, krow);
+          tma_load_2d(sK + st * kTileBytes2 + kSpanBytes, &tm, k_full + 8 * st, (H + w.kvh) * kTcHd + 64, krow);
+          mbar_wait(v_empty + 8 * st, ph ^ 1);
+          mbar_expect_tx(v_full + 8 * st, kTileBytes2);
+          tma_load_2d(sV + st * kTileBytes2, &tm, v_full + 8 * st, (H + KV + w.kvh) * kTcHd, krow);
+          tma_load_2d(sV + st * kTileBytes2 + kSpanBytes, &tm, v_full + 8 * st, (H + KV + w.kvh) * kTcHd + 64, krow);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       // ---------------- MMA issuer ----------------
       constexpr uint32_t idesc_s = make_idesc_attn(false), idesc_o = make_idesc_attn(true);
-      const int n = t_end - t_begin;
-      auto issue_s = [&](int it) {  // S(it) = Q K^T into score buffer it & 1
-        const int st = it & 1;
-        mbar_wait(k_full + 8 * st, (it >> 1) & 1);
-        mbar_wait(s_empty + 8 * st, ((it >> 1) & 1) ^ 1);  // softmax of tile it-2 has read this buffer
+      auto issue_s = [&](int g, bool last_of_item) {  // S(g) = Q K^T into score buffer g & 1
+        const int st = g & 1;
+        mbar_wait(k_full + 8 * st, (g >> 1) & 1);
+        mbar_wait(s_empty + 8 * st, ((g >> 1) & 1) ^ 1);  // the softmax of tile g-2 has read this buffer
         tcgen05_fence_after();
 #pragma unroll
         for (int kk = 0; kk < kTcHd / kUmmaK; ++kk) {
@@ -193,165 +227,186 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
         }
         umma_commit(s_full + 8 * st);
         umma_commit(k_empty + 8 * st);
+        if (last_of_item) umma_commit(q_empty);  // Q may be replaced by the next item's
       };
-      mbar_wait(q_full, 0);
-      issue_s(0);
-      for (int it = 0; it < n; ++it) {
-        if (it + 1 < n) issue_s(it + 1);
-        const int st = it & 1;
-        mbar_wait(p_full, it & 1);                 // P(it) in shared memory, O rescaled
-        mbar_wait(v_full + 8 * st, (it >> 1) & 1);
-        tcgen05_fence_after();
+      int g = 0;
+      TcItem w;
+      for (int n = 0; get_item(n, w); ++n) {
+        const int nt = w.t_end - w.t_begin;
+        mbar_wait(q_full, n & 1);
+        issue_s(g, nt == 1);
+        for (int it = 0; it < nt; ++it, ++g) {
+          // S of the next tile goes out before this tile's P is waited for: the tensor pipe works on the next
+          // scores while the softmax warps exponentiate the current ones
+          if (it + 1 < nt) issue_s(g + 1, it + 2 == nt);
+          const int st = g & 1;
+          mbar_wait(p_full, g & 1);                 // P(g) in shared memory, O rescaled (or, it == 0, read out)
+          mbar_wait(v_full + 8 * st, (g >> 1) & 1);
+          tcgen05_fence_after();
 #pragma unroll
-        for (int kk = 0; kk < kTcTile / kUmmaK; ++kk) {
-          // A = P: K-major, k-step = 16 tokens; B = V: MN-major, 16 tokens = two 8-row groups (2048 B)
-          const uint64_t adesc = make_smem_desc(sP + (kk >> 2) * kSpanBytes + (kk & 3) * 32);
-          const uint64_t bdesc = make_smem_desc_mn(sV + st * kTileBytes2 + kk * 2048);
-          umma_bf16(tO, adesc, bdesc, idesc_o, (it > 0 || kk > 0) ? 1u : 0u);
+          for (int kk = 0; kk < kTcTile / kUmmaK; ++kk) {
+            // A = P: K-major, k-step = 16 tokens; B = V: MN-major, 16 tokens = two 8-row groups (2048 B)
+            const uint64_t adesc = make_smem_desc(sP + (kk >> 2) * kSpanBytes + (kk & 3) * 32);
+            const uint64_t bdesc = make_smem_desc_mn(sV + st * kTileBytes2 + kk * 2048);
+            umma_bf16(tO, adesc, bdesc, idesc_o, (it > 0 || kk > 0) ? 1u : 0u);
+          }
+          umma_commit(pv_done);
+          umma_commit(v_empty + 8 * st);
         }
-        umma_commit(pv_done);
-        umma_commit(v_empty + 8 * st);
       }
     }
   } else {
-    // ---------------- softmax + epilogue: 8 warps; a query row is shared by two threads ----------------
+    // ---------------- softmax + output pass: 8 warps; a query row is shared by two threads ----------------
     // warps w and w+4 own the same TMEM lane quadrant; `half` 0 takes score/output columns 0-63,
     // half 1 columns 64-127.  Only the row maximum has to be exchanged per tile (shared memory + one
-    // named barrier); each thread keeps the running sum of its own columns until the epilogue.
+    // named barrier); each thread keeps the running sum of its own columns until the output pass.
     const int sw = warp - 2;
     const int quad = warp & 3, half = sw >> 2;
     const int row = quad * 32 + lane;           // TMEM lane
-    const int qrel = q0 + row;                  // row of the chunk / prompt
-    const int qrow = qpos0 + row;               // absolute position in the sequence
     const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
     const uint32_t col0 = half * 64;
-    float* xch = reinterpret_cast<float*>(bar_mem + 256);  // [2 parities][2 halves][128 rows]
-    float m_run = -INFINITY, l_run = 0.f;
-    int it = 0;
-    for (int j = t_begin; j < t_end; ++j, ++it) {
-      const int st = it & 1;
-      mbar_wait(s_full + 8 * st, (it >> 1) & 1);
-      tcgen05_fence_after();
-      float s[64];
-      {
-        uint32_t r0[32], r1[32];  // both halves requested before the one wait: one TMEM round trip per tile
-        tmem_ld_32x32(tS + st * 128 + lane_off + col0, r0);
-        tmem_ld_32x32(tS + st * 128 + lane_off + col0 + 32, r1);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          s[i] = __uint_as_float(r0[i]);
-          s[32 + i] = __uint_as_float(r1[i]);
-        }
-      }
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(s_empty + 8 * st);  // score buffer may be overwritten by S(it+2)
-      const bool need_mask = (j * kTcTile + kTcTile - 1 > qpos0) ||
-                             (window > 0 && j * kTcTile < qpos0 + kTcTile - window + 1);
-      if (need_mask) {
-#pragma unroll
-        for (int i = 0; i < 64; ++i) {
-          const int tok = j * kTcTile + (int)col0 + i;
-          if (tok > qrow || (window > 0 && tok <= qrow - window)) s[i] = -INFINITY;
-        }
-      }
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the 64-long one is latency-bound
-#pragma unroll
-      for (int i = 0; i < 64; i += 4) {
-        mx4[0] = fmaxf(mx4[0], s[i]);
-        mx4[1] = fmaxf(mx4[1], s[i + 1]);
-        mx4[2] = fmaxf(mx4[2], s[i + 2]);
-        mx4[3] = fmaxf(mx4[3], s[i + 3]);
-      }
-      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      xch[(it & 1) * 256 + half * 128 + row] = mx;
-      // only the two warps that share a TMEM lane quadrant meet (named barrier 1 + quad, 64 threads): the four
-      // quadrants do not wait for each other
-      asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
-      mx = fmaxf(mx, xch[(it & 1) * 256 + (half ^ 1) * 128 + row]);
-      // Lazy reference maximum: the exponentials only need a COMMON reference per row, not the true running
-      // maximum, so m_run moves only when the tile's maximum exceeds it by more than 2^kLazyLog2 (p stays
-      // <= 256, exact in bf16's range; sums are fp32).  Then corr == 1 on almost every tile and the
-      // TMEM round trip that rescales O below is skipped.  (-inf - -inf = NaN compares false: a fully
-      // masked tile leaves m_run alone.)
-      constexpr float kLazyLog2 = 8.f;
-      const float m_new = ((mx - m_run) * scale_log2 > kLazyLog2) ? mx : m_run;
-      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float corr = ex2_ftz((m_run - m_use) * scale_log2);
-      m_run = m_new;
-      // p = 2^(s*scale - m*scale): one FFMA feeds each exp2; four partial sums
-      const float ms = m_use * scale_log2;
-      float rs4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int i = 0; i < 64; i += 4) {
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          s[i + u] = ex2_ftz(fmaf(s[i + u], scale_log2, -ms));
-          rs4[u] += s[i + u];
-        }
-      }
-      const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
-      l_run = l_run * corr + rs;
-      // previous P.V must have finished before P is overwritten and O is rescaled
-      if (it > 0) {
-        mbar_wait(pv_done, (it - 1) & 1);
+    float* xch = reinterpret_cast<float*>(bar_mem + 256);           // row maxima: [2 parities][2 halves][128 rows]
+    float* xch_l = reinterpret_cast<float*>(bar_mem + 256 + 2048);  // row sums of the output pass: [2 halves][128 rows]
+    int g = 0;
+    TcItem w;
+    for (int n = 0; get_item(n, w); ++n) {
+      const int qrel = w.q0 + row;                // row of the chunk / prompt
+      const int qrow = w.qpos0 + row;             // absolute position in the sequence
+      float m_run = -INFINITY, l_run = 0.f;
+      for (int j = w.t_begin; j < w.t_end; ++j, ++g) {
+        const bool first = j == w.t_begin;
+        const int st = g & 1;
+        mbar_wait(s_full + 8 * st, (g >> 1) & 1);
         tcgen05_fence_after();
-      }
-      // P (bf16) -> shared memory, K-major SWIZZLE_128B: span `half` = this thread's 64 tokens
-      uint8_t* prow = smem + (sP - sQ) + half * kSpanBytes + row * 128;
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {  // 8 chunks of 8 tokens (16 B)
-        uint4 u;
-        u.x = pack_bf16(s[c * 8 + 0], s[c * 8 + 1]);
-        u.y = pack_bf16(s[c * 8 + 2], s[c * 8 + 3]);
-        u.z = pack_bf16(s[c * 8 + 4], s[c * 8 + 5]);
-        u.w = pack_bf16(s[c * 8 + 6], s[c * 8 + 7]);
-        *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = u;
-      }
-      // (skipped when no row of this warp moved its maximum: corr == 1 exactly, nothing to do)
-      if (it > 0 && !__all_sync(0xffffffffu, corr == 1.f)) {
-        // O *= corr on this thread's 64 output columns; TMEM -> registers -> TMEM
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t r[32];
-          tmem_ld_32x32(tO + lane_off + col0 + c * 32, r);
+        float s[64];
+        {
+          uint32_t r0[32], r1[32];  // both halves requested before the one wait: one TMEM round trip per tile
+          tmem_ld_32x32(tS + st * 128 + lane_off + col0, r0);
+          tmem_ld_32x32(tS + st * 128 + lane_off + col0 + 32, r1);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * corr);
-          tmem_st_32x32(tO + lane_off + col0 + c * 32, r);
+          for (int i = 0; i < 32; ++i) {
+            s[i] = __uint_as_float(r0[i]);
+            s[32 + i] = __uint_as_float(r1[i]);
+          }
         }
-        tmem_st_wait();
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_empty + 8 * st);  // score buffer may be overwritten by S(g+2)
+        const bool need_mask = (j * kTcTile + kTcTile - 1 > w.qpos0) ||
+                               (window > 0 && j * kTcTile < w.qpos0 + kTcTile - window + 1);
+        if (need_mask) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) {
+            const int tok = j * kTcTile + (int)col0 + i;
+            if (tok > qrow || (window > 0 && tok <= qrow - window)) s[i] = -INFINITY;
+          }
+        }
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the 64-long one is latency-bound
+#pragma unroll
+        for (int i = 0; i < 64; i += 4) {
+          mx4[0] = fmaxf(mx4[0], s[i]);
+          mx4[1] = fmaxf(mx4[1], s[i + 1]);
+          mx4[2] = fmaxf(mx4[2], s[i + 2]);
+          mx4[3] = fmaxf(mx4[3], s[i + 3]);
+        }
+        float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        xch[(g & 1) * 256 + half * 128 + row] = mx;
+        // only the two warps that share a TMEM lane quadrant meet (named barrier 1 + quad, 64 threads): the four
+        // quadrants do not wait for each other
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+        mx = fmaxf(mx, xch[(g & 1) * 256 + (half ^ 1) * 128 + row]);
+        // Lazy reference maximum: the exponentials only need a COMMON reference per row, not the true running
+        // maximum, so m_run moves only when the tile's maximum exceeds it by more than 2^kLazyLog2 (p stays
+        // <= 256, exact in bf16's range; sums are fp32).  Then corr == 1 on almost every tile and the
+        // TMEM round trip that rescales O below is skipped.  (-inf - -inf = NaN compares false: a fully
+        // masked tile leaves m_run alone.)
+        constexpr float kLazyLog2 = 8.f;
+        const float m_new = ((mx - m_run) * scale_log2 > kLazyLog2) ? mx : m_run;
+        const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+        const float corr = ex2_ftz((m_run - m_use) * scale_log2);
+        m_run = m_new;
+        // p = 2^(s*scale - m*scale): one FFMA feeds each exp2; four partial sums
+        const float ms = m_use * scale_log2;
+        float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int i = 0; i < 64; i += 4) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            s[i + u] = ex2_ftz(fmaf(s[i + u], scale_log2, -ms));
+            rs4[u] += s[i + u];
+          }
+        }
+        const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
+        l_run = l_run * corr + rs;
+        // the previous P.V of this item must have finished before P is overwritten and O is rescaled (an item's
+        // first tile: the output pass of the item before has waited for its last P.V already)
+        if (!first) {
+          mbar_wait(pv_done, (g - 1) & 1);
+          tcgen05_fence_after();
+        }
+        // P (bf16) -> shared memory, K-major SWIZZLE_128B: span `half` = this thread's 64 tokens
+        uint8_t* prow = smem + (sP - sQ) + half * kSpanBytes + row * 128;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {  // 8 chunks of 8 tokens (16 B)
+          uint4 u;
+          u.x = pack_bf16(s[c * 8 + 0], s[c * 8 + 1]);
+          u.y = pack_bf16(s[c * 8 + 2], s[c * 8 + 3]);
+          u.z = pack_bf16(s[c * 8 + 4], s[c * 8 + 5]);
+          u.w = pack_bf16(s[c * 8 + 6], s[c * 8 + 7]);
+          *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = u;
+        }
+        // (skipped when no row of this warp moved its maximum: corr == 1 exactly, nothing to do)
+        if (!first && !__all_sync(0xffffffffu, corr == 1.f)) {
+          // O *= corr on this thread's 64 output columns; TMEM -> registers -> TMEM
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32(tO + lane_off + col0 + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * corr);
+            tmem_st_32x32(tO + lane_off + col0 + c * 32, r);
+          }
+          tmem_st_wait();
+        }
+        fence_proxy_async();       // P visible to the tensor core's (async proxy) shared-memory reads
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_full);
       }
-      fence_proxy_async();       // P visible to the tensor core's (async proxy) shared-memory reads
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
-    }
-    // ---- epilogue: O / l -> bf16 (the two halves of a row add their partial sums) ----
-    xch[(it & 1) * 256 + half * 128 + row] = l_run;
-    asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
-    l_run += xch[(it & 1) * 256 + (half ^ 1) * 128 + row];
-    mbar_wait(pv_done, (it - 1) & 1);
-    tcgen05_fence_after();
-    const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-    bf16* dst = out + ((size_t)(row_base + qrel)) * ((size_t)H * kTcHd) + (size_t)h * kTcHd + col0;
+      // ---- output pass: O / l -> bf16 (the two halves of a row add their partial sums) ----
+      xch_l[half * 128 + row] = l_run;
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+      l_run += xch_l[(half ^ 1) * 128 + row];
+      mbar_wait(pv_done, (g - 1) & 1);
+      tcgen05_fence_after();
+      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+      bf16* dst = out + ((size_t)(w.row_base + qrel)) * ((size_t)H * kTcHd) + (size_t)w.h * kTcHd + col0;
+      {
+        uint32_t r0[32], r1[32];
+        tmem_ld_32x32(tO + lane_off + col0, r0);
+        tmem_ld_32x32(tO + lane_off + col0 + 32, r1);
+        tmem_ld_wait();
+        if (qrel < T) {
 #pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32(tO + lane_off + col0 + c * 32, r);
-      tmem_ld_wait();
-      if (qrel < T) {
+          for (int gq = 0; gq < 4; ++gq) {
+            float v[8];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float v[8];
+            for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r0[gq * 8 + i]) * inv;
+            st_16B(dst + gq * 8, pack8(v));
+          }
 #pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[g * 8 + i]) * inv;
-          st_16B(dst + c * 32 + g * 8, pack8(v));
+          for (int gq = 0; gq < 4; ++gq) {
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r1[gq * 8 + i]) * inv;
+            st_16B(dst + 32 + gq * 8, pack8(v));
+          }
         }
       }
+      tcgen05_fence_before();  // O has been read: the next item's first P.V (after its P) may overwrite it
     }
-    tcgen05_fence_before();
   }
   __syncthreads();
   if (warp == 1) {
@@ -369,7 +424,7 @@ extern "C" int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T
   DLI_CHECK_ARG(hd == 128, "dli_attn_prefill_tc_bf16: head_dim must be 128 (got %d); use dli_attn_prefill_bf16", hd);
   DLI_CHECK_ARG(B >= 0 && T >= 0 && H > 0 && KV > 0 && H % KV == 0 && window >= 0,
                 "dli_attn_prefill_tc_bf16: bad sizes B=%d T=%d H=%d KV=%d", B, T, H, KV);
-  DLI_CHECK_ARG(B <= 65535 && T <= 65535 * 64, "dli_attn_prefill_tc_bf16: B/T out of grid range");
+  DLI_CHECK_ARG((long long)((T + 127) / 128) * H * B <= 0x7fffffffLL, "dli_attn_prefill_tc_bf16: too many query tiles");
   DLI_CHECK_ARG(aligned16(qkv) && aligned16(out), "dli_attn_prefill_tc_bf16: pointers must be 16-byte aligned");
   if (B == 0 || T == 0) return DLI_OK;
   static PerDeviceOnce once;
@@ -380,10 +435,12 @@ extern "C" int dli_attn_prefill_tc_bf16(const void* qkv, void* out, int B, int T
   // the packed qkv matrix [B*T, cols]; box = 128 rows x 64 columns (one swizzle span)
   int rc = make_tmap(&tm, qkv, B * T, cols, 128);
   if (rc != DLI_OK) return rc;
-  dim3 grid(H, B, (T + kTcTile - 1) / kTcTile);
+  const int n_qtiles = (T + kTcTile - 1) / kTcTile;
+  const long long n_items = (long long)n_qtiles * H * B;
+  dim3 grid((unsigned)(n_items < sm_count_cached() ? n_items : sm_count_cached()));  // persistent: one CTA per SM
   DLI_LAUNCH("attn_prefill_tc_kernel", attn_prefill_tc_kernel<false>, grid, dim3(kTcThreads), (size_t)kTcSmem,
              static_cast<cudaStream_t>(stream), tm, tm, tm, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window,
-             (const int32_t*)nullptr, 0, 0, 0, 0);
+             (const int32_t*)nullptr, 0, 0, 0, 0, B, n_qtiles);
   return DLI_OK;
 }
 
@@ -409,10 +466,12 @@ int launch_attn_prefill_tc_paged(const void* qkv, void* out, const void* k_cache
   if (rc != DLI_OK) return rc;
   int shift = 0;
   while ((1 << shift) < page_size) ++shift;
-  dim3 grid(H, B, (T + kTcTile - 1) / kTcTile);
+  const int n_qtiles = (T + kTcTile - 1) / kTcTile;
+  const long long n_items = (long long)n_qtiles * H * B;
+  dim3 grid((unsigned)(n_items < sm_count_cached() ? n_items : sm_count_cached()));
   DLI_LAUNCH("attn_prefill_tc_kernel", attn_prefill_tc_kernel<true>, grid, dim3(kTcThreads), (size_t)kTcSmem, s, tm,
              tmK, tmV, (bf16*)out, T, H, KV, scale * 1.4426950408889634f, window, page_table, max_pages, shift, prefix,
-             (int)rows);
+             (int)rows, B, n_qtiles);
   return DLI_OK;
 }
 

@@ -10,20 +10,13 @@ OUT = os.path.join(ROOT, "scratch", "_abl")
 src = open(os.path.join(PKG, "csrc", "attn_prefill_tc.cu")).read()
 
 EDITS = {
-    "noqk": [("""          umma_bf16(tS + st * 128, make_smem_desc(sQ + off), make_smem_desc(sK + st * kTileBytes2 + off), idesc_s,
-                    kk > 0 ? 1u : 0u);""", "          if (off == 0xffffffu) umma_bf16(tS + st * 128, make_smem_desc(sQ + off), make_smem_desc(sK + st * kTileBytes2 + off), idesc_s, kk > 0 ? 1u : 0u);")],
-    "nopv": [("          umma_bf16(tO, adesc, bdesc, idesc_o, (it > 0 || kk > 0) ? 1u : 0u);", "          if (it == 0x7fffff) umma_bf16(tO, adesc, bdesc, idesc_o, (it > 0 || kk > 0) ? 1u : 0u);")],
-    "notma": [("""        mbar_expect_tx(k_full + 8 * st, kTileBytes2);
-        tma_load_2d(sK + st * kTileBytes2, &tm, k_full + 8 * st, (H + kvh) * kTcHd, krow);
-        tma_load_2d(sK + st * kTileBytes2 + kSpanBytes, &tm, k_full + 8 * st, (H + kvh) * kTcHd + 64, krow);""",
-               "        mbar_expect_tx(k_full + 8 * st, 0);"),
-              ("""        mbar_expect_tx(v_full + 8 * st, kTileBytes2);
-        tma_load_2d(sV + st * kTileBytes2, &tm, v_full + 8 * st, (H + KV + kvh) * kTcHd, krow);
-        tma_load_2d(sV + st * kTileBytes2 + kSpanBytes, &tm, v_full + 8 * st, (H + KV + kvh) * kTcHd + 64, krow);""",
-               "        mbar_expect_tx(v_full + 8 * st, 0);")],
+    "base": [],
+    "nostore": [("st_16B(dst + gq * 8, pack8(v));", "if (inv == 123.f) st_16B(dst + gq * 8, pack8(v));"),
+                ("st_16B(dst + 32 + gq * 8, pack8(v));", "if (inv == 123.f) st_16B(dst + 32 + gq * 8, pack8(v));")],
+    "nomask": [("if (need_mask) {", "if (need_mask && scale_log2 == 123.f) {")],
+    "noepi": [("if (qrel < T) {", "if (qrel < T && inv == 123.f) {")],
 }
-EDITS["nomma"] = EDITS["noqk"] + EDITS["nopv"]
-EDITS["nomma_notma"] = EDITS["nomma"] + EDITS["notma"]
+EDITS["nomask_noepi"] = EDITS["nomask"] + EDITS["noepi"]
 os.makedirs(OUT, exist_ok=True)
 objs = [os.path.join(PKG, "build", f) for f in os.listdir(os.path.join(PKG, "build")) if f.endswith(".o") and f != "attn_prefill_tc.o"]
 for name, edits in EDITS.items():
