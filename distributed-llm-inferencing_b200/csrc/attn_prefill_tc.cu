@@ -8,8 +8,8 @@
 //                 K-major swizzled layout), B = V tile as an MN-major operand (hd contiguous,
 //                 tokens along K), exactly as TMA lands the [tokens, hd] rows
 // TMEM: S0 | S1 (two score buffers, 128 columns each) | O (128 columns).
-// Roles (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-9 =
-// softmax + epilogue: two threads per query row (TMEM lane), 64 columns each, fp32 online softmax.
+// Roles (576 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-17 =
+// softmax + output pass: four threads per query row (TMEM lane), 32 columns each, fp32 online softmax.
 // The MMA warp issues S(j+1) before it waits for the softmax of tile j, so the tensor pipe
 // works on the next scores while the SFUs exponentiate the current ones; P/V of tile j are
 // multiplied as soon as P(j) is in shared memory and O has been rescaled.
@@ -18,14 +18,18 @@
 
 namespace dli {
 
-constexpr int kTcThreads = 320;  // TMA warp + MMA warp + 8 softmax warps
+constexpr int kRowThreads = 4;                 // softmax threads per query row (each owns 128 / kRowThreads columns)
+constexpr int kSmWarps = 4 * kRowThreads;      // softmax warps: kRowThreads per TMEM lane quadrant
+constexpr int kSmCols = 128 / kRowThreads;     // score / output columns per softmax thread
+constexpr int kTcThreads = 64 + 32 * kSmWarps;  // TMA warp + MMA warp + softmax warps
 constexpr int kTcTile = 128;      // query rows per CTA and tokens per KV tile
 constexpr int kTcHd = 128;
 constexpr int kSpanBytes = 128 * 64 * 2;  // one [128 rows x 64 elements] swizzled sub-tile: 16 KB
 constexpr int kTileBytes2 = 2 * kSpanBytes;  // a [128 x 128] bf16 operand tile: 32 KB
 
-// smem: Q | K0 K1 | V0 V1 | P | barriers
-constexpr int kTcSmem = 6 * kTileBytes2 + 1024 + 256 + 2048 + 1024;  // + barriers, row max exchange, row sum exchange
+// smem: Q | K0 K1 | V0 V1 | barriers
+// + alignment slack, barriers, row max exchange [2][kRowThreads][128], row sum exchange [kRowThreads][128]
+constexpr int kTcSmem = 5 * kTileBytes2 + 1024 + 256 + 3 * kRowThreads * 128 * 4;
 
 __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32]) {
   asm volatile(
@@ -36,6 +40,14 @@ __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r
       "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
       "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
       "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
       : "memory");
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
@@ -83,14 +95,13 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
   const uint32_t sQ = smem_addr(smem);
   const uint32_t sK = sQ + kTileBytes2;          // 2 stages
   const uint32_t sV = sK + 2 * kTileBytes2;      // 2 stages
-  const uint32_t sP = sV + 2 * kTileBytes2;
-  uint8_t* bar_mem = smem + 6 * kTileBytes2;
+  uint8_t* bar_mem = smem + 5 * kTileBytes2;
   const uint32_t bars = smem_addr(bar_mem);
   // barrier slots (8 B each)
   const uint32_t q_full = bars, k_full = bars + 8, k_empty = bars + 24, v_full = bars + 40, v_empty = bars + 56,
-                 s_full = bars + 72, s_empty = bars + 88, p_full = bars + 104, pv_done = bars + 112,
-                 q_empty = bars + 120;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_mem + 128);
+                 s_full = bars + 72, s_empty = bars + 88, p_full = bars + 104, pv_done = bars + 112 /* 2 slots */,
+                 q_empty = bars + 128;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_mem + 136);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_hb = H * B;
@@ -126,10 +137,11 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
       mbar_init(v_full + 8 * i, 1);
       mbar_init(v_empty + 8 * i, 1);
       mbar_init(s_full + 8 * i, 1);
-      mbar_init(s_empty + 8 * i, 8);  // one arrive per softmax warp
+      mbar_init(s_empty + 8 * i, kSmWarps);  // one arrive per softmax warp
     }
-    mbar_init(p_full, 8);
+    mbar_init(p_full, kSmWarps);
     mbar_init(pv_done, 1);
+    mbar_init(pv_done + 8, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(smem_addr(tmem_ptr_smem), 512);
@@ -138,7 +150,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  const uint32_t tS = tmem_base, tO = tmem_base + 256;  // S0 | S1 | O, 128 columns each
+  // S0 | S1 | O (128 columns each) | P0 | P1 (64 columns each: 128 bf16 probabilities per row, two per column)
+  const uint32_t tS = tmem_base, tO = tmem_base + 256, tP = tmem_base + 384;
 
   // Running counters, the same in every role by construction: n = items this CTA has started, g = key tiles it has
   // started over all items.  The K/V/S buffers alternate with g and the barrier parities follow g (Q: n).
@@ -211,23 +224,32 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ---------------- MMA issuer ----------------
+    {
+      // ---------------- MMA issuer: the whole warp runs the loop (uniform values stay in uniform registers), one
+      // elected lane issues each tcgen05 instruction ----------------
       constexpr uint32_t idesc_s = make_idesc_attn(false), idesc_o = make_idesc_attn(true);
+      // operand descriptors: the 14-bit start-address field (bytes >> 4) advances with the k-step, so a k-step is
+      // an add on the low word.  Q/K: 16 elements = 32 B inside a 64-element span, spans kSpanBytes apart;
+      // V (MN-major): 16 tokens = two 8-row groups = 2048 B
+      const uint64_t qdesc = make_smem_desc(sQ);
+      const uint64_t kdesc0 = make_smem_desc(sK), vdesc0 = make_smem_desc_mn(sV);
       auto issue_s = [&](int g, bool last_of_item) {  // S(g) = Q K^T into score buffer g & 1
         const int st = g & 1;
         mbar_wait(k_full + 8 * st, (g >> 1) & 1);
         mbar_wait(s_empty + 8 * st, ((g >> 1) & 1) ^ 1);  // the softmax of tile g-2 has read this buffer
         tcgen05_fence_after();
+        const uint64_t kdesc = kdesc0 + (uint64_t)(st * (kTileBytes2 >> 4));
+        if (elect_one()) {
 #pragma unroll
-        for (int kk = 0; kk < kTcHd / kUmmaK; ++kk) {
-          const uint32_t off = (kk >> 2) * kSpanBytes + (kk & 3) * 32;
-          umma_bf16(tS + st * 128, make_smem_desc(sQ + off), make_smem_desc(sK + st * kTileBytes2 + off), idesc_s,
-                    kk > 0 ? 1u : 0u);
+          for (int kk = 0; kk < kTcHd / kUmmaK; ++kk) {
+            const uint32_t off = ((kk >> 2) * kSpanBytes + (kk & 3) * 32) >> 4;
+            umma_bf16(tS + st * 128, qdesc + off, kdesc + off, idesc_s, kk > 0 ? 1u : 0u);
+          }
+          umma_commit(s_full + 8 * st);
+          umma_commit(k_empty + 8 * st);
+          if (last_of_item) umma_commit(q_empty);  // Q may be replaced by the next item's
         }
-        umma_commit(s_full + 8 * st);
-        umma_commit(k_empty + 8 * st);
-        if (last_of_item) umma_commit(q_empty);  // Q may be replaced by the next item's
+        __syncwarp();
       };
       int g = 0;
       TcItem w;
@@ -240,33 +262,38 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
           // scores while the softmax warps exponentiate the current ones
           if (it + 1 < nt) issue_s(g + 1, it + 2 == nt);
           const int st = g & 1;
-          mbar_wait(p_full, g & 1);                 // P(g) in shared memory, O rescaled (or, it == 0, read out)
+          mbar_wait(p_full, g & 1);                 // P(g) in tensor memory, O rescaled (or, it == 0, read out)
           mbar_wait(v_full + 8 * st, (g >> 1) & 1);
           tcgen05_fence_after();
+          const uint64_t vdesc = vdesc0 + (uint64_t)(st * (kTileBytes2 >> 4));
+          if (elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < kTcTile / kUmmaK; ++kk) {
-            // A = P: K-major, k-step = 16 tokens; B = V: MN-major, 16 tokens = two 8-row groups (2048 B)
-            const uint64_t adesc = make_smem_desc(sP + (kk >> 2) * kSpanBytes + (kk & 3) * 32);
-            const uint64_t bdesc = make_smem_desc_mn(sV + st * kTileBytes2 + kk * 2048);
-            umma_bf16(tO, adesc, bdesc, idesc_o, (it > 0 || kk > 0) ? 1u : 0u);
+            for (int kk = 0; kk < kTcTile / kUmmaK; ++kk) {
+              // A = P from tensor memory: k-step = 16 tokens = 8 columns; B = V, 16 tokens further per k-step
+              umma_bf16_ts(tO, tP + st * 64 + kk * 8, vdesc + (uint64_t)(kk * (2048 >> 4)), idesc_o,
+                           (it > 0 || kk > 0) ? 1u : 0u);
+            }
+            umma_commit(pv_done + 8 * st);
+            umma_commit(v_empty + 8 * st);
           }
-          umma_commit(pv_done);
-          umma_commit(v_empty + 8 * st);
+          __syncwarp();
         }
       }
     }
   } else {
-    // ---------------- softmax + output pass: 8 warps; a query row is shared by two threads ----------------
-    // warps w and w+4 own the same TMEM lane quadrant; `half` 0 takes score/output columns 0-63,
-    // half 1 columns 64-127.  Only the row maximum has to be exchanged per tile (shared memory + one
-    // named barrier); each thread keeps the running sum of its own columns until the output pass.
+    // ---------------- softmax + output pass: kSmWarps warps; a query row is shared by kRowThreads threads ------------
+    // The kRowThreads warps w, w+4, ... own the same TMEM lane quadrant (w % 4); `part` selects the thread's kSmCols
+    // score/output columns.  Only the row maximum has to be exchanged per tile (shared memory + one named barrier
+    // per quadrant); each thread keeps the running sum of its own columns until the output pass.  With four warps
+    // per scheduler instead of two the TMEM loads, exchanges and fences of one warp hide behind the arithmetic of
+    // the others (the loop was latency-bound at two).
     const int sw = warp - 2;
-    const int quad = warp & 3, half = sw >> 2;
+    const int quad = warp & 3, part = sw >> 2;
     const int row = quad * 32 + lane;           // TMEM lane
     const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
-    const uint32_t col0 = half * 64;
-    float* xch = reinterpret_cast<float*>(bar_mem + 256);           // row maxima: [2 parities][2 halves][128 rows]
-    float* xch_l = reinterpret_cast<float*>(bar_mem + 256 + 2048);  // row sums of the output pass: [2 halves][128 rows]
+    const uint32_t col0 = part * kSmCols;
+    float* xch = reinterpret_cast<float*>(bar_mem + 256);                        // row maxima: [2 parities][parts][128 rows]
+    float* xch_l = xch + 2 * kRowThreads * 128;                                  // row sums of the output pass: [parts][128 rows]
     int g = 0;
     TcItem w;
     for (int n = 0; get_item(n, w); ++n) {
@@ -278,17 +305,16 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
         const int st = g & 1;
         mbar_wait(s_full + 8 * st, (g >> 1) & 1);
         tcgen05_fence_after();
-        float s[64];
+        float s[kSmCols];
         {
-          uint32_t r0[32], r1[32];  // both halves requested before the one wait: one TMEM round trip per tile
-          tmem_ld_32x32(tS + st * 128 + lane_off + col0, r0);
-          tmem_ld_32x32(tS + st * 128 + lane_off + col0 + 32, r1);
+          uint32_t r[kSmCols / 32][32];  // all pieces requested before the one wait: one TMEM round trip per tile
+#pragma unroll
+          for (int c = 0; c < kSmCols / 32; ++c) tmem_ld_32x32(tS + st * 128 + lane_off + col0 + c * 32, r[c]);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            s[i] = __uint_as_float(r0[i]);
-            s[32 + i] = __uint_as_float(r1[i]);
-          }
+          for (int c = 0; c < kSmCols / 32; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(r[c][i]);
         }
         tcgen05_fence_before();
         __syncwarp();
@@ -297,25 +323,27 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
                                (window > 0 && j * kTcTile < w.qpos0 + kTcTile - window + 1);
         if (need_mask) {
 #pragma unroll
-          for (int i = 0; i < 64; ++i) {
+          for (int i = 0; i < kSmCols; ++i) {
             const int tok = j * kTcTile + (int)col0 + i;
             if (tok > qrow || (window > 0 && tok <= qrow - window)) s[i] = -INFINITY;
           }
         }
-        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: the 64-long one is latency-bound
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // four chains: one long chain is latency-bound
 #pragma unroll
-        for (int i = 0; i < 64; i += 4) {
+        for (int i = 0; i < kSmCols; i += 4) {
           mx4[0] = fmaxf(mx4[0], s[i]);
           mx4[1] = fmaxf(mx4[1], s[i + 1]);
           mx4[2] = fmaxf(mx4[2], s[i + 2]);
           mx4[3] = fmaxf(mx4[3], s[i + 3]);
         }
         float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-        xch[(g & 1) * 256 + half * 128 + row] = mx;
-        // only the two warps that share a TMEM lane quadrant meet (named barrier 1 + quad, 64 threads): the four
-        // quadrants do not wait for each other
-        asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
-        mx = fmaxf(mx, xch[(g & 1) * 256 + (half ^ 1) * 128 + row]);
+        float* xrow = xch + (g & 1) * (kRowThreads * 128) + row;
+        xrow[part * 128] = mx;
+        // only the warps that share a TMEM lane quadrant meet (named barrier 1 + quad): the four quadrants do not
+        // wait for each other
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + quad), "n"(32 * kRowThreads) : "memory");
+#pragma unroll
+        for (int q = 0; q < kRowThreads; ++q) mx = fmaxf(mx, xrow[q * 128]);
         // Lazy reference maximum: the exponentials only need a COMMON reference per row, not the true running
         // maximum, so m_run moves only when the tile's maximum exceeds it by more than 2^kLazyLog2 (p stays
         // <= 256, exact in bf16's range; sums are fp32).  Then corr == 1 on almost every tile and the
@@ -330,7 +358,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
         const float ms = m_use * scale_log2;
         float rs4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int i = 0; i < 64; i += 4) {
+        for (int i = 0; i < kSmCols; i += 4) {
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             s[i + u] = ex2_ftz(fmaf(s[i + u], scale_log2, -ms));
@@ -339,28 +367,26 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
         }
         const float rs = (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
         l_run = l_run * corr + rs;
-        // the previous P.V of this item must have finished before P is overwritten and O is rescaled (an item's
-        // first tile: the output pass of the item before has waited for its last P.V already)
-        if (!first) {
-          mbar_wait(pv_done, (g - 1) & 1);
-          tcgen05_fence_after();
-        }
-        // P (bf16) -> shared memory, K-major SWIZZLE_128B: span `half` = this thread's 64 tokens
-        uint8_t* prow = smem + (sP - sQ) + half * kSpanBytes + row * 128;
+        // P (bf16, two tokens per 32-bit column) -> tensor memory, buffer g & 1: the A operand of this tile's P.V.
+        // The buffer's previous reader, P.V(g-2), has finished: S(g) was issued after it and is complete.
+        {
+          static_assert(kSmCols == 32, "P store below writes 16 packed columns per thread");
+          uint32_t pk[16];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {  // 8 chunks of 8 tokens (16 B)
-          uint4 u;
-          u.x = pack_bf16(s[c * 8 + 0], s[c * 8 + 1]);
-          u.y = pack_bf16(s[c * 8 + 2], s[c * 8 + 3]);
-          u.z = pack_bf16(s[c * 8 + 4], s[c * 8 + 5]);
-          u.w = pack_bf16(s[c * 8 + 6], s[c * 8 + 7]);
-          *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = u;
+          for (int c = 0; c < 16; ++c) pk[c] = pack_bf16(s[2 * c], s[2 * c + 1]);
+          tmem_st_32x16(tP + st * 64 + lane_off + (col0 >> 1), pk);
         }
         // (skipped when no row of this warp moved its maximum: corr == 1 exactly, nothing to do)
         if (!first && !__all_sync(0xffffffffu, corr == 1.f)) {
-          // O *= corr on this thread's 64 output columns; TMEM -> registers -> TMEM
+          // O *= corr on this thread's output columns; TMEM -> registers -> TMEM.  The previous P.V of this item
+          // must have finished first.  P.V(t) completes barrier pv_done[t & 1]; the softmax warps do not wait for
+          // every P.V any more, so the parity test must be safe without that: S(g) complete implies P.V(g-3)
+          // complete (issued earlier, same pipe), and P.V(g+1) cannot start before this warp delivers P(g+1) —
+          // barrier (g-1) & 1 is in the phase of P.V(g-1) or just past it, never further.
+          mbar_wait(pv_done + 8 * ((g - 1) & 1), ((g - 1) >> 1) & 1);
+          tcgen05_fence_after();
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
+          for (int c = 0; c < kSmCols / 32; ++c) {
             uint32_t r[32];
             tmem_ld_32x32(tO + lane_off + col0 + c * 32, r);
             tmem_ld_wait();
@@ -368,41 +394,37 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tm, const __grid_cons
             for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * corr);
             tmem_st_32x32(tO + lane_off + col0 + c * 32, r);
           }
-          tmem_st_wait();
         }
-        fence_proxy_async();       // P visible to the tensor core's (async proxy) shared-memory reads
+        tmem_st_wait();            // P (and O) are in tensor memory before the MMA warp is told
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(p_full);
       }
-      // ---- output pass: O / l -> bf16 (the two halves of a row add their partial sums) ----
-      xch_l[half * 128 + row] = l_run;
-      asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
-      l_run += xch_l[(half ^ 1) * 128 + row];
-      mbar_wait(pv_done, (g - 1) & 1);
+      // ---- output pass: O / l -> bf16 (the threads of a row add their partial sums, all in the same order) ----
+      xch_l[part * 128 + row] = l_run;
+      asm volatile("bar.sync %0, %1;" ::"r"(1 + quad), "n"(32 * kRowThreads) : "memory");
+      l_run = xch_l[row];
+#pragma unroll
+      for (int q = 1; q < kRowThreads; ++q) l_run += xch_l[q * 128 + row];
+      mbar_wait(pv_done + 8 * ((g - 1) & 1), ((g - 1) >> 1) & 1);  // the item's last P.V (same argument as above)
       tcgen05_fence_after();
       const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
       bf16* dst = out + ((size_t)(w.row_base + qrel)) * ((size_t)H * kTcHd) + (size_t)w.h * kTcHd + col0;
       {
-        uint32_t r0[32], r1[32];
-        tmem_ld_32x32(tO + lane_off + col0, r0);
-        tmem_ld_32x32(tO + lane_off + col0 + 32, r1);
+        uint32_t r[kSmCols / 32][32];
+#pragma unroll
+        for (int c = 0; c < kSmCols / 32; ++c) tmem_ld_32x32(tO + lane_off + col0 + c * 32, r[c]);
         tmem_ld_wait();
         if (qrel < T) {
 #pragma unroll
-          for (int gq = 0; gq < 4; ++gq) {
-            float v[8];
+          for (int c = 0; c < kSmCols / 32; ++c)
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r0[gq * 8 + i]) * inv;
-            st_16B(dst + gq * 8, pack8(v));
-          }
+            for (int gq = 0; gq < 4; ++gq) {
+              float v[8];
 #pragma unroll
-          for (int gq = 0; gq < 4; ++gq) {
-            float v[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r1[gq * 8 + i]) * inv;
-            st_16B(dst + 32 + gq * 8, pack8(v));
-          }
+              for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[c][gq * 8 + i]) * inv;
+              st_16B(dst + c * 32 + gq * 8, pack8(v));
+            }
         }
       }
       tcgen05_fence_before();  // O has been read: the next item's first P.V (after its P) may overwrite it
