@@ -126,17 +126,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(BN);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % Cfg::kStages;
-        const uint32_t ph = (kb / Cfg::kStages) & 1;
-        mbar_wait(full_bar + 8 * s, ph);
-        tcgen05_fence_after();
-        const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
-        const uint32_t sB = sA + Cfg::kABytes;
-        const uint64_t adesc = make_smem_desc(sA);
-        const uint64_t bdesc = make_smem_desc(sB);
+    // MMA issuer: the whole warp walks the loop with warp-uniform values (descriptors stay in uniform registers),
+    // one elected lane issues
+    constexpr uint32_t idesc = make_idesc(BN);
+    const uint64_t adesc0 = make_smem_desc(smem_addr(smem));
+    const uint64_t bdesc0 = make_smem_desc(smem_addr(smem) + Cfg::kABytes);
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % Cfg::kStages;
+      const uint32_t ph = (kb / Cfg::kStages) & 1;
+      mbar_wait(full_bar + 8 * s, ph);
+      tcgen05_fence_after();
+      const uint64_t adesc = adesc0 + (uint64_t)(s * (Cfg::kStageBytes >> 4));  // start-address field: bytes >> 4
+      const uint64_t bdesc = bdesc0 + (uint64_t)(s * (Cfg::kStageBytes >> 4));
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < kBlockK / kUmmaK; ++k) {
           // advancing 16 elements (32 bytes) along K inside the swizzle span: +2 in the >>4 address field
@@ -148,9 +150,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
         umma_commit(empty_bar + 8 * s);  // frees the smem slot when these MMAs retire
+        if (kb == num_kb - 1) umma_commit(tmem_full_bar);  // accumulator complete
       }
-      umma_commit(tmem_full_bar);  // accumulator complete
+      __syncwarp();
     }
+    if (num_kb <= 0 && elect_one()) umma_commit(tmem_full_bar);
   } else {
     // ---- epilogue warps 2..5: TMEM lane quadrant = warp % 4 -----------------------------
     const int quad = warp & 3;
@@ -499,27 +503,31 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(BN);
-      uint32_t kc = 0, tl = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
-        const uint32_t as = tl & 1;
-        mbar_wait(tempty_bar + 8 * as, ((tl >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+    // MMA issuer: the whole warp walks the loop with warp-uniform values (descriptors stay in uniform registers:
+    // no per-instruction R2UR chain as under a `lane == 0` branch), one elected lane issues
+    constexpr uint32_t idesc = make_idesc(BN);
+    const uint64_t adesc0 = make_smem_desc(smem_addr(smem));
+    const uint64_t bdesc0 = make_smem_desc(smem_addr(smem) + Cfg::kABytes);
+    uint32_t kc = 0, tl = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
+      const uint32_t as = tl & 1;
+      mbar_wait(tempty_bar + 8 * as, ((tl >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+      tcgen05_fence_after();
+      const uint32_t tacc = tmem_base + as * BN;
+      for (int kb = 0; kb < num_kb; ++kb, ++kc) {
+        const int s = kc % S;
+        mbar_wait(full_bar + 8 * s, (kc / S) & 1);
         tcgen05_fence_after();
-        const uint32_t tacc = tmem_base + as * BN;
-        for (int kb = 0; kb < num_kb; ++kb, ++kc) {
-          const int s = kc % S;
-          mbar_wait(full_bar + 8 * s, (kc / S) & 1);
-          tcgen05_fence_after();
-          const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
-          const uint64_t adesc = make_smem_desc(sA);
-          const uint64_t bdesc = make_smem_desc(sA + Cfg::kABytes);
+        const uint64_t adesc = adesc0 + (uint64_t)(s * (Cfg::kStageBytes >> 4));  // start-address field: bytes >> 4
+        const uint64_t bdesc = bdesc0 + (uint64_t)(s * (Cfg::kStageBytes >> 4));
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k)
             umma_bf16(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
           umma_commit(empty_bar + 8 * s);
+          if (kb == num_kb - 1) umma_commit(tfull_bar + 8 * as);
         }
-        umma_commit(tfull_bar + 8 * as);
+        __syncwarp();
       }
     }
   } else {

@@ -37,7 +37,7 @@ rep("        if (lane == 0) mbar_arrive(p_full);\n      }", "        if (lane ==
 rep("          if (it + 1 < nt) issue_s(g + 1, it + 2 == nt);", "          TR(1, g, 0);\n          if (it + 1 < nt) issue_s(g + 1, it + 2 == nt);\n          TR(1, g, 1);")
 rep("          mbar_wait(v_full + 8 * st, (g >> 1) & 1);\n          tcgen05_fence_after();",
     "          TR(1, g, 2);\n          mbar_wait(v_full + 8 * st, (g >> 1) & 1);\n          TR(1, g, 3);\n          tcgen05_fence_after();")
-rep("          umma_commit(v_empty + 8 * st);\n        }", "          umma_commit(v_empty + 8 * st);\n          TR(1, g, 4);\n        }")
+rep("            umma_commit(v_empty + 8 * st);\n          }\n          __syncwarp();", "            umma_commit(v_empty + 8 * st);\n          }\n          __syncwarp();\n          TR(1, g, 4);")
 # producer (unpaged)
 rep("          mbar_wait(k_empty + 8 * st, ph ^ 1);\n          mbar_expect_tx(k_full + 8 * st, kTileBytes2);\n          tma_load_2d(sK + st * kTileBytes2, &tm,",
     "          mbar_wait(k_empty + 8 * st, ph ^ 1);\n          TR(2, g, 0);\n          mbar_expect_tx(k_full + 8 * st, kTileBytes2);\n          tma_load_2d(sK + st * kTileBytes2, &tm,")
