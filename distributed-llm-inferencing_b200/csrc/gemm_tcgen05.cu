@@ -28,6 +28,8 @@
 //
 // Tensor-bound for prefill: 2*M*N*K FLOPs per launch; HBM-bound weight stream
 // for decode: N*K*2 bytes per launch.
+#include <stdlib.h>
+
 #include "tcgen05_utils.cuh"
 
 namespace dli {
@@ -404,17 +406,28 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // of weight loads before it waits for the previous kernel (programmatic dependent launch).
 // ======================================================================================
 
-template <int BN, bool kGated>
+// MT = 128-row halves of the activation tile (1 or 2).  MT = 2: the CTA multiplies a 256-row activation tile by the
+// weight tile with two MMAs per k-step (rows 0-127 and 128-255, one accumulator each) that read the SAME weight
+// tile from shared memory.  A 128 x 256 tile asks L2 for 48 KB per 64-wide k-block, i.e. per four MMAs — more than
+// one SM's share of the L2 bandwidth delivers in the time the tensor core needs for them, so the 128-row kernel
+// is bound by the operand feed (measured 0.85-0.95 of cuBLAS); 256 x 256 asks for 64 KB per EIGHT MMAs.  Its two
+// accumulators fill the 512 TMEM columns, so the epilogue is not overlapped with the next tile.
+template <int BN, bool kGated, int MT = 1>
 struct PrefillCfg {
-  static constexpr int kABytes = 128 * kBlockK * 2;
+  static constexpr int kABytes = MT * 128 * kBlockK * 2;
   static constexpr int kBBytes = BN * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStagesRaw = (216 * 1024) / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
-  static constexpr int kTmemCols = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
+  static constexpr int kAccCols = MT * BN;                          // TMEM columns of one tile's accumulators
+  static constexpr int kAccStages = 2 * kAccCols <= 512 ? 2 : 1;    // double-buffered when it fits
+  static constexpr int kTmemWant = kAccStages * kAccCols;
+  static constexpr int kTmemCols = kTmemWant <= 32 ? 32 : kTmemWant <= 64 ? 64 : kTmemWant <= 128 ? 128 : kTmemWant <= 256 ? 256 : 512;
   static constexpr int kOutCols = kGated ? 128 : BN;  // output columns per tile
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
   static_assert(!kGated || BN == 256, "gated tile is gate128|up128");
+  static_assert(MT == 1 || MT == 2, "one or two 128-row halves");
+  static_assert(kAccCols <= 512 && kStages >= 2, "tile does not fit TMEM / shared memory");
 };
 
 // Tile walk of the persistent kernel: m-tiles in groups of 16, inside a group m fastest, then n.  The
@@ -433,13 +446,15 @@ __device__ __forceinline__ void prefill_tile_coords(int tile, int m_tiles, int n
   m_blk = m0 + r - n_blk * gsize;
 }
 
-template <int BN, bool kGated>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// threads: TMA warp + MMA warp + four epilogue warps per 128-row half
+template <int BN, bool kGated, int MT>
+__global__ void __launch_bounds__(64 + 128 * MT, 1)
 gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const bf16* __restrict__ bias, const bf16* residual, bf16* y, int M, int N, int K,
                     int epilogue, int m_tiles, int num_tiles) {
-  using Cfg = PrefillCfg<BN, kGated>;
+  using Cfg = PrefillCfg<BN, kGated, MT>;
   constexpr int S = Cfg::kStages;
+  constexpr int kMRows = MT * 128;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* bar_mem = smem + S * Cfg::kStageBytes;
@@ -461,7 +476,7 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar + 8 * a, 1);
-      mbar_init(tempty_bar + 8 * a, 4);  // one arrive per epilogue warp
+      mbar_init(tempty_bar + 8 * a, 4 * MT);  // one arrive per epilogue warp
     }
     fence_barrier_init();
   }
@@ -492,12 +507,12 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const int s = kc % S;
           const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
           if ((int)kc < pre) {  // B already in flight, expect_tx already armed
-            tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, m_blk * 128);
+            tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, m_blk * kMRows);
             continue;
           }
           mbar_wait(empty_bar + 8 * s, ((kc / S) & 1) ^ 1);
           mbar_expect_tx(full_bar + 8 * s, Cfg::kStageBytes);
-          tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, m_blk * 128);
+          tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, m_blk * kMRows);
           tma_load_2d(sA + Cfg::kABytes, &tmB, full_bar + 8 * s, kb * kBlockK, n_blk * BN);
         }
       }
@@ -510,10 +525,11 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint64_t bdesc0 = make_smem_desc(smem_addr(smem) + Cfg::kABytes);
     uint32_t kc = 0, tl = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
-      const uint32_t as = tl & 1;
-      mbar_wait(tempty_bar + 8 * as, ((tl >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+      const uint32_t as = Cfg::kAccStages == 2 ? (tl & 1) : 0;
+      const uint32_t aph = Cfg::kAccStages == 2 ? ((tl >> 1) & 1) : (tl & 1);
+      mbar_wait(tempty_bar + 8 * as, aph ^ 1);  // epilogue has drained this accumulator
       tcgen05_fence_after();
-      const uint32_t tacc = tmem_base + as * BN;
+      const uint32_t tacc = tmem_base + as * Cfg::kAccCols;
       for (int kb = 0; kb < num_kb; ++kb, ++kc) {
         const int s = kc % S;
         mbar_wait(full_bar + 8 * s, (kc / S) & 1);
@@ -522,8 +538,12 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const uint64_t bdesc = bdesc0 + (uint64_t)(s * (Cfg::kStageBytes >> 4));
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k)
-            umma_bf16(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+#pragma unroll
+            for (int h = 0; h < MT; ++h)  // rows 128 h .. 128 h + 127 of the activation tile: 128 rows x 128 B further
+              umma_bf16(tacc + h * BN, adesc + (uint64_t)(h * (128 * 128 >> 4)) + 2 * k, bdesc + 2 * k, idesc,
+                        (kb > 0 || k > 0) ? 1u : 0u);
+          }
           umma_commit(empty_bar + 8 * s);
           if (kb == num_kb - 1) umma_commit(tfull_bar + 8 * as);
         }
@@ -537,15 +557,16 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
       int m_blk, n_blk;
       prefill_tile_coords(tile, m_tiles, num_tiles, m_blk, n_blk);
-      const uint32_t as = tl & 1;
-      mbar_wait(tfull_bar + 8 * as, (tl >> 1) & 1);
+      const uint32_t as = Cfg::kAccStages == 2 ? (tl & 1) : 0;
+      mbar_wait(tfull_bar + 8 * as, Cfg::kAccStages == 2 ? ((tl >> 1) & 1) : (tl & 1));
       tcgen05_fence_after();
-      const uint32_t lane_base = tmem_base + as * BN + ((uint32_t)(quad * 32) << 16);
-      const int m = m_blk * 128 + quad * 32 + lane;
       const int n_tile0 = n_blk * Cfg::kOutCols;
       const int n_out = kGated ? N / 2 : N;
 #pragma unroll 1
       for (int c0 = 0; c0 < Cfg::kOutCols; c0 += 16) {
+        const int h = (warp - 2) >> 2;  // warps 2-5: rows 0-127 of the tile, warps 6-9 (MT = 2): rows 128-255
+        const uint32_t lane_base = tmem_base + as * Cfg::kAccCols + h * BN + ((uint32_t)(quad * 32) << 16);
+        const int m = m_blk * kMRows + h * 128 + quad * 32 + lane;
         uint32_t r[16], r2[16];
         tmem_ld_32x16(lane_base + c0, r);
         if (kGated) tmem_ld_32x16(lane_base + 128 + c0, r2);
@@ -603,23 +624,23 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---- host side ---------------------------------------------------------------------------
-template <int BN, bool kGated>
+template <int BN, bool kGated, int MT = 1>
 static int launch_prefill_gemm(const void* x, const void* w, const void* bias, const void* residual, void* y, int M,
                                int N /* rows of w */, int K, int epilogue, cudaStream_t s) {
-  using Cfg = PrefillCfg<BN, kGated>;
+  using Cfg = PrefillCfg<BN, kGated, MT>;
   static PerDeviceOnce once;
-  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated>,
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated, MT>,
                                                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                                     Cfg::kSmemBytes)));
   CUtensorMap tmA, tmB;
   int rc;
-  if ((rc = make_tmap(&tmA, x, M, K, 128)) != DLI_OK) return rc;
+  if ((rc = make_tmap(&tmA, x, M, K, MT * 128)) != DLI_OK) return rc;
   if ((rc = make_tmap(&tmB, w, N, K, BN)) != DLI_OK) return rc;
-  const int m_tiles = (M + 127) / 128, n_tiles = (N + BN - 1) / BN;
+  const int m_tiles = (M + MT * 128 - 1) / (MT * 128), n_tiles = (N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles;
   const int sms = sm_count_cached();
   const int grid = num_tiles < sms ? num_tiles : sms;
-  DLI_LAUNCH("gemm_prefill_kernel", gemm_prefill_kernel<BN, kGated>, dim3(grid), dim3(kGemmThreads),
+  DLI_LAUNCH("gemm_prefill_kernel", (gemm_prefill_kernel<BN, kGated, MT>), dim3(grid), dim3(64 + 128 * MT),
              (size_t)Cfg::kSmemBytes, s, tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue,
              m_tiles, num_tiles);
   return DLI_OK;
@@ -695,14 +716,33 @@ int dli_gemm_bf16(const void* x, const void* w, const void* bias, const void* re
   if (M <= 64) return launch_gemm<64, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   if (M <= 128) return launch_gemm<128, true, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   if (N % 256 == 0 || N >= 2048) {
-    // Wave quantisation: the persistent kernel walks m_tiles x n_tiles tiles on one CTA per SM, and a 2k-token
-    // prefill has few of them (o / down: 16 x 16 = 256 tiles = 1.73 waves of 148, qkv 2.59).  240-column tiles
-    // (UMMA N = 240) give 288 and 416 tiles = 1.95 and 2.81 waves: the same number of rounds of shorter tiles.
-    // Cost model: rounds x tile width; 256 wins whenever M is large (tens of thousands of rows).
+    // Tile choice for the persistent kernel (one CTA per SM walks rounds of tiles).  Two effects, both measured on
+    // B200 (scratch/exp_gemm_vs_cublas.py, profiles/r2_notes.md): (1) wave quantisation — a 2k-token prefill has
+    // few tiles, so the tile WIDTH is chosen to fill whole rounds (UMMA N may be any multiple of 16: 240-column
+    // tiles turn 256 / 384 tiles = 1.73 / 2.59 waves into 288 / 416 = 1.95 / 2.81); (2) operand feed — a 256-row
+    // tile (two MMAs per weight sub-tile) needs less L2 bandwidth per MMA than a 128-row tile, but its two
+    // accumulators fill TMEM, so its epilogue (about 3 us) is not overlapped: it wins where it makes ONE round of
+    // what were two (o / down projection at 2 048 rows: 56.6 -> 52.0 us, 179.1 -> 163.0 us; cuBLAS 51 / 157).
+    // cost (us) = rounds x (k-blocks x rows/128 x width x c + epilogue), c fitted per tile shape.
     const int sms = sm_count_cached() > 0 ? sm_count_cached() : 148;
-    const long long m_tiles = (M + 127) / 128;
-    auto cost = [&](int bn) { return ((m_tiles * ((N + bn - 1) / bn) + sms - 1) / sms) * bn; };
-    if (cost(240) < cost(256)) return launch_gemm<240, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+    const double kbs = K / 64;
+    struct Shape { int mt, bn; double c, epi; };
+    static const Shape shapes[] = {{1, 256, 1.60e-3, 0.5}, {1, 240, 1.72e-3, 0.5}, {2, 256, 1.48e-3, 3.0}, {2, 240, 1.55e-3, 3.0}};
+    static const int force = getenv("DLI_GEMM_TILE") ? atoi(getenv("DLI_GEMM_TILE")) : 0;  // measurement knob: mt * 1000 + bn
+    int best_mt = 1, best_bn = 256;
+    double best = 1e30;
+    for (const Shape& c : shapes) {
+      if (c.mt == 2 && M <= 128) continue;
+      const long long tiles = (long long)((M + c.mt * 128 - 1) / (c.mt * 128)) * ((N + c.bn - 1) / c.bn);
+      const double v = (double)((tiles + sms - 1) / sms) * (kbs * c.mt * c.bn * c.c + c.epi);
+      if (v < best) best = v, best_mt = c.mt, best_bn = c.bn;
+    }
+    if (force) best_mt = force / 1000, best_bn = force % 1000;
+    if (best_mt == 2) {
+      if (best_bn == 240) return launch_prefill_gemm<240, false, 2>(x, w, bias, residual, y, M, N, K, epilogue, s);
+      return launch_prefill_gemm<256, false, 2>(x, w, bias, residual, y, M, N, K, epilogue, s);
+    }
+    if (best_bn == 240) return launch_gemm<240, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
     return launch_gemm<256, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   }
   if (N % 128 == 0 || N > 128) return launch_gemm<128, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
@@ -724,6 +764,8 @@ int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, in
   if (M <= 32) return launch_gemm<32, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
   if (M <= 64) return launch_gemm<64, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
   if (M <= 128) return launch_gemm<128, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
+  // (256-row tiles measured slower here: 420 against 332 us at 2 048 rows — the gated epilogue is long and would
+  // not be overlapped, and 896 tiles make 7 rounds where 1 792 make 13 half as long)
   return launch_gemm<256, false, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
 }
 

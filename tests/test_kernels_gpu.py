@@ -417,7 +417,8 @@ def test_gemv_gated_silu(cuda, M, F, K):
     "M,N,K",
     [(2048, 6144, 4096), (2048, 4096, 4096), (2048, 4096, 14336), (300, 2560, 2048),  # 2k rows: 240-column tiles (129, 512, 128), (1000, 48, 64),
      (5, 4096, 4096), (16, 1024, 512), (32, 6144, 4096), (64, 2048, 2048), (100, 384, 256), (128, 128256, 256),
-     (4741, 1280, 256), (8192, 768, 128)],  # > 16 row tiles: grouped tile walk, partial last group
+     (4741, 1280, 256), (8192, 768, 128),  # > 16 row tiles: grouped tile walk, partial last group
+     (2000, 4096, 2048), (1900, 2048, 4096), (300, 4096, 8192)],  # 256-row tiles (one round), ragged last row tile
 )
 def test_gemm_tcgen05(cuda, M, N, K):
     from dli_b200 import ops
