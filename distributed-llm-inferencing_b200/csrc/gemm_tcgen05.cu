@@ -447,25 +447,14 @@ __device__ __forceinline__ void prefill_tile_coords(int tile, int m_tiles, int n
 }
 
 // threads: TMA warp + MMA warp + four epilogue warps per 128-row half
-// kPair: the kernel is launched as clusters of two CTAs that work on two vertically adjacent tiles (row tiles 2p and
-// 2p + 1 of the same weight tile).  Each CTA loads its own activation tile and HALF of the weight tile, which TMA
-// multicasts into both CTAs' shared memory: per CTA 16 + BN/8 KB come from L2 per k-block instead of 16 + BN/4 —
-// the operand feed of a 256-row tile with the TMEM budget (two accumulator stages, overlapped epilogue) of a
-// 128-row one.  A stage is free when BOTH CTAs' MMAs have read it (the peer writes half of it): the MMA warp's
-// commit arrives on the `empty` barrier of both CTAs.  m_tiles / num_tiles then count PAIRS of row tiles.
-template <int BN, bool kGated, int MT, bool kPair>
+template <int BN, bool kGated, int MT>
 __global__ void __launch_bounds__(64 + 128 * MT, 1)
 gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const bf16* __restrict__ bias, const bf16* residual, bf16* y, int M, int N, int K,
                     int epilogue, int m_tiles, int num_tiles) {
   using Cfg = PrefillCfg<BN, kGated, MT>;
-  static_assert(!kPair || MT == 1, "pairs share the weight tile between two 128-row CTAs");
   constexpr int S = Cfg::kStages;
   constexpr int kMRows = MT * 128;
-  const int walker = kPair ? blockIdx.x >> 1 : blockIdx.x;        // which sequence of (pairs of) tiles
-  const int n_walkers = kPair ? gridDim.x >> 1 : gridDim.x;
-  const int rank = kPair ? (blockIdx.x & 1) : 0;                  // CTA rank in the cluster (cluster = 2 along x)
-  constexpr uint16_t kBoth = 3;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* bar_mem = smem + S * Cfg::kStageBytes;
@@ -483,7 +472,7 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmB);
     for (int s = 0; s < S; ++s) {
       mbar_init(full_bar + 8 * s, 1);
-      mbar_init(empty_bar + 8 * s, kPair ? 2 : 1);  // pairs: both CTAs' MMA warps release a stage
+      mbar_init(empty_bar + 8 * s, 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar + 8 * a, 1);
@@ -494,35 +483,26 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 1) tmem_alloc(smem_addr(tmem_ptr_smem), Cfg::kTmemCols);
   tcgen05_fence_before();
   __syncthreads();
-  if (kPair) cluster_barrier_sync();  // the peer's barriers exist before anything is sent to them
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   if (warp == 0) {
     if (lane == 0) {
-      // weight (B) tile of a stage: the whole tile, or (pairs) this CTA's half of it into both CTAs
-      auto load_b = [&](uint32_t sB, uint32_t bar, int kb, int n_blk) {
-        if (kPair)
-          tma_load_2d_mc(sB + rank * (BN / 2) * 128, &tmB, bar, kb * kBlockK, n_blk * BN + rank * (BN / 2), kBoth);
-        else
-          tma_load_2d(sB, &tmB, bar, kb * kBlockK, n_blk * BN);
-      };
       // ring of weight (B) loads for the first tile goes out before the dependency wait
-      const int first = walker;
+      const int first = blockIdx.x;
       const int pre = (first < num_tiles) ? min(S, num_kb) : 0;
       int first_m = 0, first_n = 0;
       if (pre) prefill_tile_coords(first, m_tiles, num_tiles, first_m, first_n);
       for (int kb = 0; kb < pre; ++kb) {
         const uint32_t sA = smem_addr(smem + kb * Cfg::kStageBytes);
         mbar_expect_tx(full_bar + 8 * kb, Cfg::kStageBytes);
-        load_b(sA + Cfg::kABytes, full_bar + 8 * kb, kb, first_n);
+        tma_load_2d(sA + Cfg::kABytes, &tmB, full_bar + 8 * kb, kb * kBlockK, first_n * BN);
       }
       pdl_wait();
       uint32_t kc = 0;
-      for (int tile = walker; tile < num_tiles; tile += n_walkers) {
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int m_blk, n_blk;
         prefill_tile_coords(tile, m_tiles, num_tiles, m_blk, n_blk);
-        if (kPair) m_blk = 2 * m_blk + rank;
         for (int kb = 0; kb < num_kb; ++kb, ++kc) {
           const int s = kc % S;
           const uint32_t sA = smem_addr(smem + s * Cfg::kStageBytes);
@@ -533,7 +513,7 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait(empty_bar + 8 * s, ((kc / S) & 1) ^ 1);
           mbar_expect_tx(full_bar + 8 * s, Cfg::kStageBytes);
           tma_load_2d(sA, &tmA, full_bar + 8 * s, kb * kBlockK, m_blk * kMRows);
-          load_b(sA + Cfg::kABytes, full_bar + 8 * s, kb, n_blk);
+          tma_load_2d(sA + Cfg::kABytes, &tmB, full_bar + 8 * s, kb * kBlockK, n_blk * BN);
         }
       }
     }
@@ -544,7 +524,7 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint64_t adesc0 = make_smem_desc(smem_addr(smem));
     const uint64_t bdesc0 = make_smem_desc(smem_addr(smem) + Cfg::kABytes);
     uint32_t kc = 0, tl = 0;
-    for (int tile = walker; tile < num_tiles; tile += n_walkers, ++tl) {
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
       const uint32_t as = Cfg::kAccStages == 2 ? (tl & 1) : 0;
       const uint32_t aph = Cfg::kAccStages == 2 ? ((tl >> 1) & 1) : (tl & 1);
       mbar_wait(tempty_bar + 8 * as, aph ^ 1);  // epilogue has drained this accumulator
@@ -564,8 +544,7 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               umma_bf16(tacc + h * BN, adesc + (uint64_t)(h * (128 * 128 >> 4)) + 2 * k, bdesc + 2 * k, idesc,
                         (kb > 0 || k > 0) ? 1u : 0u);
           }
-          if (kPair) umma_commit_mc(empty_bar + 8 * s, kBoth);
-          else umma_commit(empty_bar + 8 * s);
+          umma_commit(empty_bar + 8 * s);
           if (kb == num_kb - 1) umma_commit(tfull_bar + 8 * as);
         }
         __syncwarp();
@@ -575,10 +554,9 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int quad = warp & 3;
     pdl_wait();  // residual / bias may come from the previous kernel
     uint32_t tl = 0;
-    for (int tile = walker; tile < num_tiles; tile += n_walkers, ++tl) {
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tl) {
       int m_blk, n_blk;
       prefill_tile_coords(tile, m_tiles, num_tiles, m_blk, n_blk);
-      if (kPair) m_blk = 2 * m_blk + rank;
       const uint32_t as = Cfg::kAccStages == 2 ? (tl & 1) : 0;
       mbar_wait(tfull_bar + 8 * as, Cfg::kAccStages == 2 ? ((tl >> 1) & 1) : (tl & 1));
       tcgen05_fence_after();
@@ -639,7 +617,6 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
   tcgen05_fence_before();
   __syncthreads();
-  if (kPair) cluster_barrier_sync();  // the peer's last commits arrive on this CTA's barriers: stay until it is done too
   if (warp == 1) {
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
@@ -647,71 +624,23 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---- host side ---------------------------------------------------------------------------
-// Is `p` ordinary device memory of the CURRENT device?  (The pair kernel multicasts the weight tile: TMA multicast
-// loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.)
-// Answers are cached per pointer; anything else — a peer's allocation, managed or host memory — is "no".
-static bool is_local_device_memory(const void* p) {
-  struct Slot { const void* p; int dev; bool ok; };
-  thread_local Slot cache[64] = {};
-  int dev = -1;
-  if (cudaGetDevice(&dev) != cudaSuccess) return false;
-  Slot& sl = cache[(reinterpret_cast<uintptr_t>(p) >> 8) & 63];
-  if (sl.p == p && sl.dev == dev) return sl.ok;
-  cudaPointerAttributes at;
-  bool ok = cudaPointerGetAttributes(&at, p) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device == dev;
-  if (!ok) cudaGetLastError();
-  sl = {p, dev, ok};
-  return ok;
-}
-
-template <int BN, bool kGated, int MT = 1, bool kPair = false>
+template <int BN, bool kGated, int MT = 1>
 static int launch_prefill_gemm(const void* x, const void* w, const void* bias, const void* residual, void* y, int M,
                                int N /* rows of w */, int K, int epilogue, cudaStream_t s) {
   using Cfg = PrefillCfg<BN, kGated, MT>;
   static PerDeviceOnce once;
-  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated, MT, kPair>,
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated, MT>,
                                                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                                     Cfg::kSmemBytes)));
   CUtensorMap tmA, tmB;
   int rc;
   if ((rc = make_tmap(&tmA, x, M, K, MT * 128)) != DLI_OK) return rc;
-  if ((rc = make_tmap(&tmB, w, N, K, kPair ? BN / 2 : BN)) != DLI_OK) return rc;
-  const int row_tiles = (M + MT * 128 - 1) / (MT * 128), n_tiles = (N + BN - 1) / BN;
-  const int m_tiles = kPair ? (row_tiles + 1) / 2 : row_tiles;  // pairs of row tiles
+  if ((rc = make_tmap(&tmB, w, N, K, BN)) != DLI_OK) return rc;
+  const int m_tiles = (M + MT * 128 - 1) / (MT * 128), n_tiles = (N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles;
   const int sms = sm_count_cached();
-  if constexpr (kPair) {
-    // clusters that can be resident at once (an SM without a free neighbour in its GPC hosts none): the persistent
-    // walk must not count on more
-    static PerDeviceOnce occ;
-    DLI_ONCE_PER_DEVICE(occ, odev, {
-      cudaLaunchConfig_t cfg = {};
-      cfg.gridDim = dim3(sms & ~1);
-      cfg.blockDim = dim3(64 + 128 * MT);
-      cfg.dynamicSmemBytes = Cfg::kSmemBytes;
-      cudaLaunchAttribute at[1];
-      at[0].id = cudaLaunchAttributeClusterDimension;
-      at[0].val.clusterDim.x = 2;
-      at[0].val.clusterDim.y = at[0].val.clusterDim.z = 1;
-      cfg.attrs = at;
-      cfg.numAttrs = 1;
-      int n = 0;
-      if (cudaOccupancyMaxActiveClusters(&n, gemm_prefill_kernel<BN, kGated, MT, kPair>, &cfg) != cudaSuccess || n <= 0) {
-        cudaGetLastError();
-        n = sms / 2;
-      }
-      occ.value[odev] = n;
-    });
-    const int max_clusters = occ.value[odev];
-    const int walkers = num_tiles < max_clusters ? num_tiles : max_clusters;
-    cudaError_t e = launch_kernel_cluster(gemm_prefill_kernel<BN, kGated, MT, kPair>, dim3(2 * walkers), dim3(64 + 128 * MT),
-                                          (size_t)Cfg::kSmemBytes, s, 2u, tmA, tmB, (const bf16*)bias, (const bf16*)residual,
-                                          (bf16*)y, M, N, K, epilogue, m_tiles, num_tiles);
-    if (e != cudaSuccess) return fail(DLI_ERR_CUDA, "gemm_prefill_kernel (pairs): %s", cudaGetErrorString(e));
-    return DLI_OK;
-  }
   const int grid = num_tiles < sms ? num_tiles : sms;
-  DLI_LAUNCH("gemm_prefill_kernel", (gemm_prefill_kernel<BN, kGated, MT, kPair>), dim3(grid), dim3(64 + 128 * MT),
+  DLI_LAUNCH("gemm_prefill_kernel", (gemm_prefill_kernel<BN, kGated, MT>), dim3(grid), dim3(64 + 128 * MT),
              (size_t)Cfg::kSmemBytes, s, tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue,
              m_tiles, num_tiles);
   return DLI_OK;
@@ -809,11 +738,6 @@ int dli_gemm_bf16(const void* x, const void* w, const void* bias, const void* re
       if (v < best) best = v, best_mt = c.mt, best_bn = c.bn;
     }
     if (force) best_mt = force / 1000, best_bn = force % 1000;
-    if (best_mt == 3 && is_local_device_memory(w)) {  // pairs of 128-row CTAs sharing the weight tile
-      if (best_bn == 240) return launch_prefill_gemm<240, false, 1, true>(x, w, bias, residual, y, M, N, K, epilogue, s);
-      return launch_prefill_gemm<256, false, 1, true>(x, w, bias, residual, y, M, N, K, epilogue, s);
-    }
-    if (best_mt == 3) best_mt = 1;
     if (best_mt == 2) {
       if (best_bn == 240) return launch_prefill_gemm<240, false, 2>(x, w, bias, residual, y, M, N, K, epilogue, s);
       return launch_prefill_gemm<256, false, 2>(x, w, bias, residual, y, M, N, K, epilogue, s);
@@ -842,9 +766,6 @@ int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, in
   if (M <= 128) return launch_gemm<128, true, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
   // (256-row tiles measured slower here: 420 against 332 us at 2 048 rows — the gated epilogue is long and would
   // not be overlapped, and 896 tiles make 7 rounds where 1 792 make 13 half as long)
-  static const int force_g = getenv("DLI_GEMM_TILE") ? atoi(getenv("DLI_GEMM_TILE")) : 0;  // measurement knob
-  if (force_g / 1000 == 3 && is_local_device_memory(w_gu))
-    return launch_prefill_gemm<256, true, 1, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
   return launch_gemm<256, false, true>(x, w_gu, nullptr, nullptr, y, M, N2, K, 0, s);
 }
 

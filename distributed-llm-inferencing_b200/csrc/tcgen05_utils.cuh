@@ -99,25 +99,6 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "}\n" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-// ---- two-CTA clusters that share one operand (this GPU's memory only) ----------------------------------------
-// The same tile lands at the same shared-memory offset of every CTA in `mask`, and each CTA's mbarrier at the
-// same offset receives the bytes.  Tensor maps passed here cover this GPU's own memory (weights); the launchers
-// check that before they choose a kernel that uses it.
-__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1, uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%4, %5}], [%2], %3;"
-      ::"r"(dst), "l"(tmap), "r"(bar), "h"(mask), "r"(c0), "r"(c1)
-      : "memory");
-}
-// mbarrier arrive, at the same offset in every CTA of `mask`, once all MMAs issued so far by this thread have completed
-__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask)
-               : "memory");
-}
-__device__ __forceinline__ void cluster_barrier_sync() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
 // D[tmem] (+)= A[tmem] * B[smem]: A is read from tensor memory (lane = row, each 32-bit column = two consecutive
 // K elements), K-major only.
 __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
