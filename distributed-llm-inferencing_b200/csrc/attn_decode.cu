@@ -116,8 +116,17 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
                       (size_t)(gridDim.x - num_splits) * KV * gridDim.z);
     return;
   }
-  pdl_wait();  // seq_lens, q and the cache pages come from earlier kernels of the stream
-  pdl_trigger();
+  // Fused form: only q and the new token's k, v come from the kernel just before this one (the qkv projection);
+  // the sequence length, the page table and the cache pages of the OLD tokens were written at least one kernel
+  // earlier, and that kernel is complete once this one runs at all (every kernel of the library waits for its
+  // predecessor before it lets its successor start).  So the dependency wait moves below the K/V requests: the
+  // sequence-length -> page-table -> K/V chain (2.7 us of the 6.5 us this kernel took after the wait at batch 1,
+  // scratch/trace_decode_run.py) runs while the projection drains.  The unfused form reads K/V that the rope
+  // kernel just before it appended: it waits first.
+  if (!fused) {
+    pdl_wait();
+    pdl_trigger();
+  }
   const int seq_len = seq_lens[b];
   const int first_tok = (window > 0 && seq_len > window) ? seq_len - window : 0;
   const int tile_lo = first_tok / kAttnTile;
@@ -127,14 +136,6 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
   const int t_end = min(t_begin + tps, tile_hi);
   const int page_mask = (1 << page_shift) - 1;
   const int32_t* pt = page_table + (size_t)b * max_pages;
-
-  // ---- stage Q (rows >= G are zero) -------------------------------------------------
-  for (int id = tid; id < 16 * CH; id += kAttnThreads) {
-    const int row = id / CH, c = id - row * CH;
-    const bool valid = row < G;
-    const bf16* src = q + (size_t)b * q_stride + (size_t)(kvh * G + (valid ? row : 0)) * HD + c * 8;
-    cp_async_16B(sQ + swz<RB>(row, c), src, valid ? 16 : 0);
-  }
 
   auto load_tile = [&](int tile, int stage) {
     const uint32_t dK = sK + stage * L::kTileBytes, dV = sV + stage * L::kTileBytes;
@@ -167,6 +168,18 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
     if (t_begin + st < t_end) load_tile(t_begin + st, st);
     cp_async_commit();
   }
+  if (fused) {
+    pdl_wait();  // q and the new token's k, v
+    pdl_trigger();
+  }
+  // ---- stage Q (rows >= G are zero): its own commit group, the newest; the first tile waits for all groups ----
+  for (int id = tid; id < 16 * CH; id += kAttnThreads) {
+    const int row = id / CH, c = id - row * CH;
+    const bool valid = row < G;
+    const bf16* src = q + (size_t)b * q_stride + (size_t)(kvh * G + (valid ? row : 0)) * HD + c * 8;
+    cp_async_16B(sQ + swz<RB>(row, c), src, valid ? 16 : 0);
+  }
+  cp_async_commit();
 
   // Fused form: cos/sin of the new position, and on the CTA that owns the last tile the new token's k, v and cache
   // page, are needed only once the first K/V tile has landed.  Requested here, their round trips hide under that
@@ -195,7 +208,8 @@ paged_attn_decode_kernel(const bf16* __restrict__ q, int q_stride,
 
   for (int tile = t_begin; tile < t_end; ++tile) {
     const int stage = (tile - t_begin) % NS;
-    cp_async_wait<NS - 1>();  // all but the newest NS-1 groups have landed: this tile is in
+    if (tile == t_begin) cp_async_wait<0>();  // Q (the newest group) and every stage requested so far
+    else cp_async_wait<NS - 1>();             // all but the newest NS-1 groups have landed: this tile is in
     __syncthreads();
     const uint32_t cK = sK + stage * L::kTileBytes, cV = sV + stage * L::kTileBytes;
     if (fused && tile == tile_hi - 1) {

@@ -43,6 +43,30 @@ def test_add_rmsnorm(cuda, rows, d, with_res):
     _ulp_close(y, ref)
 
 
+@pytest.mark.parametrize("d", [2048, 4096, 8192])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_rmsnorm_of_many_rows_has_the_bits_of_the_row_by_row_kernel(cuda, d, with_res):
+    """>= 64 rows take the warp-per-row kernel (prompt passes), fewer the CTA-per-row kernel (decode steps): a token must
+    be normalised to the same bits either way, so the two kernels add the squares in the same order."""
+    from dli_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(d + with_res)
+    rows = 203
+    x = (torch.randn(rows, d, device=cuda, generator=g) * 3).to(BF)
+    res = torch.randn(rows, d, device=cuda, generator=g).to(BF) if with_res else None
+    w = (1 + 0.1 * torch.randn(d, device=cuda, generator=g)).to(BF)
+    h_many = torch.empty_like(x)
+    y_many = ops.add_rmsnorm(x, w, 1e-5, residual=res, resid_out=h_many)
+    for i in range(0, rows, 29):
+        sl = slice(i, min(i + 29, rows))
+        h_few = torch.empty_like(x[sl])
+        y_few = ops.add_rmsnorm(x[sl].contiguous(), w, 1e-5, residual=None if res is None else res[sl].contiguous(), resid_out=h_few)
+        assert torch.equal(y_many[sl], y_few) and torch.equal(h_many[sl], h_few)
+    hf = (x if res is None else res + x).float()
+    ref = w * (hf * torch.rsqrt(hf.pow(2).mean(-1, keepdim=True) + 1e-5)).to(BF)
+    _ulp_close(y_many, ref)
+
+
 @pytest.mark.parametrize("rows,d", [(1, 768), (9, 1024), (4, 4096)])
 def test_add_layernorm(cuda, rows, d):
     from dli_b200 import ops
