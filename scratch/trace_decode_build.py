@@ -38,13 +38,18 @@ objs = [patch("gemv.cu", "gemv", [
     ("  if (cand) {\n    // per-CTA candidate", "  TL_END()\n  if (cand) {\n    // per-CTA candidate"),
 ]), patch("attn_decode.cu", "attn", [
     ("  if (!fused) {\n    pdl_wait();\n    pdl_trigger();\n  }\n  const int seq_len = seq_lens[b];",
-     "  TL_BEGIN(1)\n  unsigned long long tA__ = 0, tB__ = 0;\n  if (!fused) {\n    pdl_wait();\n    pdl_trigger();\n  }\n  const int seq_len = seq_lens[b];"),
+     "  TL_BEGIN(1)\n  unsigned long long tA__ = 0, tB__ = 0, tC__ = 0, tD__ = 0, tE__ = 0;\n  if (!fused) {\n    pdl_wait();\n    pdl_trigger();\n  }\n  const int seq_len = seq_lens[b];"),
     ("  if (fused) {\n    pdl_wait();  // q and the new token's k, v\n    pdl_trigger();\n  }",
      "  if (tl__) tA__ = gtime();\n  if (fused) {\n    pdl_wait();  // q and the new token's k, v\n    pdl_trigger();\n  }\n  TL_WAITED()"),
     ("    else cp_async_wait<NS - 1>();             // all but the newest NS-1 groups have landed: this tile is in\n    __syncthreads();",
      "    else cp_async_wait<NS - 1>();             // all but the newest NS-1 groups have landed: this tile is in\n    __syncthreads();\n    if (tl__ && tile == t_begin) tB__ = gtime();"),
+    ("      if (!kStreamQ) {\n#pragma unroll\n        for (int kk = 0; kk < HD / 16; ++kk) {\n          const int mi = lane >> 3;\n          ldmatrix_x4(qf[kStreamQ ? 0 : kk],",
+     "      if (tl__) tC__ = gtime();\n      if (!kStreamQ) {\n#pragma unroll\n        for (int kk = 0; kk < HD / 16; ++kk) {\n          const int mi = lane >> 3;\n          ldmatrix_x4(qf[kStreamQ ? 0 : kk],"),
+    ("    __syncthreads();  // every warp is done with this stage: refill it", "    if (tl__ && tile == t_begin) tD__ = gtime();\n    __syncthreads();  // every warp is done with this stage: refill it"),
+    ("  __syncthreads();\n  for (int idx = tid; idx < G * HD; idx += kAttnThreads) {\n    const int row = idx / HD, col = idx - row * HD;\n    float mmax = -INFINITY;",
+     "  __syncthreads();\n  if (tl__) tE__ = gtime();\n  for (int idx = tid; idx < G * HD; idx += kAttnThreads) {\n    const int row = idx / HD, col = idx - row * HD;\n    float mmax = -INFINITY;"),
     ("  if (num_splits > 1 && cluster_merge) {",
-     "  TL_END()\n  if (tl__) { unsigned int i = atomicAdd(&g_tl_n_attn, 1u); if (i < (1u << 14)) { g_tl_attn[4 * i] = (2ull << 32) | blockIdx.x; g_tl_attn[4 * i + 1] = tA__; g_tl_attn[4 * i + 2] = tB__; g_tl_attn[4 * i + 3] = gtime(); } }\n  if (num_splits > 1 && cluster_merge) {"),
+     "  TL_END()\n  if (tl__) { unsigned int i = atomicAdd(&g_tl_n_attn, 1u); if (i < (1u << 14)) { g_tl_attn[4 * i] = (2ull << 32) | blockIdx.x; g_tl_attn[4 * i + 1] = tA__; g_tl_attn[4 * i + 2] = tB__; g_tl_attn[4 * i + 3] = gtime(); } i = atomicAdd(&g_tl_n_attn, 1u); if (i < (1u << 14)) { g_tl_attn[4 * i] = (4ull << 32) | blockIdx.x; g_tl_attn[4 * i + 1] = tC__; g_tl_attn[4 * i + 2] = tD__; g_tl_attn[4 * i + 3] = tE__; } }\n  if (num_splits > 1 && cluster_merge) {"),
     ("  const int lane = threadIdx.x & 31;\n  pdl_wait();\n  pdl_trigger();\n  if (bh >= n_bh) return;",
      "  const int lane = threadIdx.x & 31;\n  TL_BEGIN(3)\n  pdl_wait();\n  TL_WAITED()\n  pdl_trigger();\n  if (bh >= n_bh) return;"),
     ("    *reinterpret_cast<uint32_t*>(o + i) = pack_bf16(acc[i] * inv, acc[i + 1] * inv);\n}",

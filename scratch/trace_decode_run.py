@@ -40,7 +40,7 @@ ev = drain(lib.dli_dbg_tl_gemv) + drain(lib.dli_dbg_tl_attn) + drain(lib.dli_dbg
 ev = [e for e in ev if e[2] or e[3]]
 ev.sort(key=lambda e: e[2] if e[0] != 2 else e[2])
 t0 = min(e[2] for e in ev)
-names = {106144: "qkv gemm", 104096: "o/down gemm", 128672: "gate/up gemm", 6144: "qkv gemv", 4096: "o/down gemv", 14336: "gate/up gemv", 1: "attention", 2: "attention (K/V issued, first tile landed, exit)", 3: "merge"}
+names = {106144: "qkv gemm", 104096: "o/down gemm", 128672: "gate/up gemm", 6144: "qkv gemv", 4096: "o/down gemv", 14336: "gate/up gemv", 1: "attention", 2: "attention (K/V issued, first tile landed, exit)", 3: "merge", 4: "attention (Q rotated, first P.V done, partials in smem)"}
 print("kernel, CTA: entry / after dependency wait / exit   (ns since the step's first stamp)")
 for k, blk, a, b, c in ev:
     print(f"{names.get(k, str(k)):48s} cta {blk:4d}: {a - t0:8d} {b - t0:8d} {c - t0:8d}   (wait {b - a:6d}, body {c - b:6d})")
