@@ -4,15 +4,15 @@
 // length-sorted list of items (see TcItem below).  Both GEMMs of flash attention are tcgen05.mma
 // with fp32 accumulators in TMEM:
 //   S = Q K^T   : A = Q tile, B = K tile, both K-major (hd contiguous), SWIZZLE_128B, via TMA
-//   O += P V    : A = P (bf16, written to shared memory by the softmax warps in the same
-//                 K-major swizzled layout), B = V tile as an MN-major operand (hd contiguous,
-//                 tokens along K), exactly as TMA lands the [tokens, hd] rows
-// TMEM: S0 | S1 (two score buffers, 128 columns each) | O (128 columns).
+//   O += P V    : A = P (bf16, two per 32-bit column, written to TENSOR memory by the softmax warps with
+//                 tcgen05.st; the TS form of the MMA reads it there), B = V tile as an MN-major operand
+//                 (hd contiguous, tokens along K), exactly as TMA lands the [tokens, hd] rows
+// TMEM: S0 | S1 (two score buffers, 128 columns each) | O (128 columns) | P0 | P1 (64 columns each).
 // Roles (576 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner, warps 2-17 =
 // softmax + output pass: four threads per query row (TMEM lane), 32 columns each, fp32 online softmax.
 // The MMA warp issues S(j+1) before it waits for the softmax of tile j, so the tensor pipe
 // works on the next scores while the SFUs exponentiate the current ones; P/V of tile j are
-// multiplied as soon as P(j) is in shared memory and O has been rescaled.
+// multiplied as soon as P(j) is in tensor memory and (rarely, see the lazy maximum) O has been rescaled.
 // The T x T score matrix never leaves the SM.  FLOPs per head: 4 * T^2/2 * hd (causal).
 #include "tcgen05_utils.cuh"
 
@@ -22,7 +22,8 @@ constexpr int kRowThreads = 4;                 // softmax threads per query row 
 constexpr int kSmWarps = 4 * kRowThreads;      // softmax warps: kRowThreads per TMEM lane quadrant
 constexpr int kSmCols = 128 / kRowThreads;     // score / output columns per softmax thread
 constexpr int kTcThreads = 64 + 32 * kSmWarps;  // TMA warp + MMA warp + softmax warps
-constexpr int kTcTile = 128;      // query rows per CTA and tokens per KV tile
+static_assert(kRowThreads == 4, "the P store writes 16 packed columns per thread; the TMEM map assumes 4 x 32 columns");
+constexpr int kTcTile = 128;      // query rows per item and tokens per KV tile
 constexpr int kTcHd = 128;
 constexpr int kSpanBytes = 128 * 64 * 2;  // one [128 rows x 64 elements] swizzled sub-tile: 16 KB
 constexpr int kTileBytes2 = 2 * kSpanBytes;  // a [128 x 128] bf16 operand tile: 32 KB
