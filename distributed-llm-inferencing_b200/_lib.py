@@ -59,6 +59,7 @@ SIGNATURES = {
     "dli_gemv_mma_gated_silu_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "dli_gemm_gated_silu_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "dli_linear_gated_silu_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "dli_gemm_qkv_rope_append_bf16": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp]),
     "dli_argmax_bf16": (_i, [_vp, _i, _vp, _i, _i, _vp]),
     "dli_argmax_candidate_bf16": (_i, [_vp, _i, _i, _vp, _i, _i, _vp]),
     "dli_argmax_merge": (_i, [_vp, _i, _i, _vp, _vp]),

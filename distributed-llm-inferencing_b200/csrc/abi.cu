@@ -69,7 +69,7 @@ extern "C" {
 
 const char* dli_last_error(void) { return dli::g_err; }
 
-int dli_version(void) { return 1003; }  // 1003: + dli_gemv_argmax_bf16; per-device kernel set-up
+int dli_version(void) { return 1004; }  // 1004: + dli_gemm_qkv_rope_append_bf16 (1003: + dli_gemv_argmax_bf16; per-device kernel set-up)
 
 int dli_set_pdl(int enable) {
   const int before = dli::pdl_enabled() ? 1 : 0;

@@ -446,12 +446,29 @@ __device__ __forceinline__ void prefill_tile_coords(int tile, int m_tiles, int n
   m_blk = m0 + r - n_blk * gsize;
 }
 
+// kRope (the qkv projection of a prompt pass, head_dim 128, 128 x 256 tiles = two whole heads per tile): the epilogue
+// rotates q and k (rotate-half RoPE with the rounding points of apply_rotary_pos_emb on bf16 tensors,
+// TF:models/llama/modeling_llama.py:138-168, applied to the bf16-rounded projection exactly as the separate
+// rope_kv_append_kernel applies it to the stored one) and appends k and v to the paged cache — the work of
+// dli_rope_kv_append_bf16 without a second pass over the qkv matrix.
+struct RopeArgs {
+  const bf16* cos_t;           // [max_pos, 64]
+  const bf16* sin_t;
+  const int32_t* positions;    // [M]
+  const int32_t* seq_ids;      // [M]
+  const int32_t* page_table;   // [n_seqs, max_pages]
+  bf16* k_cache;               // [num_pages, KV, page_size, 128]
+  bf16* v_cache;
+  int max_pages, H, KV, page_shift;
+};
+
 // threads: TMA warp + MMA warp + four epilogue warps per 128-row half
-template <int BN, bool kGated, int MT>
+template <int BN, bool kGated, int MT, bool kRope = false>
 __global__ void __launch_bounds__(64 + 128 * MT, 1)
 gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const bf16* __restrict__ bias, const bf16* residual, bf16* y, int M, int N, int K,
-                    int epilogue, int m_tiles, int num_tiles) {
+                    int epilogue, int m_tiles, int num_tiles, const __grid_constant__ RopeArgs rope) {
+  static_assert(!kRope || (BN == 256 && !kGated && MT == 1), "the RoPE epilogue works on two whole 128-wide heads");
   using Cfg = PrefillCfg<BN, kGated, MT>;
   constexpr int S = Cfg::kStages;
   constexpr int kMRows = MT * 128;
@@ -562,6 +579,76 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tcgen05_fence_after();
       const int n_tile0 = n_blk * Cfg::kOutCols;
       const int n_out = kGated ? N / 2 : N;
+      if constexpr (kRope) {
+        const uint32_t lane_base = tmem_base + as * Cfg::kAccCols + ((uint32_t)(quad * 32) << 16);
+        const int m = m_blk * 128 + quad * 32 + lane;
+        const bool live = m < M;
+        int pos = 0;
+        size_t cache_row = 0;  // ((page * KV) * page_size + slot): + kvh * page_size gives the token's row of a kv head
+        if (live) {
+          pos = rope.positions[m];
+          const int page = rope.page_table[(size_t)rope.seq_ids[m] * rope.max_pages + (pos >> rope.page_shift)];
+          cache_row = ((size_t)page * rope.KV << rope.page_shift) + (pos & ((1 << rope.page_shift) - 1));
+        }
+#pragma unroll 1
+        for (int hh = 0; hh < 2; ++hh) {
+          const int head = (n_tile0 >> 7) + hh;  // q heads, then k heads, then v heads
+          if (head >= rope.H + 2 * rope.KV) break;
+          bf16* yrow = y + (size_t)m * N + (size_t)head * 128;
+          if (head < rope.H + rope.KV) {
+            bf16* crow = head >= rope.H ? rope.k_cache + (cache_row + ((size_t)(head - rope.H) << rope.page_shift)) * 128 : nullptr;
+#pragma unroll 1
+            for (int j = 0; j < 4; ++j) {  // 16 rotation pairs (i, i + 64) per step
+              uint32_t r1[16], r2[16];
+              tmem_ld_32x16(lane_base + hh * 128 + j * 16, r1);
+              tmem_ld_32x16(lane_base + hh * 128 + 64 + j * 16, r2);
+              tmem_ld_wait();
+              if (live) {
+                float c[16], sn[16], o1[16], o2[16];
+                unpack8(ld_16B(rope.cos_t + (size_t)pos * 64 + j * 16), c);
+                unpack8(ld_16B(rope.cos_t + (size_t)pos * 64 + j * 16 + 8), c + 8);
+                unpack8(ld_16B(rope.sin_t + (size_t)pos * 64 + j * 16), sn);
+                unpack8(ld_16B(rope.sin_t + (size_t)pos * 64 + j * 16 + 8), sn + 8);
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                  const float x1 = round_bf16(__uint_as_float(r1[e])), x2 = round_bf16(__uint_as_float(r2[e]));
+                  o1[e] = round_bf16(x1 * c[e]) + round_bf16(-x2 * sn[e]);
+                  o2[e] = round_bf16(x2 * c[e]) + round_bf16(x1 * sn[e]);
+                }
+#pragma unroll
+                for (int v8 = 0; v8 < 2; ++v8) {
+                  const uint4 u1 = pack8(o1 + v8 * 8), u2 = pack8(o2 + v8 * 8);
+                  st_16B(yrow + j * 16 + v8 * 8, u1);
+                  st_16B(yrow + 64 + j * 16 + v8 * 8, u2);
+                  if (crow) {
+                    st_16B(crow + j * 16 + v8 * 8, u1);
+                    st_16B(crow + 64 + j * 16 + v8 * 8, u2);
+                  }
+                }
+              }
+            }
+          } else {
+            bf16* crow = rope.v_cache + (cache_row + ((size_t)(head - rope.H - rope.KV) << rope.page_shift)) * 128;
+#pragma unroll 1
+            for (int j = 0; j < 8; ++j) {
+              uint32_t r1[16];
+              tmem_ld_32x16(lane_base + hh * 128 + j * 16, r1);
+              tmem_ld_wait();
+              if (live) {
+                float v[16];
+#pragma unroll
+                for (int e = 0; e < 16; ++e) v[e] = __uint_as_float(r1[e]);
+#pragma unroll
+                for (int v8 = 0; v8 < 2; ++v8) {
+                  const uint4 u = pack8(v + v8 * 8);
+                  st_16B(yrow + j * 16 + v8 * 8, u);
+                  st_16B(crow + j * 16 + v8 * 8, u);
+                }
+              }
+            }
+          }
+        }
+      } else
 #pragma unroll 1
       for (int c0 = 0; c0 < Cfg::kOutCols; c0 += 16) {
         const int h = (warp - 2) >> 2;  // warps 2-5: rows 0-127 of the tile, warps 6-9 (MT = 2): rows 128-255
@@ -624,12 +711,13 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---- host side ---------------------------------------------------------------------------
-template <int BN, bool kGated, int MT = 1>
+template <int BN, bool kGated, int MT = 1, bool kRope = false>
 static int launch_prefill_gemm(const void* x, const void* w, const void* bias, const void* residual, void* y, int M,
-                               int N /* rows of w */, int K, int epilogue, cudaStream_t s) {
+                               int N /* rows of w */, int K, int epilogue, cudaStream_t s,
+                               const RopeArgs& rope = RopeArgs{}) {
   using Cfg = PrefillCfg<BN, kGated, MT>;
   static PerDeviceOnce once;
-  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated, MT>,
+  DLI_ONCE_PER_DEVICE(once, dev, DLI_CUDA_CALL(cudaFuncSetAttribute(gemm_prefill_kernel<BN, kGated, MT, kRope>,
                                                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                                     Cfg::kSmemBytes)));
   CUtensorMap tmA, tmB;
@@ -640,9 +728,9 @@ static int launch_prefill_gemm(const void* x, const void* w, const void* bias, c
   const int num_tiles = m_tiles * n_tiles;
   const int sms = sm_count_cached();
   const int grid = num_tiles < sms ? num_tiles : sms;
-  DLI_LAUNCH("gemm_prefill_kernel", (gemm_prefill_kernel<BN, kGated, MT>), dim3(grid), dim3(64 + 128 * MT),
+  DLI_LAUNCH("gemm_prefill_kernel", (gemm_prefill_kernel<BN, kGated, MT, kRope>), dim3(grid), dim3(64 + 128 * MT),
              (size_t)Cfg::kSmemBytes, s, tmA, tmB, (const bf16*)bias, (const bf16*)residual, (bf16*)y, M, N, K, epilogue,
-             m_tiles, num_tiles);
+             m_tiles, num_tiles, rope);
   return DLI_OK;
 }
 
@@ -748,6 +836,41 @@ int dli_gemm_bf16(const void* x, const void* w, const void* bias, const void* re
   if (N % 128 == 0 || N > 128) return launch_gemm<128, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   if (N > 32) return launch_gemm<64, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
   return launch_gemm<32, false, false>(x, w, bias, residual, y, M, N, K, epilogue, s);
+}
+
+int dli_gemm_qkv_rope_append_bf16(const void* x, const void* w_qkv, void* qkv, int M, int K, const void* cos,
+                                  const void* sin, const int32_t* positions, const int32_t* seq_ids,
+                                  const int32_t* page_table, int max_pages, void* k_cache, void* v_cache, int H, int KV,
+                                  int hd, int page_size, dli_stream_t stream) {
+  using namespace dli;
+  DLI_CHECK_ARG(x && w_qkv && qkv && cos && sin && positions && seq_ids && page_table && k_cache && v_cache,
+                "dli_gemm_qkv_rope_append_bf16: null pointer");
+  DLI_CHECK_ARG(hd == 128 && H > 0 && KV > 0 && H % 2 == 0 && KV % 2 == 0,
+                "dli_gemm_qkv_rope_append_bf16: needs head_dim 128 and even head counts (got hd=%d H=%d KV=%d); use "
+                "dli_gemm_bf16 + dli_rope_kv_append_bf16", hd, H, KV);
+  DLI_CHECK_ARG(M > 128 && K > 0 && K % 64 == 0,
+                "dli_gemm_qkv_rope_append_bf16: a prompt pass of more than 128 rows, K %% 64 == 0 (got M=%d K=%d)", M, K);
+  DLI_CHECK_ARG(page_size >= 8 && (page_size & (page_size - 1)) == 0 && max_pages > 0,
+                "dli_gemm_qkv_rope_append_bf16: page_size must be a power of two >= 8 (got %d)", page_size);
+  DLI_CHECK_ARG(aligned16(x) && aligned16(w_qkv) && aligned16(qkv) && aligned16(cos) && aligned16(sin) &&
+                    aligned16(k_cache) && aligned16(v_cache),
+                "dli_gemm_qkv_rope_append_bf16: pointers must be 16-byte aligned");
+  int shift = 0;
+  while ((1 << shift) < page_size) ++shift;
+  RopeArgs ra;
+  ra.cos_t = (const bf16*)cos;
+  ra.sin_t = (const bf16*)sin;
+  ra.positions = positions;
+  ra.seq_ids = seq_ids;
+  ra.page_table = page_table;
+  ra.k_cache = (bf16*)k_cache;
+  ra.v_cache = (bf16*)v_cache;
+  ra.max_pages = max_pages;
+  ra.H = H;
+  ra.KV = KV;
+  ra.page_shift = shift;
+  return launch_prefill_gemm<256, false, 1, true>(x, w_qkv, nullptr, nullptr, qkv, M, (H + 2 * KV) * hd, K, 0,
+                                                  static_cast<cudaStream_t>(stream), ra);
 }
 
 int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, int F, int K, dli_stream_t stream) {

@@ -240,6 +240,8 @@ class ShardEngine:
         torch.cuda.set_device(self.device)
         self.sms = ops.sm_count()
         self.l2_prefetch = os.environ.get("DLI_L2_PREFETCH", "0") == "1"
+        # prompt passes: qkv projection + RoPE + cache append as one kernel (DLI_FUSE_QKV_ROPE=0: three steps as before)
+        self.fuse_qkv_rope = os.environ.get("DLI_FUSE_QKV_ROPE", "1") == "1"
         # kernels may start (and prefetch weights) while their predecessor drains
         ops.set_pdl(os.environ.get("DLI_PDL", "1") == "1")
         self.w: Dict[str, torch.Tensor] = {}
@@ -465,7 +467,14 @@ class ShardEngine:
                 ops.rmsnorm_linear(res, L["ln1"], s.eps, L["wqkv"], out=qkv)
             elif s.arch == "llama":
                 ops.add_rmsnorm(res, L["ln1"], s.eps, out=x)
-                lin(x, L["wqkv"], out=qkv)
+                # a prompt pass: RoPE and the cache append ride in the projection's epilogue (same bits)
+                fused_rope = (not decode and self.fuse_qkv_rope
+                              and ops.qkv_rope_append_supported(rows, x.shape[1], H, KV, hd, None))
+                if fused_rope:
+                    ops.linear_qkv_rope_append(x, L["wqkv"], qkv, self.cos, self.sin, positions, seq_ids,
+                                               self.kv.page_table, self.kv.k[li], self.kv.v[li], H, KV, hd)
+                else:
+                    lin(x, L["wqkv"], out=qkv)
             else:
                 ops.add_layernorm(res, L["ln1"], L["ln1b"], s.eps, out=x)
                 lin(x, L["wqkv"], bias=L["bqkv"], out=qkv)
@@ -479,8 +488,9 @@ class ShardEngine:
                                             prefetch_a=L["wo"] if self.l2_prefetch else None,
                                             prefetch_b=L.get("wgu_head") if self.l2_prefetch else None)
             else:
-                ops.rope_kv_append(qkv, self.cos, self.sin, positions, seq_ids, self.kv.page_table,
-                                   self.kv.k[li], self.kv.v[li], H, KV, hd)
+                if not (s.arch == "llama" and fused_rope):
+                    ops.rope_kv_append(qkv, self.cos, self.sin, positions, seq_ids, self.kv.page_table,
+                                       self.kv.k[li], self.kv.v[li], H, KV, hd)
                 if len(prefill_shape) > 2:  # a chunk at positions prefix..: keys/values from the paged cache
                     ops.attn_prefill_paged(qkv, attn, self.kv.k[li], self.kv.v[li], st["page_rows"], prefill_shape[0],
                                            prefill_shape[1], prefill_shape[2], H, KV, hd, self.scale,

@@ -94,6 +94,27 @@ def rope_kv_append(qkv, cos, sin, positions, seq_ids, page_table, k_cache, v_cac
     launch_count += 1
 
 
+def qkv_rope_append_supported(rows, K, H, KV, hd, bias) -> bool:
+    """Can the qkv projection of this prompt pass run as ONE kernel with RoPE and the cache append in its epilogue?"""
+    return rows > 128 and hd == 128 and H % 2 == 0 and KV % 2 == 0 and K % 64 == 0 and bias is None
+
+
+def linear_qkv_rope_append(x, w_qkv, qkv, cos, sin, positions, seq_ids, page_table, k_cache, v_cache, H, KV, hd):
+    """qkv = x @ w_qkv.T with q, k rotated and k, v appended to the paged cache in the GEMM's epilogue (a prompt pass;
+    the same bits as linear() followed by rope_kv_append())."""
+    global launch_count
+    _req(x), _req(w_qkv), _req(qkv), _req(cos), _req(sin), _req(k_cache), _req(v_cache)
+    _req(positions, torch.int32), _req(seq_ids, torch.int32), _req(page_table, torch.int32)
+    M, K = x.shape
+    if w_qkv.shape != ((H + 2 * KV) * hd, K) or qkv.shape != (M, (H + 2 * KV) * hd):
+        raise ValueError("linear_qkv_rope_append: shapes do not match H, KV, hd")
+    _lib.check("dli_gemm_qkv_rope_append_bf16", _lib.load().dli_gemm_qkv_rope_append_bf16(
+        _p(x), _p(w_qkv), _p(qkv), M, K, _p(cos), _p(sin), _p(positions), _p(seq_ids), _p(page_table),
+        page_table.shape[1], _p(k_cache), _p(v_cache), H, KV, hd, k_cache.shape[2], _stream()))
+    launch_count += 1
+    return qkv
+
+
 def attn_decode_scratch_bytes(B, H, hd, num_splits) -> int:
     return int(_lib.load().dli_paged_attn_decode_scratch_bytes(B, H, hd, num_splits))
 

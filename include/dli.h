@@ -263,6 +263,25 @@ int dli_gemm_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M, in
 int dli_linear_gated_silu_bf16(const void* x, const void* w_gu, void* y, int M,
                                int F, int K, dli_stream_t stream);
 
+/* The qkv projection of a PROMPT pass fused with RoPE and the KV-cache append:
+ *   qkv = x @ w_qkv^T  (rounded to bf16), then exactly what dli_rope_kv_append_bf16
+ *   does to that matrix — q and k rotated in place (rotate-half, each product and
+ *   the sum rounded to bf16 as apply_rotary_pos_emb does on bf16 tensors), k and v
+ *   of every row written to the sequence's cache page — in the GEMM's epilogue,
+ *   without a second pass over the [M, (H+2KV)*hd] matrix.  Bit-identical to
+ *   dli_gemm_bf16 followed by dli_rope_kv_append_bf16.
+ * Replaces: q_proj/k_proj/v_proj + apply_rotary_pos_emb + DynamicCache.update
+ *   (TF:models/llama/modeling_llama.py:262-264,138-168; TF:cache_utils.py:102-121).
+ * x [M, K], w_qkv [(H+2KV)*hd, K], qkv [M, (H+2KV)*hd]; cos / sin bf16 [max_pos, hd/2];
+ * positions / seq_ids int32 [M]; page_table int32 [n_seqs, max_pages];
+ * k_cache / v_cache [num_pages, KV, page_size, hd].  Needs hd == 128, H and KV even,
+ * M > 128, K % 64 == 0, no bias (anything else: the two separate calls). */
+int dli_gemm_qkv_rope_append_bf16(const void* x, const void* w_qkv, void* qkv, int M, int K,
+                                  const void* cos, const void* sin, const int32_t* positions,
+                                  const int32_t* seq_ids, const int32_t* page_table,
+                                  int max_pages, void* k_cache, void* v_cache, int H, int KV,
+                                  int hd, int page_size, dli_stream_t stream);
+
 /* Split-K variants of the tensor-core GEMM for batched decode (4 < M <= 128),
  * where the kernel is a weight stream and a matrix with few 128-row tiles would
  * leave most SMs (and most of HBM's bandwidth) idle: K is split over about

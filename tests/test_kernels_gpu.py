@@ -170,6 +170,38 @@ def test_rope_kv_append_exact(cuda, H, KV, hd, page):
         assert torch.equal(vc[pg, :, off, :], v[r])
 
 
+@pytest.mark.parametrize("B,T,H,KV,K", [(1, 2048, 32, 8, 4096), (3, 101, 4, 2, 256), (2, 130, 64, 8, 512)])
+def test_qkv_projection_with_rope_and_append_in_its_epilogue_equals_the_three_steps(cuda, B, T, H, KV, K):
+    """dli_gemm_qkv_rope_append_bf16 (prompt passes) == dli_gemm_bf16 + dli_rope_kv_append_bf16, bit for bit: the packed
+    qkv matrix (q, k rotated; ragged last row tile) and every cache row written."""
+    from dli_b200 import ops
+
+    hd, page = 128, 16
+    g = torch.Generator(device="cuda").manual_seed(B * 1000 + T)
+    rows, max_pos = B * T, T + 40
+    x = torch.randn(rows, K, device=cuda, generator=g).to(BF)
+    w = (torch.randn((H + 2 * KV) * hd, K, device=cuda, generator=g) * 0.05).to(BF)
+    cos, sin = _hf_rope_tables(hd, 500000.0, max_pos, cuda)
+    start = torch.randint(0, 40, (B,), device=cuda, generator=g)
+    positions = (start[:, None] + torch.arange(T, device=cuda)[None]).reshape(-1).int()
+    seq_ids = torch.arange(B, device=cuda).repeat_interleave(T).int()
+    max_pages = (max_pos + page - 1) // page
+    page_table = torch.randperm(B * max_pages, device=cuda, generator=g).int().reshape(B, max_pages).contiguous()
+    assert ops.qkv_rope_append_supported(rows, K, H, KV, hd, None)
+
+    k1 = torch.zeros(B * max_pages, KV, page, hd, device=cuda, dtype=BF)
+    v1 = torch.zeros_like(k1)
+    qkv1 = ops.linear(x, w)
+    ops.rope_kv_append(qkv1, cos, sin, positions, seq_ids, page_table, k1, v1, H, KV, hd)
+
+    k2, v2 = torch.zeros_like(k1), torch.zeros_like(k1)
+    qkv2 = torch.empty_like(qkv1)
+    ops.linear_qkv_rope_append(x, w, qkv2, cos, sin, positions, seq_ids, page_table, k2, v2, H, KV, hd)
+    assert torch.equal(qkv1, qkv2)
+    assert torch.equal(k1, k2) and torch.equal(v1, v2)
+    assert k1.abs().sum() > 0 and not ops.qkv_rope_append_supported(64, K, H, KV, hd, None)
+
+
 def test_kv_append_without_rope(cuda):
     from dli_b200 import ops
 
